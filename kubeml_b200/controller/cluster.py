@@ -1,0 +1,132 @@
+"""`Cluster`: the whole control plane assembled in one process.
+
+The reference deploys controller, scheduler, parameter server and storage as four Deployments
+plus one pod per job (ml/charts/kubeml/templates/deployment.yaml:11-218) and the closest thing it
+has to a single-process harness is ml/tests/integration.go:13-35, which starts three roles as
+goroutines on debug ports.  On a single 8xB200 host that harness *is* the deployment: the roles
+are plain objects wired by reference, optionally also served over HTTP (`serve()`), and jobs are
+threads that drive warm workers.
+"""
+from __future__ import annotations
+
+import logging
+import os
+from typing import Any, Callable, Dict, List, Optional
+
+from ..api import const
+from ..api.types import TrainTask
+from ..model.store import TensorStore
+from ..ps.parameter_server import ParameterServer
+from ..runtime.functions import FunctionRegistry
+from ..runtime.services import Services
+from ..scheduler.scheduler import Scheduler
+from ..storage.service import StorageService
+from ..storage.store import ShardStore
+from ..train.history import HistoryStore
+from ..train.invoker import Invoker, ThreadInvoker
+from ..train.job import TrainJob
+from .controller import Controller
+
+
+class Cluster:
+    def __init__(self, home: Optional[str] = None, max_parallelism: Optional[int] = None,
+                 invoker_factory: Optional[Callable[["Cluster", TrainTask], Invoker]] = None,
+                 options: Optional[dict] = None, start: bool = True):
+        self.home = home or const.home()
+        os.makedirs(self.home, exist_ok=True)
+        self.shard_store = ShardStore(os.path.join(self.home, "datasets"))
+        self.tensor_store = TensorStore()
+        self.histories = HistoryStore(os.path.join(self.home, "history"))
+        self.functions = FunctionRegistry(os.path.join(self.home, "functions"))
+        self.checkpoint_dir = os.path.join(self.home, "checkpoints")
+        self.options = dict(options or {})
+        self.max_parallelism = max_parallelism or self._detect_max_parallelism()
+        self.invoker_factory = invoker_factory or self._default_invoker
+
+        self.scheduler = Scheduler(max_parallelism=self.max_parallelism)
+        self.ps = ParameterServer(self._make_job, scheduler=self.scheduler)
+        self.scheduler.ps = self.ps
+        self.storage = StorageService(self.shard_store)
+        self.controller = Controller(self.scheduler, self.ps, self.storage, self.histories,
+                                     self.functions)
+        self._servers: list = []
+        self.jobs: Dict[str, TrainJob] = {}
+        if start:
+            self.scheduler.start()
+
+    @staticmethod
+    def _detect_max_parallelism() -> int:
+        try:
+            import torch
+            if torch.cuda.is_available():
+                return max(1, min(const.MAX_GPUS, torch.cuda.device_count()))
+        except Exception:  # noqa: BLE001
+            pass
+        return const.MAX_GPUS
+
+    # ---- job factory ---------------------------------------------------------------------
+    def _default_invoker(self, cluster: "Cluster", task: TrainTask) -> Invoker:
+        job_holder: Dict[str, Any] = {}
+        services = Services(shard_store=self.shard_store, tensor_store=self.tensor_store,
+                            barrier=lambda job_id, func_id: self.jobs[job_id].next_iteration(job_id, func_id),
+                            options=self.options)
+        device_sync = None
+        try:
+            import torch
+            if torch.cuda.is_available() and not self.options.get("force_host_sync"):
+                from ..parallel.device_sync import ThreadedDeviceSyncGroup
+                device_sync = ThreadedDeviceSyncGroup.for_job(task.job.id, self.max_parallelism)
+        except ImportError:
+            device_sync = None
+        if device_sync is not None:
+            services.device_sync = device_sync
+        gpu_ids = None
+        try:
+            import torch
+            if torch.cuda.is_available():
+                gpu_ids = list(range(torch.cuda.device_count()))
+        except Exception:  # noqa: BLE001
+            pass
+        return ThreadInvoker(services, self.functions, max_parallelism=self.max_parallelism,
+                             gpu_ids=gpu_ids)
+
+    def _make_job(self, task: TrainTask, ps: ParameterServer) -> TrainJob:
+        invoker = self.invoker_factory(self, task)
+        device_mode = getattr(getattr(invoker, "services", None), "device_sync", None) is not None
+        job = TrainJob(task, invoker, self.tensor_store, history_store=self.histories,
+                       scheduler=self.scheduler, ps=ps, device_mode=device_mode,
+                       checkpoint_dir=self.checkpoint_dir)
+        self.jobs[task.job.id] = job
+        return job
+
+    # ---- convenience ---------------------------------------------------------------------
+    def wait(self, job_id: str, timeout: Optional[float] = None) -> Optional[str]:
+        import time
+        t0 = time.time()
+        while job_id not in self.jobs:            # the scheduler thread has not created it yet
+            if timeout is not None and time.time() - t0 > timeout:
+                raise TimeoutError(job_id)
+            time.sleep(0.005)
+        return self.ps.wait(job_id, timeout)
+
+    def serve(self, host: str = const.HOST, controller_port: int = const.CONTROLLER_PORT,
+              scheduler_port: Optional[int] = None, ps_port: Optional[int] = None,
+              storage_port: Optional[int] = None) -> "Cluster":
+        self._servers.append(self.controller.serve(host, controller_port))
+        if scheduler_port:
+            self._servers.append(self.scheduler.serve(host, scheduler_port))
+        if ps_port:
+            self._servers.append(self.ps.serve(host, ps_port))
+        if storage_port:
+            self._servers.append(self.storage.serve(host, storage_port))
+        return self
+
+    @property
+    def controller_port(self) -> int:
+        return self._servers[0].port if self._servers else 0
+
+    def shutdown(self) -> None:
+        self.scheduler.stop()
+        for s in self._servers:
+            s.stop()
+        self._servers.clear()

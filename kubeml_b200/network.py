@@ -1,0 +1,291 @@
+"""`KubeModel`: the user-facing training abstraction (reference:
+python/kubeml/kubeml/network.py:29-476).
+
+Public surface kept: `KubeModel(network, dataset, gpu=False)`; overridables
+`configure_optimizers() -> Optimizer`, `init()`, `train(batch, batch_index) -> float`,
+`validate(batch, batch_index) -> (accuracy, loss)`, `infer(data)`; proxies `__call__`,
+`parameters()`, `apply()`; attributes `lr, batch_size, epoch, optimizer, logger, device, args,
+task, platform`; and `start()`, which dispatches on the invocation's `task`
+(init | train | val | infer) and returns the function result.
+
+What changed underneath: the invocation arrives through the worker runtime rather
+than Flask; weights move through a `sync` engine (host tensor store or the device arena) rather
+than RedisAI; `train`/`validate` may return 0-dim tensors, which are accumulated on the device
+and read back once per round instead of one `.item()` sync per batch.
+"""
+from __future__ import annotations
+
+import logging
+import os
+from abc import ABC
+from collections import defaultdict
+from typing import Any, Callable, Iterable, List, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .args import _KubeArgs
+from .dataset import KubeDataset
+from .exceptions import (DataError, InvalidFormatError, KubeMLException, StorageError)
+from .runtime.context import current_invocation
+from .util import get_gpu, get_subset_period, split_minibatches
+
+Number = Union[float, torch.Tensor]
+
+
+class KubeModel(ABC):
+    def __init__(self, network: nn.Module, dataset: KubeDataset, gpu: bool = False):
+        self._network = network
+        self._dataset = dataset
+        self.platform = "gpu" if gpu else "cpu"
+        self.device = None
+        self.args = None
+        self.logger = None
+
+        # refreshed from the invocation arguments on every call (network.py:43-49)
+        self.lr = None
+        self.batch_size = None
+        self.task = None
+        self.optimizer = None
+        self.epoch = None
+
+        self._sync = None
+        self._inv = None
+        # device-timed seconds spent in merges during the last train task (history extension)
+        self.merge_seconds = 0.0
+        self.h2d_bytes = 0
+
+    # ---- proxies to the wrapped module (network.py:55-89) -------------------------------------
+    def __call__(self, *args, **kwargs):
+        return self._network(*args, **kwargs)
+
+    def parameters(self):
+        return self._network.parameters()
+
+    def apply(self, fn: Callable[[nn.Module], None]):
+        self._network.apply(fn)
+        return self
+
+    # ---- invocation plumbing ---------------------------------------------------------------
+    def _read_args(self) -> None:
+        self.args = _KubeArgs.parse()
+        self.lr = self.args.lr
+        self.batch_size = self.args.batch_size
+        self.task = self.args._task
+        self.epoch = self.args.epoch
+
+    def _get_logger(self) -> None:
+        self.logger = self._inv.logger
+
+    def _make_sync(self):
+        sv = self._inv.services
+        if sv is None:
+            raise KubeMLException("invocation carries no services", 500)
+        if sv.device_sync is not None and self.platform == "gpu":
+            return sv.device_sync
+        from .train.sync import HostSync
+        return HostSync(sv.tensor_store, sv.barrier)
+
+    def start(self) -> Tuple[Any, int]:
+        """Run the task named by the invocation; returns `(json_payload, 200)` like the
+        reference's `(flask.Response, 200)` (network.py:146-172)."""
+        self._inv = current_invocation()
+        self._read_args()
+        self._get_logger()
+        self._sync = self._make_sync()
+
+        if self.task == "init":
+            return self.__initialize(), 200
+        if self.task == "train":
+            loss = self.__train()
+            return {"loss": loss, "merge_seconds": self.merge_seconds,
+                    "h2d_bytes": self.h2d_bytes}, 200
+        if self.task == "val":
+            acc, loss, length = self.__validate()
+            return {"loss": loss, "accuracy": acc, "length": length}, 200
+        if self.task == "infer":
+            return {"predictions": self.__infer()}, 200
+        raise KubeMLException(f"Task {self.task} not recognized", 400)
+
+    # ---- optimizer (network.py:99-138) ---------------------------------------------------------
+    def _config_optimizer(self) -> None:
+        self.optimizer = self.configure_optimizers()
+
+    def _reset_optimizer_state(self) -> None:
+        """Momentum & co. are discarded at every sync: state carried over from a pre-merge
+        model "can hinder progress" (network.py:121-128)."""
+        if self.optimizer is None:
+            return
+        reset = getattr(self.optimizer, "reset_state", None)
+        if callable(reset):
+            reset()
+        else:
+            self.optimizer.state = defaultdict(dict)
+
+    # ---- task: init ------------------------------------------------------------------------
+    def __initialize(self) -> List[str]:
+        self.init()
+        try:
+            return self._sync.publish_reference(self.args._job_id, self._network)
+        except KeyError as e:
+            raise StorageError(e)
+
+    # ---- hooks (network.py:191-224) ------------------------------------------------------------
+    def _on_train_start(self) -> None:
+        self._set_device()
+        self._network.train()
+        self._sync.attach(self)
+        self._config_optimizer()
+
+    def _on_train_end(self) -> None:
+        pass
+
+    def _on_iteration_start(self) -> None:
+        self._sync.load_reference(self.args._job_id, self._network)
+        self._reset_optimizer_state()
+
+    def _on_iteration_end(self) -> None:
+        self._sync.publish_replica(self.args._job_id, self.args._func_id, self._network)
+
+    def _batch_to_device(self, batch):
+        """network.py:226-250: tensors, tuples and sequences of tensors are moved; anything else
+        is passed through."""
+        if isinstance(batch, torch.Tensor):
+            return batch.to(self.device, non_blocking=True)
+        if isinstance(batch, tuple):
+            return tuple(_to(e, self.device) for e in batch)
+        if isinstance(batch, Sequence) and not isinstance(batch, (str, bytes)):
+            return type(batch)([_to(e, self.device) for e in batch])
+        return batch
+
+    # ---- task: train (network.py:252-310) ------------------------------------------------------
+    def __train(self) -> float:
+        self._on_train_start()
+        a = self.args
+        assigned = split_minibatches(range(self._dataset.num_docs), a._N)[a._func_id]
+        per_iter = get_subset_period(a._K, a.batch_size, assigned)
+        self.logger.debug("Subsets per iteration: %s", per_iter)
+        intervals = range(assigned.start, assigned.stop, per_iter) if per_iter > 0 else range(0)
+
+        fault = (self._inv.services.options or {}).get("inject_fault")
+        loss: Number = 0.0
+        num_iterations = 0
+        self.merge_seconds = 0.0
+        self.h2d_bytes = 0
+        self._dataset._want_pinned = (self.device.type == "cuda"
+                                      and self._dataset._has_batch_transform())
+        for round_idx, i in enumerate(intervals):
+            self._dataset._load_train_data(start=i, end=min(assigned.stop, i + per_iter))
+            batches = self._dataset._batches(self.batch_size, self.device)
+            num_iterations += len(batches)
+
+            self._on_iteration_start()
+            for idx, batch in enumerate(batches):
+                if fault and fault(a._func_id, a.epoch, round_idx, idx):
+                    raise KubeMLException(f"injected fault in function {a._func_id}", 500)
+                if not isinstance(batches, _sliced_type()):
+                    batch = self._batch_to_device(batch)
+                loss = loss + self.train(batch, idx)
+            self._on_iteration_end()
+            self.h2d_bytes += getattr(batches, "h2d_bytes", 0)
+
+            # every round but the last blocks on the merge barrier (network.py:305-306)
+            if i != intervals[-1]:
+                self._sync.arrive(a._job_id, a._func_id, round_idx)
+
+        self._sync.end_epoch(a._job_id, a._func_id, len(intervals))
+        self.merge_seconds = float(getattr(self._sync, "merge_seconds", 0.0))
+        self._on_train_end()
+        if num_iterations == 0:
+            return 0.0
+        return float(self._sync.drain_losses(loss)) / num_iterations
+
+    # ---- task: val (network.py:312-360) ----------------------------------------------------------
+    def _on_validation_start(self) -> None:
+        self._set_device()
+        self._network.eval()
+        self._sync.attach(self)
+
+    def __validate(self) -> Tuple[float, float, int]:
+        self._on_validation_start()
+        a = self.args
+        assigned = split_minibatches(range(self._dataset.num_val_docs), a._N)[a._func_id]
+        if len(assigned) == 0:
+            return 0.0, 0.0, 0
+        self._dataset._want_pinned = (self.device.type == "cuda"
+                                      and self._dataset._has_batch_transform())
+        self._dataset._load_validation_data(start=assigned.start, end=assigned.stop)
+        batches = self._dataset._batches(self.batch_size, self.device)
+
+        acc: Number = 0.0
+        loss: Number = 0.0
+        self._sync.load_reference(a._job_id, self._network)
+        with torch.no_grad():
+            for idx, batch in enumerate(batches):
+                if not isinstance(batches, _sliced_type()):
+                    batch = self._batch_to_device(batch)
+                _acc, _loss = self.validate(batch, idx)
+                acc = acc + _acc
+                loss = loss + _loss
+        n = len(batches)
+        return float(acc) / n, float(loss) / n, len(self._dataset)
+
+    # ---- task: infer (made coherent — load the reference model, call infer(data)) ----
+    def __infer(self):
+        data_json = self._inv.body
+        if not data_json:
+            self.logger.error("JSON not found in request")
+            raise DataError()
+        self._set_device()
+        self._network.eval()
+        try:
+            self._sync.load_reference(self.args._job_id, self._network)
+        except (KubeMLException, KeyError):
+            self.logger.debug("no stored reference model for %s; using the function's weights",
+                              self.args._job_id)
+        with torch.no_grad():
+            preds = self.infer(data_json)
+        if isinstance(preds, torch.Tensor):
+            return preds.cpu().numpy().tolist()
+        if isinstance(preds, np.ndarray):
+            return preds.tolist()
+        if isinstance(preds, list):
+            return preds
+        raise InvalidFormatError()
+
+    # ---- device (network.py:379-393) -----------------------------------------------------------
+    def _set_device(self) -> None:
+        if self.platform == "cpu" or not torch.cuda.is_available():
+            self.device = torch.device("cpu")
+            return
+        gpu_id = get_gpu(self.args._func_id)
+        self.device = torch.device(f"cuda:{gpu_id}")
+        torch.cuda.set_device(self.device)
+        self._network = self._network.to(self.device)
+        self.logger.debug("Set device to %s", self.device)
+
+    # ---- user overridables (network.py:463-476) ------------------------------------------------
+    def configure_optimizers(self) -> torch.optim.Optimizer:
+        pass
+
+    def init(self):
+        pass
+
+    def train(self, batch, batch_index: int) -> Number:
+        pass
+
+    def validate(self, batch, batch_index: int) -> Tuple[Number, Number]:
+        pass
+
+    def infer(self, data: List[Any]) -> Union[torch.Tensor, np.ndarray, List[float]]:
+        pass
+
+
+def _to(e, device):
+    return e.to(device, non_blocking=True) if isinstance(e, torch.Tensor) else e
+
+
+def _sliced_type():
+    from .dataset import SlicedBatches
+    return SlicedBatches

@@ -1,0 +1,142 @@
+"""Parameter server (reference: ml/pkg/ps/api.go:16-360, parameter_server.go:73-105,
+job_pod.go:18-242).
+
+The reference keeps `jobIndex[jobId] -> TrainTask`, and for every new task either creates a
+Kubernetes Pod+Service `job-<id>` running the job binary or (STANDALONE_JOBS=false) runs the job
+as a goroutine.  On one host the second form is the only one that makes sense: a job is a thread
+of the control plane driving warm GPU workers through an invoker chosen by `job_factory`.
+The retry-on-start loop (api.go:192-207) disappears with the pod.
+"""
+from __future__ import annotations
+
+import logging
+import threading
+from typing import Any, Callable, Dict, List, Optional
+
+from ..api.types import JobState, MetricUpdate, TrainTask
+from ..exceptions import KubeMLException
+from ..httpd import Request, Router, Server
+from ..train.job import TrainJob
+from .metrics import MetricsRegistry
+
+JobFactory = Callable[[TrainTask, "ParameterServer"], TrainJob]
+
+
+class ParameterServer:
+    def __init__(self, job_factory: JobFactory, scheduler: Any = None):
+        self.job_factory = job_factory
+        self.scheduler = scheduler
+        self.metrics = MetricsRegistry()
+        self.log = logging.getLogger("kubeml.ps")
+        self._index: Dict[str, TrainTask] = {}
+        self._threads: Dict[str, threading.Thread] = {}
+        self._finished: Dict[str, Optional[str]] = {}    # job id -> error text (None = ok)
+        self._mu = threading.Lock()
+
+    # ---- scheduler-facing ----------------------------------------------------------------
+    def start_task(self, task: TrainTask) -> None:
+        """POST /start (api.go:139-222)."""
+        with self._mu:
+            if task.job.id in self._index:
+                raise KubeMLException(f"task {task.job.id} already exists", 400)
+            self._index[task.job.id] = task
+        job = self.job_factory(task, self)
+        task.job.handle = job
+        self.metrics.task_started("train")
+        t = threading.Thread(target=job.train, daemon=True, name=f"job-{task.job.id}")
+        with self._mu:
+            self._threads[task.job.id] = t
+        t.start()
+
+    def update_task(self, task: TrainTask) -> None:
+        """POST /update/{jobId} (api.go:72-119): relay the new parallelism to the job."""
+        with self._mu:
+            cur = self._index.get(task.job.id)
+        if cur is None or cur.job.handle is None:
+            raise KubeMLException(f"task {task.job.id} does not exist", 404)
+        cur.job.handle.update_task(JobState(parallelism=task.job.state.parallelism,
+                                            elapsed_time=task.job.state.elapsed_time))
+
+    # ---- job-facing ----------------------------------------------------------------------
+    def update_metrics(self, job_id: str, m: MetricUpdate) -> None:
+        """POST /metrics/{jobId} (api.go:226-257)."""
+        self.metrics.update(job_id, m)
+
+    def job_finished(self, job_id: str, err: Optional[BaseException] = None) -> None:
+        """POST /finish/{jobId} (api.go:261-333): clear gauges, tell the scheduler, drop the entry."""
+        self.metrics.clear(job_id)
+        self.metrics.task_finished("train")
+        if self.scheduler is not None:
+            try:
+                self.scheduler.finish_job(job_id)
+            except Exception as e:  # noqa: BLE001
+                self.log.error("error notifying scheduler: %s", e)
+        with self._mu:
+            self._index.pop(job_id, None)
+            self._finished[job_id] = None if err is None else str(err)
+        if err is not None:
+            self.log.error("job %s exited with error: %s", job_id, err)
+
+    # ---- controller-facing ---------------------------------------------------------------
+    def list_tasks(self) -> List[TrainTask]:
+        with self._mu:
+            return list(self._index.values())
+
+    def stop_task(self, job_id: str) -> None:
+        """DELETE /stop/{jobId} (api.go:16-66)."""
+        with self._mu:
+            task = self._index.get(job_id)
+        if task is None or task.job.handle is None:
+            raise KubeMLException(f"task {job_id} not found", 404)
+        task.job.handle.stop()
+
+    def wait(self, job_id: str, timeout: Optional[float] = None) -> Optional[str]:
+        """Block until a job's thread ended; returns its error text or None (no reference
+        counterpart; the CLI there polls `task list`)."""
+        with self._mu:
+            t = self._threads.get(job_id)
+        if t is not None:
+            t.join(timeout)
+            if t.is_alive():
+                raise TimeoutError(job_id)
+        with self._mu:
+            return self._finished.get(job_id)
+
+    def infer(self, model_id: str, data: Any) -> Any:
+        """Run `task=infer` of the job's function on its reference model."""
+        with self._mu:
+            task = self._index.get(model_id)
+        if task is None or task.job.handle is None:
+            raise KubeMLException(f"model {model_id} not found (is the job still running?)", 404)
+        job: TrainJob = task.job.handle
+        self.metrics.task_started("inference")
+        try:
+            q = job._query("infer", 0, 1)
+            payload, status = job.invoker.invoke_one(0, task.request.function_name, q, body=data)
+            if status != 200:
+                raise KubeMLException(str(payload.get("error", payload)), status)
+            return payload.get("predictions")
+        finally:
+            self.metrics.task_finished("inference")
+
+    # ---- HTTP (ps/api.go:335-345 + :8080/metrics) ------------------------------------------------
+    def router(self) -> Router:
+        r = Router()
+        r.add("GET", "/health", lambda q: (200, None))
+        r.add("POST", "/start", lambda q: self.start_task(TrainTask.from_dict(q.json())))
+        r.add("POST", "/update/{jobId}", lambda q: self.update_task(TrainTask.from_dict(q.json())))
+        r.add("POST", "/metrics/{jobId}",
+              lambda q: self.update_metrics(q.params["jobId"], MetricUpdate.from_dict(q.json())))
+        r.add("POST", "/finish/{jobId}", self._http_finish)
+        r.add("DELETE", "/stop/{jobId}", lambda q: self.stop_task(q.params["jobId"]))
+        r.add("GET", "/tasks", lambda q: [t.to_dict() for t in self.list_tasks()])
+        r.add("GET", "/metrics", lambda q: (200, self.metrics.render(), "text/plain; version=0.0.4"))
+        return r
+
+    def _http_finish(self, q: Request):
+        body = q.json() or {}
+        err = KubeMLException(body["error"], int(body.get("code", 500))) if body.get("error") else None
+        self.job_finished(q.params["jobId"], err)
+
+    def serve(self, host: str, port: int) -> Server:
+        return Server(self.router(), host, port).start()
