@@ -1,0 +1,569 @@
+// tcgen05 / TMEM / TMA GEMM family for sm_100a: plain GEMMs (linear layers, im2col'd convolutions)
+// and implicit-GEMM convolution forward / data-gradient / weight-gradient.
+//
+// The reference has no kernels of its own: these shapes reach cuDNN / cuBLAS through
+// torch 1.7.1 (ml/environment/Dockerfile:3,20; ml/experiments/kubeml/function_resnet34.py:65-75 —
+// forward, F.cross_entropy, backward).  SURVEY 2.4 lists the op inventory this file covers
+// (Conv2d fwd/dgrad/wgrad, Linear fwd/bwd).
+//
+// One CTA computes one 128 x BLOCK_N output tile (optionally one K-split of it):
+//   warp 0   TMA producer: per 64-deep K chunk, cp.async.bulk.tensor boxes into a 4-stage smem ring
+//   warp 1   MMA issuer: one elected lane issues 4 x tcgen05.mma (K=16) per chunk, accumulating
+//            in TMEM; tcgen05.commit releases the smem slot / signals the epilogue
+//   warps 2-5 epilogue: tcgen05.ld the fp32 accumulator (one TMEM lane = one output row per thread),
+//            bias / ReLU / cast, store or red.add (split-K, weight gradients)
+//
+// Operands are always described by rank-4 tensor maps with 128B swizzle.  "K-major" operands keep
+// the reduction dimension contiguous (activations NHWC over channels, weights [Cout][taps*Cin]);
+// "MN-major" operands keep the M/N dimension contiguous (weight gradients reduce over pixels, so
+// both dY and X are consumed channel-contiguous exactly as they sit in memory — no transposes).
+// For convolutions the A box is a (64ch, BW, BH, BN) window of the NHWC tensor whose origin is
+// shifted by the filter tap; out-of-bounds rows/cols are zero-filled by TMA, which *is* the padding.
+#include "common.cuh"
+#include "driver_api.h"
+#include "../include/kubeml_b200.h"
+#include <cuda.h>
+
+namespace {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;            // bf16 elements = one 128-byte swizzle row
+constexpr int kStages = 4;
+constexpr int kNumThreads = 192;       // producer warp, MMA warp, 4 epilogue warps
+constexpr int kUmmaK = 16;
+
+enum OperandKind : int {
+  kMatK = 0,     // matrix, reduction dim contiguous:   coords (k, mn, 0, 0)
+  kMatMN = 1,    // matrix, M/N dim contiguous:         coords (mn, k, 0, 0)
+  kConvK = 2,    // NHWC activation, tile walks pixels, chunks walk (tap, channel block)
+  kConvMN = 3,   // NHWC activation, tile walks channels, chunks walk pixel boxes (+ fixed tap shift)
+};
+
+struct Geometry {       // how a linear index becomes a (w, h, n) box origin
+  int bw, bh, bn;       // box extent
+  int tiles_w, tiles_h; // boxes per row / per image
+};
+
+struct GemmArgs {
+  int a_kind, b_kind;
+  int m_tiles, n_tiles, splits, z_taps;  // grid = (m_tiles, n_tiles, z_taps * splits)
+  int k_chunks;                          // chunks of 64 along the reduction dim (all taps included)
+  // convolution description
+  int kw, pad_w, pad_h, cblocks;         // filter width, padding, channel blocks per tap
+  unsigned long long tap_mask;           // kConvK: taps that touch at least one real pixel
+  Geometry tile_geo;                     // kConvK: output-tile pixel box
+  Geometry chunk_geo;                    // kConvMN: reduction pixel box
+  // epilogue
+  void* out;
+  long long ldo;                         // elements between output rows
+  long long z_col_stride;                // column offset added per tap (weight gradients)
+  int m_valid, n_valid;                  // rows / columns actually present
+  const float* bias;                     // per output column, may be null
+  int relu, out_f32, atomic_add;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
+      "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
+      "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.b32 %0, 1, 0, P;\n\t}" : "=r"(pred)::"memory");
+  return pred != 0;
+}
+
+// Shared-memory matrix descriptor, 128B swizzle (cute::UMMA::SmemDescriptor: start>>4 [0,14),
+// LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout_type=2 (SWIZZLE_128B) [61,64)).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= 1ull << 46;
+  d |= 2ull << 61;
+  return d;
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D=f32 [4,6)=1, A=bf16 [7,10)=1, B=bf16
+// [10,13)=1, a_major bit 15, b_major bit 16, N>>3 [17,23), M>>4 [24,29).
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n, bool a_mn, bool b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(a_mn) << 15) |
+         (static_cast<uint32_t>(b_mn) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
+         (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void box_origin(const Geometry& g, int idx, int& w0, int& h0, int& n0) {
+  const int tw = idx % g.tiles_w;
+  const int t2 = idx / g.tiles_w;
+  w0 = tw * g.bw;
+  h0 = (t2 % g.tiles_h) * g.bh;
+  n0 = (t2 / g.tiles_h) * g.bn;
+}
+
+template <int BLOCK_N, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    const GemmArgs args) {
+  constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
+  constexpr uint32_t kBBytes = BLOCK_N * kBlockK * 2;
+  constexpr uint32_t kHalfBytes = 64 * kBlockK * 2;   // one 64-wide MN block of an MN-major operand
+  constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_b + kStages * kBBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  int* tap_list = reinterpret_cast<int*>(tmem_slot + 1);   // up to 64 entries
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int mt = blockIdx.x, nt = blockIdx.y;
+  const int z_tap = blockIdx.z / args.splits;
+  const int split = blockIdx.z % args.splits;
+  const int per = (args.k_chunks + args.splits - 1) / args.splits;
+  const int kbeg = split * per;
+  const int kend = min(args.k_chunks, kbeg + per);
+  const int nchunks = max(0, kend - kbeg);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    int n = 0;
+    for (int t = 0; t < 64; ++t) if ((args.tap_mask >> t) & 1ull) tap_list[n++] = t;
+  }
+  if (warp == 1) {   // this warp owns the TMEM allocation
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================== TMA producer =====================================
+    if (elect_one()) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      int tw0 = 0, th0 = 0, tn0 = 0;
+      if (args.a_kind == kConvK) box_origin(args.tile_geo, mt, tw0, th0, tn0);
+      const int z_dw = z_tap % max(args.kw, 1) - args.pad_w;   // kConvMN: fixed shift of this CTA's tap
+      const int z_dh = z_tap / max(args.kw, 1) - args.pad_h;
+      for (int i = 0; i < nchunks; ++i) {
+        const int kc = kbeg + i;
+        const int s = i % kStages;
+        const uint32_t ph = (i / kStages) & 1;
+        mbar_wait(empty_bar + s, ph ^ 1);
+        mbar_expect_tx(full_bar + s, kABytes + kBBytes);
+        uint8_t* sa = smem_a + s * kABytes;
+        uint8_t* sb = smem_b + s * kBBytes;
+        int cw = 0, ch = 0, cn = 0;
+        if (args.a_kind == kConvMN || args.b_kind == kConvMN) box_origin(args.chunk_geo, kc, cw, ch, cn);
+        // ---- A ----
+        if (args.a_kind == kMatK) {
+          tma_load_4d(&map_a, full_bar + s, sa, kc * kBlockK, mt * kBlockM, 0, 0);
+        } else if (args.a_kind == kConvK) {
+          const int tap = tap_list[kc / args.cblocks];
+          const int cb = kc % args.cblocks;
+          tma_load_4d(&map_a, full_bar + s, sa, cb * kBlockK, tw0 + tap % args.kw - args.pad_w,
+                      th0 + tap / args.kw - args.pad_h, tn0);
+        } else if (args.a_kind == kMatMN) {
+#pragma unroll
+          for (int hb = 0; hb < kBlockM / 64; ++hb)
+            tma_load_4d(&map_a, full_bar + s, sa + hb * kHalfBytes, mt * kBlockM + hb * 64, kc * kBlockK, 0, 0);
+        } else {
+#pragma unroll
+          for (int hb = 0; hb < kBlockM / 64; ++hb)
+            tma_load_4d(&map_a, full_bar + s, sa + hb * kHalfBytes, mt * kBlockM + hb * 64, cw, ch, cn);
+        }
+        // ---- B ----
+        if (args.b_kind == kMatK) {
+          tma_load_4d(&map_b, full_bar + s, sb, kc * kBlockK, nt * BLOCK_N, 0, 0);
+        } else if (args.b_kind == kMatMN) {
+#pragma unroll
+          for (int hb = 0; hb < BLOCK_N / 64; ++hb)
+            tma_load_4d(&map_b, full_bar + s, sb + hb * kHalfBytes, nt * BLOCK_N + hb * 64, kc * kBlockK, 0, 0);
+        } else {
+#pragma unroll
+          for (int hb = 0; hb < BLOCK_N / 64; ++hb)
+            tma_load_4d(&map_b, full_bar + s, sb + hb * kHalfBytes, nt * BLOCK_N + hb * 64, cw + z_dw, ch + z_dh, cn);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer ========================================
+    constexpr uint32_t idesc = make_idesc(kBlockM, BLOCK_N, A_MN, B_MN);
+    for (int i = 0; i < nchunks; ++i) {
+      const int s = i % kStages;
+      const uint32_t ph = (i / kStages) & 1;
+      mbar_wait(full_bar + s, ph);
+      tcgen05_fence_after();
+      if (elect_one()) {
+        const uint32_t a_addr = smem_u32(smem_a + s * kABytes);
+        const uint32_t b_addr = smem_u32(smem_b + s * kBBytes);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // K-major: 16 bf16 = 32 bytes further along the swizzled row.
+          // MN-major: 16 reduction rows = two 8-row groups of 1024 bytes.
+          const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * 2048, kHalfBytes, 1024)
+                                      : make_smem_desc(a_addr + k * 32, 16, 1024);
+          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * 2048, kHalfBytes, 1024)
+                                      : make_smem_desc(b_addr + k * 32, 16, 1024);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+        }
+      }
+      __syncwarp();
+      if (elect_one()) {
+        umma_commit(empty_bar + s);                     // frees the smem slot when the MMAs retire
+        if (i == nchunks - 1) umma_commit(tmem_full_bar);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===================================== epilogue ==========================================
+    const int q = warp & 3;                              // TMEM lane quarter this warp may read
+    const int row = mt * kBlockM + q * 32 + lane;
+    if (nchunks > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tcgen05_fence_after();
+    }
+    const bool row_ok = row < args.m_valid;
+    const long long col_base = static_cast<long long>(z_tap) * args.z_col_stride + static_cast<long long>(nt) * BLOCK_N;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      uint32_t v[32];
+      if (nchunks > 0) {
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0u;
+      }
+      if (!row_ok) continue;
+      const int ncol0 = nt * BLOCK_N + c0;                // column within the (per-tap) N range
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        f[j] = __uint_as_float(v[j]);
+        if (args.bias != nullptr && split == 0 && ncol0 + j < args.n_valid) f[j] += __ldg(args.bias + ncol0 + j);
+        if (args.relu) f[j] = fmaxf(f[j], 0.f);
+      }
+      const long long off = static_cast<long long>(row) * args.ldo + col_base + c0;
+      if (args.out_f32) {
+        float* o = static_cast<float*>(args.out) + off;
+        if (args.atomic_add) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (ncol0 + j < args.n_valid) atomicAdd(o + j, f[j]);
+        } else if (ncol0 + 32 <= args.n_valid && (off & 3) == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (ncol0 + j < args.n_valid) o[j] = f[j];
+        }
+      } else {
+        __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + off;
+        if (ncol0 + 32 <= args.n_valid && (off & 7) == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            __nv_bfloat162 p0 = __floats2bfloat162_rn(f[j], f[j + 1]);
+            __nv_bfloat162 p1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
+            __nv_bfloat162 p2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]);
+            __nv_bfloat162 p3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
+            uint4 u;
+            u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
+            u.z = *reinterpret_cast<uint32_t*>(&p2); u.w = *reinterpret_cast<uint32_t*>(&p3);
+            *reinterpret_cast<uint4*>(o + j) = u;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (ncol0 + j < args.n_valid) o[j] = __float2bfloat16_rn(f[j]);
+        }
+      }
+    }
+    tcgen05_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// host side
+// --------------------------------------------------------------------------------------------
+
+struct TensorSpec {          // rank-4 view, dim 0 innermost (contiguous)
+  const void* ptr;
+  uint64_t dim[4];
+  uint64_t stride_bytes[3];  // strides of dims 1..3
+  uint32_t box[4];
+};
+
+int encode_map(CUtensorMap* map, const TensorSpec& t) {
+  const kml::DriverApi* d = kml::driver();
+  if (!d) return 4;
+  cuuint64_t dims[4] = {t.dim[0], t.dim[1], t.dim[2], t.dim[3]};
+  cuuint64_t strides[3] = {t.stride_bytes[0], t.stride_bytes[1], t.stride_bytes[2]};
+  cuuint32_t box[4] = {t.box[0], t.box[1], t.box[2], t.box[3]};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  KML_CHECK((reinterpret_cast<uintptr_t>(t.ptr) & 15u) == 0, "tensor map base must be 16-byte aligned");
+  for (int i = 0; i < 3; ++i) KML_CHECK(strides[i] % 16 == 0, "tensor map stride %d (%llu) not a multiple of 16 bytes", i, (unsigned long long)strides[i]);
+  CUresult r = d->cuTensorMapEncodeTiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(t.ptr), dims,
+                                         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    kml::set_error("cuTensorMapEncodeTiled failed: %s (dims %llu,%llu,%llu,%llu box %u,%u,%u,%u)", kml::cu_err(r),
+                   (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)dims[2],
+                   (unsigned long long)dims[3], box[0], box[1], box[2], box[3]);
+    return 3;
+  }
+  return 0;
+}
+
+template <int BLOCK_N, bool A_MN, bool B_MN>
+int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& a, cudaStream_t s) {
+  constexpr size_t smem = kStages * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 /*align*/ + 512 /*barriers+taps*/;
+  auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN>;
+  static bool configured = false;
+  if (!configured) {
+    KML_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    configured = true;
+  }
+  dim3 grid(a.m_tiles, a.n_tiles, a.z_taps * a.splits);
+  kernel<<<grid, kNumThreads, smem, s>>>(ma, mb, a);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int launch(const TensorSpec& ta, const TensorSpec& tb, const GemmArgs& a, int block_n, cudaStream_t s) {
+  CUtensorMap ma, mb;
+  int rc = encode_map(&ma, ta);
+  if (rc) return rc;
+  rc = encode_map(&mb, tb);
+  if (rc) return rc;
+  const bool amn = a.a_kind == kMatMN || a.a_kind == kConvMN;
+  const bool bmn = a.b_kind == kMatMN || a.b_kind == kConvMN;
+  KML_CHECK(block_n == 64 || block_n == 128, "block_n must be 64 or 128");
+  KML_CHECK(!(amn && !bmn), "A MN-major with B K-major is not instantiated");
+  if (block_n == 64) {
+    if (!amn && !bmn) return launch_variant<64, false, false>(ma, mb, a, s);
+    if (!amn && bmn) return launch_variant<64, false, true>(ma, mb, a, s);
+    return launch_variant<64, true, true>(ma, mb, a, s);
+  }
+  if (!amn && !bmn) return launch_variant<128, false, false>(ma, mb, a, s);
+  if (!amn && bmn) return launch_variant<128, false, true>(ma, mb, a, s);
+  return launch_variant<128, true, true>(ma, mb, a, s);
+}
+
+inline int ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
+
+// Pixel box of `target` pixels over a W x H x N grid: whole rows first, then rows, then images.
+bool make_geometry(int W, int H, int target, Geometry* g) {
+  if (!pow2(W) || !pow2(H) || W > target) return false;
+  g->bw = W;
+  g->bh = H < target / W ? H : target / W;
+  g->bn = target / (g->bw * g->bh);
+  g->tiles_w = 1;
+  g->tiles_h = H / g->bh;
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* out,
+                  long long ldo, int M, int N, int K, const float* bias, int relu, int out_f32, int splits,
+                  int block_n, void* stream) {
+  KML_CHECK(A && B && out && M > 0 && N > 0 && K > 0, "kml_gemm_bf16: bad arguments");
+  KML_CHECK(lda % 8 == 0 && ldb % 8 == 0, "kml_gemm_bf16: leading dimensions must be multiples of 8 elements");
+  if (block_n == 0) block_n = (N > 64) ? 128 : 64;
+  if (splits < 1) splits = 1;
+  TensorSpec ta{}, tb{};
+  ta.ptr = A; tb.ptr = B;
+  // K-major [rows][K]: dim0 = K, dim1 = rows.  MN-major [K][rows]: dim0 = rows, dim1 = K.
+  ta.dim[0] = a_mn ? M : K; ta.dim[1] = a_mn ? K : M; ta.dim[2] = ta.dim[3] = 1;
+  ta.stride_bytes[0] = static_cast<uint64_t>(lda) * 2; ta.stride_bytes[1] = ta.stride_bytes[0] * ta.dim[1];
+  ta.stride_bytes[2] = ta.stride_bytes[1];
+  ta.box[0] = 64; ta.box[1] = a_mn ? kBlockK : kBlockM; ta.box[2] = ta.box[3] = 1;
+  tb.dim[0] = b_mn ? N : K; tb.dim[1] = b_mn ? K : N; tb.dim[2] = tb.dim[3] = 1;
+  tb.stride_bytes[0] = static_cast<uint64_t>(ldb) * 2; tb.stride_bytes[1] = tb.stride_bytes[0] * tb.dim[1];
+  tb.stride_bytes[2] = tb.stride_bytes[1];
+  tb.box[0] = 64; tb.box[1] = b_mn ? kBlockK : block_n; tb.box[2] = tb.box[3] = 1;
+  GemmArgs g{};
+  g.a_kind = a_mn ? kMatMN : kMatK;
+  g.b_kind = b_mn ? kMatMN : kMatK;
+  g.m_tiles = ceil_div(M, kBlockM);
+  g.n_tiles = ceil_div(N, block_n);
+  g.k_chunks = ceil_div(K, kBlockK);
+  g.splits = splits > g.k_chunks ? g.k_chunks : splits;
+  g.z_taps = 1; g.kw = 1; g.cblocks = 1;
+  g.out = out; g.ldo = ldo; g.m_valid = M; g.n_valid = N;
+  g.bias = bias; g.relu = relu; g.out_f32 = out_f32;
+  g.atomic_add = g.splits > 1;
+  KML_CHECK(!g.atomic_add || (out_f32 && !relu), "split-K needs an fp32 output (pre-zeroed) and no ReLU");
+  return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
+}
+
+int kml_conv2d_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                     int pad, const float* bias, int relu, int out_f32, int splits, int block_n, void* stream) {
+  KML_CHECK(x && w && y, "kml_conv2d_fprop: null pointer");
+  KML_CHECK(Cin % 64 == 0, "kml_conv2d_fprop: Cin (%d) must be a multiple of 64 (use the im2col path otherwise)", Cin);
+  KML_CHECK(Cout % 8 == 0, "kml_conv2d_fprop: Cout (%d) must be a multiple of 8", Cout);
+  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  KML_CHECK(Ho > 0 && Wo > 0 && KH * KW <= 64, "kml_conv2d_fprop: bad geometry");
+  GemmArgs g{};
+  KML_CHECK(make_geometry(Wo, Ho, kBlockM, &g.tile_geo),
+            "kml_conv2d_fprop: output %dx%d is not a power-of-two grid (use the im2col path)", Ho, Wo);
+  if (block_n == 0) block_n = (Cout > 64) ? 128 : 64;
+  if (splits < 1) splits = 1;
+  TensorSpec ta{}, tb{};
+  ta.ptr = x;
+  ta.dim[0] = Cin; ta.dim[1] = W; ta.dim[2] = H; ta.dim[3] = N;
+  ta.stride_bytes[0] = static_cast<uint64_t>(Cin) * 2; ta.stride_bytes[1] = ta.stride_bytes[0] * W;
+  ta.stride_bytes[2] = ta.stride_bytes[1] * H;
+  ta.box[0] = 64; ta.box[1] = g.tile_geo.bw; ta.box[2] = g.tile_geo.bh; ta.box[3] = g.tile_geo.bn;
+  const long long Kt = static_cast<long long>(KH) * KW * Cin;
+  tb.ptr = w;
+  tb.dim[0] = Kt; tb.dim[1] = Cout; tb.dim[2] = tb.dim[3] = 1;
+  tb.stride_bytes[0] = static_cast<uint64_t>(Kt) * 2; tb.stride_bytes[1] = tb.stride_bytes[0] * Cout;
+  tb.stride_bytes[2] = tb.stride_bytes[1];
+  tb.box[0] = 64; tb.box[1] = block_n; tb.box[2] = tb.box[3] = 1;
+  // Taps whose shifted window lies entirely in the zero padding contribute nothing: skip them.
+  unsigned long long mask = 0;
+  int ntaps = 0;
+  for (int kh = 0; kh < KH; ++kh)
+    for (int kw = 0; kw < KW; ++kw) {
+      const bool h_hit = (kh - pad) <= (H - 1) && (Ho - 1 + kh - pad) >= 0;
+      const bool w_hit = (kw - pad) <= (W - 1) && (Wo - 1 + kw - pad) >= 0;
+      if (h_hit && w_hit) { mask |= 1ull << (kh * KW + kw); ++ntaps; }
+    }
+  g.a_kind = kConvK; g.b_kind = kMatK;
+  g.tap_mask = mask; g.kw = KW; g.pad_w = pad; g.pad_h = pad; g.cblocks = Cin / 64;
+  const long long Mtot = static_cast<long long>(N) * Ho * Wo;
+  const int imgs_per_tile = g.tile_geo.bn;
+  g.m_tiles = g.tile_geo.tiles_h * ceil_div(N, imgs_per_tile);
+  g.n_tiles = ceil_div(Cout, block_n);
+  g.k_chunks = ntaps * g.cblocks;
+  g.splits = splits > g.k_chunks ? g.k_chunks : splits;
+  g.z_taps = 1;
+  g.out = y; g.ldo = Cout; g.m_valid = static_cast<int>(Mtot); g.n_valid = Cout;
+  g.bias = bias; g.relu = relu; g.out_f32 = out_f32; g.atomic_add = g.splits > 1;
+  KML_CHECK(!g.atomic_add || (out_f32 && !relu), "split-K needs an fp32 output (pre-zeroed) and no ReLU");
+  // B chunk index must address [tap][cblock] of the *full* filter: remap through a dense weight
+  // view is not possible when taps are skipped, so skipped taps are only allowed when the kernel
+  // can index B by the real tap.  The kernel uses kc*64 as the B column, therefore present B to it
+  // as the concatenation of the live taps.
+  if (ntaps != KH * KW) {
+    // live taps form a contiguous rectangle [kh0,kh1] x [kw0,kw1]; when it is a single row segment
+    // the B columns are contiguous and a pointer offset is enough.
+    int first = -1, last = -1;
+    for (int t = 0; t < KH * KW; ++t) if ((mask >> t) & 1ull) { if (first < 0) first = t; last = t; }
+    if (last - first + 1 == ntaps) {
+      tb.ptr = static_cast<const __nv_bfloat16*>(w) + static_cast<long long>(first) * Cin;
+      tb.dim[0] = Kt - static_cast<long long>(first) * Cin;
+    } else {
+      // fall back to all taps (zeros are loaded, results identical)
+      mask = 0;
+      for (int t = 0; t < KH * KW; ++t) mask |= 1ull << t;
+      g.tap_mask = mask;
+      g.k_chunks = KH * KW * g.cblocks;
+      g.splits = splits > g.k_chunks ? g.k_chunks : splits;
+      g.atomic_add = g.splits > 1;
+    }
+  }
+  return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
+}
+
+int kml_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                     int pad, int splits, int block_n, void* stream) {
+  KML_CHECK(x && dy && dw, "kml_conv2d_wgrad: null pointer");
+  KML_CHECK(Cin % 8 == 0 && Cout % 8 == 0, "kml_conv2d_wgrad: channel counts must be multiples of 8");
+  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  KML_CHECK(Ho > 0 && Wo > 0, "kml_conv2d_wgrad: bad geometry");
+  GemmArgs g{};
+  KML_CHECK(make_geometry(Wo, Ho, kBlockK, &g.chunk_geo),
+            "kml_conv2d_wgrad: output %dx%d is not a power-of-two grid (use the im2col path)", Ho, Wo);
+  if (block_n == 0) block_n = (Cin > 64) ? 128 : 64;
+  TensorSpec ta{}, tb{};
+  ta.ptr = dy;   // A = dY^T: M = Cout (contiguous), reduction over output pixels
+  ta.dim[0] = Cout; ta.dim[1] = Wo; ta.dim[2] = Ho; ta.dim[3] = N;
+  ta.stride_bytes[0] = static_cast<uint64_t>(Cout) * 2; ta.stride_bytes[1] = ta.stride_bytes[0] * Wo;
+  ta.stride_bytes[2] = ta.stride_bytes[1] * Ho;
+  ta.box[0] = 64; ta.box[1] = g.chunk_geo.bw; ta.box[2] = g.chunk_geo.bh; ta.box[3] = g.chunk_geo.bn;
+  tb.ptr = x;    // B = X shifted by the tap: N = Cin (contiguous)
+  tb.dim[0] = Cin; tb.dim[1] = W; tb.dim[2] = H; tb.dim[3] = N;
+  tb.stride_bytes[0] = static_cast<uint64_t>(Cin) * 2; tb.stride_bytes[1] = tb.stride_bytes[0] * W;
+  tb.stride_bytes[2] = tb.stride_bytes[1] * H;
+  tb.box[0] = 64; tb.box[1] = g.chunk_geo.bw; tb.box[2] = g.chunk_geo.bh; tb.box[3] = g.chunk_geo.bn;
+  g.a_kind = kConvMN; g.b_kind = kConvMN;
+  g.kw = KW; g.pad_w = pad; g.pad_h = pad; g.cblocks = 1;
+  g.m_tiles = ceil_div(Cout, kBlockM);
+  g.n_tiles = ceil_div(Cin, block_n);
+  g.k_chunks = g.chunk_geo.tiles_h * ceil_div(N, g.chunk_geo.bn);
+  if (splits < 1) splits = 1;
+  g.splits = splits > g.k_chunks ? g.k_chunks : splits;
+  g.z_taps = KH * KW;
+  g.out = dw; g.ldo = static_cast<long long>(KH) * KW * Cin; g.z_col_stride = Cin;
+  g.m_valid = Cout; g.n_valid = Cin;
+  g.out_f32 = 1; g.atomic_add = g.splits > 1;
+  return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

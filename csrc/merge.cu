@@ -1,0 +1,229 @@
+// K-AVG model merge over NVLink peer memory — one kernel per rank, no NCCL.
+//
+// What the reference does per sync round: every worker serialises its state_dict to
+// RedisAI, the Go job fetches all N copies, sums them on the CPU under a mutex
+// (ml/pkg/model/model.go:249-302), divides by N (ml/pkg/model/parallelSGD.go:26-54), writes the result
+// back (model.go:135-161) and every worker downloads it again (python/kubeml/kubeml/network.py:416-442)
+// after an HTTP barrier (ml/pkg/train/api.go:100-126): (3N+1)x|model| bytes through one TCP endpoint.
+//
+// Here every replica lives in a VMM arena mapped into all peers.  Each participating rank runs
+// this kernel on its own GPU:
+//   phase 0  (optional) last local SGD step of the round on the own replica, fused
+//   barrier  release/acquire flags in peer memory: all replicas are final
+//   phase 1  the rank owns 1/P of the buffer: for each float4 it loads that element from every
+//            participant (plain peer loads, or one multimem.ld_reduce through the switch), sums in
+//            rank order in fp32, scales by 1/P and stores the result into *every* replica
+//            (peer stores, or one multimem.st); int64 counters are summed and divided with
+//            truncation like parallelSGD.go:42-43
+//   phase 2  momentum buffer zeroed (the reference's optimizer reset, network.py:121-128)
+//   barrier  all writes have landed before anyone runs its next local step
+#include "common.cuh"
+#include "../include/kubeml_b200.h"
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
+
+namespace {
+
+constexpr int kThreads = 512;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_cg_f4(float4* p, const float4& v) {
+  asm volatile("st.global.cg.v4.f32 [%0], {%1,%2,%3,%4};"
+               ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 mc_ld_reduce_f4(const float4* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_f4(float4* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// Cross-rank barrier executed by one thread of the grid.  slot = phase*KML_MAX_RANKS + writer.
+__device__ void rank_barrier(const kml_merge_params& p, int phase, uint32_t gen) {
+  __threadfence_system();
+#pragma unroll
+  for (int r = 0; r < KML_MAX_RANKS; ++r)
+    if ((p.participants >> r) & 1u) st_release_sys(p.flags[r] + phase * KML_MAX_RANKS + p.my_rank, gen);
+  const unsigned long long limit = p.timeout_cycles ? p.timeout_cycles : 8000000000ull;
+  const long long t0 = clock64();
+#pragma unroll
+  for (int r = 0; r < KML_MAX_RANKS; ++r) {
+    if (!((p.participants >> r) & 1u)) continue;
+    const uint32_t* f = p.flags[p.my_rank] + phase * KML_MAX_RANKS + r;
+    // generations only grow, so ">=" tolerates a fast peer that already moved on
+    while (static_cast<int32_t>(ld_acquire_sys(f) - gen) < 0) {
+      if (static_cast<unsigned long long>(clock64() - t0) > limit) {
+        if (p.status) atomicExch(p.status, 1 + r);
+        break;
+      }
+      __nanosleep(64);
+    }
+  }
+  __threadfence_system();
+}
+
+template <bool kMcast>
+__global__ void __launch_bounds__(kThreads)
+kavg_merge_kernel(const kml_merge_params p) {
+  cg::grid_group grid = cg::this_grid();
+  const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t n4 = p.n_f32 / 4;
+  const bool sync_ranks = p.generation != 0;
+
+  // ---- phase 0: fused last local step on the own replica --------------------------------------
+  if (p.fuse_sgd) {
+    float4* w = reinterpret_cast<float4*>(p.replica[p.my_rank]);
+    const float4* g = reinterpret_cast<const float4*>(p.grad);
+    const float4* m = reinterpret_cast<const float4*>(p.momentum_buf);
+    const bool has_m = p.momentum != 0.f && m != nullptr;
+    for (size_t i = tid; i < n4; i += nthreads) {
+      float4 wv = w[i], gv = __ldcs(g + i);
+      float4 d;
+      d.x = fmaf(p.weight_decay, wv.x, gv.x); d.y = fmaf(p.weight_decay, wv.y, gv.y);
+      d.z = fmaf(p.weight_decay, wv.z, gv.z); d.w = fmaf(p.weight_decay, wv.w, gv.w);
+      if (has_m) {
+        float4 mv = __ldcs(m + i);
+        d.x = fmaf(p.momentum, mv.x, d.x); d.y = fmaf(p.momentum, mv.y, d.y);
+        d.z = fmaf(p.momentum, mv.z, d.z); d.w = fmaf(p.momentum, mv.w, d.w);
+      }
+      wv.x = fmaf(-p.lr, d.x, wv.x); wv.y = fmaf(-p.lr, d.y, wv.y);
+      wv.z = fmaf(-p.lr, d.z, wv.z); wv.w = fmaf(-p.lr, d.w, wv.w);
+      w[i] = wv;
+    }
+  }
+
+  if (sync_ranks) {
+    grid.sync();
+    if (tid == 0) rank_barrier(p, 0, p.generation);
+    grid.sync();
+  } else if (p.fuse_sgd) {
+    grid.sync();
+  }
+
+  // ---- phase 1: reduce my slice, write everyone -----------------------------------------------
+  int nparts = __popc(p.participants);
+  int pos = __popc(p.participants & ((1u << p.my_rank) - 1u));
+  size_t begin = 0, end = n4;
+  if (sync_ranks) {
+    begin = n4 * pos / nparts;
+    end = n4 * (pos + 1) / nparts;
+  }
+  const float inv = 1.0f / static_cast<float>(nparts);
+
+  if constexpr (kMcast) {
+    float4* mc = reinterpret_cast<float4*>(p.mcast);
+    for (size_t i = begin + tid; i < end; i += nthreads) {
+      float4 s = mc_ld_reduce_f4(mc + i);
+      s.x *= inv; s.y *= inv; s.z *= inv; s.w *= inv;
+      mc_st_f4(mc + i, s);
+    }
+  } else {
+    for (size_t i = begin + tid; i < end; i += nthreads) {
+      float4 v[KML_MAX_RANKS];
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r)
+        if ((p.participants >> r) & 1u) v[r] = ld_cg_f4(reinterpret_cast<const float4*>(p.replica[r]) + i);
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      bool first = true;
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r) {
+        if (!((p.participants >> r) & 1u)) continue;
+        if (first) { s = v[r]; first = false; }
+        else { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+      }
+      // true division keeps bit-parity with the CPU oracle (sum then divide)
+      s.x = s.x / static_cast<float>(nparts); s.y = s.y / static_cast<float>(nparts);
+      s.z = s.z / static_cast<float>(nparts); s.w = s.w / static_cast<float>(nparts);
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r)
+        if ((p.write_mask >> r) & 1u) st_cg_f4(reinterpret_cast<float4*>(p.replica[r]) + i, s);
+    }
+  }
+
+  // int64 counters: the lowest participating rank handles them all (a few dozen scalars)
+  if (p.n_i64 && pos == 0) {
+    for (size_t i = tid; i < p.n_i64; i += nthreads) {
+      long long s = 0;
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r)
+        if ((p.participants >> r) & 1u) s += p.ireplica[r][i];
+      s = s / static_cast<long long>(nparts);  // C++ '/' truncates toward zero like Go
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r)
+        if ((p.write_mask >> r) & 1u) p.ireplica[r][i] = s;
+    }
+  }
+
+  // ---- phase 2: optimizer reset -----------------------------------------------------------------
+  if (p.momentum_buf) {
+    float4* m = reinterpret_cast<float4*>(p.momentum_buf);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (size_t i = tid; i < n4; i += nthreads) __stcs(m + i, z);
+  }
+
+  if (sync_ranks) {
+    grid.sync();
+    if (tid == 0) rank_barrier(p, 1, p.generation);
+    grid.sync();
+  }
+}
+
+}  // namespace
+
+extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
+  KML_CHECK(pp != nullptr, "kml_kavg_merge: null params");
+  kml_merge_params p = *pp;
+  KML_CHECK(p.my_rank >= 0 && p.my_rank < KML_MAX_RANKS, "my_rank %d out of range", p.my_rank);
+  KML_CHECK(p.participants != 0 && ((p.participants >> p.my_rank) & 1u),
+            "rank %d launches a merge it does not take part in (mask %#x)", p.my_rank, p.participants);
+  KML_CHECK(p.n_f32 % 4 == 0, "n_f32 (%zu) must be a multiple of 4", p.n_f32);
+  for (int r = 0; r < KML_MAX_RANKS; ++r) {
+    if (((p.participants | p.write_mask) >> r) & 1u) {
+      KML_CHECK(p.replica[r] != nullptr, "replica[%d] is null", r);
+      KML_CHECK((reinterpret_cast<uintptr_t>(p.replica[r]) & 15u) == 0, "replica[%d] not 16-byte aligned", r);
+      KML_CHECK(p.n_i64 == 0 || p.ireplica[r] != nullptr, "ireplica[%d] is null", r);
+    }
+    if (p.generation != 0 && ((p.participants >> r) & 1u))
+      KML_CHECK(p.flags[r] != nullptr, "flags[%d] is null", r);
+  }
+  if (p.fuse_sgd) KML_CHECK(p.grad != nullptr, "fuse_sgd set without grad");
+  const bool use_mc = p.mcast != nullptr && p.generation != 0;
+
+  int dev = 0;
+  KML_CUDA(cudaGetDevice(&dev));
+  auto kernel = use_mc ? kavg_merge_kernel<true> : kavg_merge_kernel<false>;
+  static int occ[2] = {0, 0};
+  if (occ[use_mc] == 0) {
+    int o = 0;
+    KML_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, kThreads, 0));
+    occ[use_mc] = o > 0 ? o : 1;
+  }
+  const size_t n4 = p.n_f32 / 4;
+  int max_blocks = kml::num_sms() * (occ[use_mc] > 2 ? 2 : occ[use_mc]);
+  size_t want = (n4 + kThreads - 1) / kThreads;
+  int blocks = static_cast<int>(want < static_cast<size_t>(max_blocks) ? (want ? want : 1) : max_blocks);
+  void* args[] = {&p};
+  KML_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3(blocks), dim3(kThreads), args, 0,
+                                       static_cast<cudaStream_t>(stream)));
+  kml::count_launch();
+  return 0;
+}

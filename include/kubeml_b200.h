@@ -1,0 +1,122 @@
+/*
+ * kubeml_b200 native runtime — C ABI.
+ *
+ * One shared library (kubeml_b200/_native/libkubeml_b200.so), built for sm_100a only, called from
+ * Python through ctypes with raw device pointers and a cudaStream_t.  Every function returns 0 on
+ * success or a non-zero code; kml_last_error() returns the message of the last failure on the
+ * calling thread.  Nothing here allocates device memory unless its comment says so.
+ *
+ * Reference parity is cited per entry point as path:line into zzengcs/kubeML.
+ */
+#ifndef KUBEML_B200_H
+#define KUBEML_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KML_MAX_RANKS 8
+
+const char* kml_last_error(void);
+int kml_version(void);
+/* Number of kernels this library has launched in the calling process (bench "gpu_launches"). */
+unsigned long long kml_launch_count(void);
+void kml_reset_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Weight arena: device memory allocated through the CUDA VMM API so that it can be exported to the
+ * other per-GPU worker processes as a POSIX fd and mapped there as peer memory, and bound to an
+ * NVSwitch multicast object.  Replaces the RedisAI tensor store of the reference
+ * (python/kubeml/kubeml/network.py:416-461, ml/pkg/model/model.go:135-161, 249-269).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct kml_arena kml_arena_t;
+
+/* Allocates `bytes` (rounded up to the allocation granularity) on `device`.  want_fabric_fd != 0
+ * makes the allocation exportable.  *out receives the handle. */
+int kml_arena_create(int device, size_t bytes, int exportable, kml_arena_t** out);
+int kml_arena_destroy(kml_arena_t* a);
+void* kml_arena_ptr(const kml_arena_t* a);
+size_t kml_arena_size(const kml_arena_t* a);
+/* Returns a new fd owned by the caller (close it after sending it to the peers). */
+int kml_arena_export_fd(kml_arena_t* a, int* fd_out);
+/* Maps a peer's exported allocation (fd received over a Unix socket) into this process with
+ * read/write access for `device`.  The fd may be closed afterwards. */
+int kml_arena_import_fd(int device, int fd, size_t bytes, kml_arena_t** out);
+/* Grants `device` access to an arena owned by this process (single-process multi-GPU). */
+int kml_arena_grant_access(kml_arena_t* a, int device);
+
+/* Multicast (NVLS) object spanning `num_devices` GPUs.  Rank 0 creates and exports it, the others
+ * import; everyone then adds its device, binds its arena and maps the multicast VA. */
+typedef struct kml_mcast kml_mcast_t;
+int kml_mcast_supported(int device, int* supported);
+int kml_mcast_create(int num_devices, size_t bytes, kml_mcast_t** out);
+int kml_mcast_export_fd(kml_mcast_t* m, int* fd_out);
+int kml_mcast_import_fd(int fd, int num_devices, size_t bytes, kml_mcast_t** out);
+int kml_mcast_add_device(kml_mcast_t* m, int device);
+int kml_mcast_bind(kml_mcast_t* m, int device, kml_arena_t* arena, void** mc_ptr_out);
+int kml_mcast_destroy(kml_mcast_t* m);
+
+/* ------------------------------------------------------------------------------------------------
+ * K-AVG merge (the north-star kernel).  Replaces Model.Update + ParallelSGD.Average + Model.Save +
+ * N x __load_model (ml/pkg/model/model.go:249-302, parallelSGD.go:26-54, network.py:416-442) and the
+ * HTTP /next barrier (ml/pkg/train/api.go:100-126) with one kernel per rank.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  /* replica[r]: address, valid on the calling GPU, of rank r's fp32 weight region (peer mapped).
+   * Only ranks in `participants` are read; every rank in `write_mask` is written. */
+  float* replica[KML_MAX_RANKS];
+  long long* ireplica[KML_MAX_RANKS]; /* int64 region (BatchNorm num_batches_tracked), may be NULL */
+  uint32_t* flags[KML_MAX_RANKS];     /* flags[r]: rank r's signal pad, >= 2*KML_MAX_RANKS words  */
+  float* mcast;                       /* multicast address of the fp32 region, or NULL           */
+  size_t n_f32;                       /* floats per replica (multiple of 4, 16-byte aligned)     */
+  size_t n_i64;
+  int my_rank;
+  uint32_t participants;              /* bit r: rank r contributes a replica this round          */
+  uint32_t write_mask;                /* bit r: rank r receives the merged model                 */
+  uint32_t generation;                /* strictly increasing per merge; 0 disables the barrier   */
+  /* Fused last local step of the round + optimizer reset (network.py:121-128): applied to this
+   * rank's own replica before the exchange when fuse_sgd != 0. */
+  int fuse_sgd;
+  const float* grad;
+  float* momentum_buf;                /* zeroed after the merge when non-NULL (optimizer reset)   */
+  float lr, weight_decay, momentum;
+  unsigned long long timeout_cycles;  /* spin limit for the cross-rank barrier; 0 = default       */
+  int* status;                        /* device int, set non-zero if the barrier timed out        */
+} kml_merge_params;
+
+/* Launches the merge on `stream` of the current device.  With generation == 0 no cross-rank
+ * barrier is executed and the calling rank reduces the whole buffer (single-GPU emulation). */
+int kml_kavg_merge(const kml_merge_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Optimizers over the flat arena (torch.optim.SGD / Adam semantics; function_lenet.py:79-81,
+ * function_resnet34.py:62, function_vgg11.py).  One launch covers every parameter.
+ * w_bf16 (optional) receives the updated weights rounded to bf16 for the tensor-core operands.
+ * ---------------------------------------------------------------------------------------------- */
+int kml_sgd_step(float* w, const float* g, float* momentum_buf, size_t n, float lr,
+                 float weight_decay, float momentum, int nesterov, void* w_bf16, void* stream);
+int kml_adam_step(float* w, const float* g, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
+                  float beta1, float beta2, float eps, float weight_decay, int step, void* w_bf16,
+                  void* stream);
+int kml_cast_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* stream);
+int kml_fill_f32(float* dst, float value, size_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fused softmax-cross-entropy (F.cross_entropy, mean reduction; function_resnet34.py:69) forward +
+ * backward + accuracy count in one launch.  logits [rows, classes] fp32 or bf16 (logits_bf16 != 0),
+ * labels int64.  Outputs: *loss (mean), dlogits (same dtype/shape as logits, already divided by
+ * rows, may be NULL), *correct (int, argmax == label, may be NULL).  `scratch` must hold
+ * kml_softmax_ce_scratch_bytes(rows) bytes of device memory; the kernel leaves it re-usable.
+ * ---------------------------------------------------------------------------------------------- */
+size_t kml_softmax_ce_scratch_bytes(int rows);
+int kml_softmax_ce(const void* logits, int logits_bf16, const long long* labels, int rows,
+                   int classes, float* loss, void* dlogits, int* correct, void* scratch,
+                   void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KUBEML_B200_H */

@@ -1,0 +1,136 @@
+"""Loader and ctypes signatures for the native runtime (csrc/, include/kubeml_b200.h).
+
+The shared object is built in-tree by `kubeml_b200/_native/build.py` (plain nvcc, sm_100a only)
+and travels with the source snapshot.  On a GPU box a missing or stale library is a hard error:
+CUDA ops never fall back silently.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+from ctypes import (POINTER, Structure, c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint32,
+                    c_ulonglong, c_void_p)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkubeml_b200.so")
+KML_MAX_RANKS = 8
+
+_lib = None
+_lock = threading.Lock()
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class MergeParams(Structure):
+    _fields_ = [
+        ("replica", c_void_p * KML_MAX_RANKS),
+        ("ireplica", c_void_p * KML_MAX_RANKS),
+        ("flags", c_void_p * KML_MAX_RANKS),
+        ("mcast", c_void_p),
+        ("n_f32", c_size_t),
+        ("n_i64", c_size_t),
+        ("my_rank", c_int),
+        ("participants", c_uint32),
+        ("write_mask", c_uint32),
+        ("generation", c_uint32),
+        ("fuse_sgd", c_int),
+        ("grad", c_void_p),
+        ("momentum_buf", c_void_p),
+        ("lr", c_float),
+        ("weight_decay", c_float),
+        ("momentum", c_float),
+        ("timeout_cycles", c_ulonglong),
+        ("status", c_void_p),
+    ]
+
+
+def _declare(lib) -> None:
+    def sig(name, restype, *argtypes):
+        fn = getattr(lib, name)
+        fn.restype = restype
+        fn.argtypes = list(argtypes)
+
+    sig("kml_last_error", c_char_p)
+    sig("kml_version", c_int)
+    sig("kml_launch_count", c_ulonglong)
+    sig("kml_reset_launch_count", None)
+    # arena
+    sig("kml_arena_create", c_int, c_int, c_size_t, c_int, POINTER(c_void_p))
+    sig("kml_arena_destroy", c_int, c_void_p)
+    sig("kml_arena_ptr", c_void_p, c_void_p)
+    sig("kml_arena_size", c_size_t, c_void_p)
+    sig("kml_arena_export_fd", c_int, c_void_p, POINTER(c_int))
+    sig("kml_arena_import_fd", c_int, c_int, c_int, c_size_t, POINTER(c_void_p))
+    sig("kml_arena_grant_access", c_int, c_void_p, c_int)
+    sig("kml_mcast_supported", c_int, c_int, POINTER(c_int))
+    sig("kml_mcast_create", c_int, c_int, c_size_t, POINTER(c_void_p))
+    sig("kml_mcast_export_fd", c_int, c_void_p, POINTER(c_int))
+    sig("kml_mcast_import_fd", c_int, c_int, c_int, c_size_t, POINTER(c_void_p))
+    sig("kml_mcast_add_device", c_int, c_void_p, c_int)
+    sig("kml_mcast_bind", c_int, c_void_p, c_int, c_void_p, POINTER(c_void_p))
+    sig("kml_mcast_destroy", c_int, c_void_p)
+    # merge / optim / loss
+    sig("kml_kavg_merge", c_int, POINTER(MergeParams), c_void_p)
+    sig("kml_sgd_step", c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float,
+        c_int, c_void_p, c_void_p)
+    sig("kml_adam_step", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float,
+        c_float, c_float, c_float, c_int, c_void_p, c_void_p)
+    sig("kml_cast_f32_to_bf16", c_int, c_void_p, c_void_p, c_size_t, c_void_p)
+    sig("kml_fill_f32", c_int, c_void_p, c_float, c_size_t, c_void_p)
+    sig("kml_softmax_ce_scratch_bytes", c_size_t, c_int)
+    sig("kml_softmax_ce", c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p,
+        c_void_p, c_void_p, c_void_p)
+    # tcgen05 GEMM family
+    sig("kml_gemm_bf16", c_int, c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong, c_void_p,
+        c_longlong, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p)
+    sig("kml_conv2d_fprop", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p)
+    sig("kml_conv2d_wgrad", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_int, c_int, c_int, c_int, c_void_p)
+    for name, s in _EXTRA_SIGS.items():
+        if hasattr(lib, name):
+            sig(name, *s)
+
+
+# filled by later modules of this package (norm, pool, ...) before the first load
+_EXTRA_SIGS: dict = {}
+
+
+def available() -> bool:
+    return os.path.isfile(LIB_PATH)
+
+
+def lib():
+    """The loaded library; raises NativeError with a build hint if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.isfile(LIB_PATH):
+                raise NativeError(
+                    f"{LIB_PATH} not found: build it with `python -m kubeml_b200._native.build` "
+                    "(or __graft_entry__.build()); CUDA ops do not fall back to PyTorch")
+            l = ctypes.CDLL(LIB_PATH)
+            _declare(l)
+            _lib = l
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = lib().kml_last_error().decode("utf-8", "replace")
+        raise NativeError(f"{what or 'native call'} failed (rc={rc}): {msg}")
+
+
+def stream_ptr(stream=None) -> int:
+    import torch
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return int(s.cuda_stream)
+
+
+def launch_count() -> int:
+    return int(lib().kml_launch_count()) if _lib is not None or available() else 0
