@@ -87,6 +87,7 @@ kavg_merge_kernel(const kml_merge_params p) {
   const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
   const size_t n4 = p.n_f32 / 4;
+  const size_t nsgd4 = p.n_sgd / 4;
   const bool sync_ranks = p.generation != 0;
 
   // ---- phase 0: fused last local step on the own replica --------------------------------------
@@ -95,7 +96,7 @@ kavg_merge_kernel(const kml_merge_params p) {
     const float4* g = reinterpret_cast<const float4*>(p.grad);
     const float4* m = reinterpret_cast<const float4*>(p.momentum_buf);
     const bool has_m = p.momentum != 0.f && m != nullptr;
-    for (size_t i = tid; i < n4; i += nthreads) {
+    for (size_t i = tid; i < nsgd4; i += nthreads) {
       float4 wv = w[i], gv = __ldcs(g + i);
       float4 d;
       d.x = fmaf(p.weight_decay, wv.x, gv.x); d.y = fmaf(p.weight_decay, wv.y, gv.y);
@@ -177,7 +178,7 @@ kavg_merge_kernel(const kml_merge_params p) {
   if (p.momentum_buf) {
     float4* m = reinterpret_cast<float4*>(p.momentum_buf);
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (size_t i = tid; i < n4; i += nthreads) __stcs(m + i, z);
+    for (size_t i = tid; i < nsgd4; i += nthreads) __stcs(m + i, z);
   }
 
   if (sync_ranks) {
@@ -206,6 +207,7 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
       KML_CHECK(p.flags[r] != nullptr, "flags[%d] is null", r);
   }
   if (p.fuse_sgd) KML_CHECK(p.grad != nullptr, "fuse_sgd set without grad");
+  KML_CHECK(p.n_sgd % 4 == 0 && p.n_sgd <= p.n_f32, "n_sgd (%zu) must be a multiple of 4 and <= n_f32", p.n_sgd);
   const bool use_mc = p.mcast != nullptr && p.generation != 0;
 
   int dev = 0;

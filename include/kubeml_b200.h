@@ -73,6 +73,7 @@ typedef struct {
   float* mcast;                       /* multicast address of the fp32 region, or NULL           */
   size_t n_f32;                       /* floats per replica (multiple of 4, 16-byte aligned)     */
   size_t n_i64;
+  size_t n_sgd;                       /* floats covered by grad/momentum_buf (parameter prefix)  */
   int my_rank;
   uint32_t participants;              /* bit r: rank r contributes a replica this round          */
   uint32_t write_mask;                /* bit r: rank r receives the merged model                 */

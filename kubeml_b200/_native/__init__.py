@@ -32,6 +32,7 @@ class MergeParams(Structure):
         ("mcast", c_void_p),
         ("n_f32", c_size_t),
         ("n_i64", c_size_t),
+        ("n_sgd", c_size_t),
         ("my_rank", c_int),
         ("participants", c_uint32),
         ("write_mask", c_uint32),

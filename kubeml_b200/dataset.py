@@ -42,6 +42,7 @@ class KubeDataset(data.Dataset, ABC):
         # page-locked views of the same rows, set when the split was staged for a GPU worker
         self._pinned_data, self._pinned_labels = None, None
         self._want_pinned = False
+        self._device_resident = False
 
         try:
             if not self._store.exists(dataset):
@@ -133,7 +134,14 @@ class SlicedBatches(BatchSource):
         self.ds, self.bs, self.device = ds, int(batch_size), device
         self.n = len(ds.data)
         self.h2d_bytes = 0
-        if device.type == "cuda" and ds._pinned_data is not None:
+        self._resident = False
+        if device.type == "cuda" and getattr(ds, "_device_resident", False):
+            # kernel-only measurements: the round's data is staged on the device up front
+            src_x = ds._pinned_data if ds._pinned_data is not None else torch.from_numpy(np.array(ds.data))
+            src_y = ds._pinned_labels if ds._pinned_labels is not None else torch.from_numpy(np.array(ds.labels))
+            self.x, self.y = src_x.to(device), src_y.to(device)
+            self._resident = True
+        elif device.type == "cuda" and ds._pinned_data is not None:
             self.x, self.y = ds._pinned_data, ds._pinned_labels
         else:
             self.x = torch.from_numpy(np.array(ds.data, copy=True))
@@ -148,7 +156,7 @@ class SlicedBatches(BatchSource):
     def _stage(self, i: int):
         lo, hi = i * self.bs, min((i + 1) * self.bs, self.n)
         xb, yb = self.x[lo:hi], self.y[lo:hi]
-        if self.device.type != "cuda":
+        if self.device.type != "cuda" or self._resident:
             return xb, yb, None
         with torch.cuda.stream(self._copy_stream):
             xd = xb.to(self.device, non_blocking=True)

@@ -55,6 +55,10 @@ class KubeModel(ABC):
         # device-timed seconds spent in merges during the last train task (history extension)
         self.merge_seconds = 0.0
         self.h2d_bytes = 0
+        self.d2h_bytes = 0
+        self.train_seconds = 0.0      # device-timed: first batch staged -> last merge done
+        self.steps = 0
+        self.gpu_launches = 0
 
     # ---- proxies to the wrapped module (network.py:55-89) -------------------------------------
     def __call__(self, *args, **kwargs):
@@ -82,8 +86,9 @@ class KubeModel(ABC):
         sv = self._inv.services
         if sv is None:
             raise KubeMLException("invocation carries no services", 500)
-        if sv.device_sync is not None and self.platform == "gpu":
-            return sv.device_sync
+        if sv.device_sync is not None and self.platform == "gpu" and torch.cuda.is_available():
+            ds = sv.device_sync
+            return ds.for_func(self.args._func_id) if hasattr(ds, "for_func") else ds
         from .train.sync import HostSync
         return HostSync(sv.tensor_store, sv.barrier)
 
@@ -100,12 +105,20 @@ class KubeModel(ABC):
         if self.task == "train":
             loss = self.__train()
             return {"loss": loss, "merge_seconds": self.merge_seconds,
-                    "h2d_bytes": self.h2d_bytes}, 200
+                    "h2d_bytes": self.h2d_bytes, "d2h_bytes": self.d2h_bytes,
+                    "train_seconds": self.train_seconds, "steps": self.steps,
+                    "gpu_launches": self.gpu_launches}, 200
         if self.task == "val":
             acc, loss, length = self.__validate()
             return {"loss": loss, "accuracy": acc, "length": length}, 200
         if self.task == "infer":
             return {"predictions": self.__infer()}, 200
+        if self.task == "join":
+            # framework-internal: an idle rank of a process-per-GPU group keeps its arena mapped
+            # into the peers and takes part in the epoch's membership barrier
+            self._set_device()
+            self._sync.attach(self)
+            return {}, 200
         raise KubeMLException(f"Task {self.task} not recognized", 400)
 
     # ---- optimizer (network.py:99-138) ---------------------------------------------------------
@@ -168,38 +181,74 @@ class KubeModel(ABC):
         self.logger.debug("Subsets per iteration: %s", per_iter)
         intervals = range(assigned.start, assigned.stop, per_iter) if per_iter > 0 else range(0)
 
-        fault = (self._inv.services.options or {}).get("inject_fault")
-        loss: Number = 0.0
+        opts = self._inv.services.options or {}
+        fault = opts.get("inject_fault")
+        on_cuda = self.device.type == "cuda"
+        loss_host = 0.0
+        loss_dev: Number = 0.0
         num_iterations = 0
         self.merge_seconds = 0.0
-        self.h2d_bytes = 0
-        self._dataset._want_pinned = (self.device.type == "cuda"
-                                      and self._dataset._has_batch_transform())
+        self.h2d_bytes = self.d2h_bytes = 0
+        self._dataset._want_pinned = on_cuda and self._dataset._has_batch_transform()
+        self._dataset._device_resident = bool(opts.get("device_resident_data"))
+        # per-step results are copied device->host asynchronously into page-locked memory and read
+        # after the round's merge was queued: one sync per round, not one `.item()` per batch
+        stage = _LossStage(self.device) if on_cuda else None
+        launches0 = _native_launches()
+        t_ev0 = t_ev1 = None
+        if on_cuda:
+            torch.cuda.synchronize(self.device)
+            t_ev0, t_ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t_ev0.record()
+        import time as _time
+        t_wall = _time.perf_counter()
         for round_idx, i in enumerate(intervals):
             self._dataset._load_train_data(start=i, end=min(assigned.stop, i + per_iter))
             batches = self._dataset._batches(self.batch_size, self.device)
             num_iterations += len(batches)
 
             self._on_iteration_start()
+            begin_round = getattr(self._sync, "begin_round", None)
+            if begin_round is not None:
+                begin_round(len(batches), self.optimizer)
+            sliced = isinstance(batches, _sliced_type())
             for idx, batch in enumerate(batches):
                 if fault and fault(a._func_id, a.epoch, round_idx, idx):
                     raise KubeMLException(f"injected fault in function {a._func_id}", 500)
-                if not isinstance(batches, _sliced_type()):
+                if not sliced:
                     batch = self._batch_to_device(batch)
-                loss = loss + self.train(batch, idx)
+                step_loss = self.train(batch, idx)
+                if stage is not None and isinstance(step_loss, torch.Tensor) and step_loss.is_cuda:
+                    stage.push(step_loss)
+                elif isinstance(step_loss, torch.Tensor):
+                    loss_dev = loss_dev + step_loss
+                else:
+                    loss_host += float(step_loss)
             self._on_iteration_end()
             self.h2d_bytes += getattr(batches, "h2d_bytes", 0)
 
             # every round but the last blocks on the merge barrier (network.py:305-306)
             if i != intervals[-1]:
                 self._sync.arrive(a._job_id, a._func_id, round_idx)
+            if stage is not None:
+                loss_host += stage.drain()
 
         self._sync.end_epoch(a._job_id, a._func_id, len(intervals))
+        if on_cuda:
+            t_ev1.record()
+            torch.cuda.synchronize(self.device)
+            self.train_seconds = t_ev0.elapsed_time(t_ev1) / 1e3
+        else:
+            self.train_seconds = _time.perf_counter() - t_wall
+        self.steps = num_iterations
+        self.gpu_launches = _native_launches() - launches0
+        if stage is not None:
+            self.d2h_bytes = stage.bytes
         self.merge_seconds = float(getattr(self._sync, "merge_seconds", 0.0))
         self._on_train_end()
         if num_iterations == 0:
             return 0.0
-        return float(self._sync.drain_losses(loss)) / num_iterations
+        return (loss_host + float(self._sync.drain_losses(loss_dev))) / num_iterations
 
     # ---- task: val (network.py:312-360) ----------------------------------------------------------
     def _on_validation_start(self) -> None:
@@ -280,6 +329,40 @@ class KubeModel(ABC):
 
     def infer(self, data: List[Any]) -> Union[torch.Tensor, np.ndarray, List[float]]:
         pass
+
+
+class _LossStage:
+    """Page-locked landing zone for per-step scalars (loss): async D2H now, read after a sync."""
+
+    def __init__(self, device: torch.device, capacity: int = 4096):
+        self.device = device
+        self.buf = torch.zeros(capacity, dtype=torch.float32).pin_memory()
+        self.n = 0
+        self.bytes = 0
+
+    def push(self, t: torch.Tensor) -> None:
+        if self.n == self.buf.numel():
+            self.drain_into = getattr(self, "drain_into", 0.0) + self.drain()
+        self.buf[self.n:self.n + 1].copy_(t.detach().reshape(1), non_blocking=True)
+        self.n += 1
+        self.bytes += 4
+
+    def drain(self) -> float:
+        if self.n == 0:
+            return getattr(self, "drain_into", 0.0)
+        torch.cuda.current_stream(self.device).synchronize()
+        v = float(self.buf[:self.n].sum()) + getattr(self, "drain_into", 0.0)
+        self.drain_into = 0.0
+        self.n = 0
+        return v
+
+
+def _native_launches() -> int:
+    try:
+        from . import _native
+        return _native.launch_count() if _native._lib is not None else 0
+    except Exception:  # noqa: BLE001
+        return 0
 
 
 def _to(e, device):

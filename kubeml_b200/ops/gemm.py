@@ -1,0 +1,106 @@
+"""Python entry points of the tcgen05 GEMM family (csrc/gemm_tcgen05.cu): plain bf16 GEMMs with
+either operand K-major or MN-major, and implicit-GEMM convolution forward / weight gradient on
+NHWC bf16 activations.  CPU tensors take an fp32 PyTorch restatement (the test oracle)."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native
+
+
+def _ptr(t: Optional[torch.Tensor]) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+              bias: Optional[torch.Tensor] = None, relu: bool = False,
+              out_dtype: torch.dtype = torch.bfloat16, out: Optional[torch.Tensor] = None,
+              splits: int = 1, block_n: int = 0) -> torch.Tensor:
+    """out[M,N] = A · B^T (+bias, ReLU) with fp32 accumulation.
+
+    a: [M,K] (a_mn=False, K contiguous) or [K,M] (a_mn=True, M contiguous), bf16
+    b: [N,K] (b_mn=False)               or [K,N] (b_mn=True), bf16
+    splits > 1 accumulates K-slices with red.add into an fp32 `out` (zeroed here if not given).
+    """
+    M = a.shape[1] if a_mn else a.shape[0]
+    K = a.shape[0] if a_mn else a.shape[1]
+    N = b.shape[1] if b_mn else b.shape[0]
+    if not a.is_cuda:
+        A = (a.t() if a_mn else a).float()
+        B = (b.t() if b_mn else b).float()
+        r = A @ B.t()
+        if bias is not None:
+            r = r + bias.float()
+        if relu:
+            r = torch.relu(r)
+        r = r.to(out_dtype)
+        if out is not None:
+            out.copy_(r) if splits == 1 else out.add_(r)
+            return out
+        return r
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "gemm_bf16 wants bf16 operands"
+    assert a.stride(-1) == 1 and b.stride(-1) == 1
+    out_f32 = out_dtype == torch.float32
+    if out is None:
+        out = (torch.zeros if splits > 1 else torch.empty)((M, N), dtype=out_dtype, device=a.device)
+    _native.check(_native.lib().kml_gemm_bf16(
+        a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(),
+        out.stride(0), M, N, K, _ptr(bias), int(relu), int(out_f32), int(splits), int(block_n),
+        _native.stream_ptr()), "kml_gemm_bf16")
+    return out
+
+
+def conv2d_fprop_supported(H: int, W: int, Cin: int, Cout: int, KH: int, KW: int, pad: int) -> bool:
+    Ho, Wo = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+    pow2 = lambda v: v > 0 and (v & (v - 1)) == 0
+    return Cin % 64 == 0 and Cout % 8 == 0 and pow2(Ho) and pow2(Wo) and Wo <= 128 and KH * KW <= 64
+
+
+def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[torch.Tensor] = None,
+                 relu: bool = False, out_dtype: torch.dtype = torch.bfloat16, splits: int = 1,
+                 block_n: int = 0) -> torch.Tensor:
+    """Stride-1 convolution, NHWC.  x: [N,H,W,Cin] bf16; w: [Cout,KH,KW,Cin] bf16 -> [N,Ho,Wo,Cout].
+    The data gradient of a stride-1 convolution is this same op applied to dY with the flipped,
+    channel-transposed filter and pad' = K-1-pad."""
+    N, H, W, Cin = x.shape
+    Cout, KH, KW, _ = w.shape
+    Ho, Wo = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+    if not x.is_cuda:
+        y = F.conv2d(x.permute(0, 3, 1, 2).float(), w.permute(0, 3, 1, 2).float(),
+                     None if bias is None else bias.float(), padding=pad)
+        if relu:
+            y = torch.relu(y)
+        return y.permute(0, 2, 3, 1).contiguous().to(out_dtype)
+    assert x.is_contiguous() and w.is_contiguous()
+    out_f32 = out_dtype == torch.float32
+    y = (torch.zeros if splits > 1 else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
+    _native.check(_native.lib().kml_conv2d_fprop(
+        x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, _ptr(bias),
+        int(relu), int(out_f32), int(splits), int(block_n), _native.stream_ptr()), "kml_conv2d_fprop")
+    return y
+
+
+def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, KH: int, KW: int, pad: int, *,
+                 out: Optional[torch.Tensor] = None, splits: int = 1, block_n: int = 0) -> torch.Tensor:
+    """Weight gradient of the stride-1 NHWC convolution: dW[Cout,KH,KW,Cin] fp32.  A caller-provided
+    `out` must hold zeros (K-splits are combined with red.add; a single split stores)."""
+    N, H, W, Cin = x.shape
+    Cout = dy.shape[3]
+    if not x.is_cuda:
+        g = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2).float(), (Cout, Cin, KH, KW),
+                                        dy.permute(0, 3, 1, 2).float(), padding=pad)
+        g = g.permute(0, 2, 3, 1).contiguous()
+        if out is not None:
+            out.add_(g)
+            return out
+        return g
+    assert x.is_contiguous() and dy.is_contiguous()
+    if out is None:
+        out = torch.zeros((Cout, KH, KW, Cin), dtype=torch.float32, device=x.device)
+    _native.check(_native.lib().kml_conv2d_wgrad(
+        x.data_ptr(), dy.data_ptr(), out.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, int(splits),
+        int(block_n), _native.stream_ptr()), "kml_conv2d_wgrad")
+    return out

@@ -1,0 +1,437 @@
+"""Device-resident K-AVG synchronisation: the GPU replacement for RedisAI + the train job's
+merger.
+
+What each verb of the worker loop (python/kubeml/kubeml/network.py:252-310) becomes:
+
+  reference                                   here
+  ------------------------------------------  ---------------------------------------------------
+  init: TENSORSET every layer  (:444-461)     rank 0 binds the module into its arena
+  load_model: TENSORGET + load_state_dict     no-op: the merged model is already in every arena
+  reset optimizer state        (:121-128)     momentum buffer zeroed inside the merge kernel
+  save_model: .cpu() + TENSORSET per layer    no-op: parameters *are* the replica
+  POST /next, block for merge  (:395-414)     csrc/merge.cu launched on the worker's own stream with
+                                              a flag barrier in peer memory; no host round-trip
+  job: Update x N, Average, Save              the same kernel: peer loads, fp32 sum, /P, peer stores
+
+Which workers take part in round i of an epoch is a pure function of (D, N, K, B)
+(`util.round_schedule`), so every rank derives the participant mask locally; that reproduces the
+shrinking WaitGroup of ml/pkg/train/job.go:414-438 without the job being involved.
+
+`RankSync` is the per-worker engine.  Two group flavours build the peer tables it needs:
+`ThreadedDeviceSyncGroup` (workers are threads of one process; arenas are made visible with
+cuMemSetAccess) and `SpmdDeviceSyncGroup` (one process per GPU; arenas travel as POSIX fds).
+"""
+from __future__ import annotations
+
+import ctypes
+import logging
+import os
+import threading
+from typing import Dict, List, Optional
+
+import torch
+
+from .. import _native
+from ..exceptions import MergeError, WorkerFault
+from ..util import round_schedule
+from .arena import ArenaLayout, WeightArena
+
+log = logging.getLogger("kubeml.device_sync")
+
+
+class PeerTable:
+    """Addresses, valid on *this* rank's GPU, of every known rank's arena regions."""
+
+    def __init__(self):
+        self.weights: Dict[int, int] = {}
+        self.counters: Dict[int, int] = {}
+        self.flags: Dict[int, int] = {}
+        self.mcast: int = 0
+        self.mcast_ranks: frozenset = frozenset()
+
+    def add(self, rank: int, base: int, layout: ArenaLayout) -> None:
+        self.weights[rank] = base + layout.off_f32
+        self.counters[rank] = base + layout.off_i64
+        self.flags[rank] = base + layout.off_flags
+
+    def mask(self) -> int:
+        m = 0
+        for r in self.weights:
+            m |= 1 << r
+        return m
+
+
+class RankSync:
+    name = "device"
+
+    def __init__(self, group: "DeviceSyncGroup", rank: int):
+        self.group = group
+        self.rank = rank
+        self.arena: Optional[WeightArena] = None
+        self.layout: Optional[ArenaLayout] = None
+        self.peers = PeerTable()
+        self.merge_seconds = 0.0
+        self.merges = 0
+        self._events: List[tuple] = []
+        self._schedule: List[List[int]] = []
+        self._epoch = 0
+        self._model = None
+        self._write_mask = 0
+        self._fused_steps = 0
+
+    # ---- init task -----------------------------------------------------------------------
+    def publish_reference(self, job_id: str, network: torch.nn.Module) -> List[str]:
+        device = next(network.parameters()).device
+        if device.type != "cuda":
+            device = torch.device("cuda", torch.cuda.current_device())
+            network.to(device)
+        self._ensure_arena(network, device, copy_in=True)
+        torch.cuda.current_stream(device).synchronize()
+        self.group.set_reference_holder(self.rank)
+        return list(self.layout.order)
+
+    # ---- per task ------------------------------------------------------------------------
+    def attach(self, kube_model) -> None:
+        """Bind the invocation's fresh module to this rank's arena and agree on membership."""
+        self._model = kube_model
+        a = kube_model.args
+        net = kube_model._network
+        joined = self.arena is None
+        self._ensure_arena(net, kube_model.device, copy_in=False)
+        if joined:
+            self.group.copy_reference_into(self)
+        self.arena.bind(net, copy_in=False)
+        if a._task in ("train", "join"):
+            self._epoch = int(a.epoch)
+            self._schedule = (round_schedule(kube_model._dataset.num_docs, a._N, a._K, a.batch_size)
+                              if a._task == "train" else [])
+            self.merge_seconds = 0.0
+            self._events = []
+            # every rank of this epoch has its arena registered once the barrier opens
+            self.group.epoch_barrier(self, a._N, ("train", self._epoch))
+            self._write_mask = self.peers.mask()
+
+    def _ensure_arena(self, network: torch.nn.Module, device: torch.device, copy_in: bool) -> None:
+        layout = ArenaLayout(network)
+        if self.arena is not None:
+            if layout.signature() != self.layout.signature():
+                raise MergeError(RuntimeError("network structure changed between invocations"))
+            if copy_in:
+                self.arena.bind(network, copy_in=True)
+            return
+        self.layout = layout
+        self.arena = WeightArena(layout, device, exportable=self.group.exportable)
+        if copy_in:
+            self.arena.bind(network, copy_in=True)
+        torch.cuda.current_stream(self.arena.device).synchronize()   # peers may read right after
+        self.group.register(self)
+
+    # ---- per round -----------------------------------------------------------------------
+    def load_reference(self, job_id: str, network: torch.nn.Module) -> None:
+        opt = getattr(self._model, "optimizer", None)
+        if opt is not None and hasattr(opt, "attach_arena") and getattr(opt, "_arena", None) is not self.arena:
+            opt.attach_arena(self.arena)
+
+    def begin_round(self, nsteps: int, optimizer) -> None:
+        """Arm the fused last step: our flat SGD skips its `nsteps`-th launch and the merge
+        kernel applies it in its phase 0."""
+        if hasattr(optimizer, "defer_step_at") and os.environ.get("KUBEML_FUSE_LAST_STEP", "1") != "0":
+            optimizer.defer_step_at(nsteps)
+
+    def publish_replica(self, job_id: str, func_id: int, network: torch.nn.Module) -> None:
+        """Parameters already are the replica `{job}:{name}/{func_id}`."""
+
+    def arrive(self, job_id: str, func_id: int, round_idx: int) -> None:
+        self._merge(round_idx)
+
+    def end_epoch(self, job_id: str, func_id: int, rounds_done: int) -> None:
+        if rounds_done > 0:
+            self._merge(rounds_done - 1)
+        stream = torch.cuda.current_stream(self.arena.device)
+        stream.synchronize()
+        for e0, e1 in self._events:
+            self.merge_seconds += e0.elapsed_time(e1) / 1e3
+        self._events = []
+        st = int(self.arena.status.item())
+        if st != 0:
+            self.arena.status.zero_()
+            raise WorkerFault(f"merge barrier timed out waiting for rank {st - 1}")
+
+    def drain_losses(self, loss) -> float:
+        return float(loss)
+
+    # ---- the merge -----------------------------------------------------------------------
+    def _merge(self, round_idx: int) -> None:
+        parts = self._schedule[round_idx] if round_idx < len(self._schedule) else [self.rank]
+        if self.rank not in parts:
+            return
+        pmask = 0
+        for r in parts:
+            pmask |= 1 << r
+        opt = getattr(self._model, "optimizer", None)
+        p = _native.MergeParams()
+        L = self.layout
+        for r, addr in self.peers.weights.items():
+            p.replica[r] = addr
+            p.ireplica[r] = self.peers.counters[r]
+            p.flags[r] = self.peers.flags[r]
+        p.n_f32 = L.n_f32
+        p.n_i64 = L.n_i64
+        p.n_sgd = L.n_param
+        p.my_rank = self.rank
+        p.participants = pmask
+        p.write_mask = self._write_mask | pmask
+        single = len(parts) == 1 and p.write_mask == pmask
+        p.generation = 0 if single else ((self._epoch & 0x7FFF) << 16) + round_idx + 1
+        use_mc = (self.peers.mcast and frozenset(parts) == self.peers.mcast_ranks
+                  and p.write_mask == pmask and os.environ.get("KUBEML_MERGE_NVLS", "1") != "0")
+        p.mcast = self.peers.mcast if use_mc else None
+        p.status = self.arena.ptr(L.off_status)
+        p.timeout_cycles = int(float(os.environ.get("KUBEML_MERGE_TIMEOUT_S", "20")) * 1.9e9)
+        if opt is not None and getattr(opt, "_deferred", False):
+            g = opt.param_groups[0]
+            p.fuse_sgd = 1
+            p.grad = self.arena.ptr(L.off_grad)
+            p.lr, p.weight_decay, p.momentum = g["lr"], g["weight_decay"], g["momentum"]
+            opt._deferred = False
+            self._fused_steps += 1
+        uses_momentum = opt is not None and bool(getattr(opt, "defaults", {}).get("momentum", 0))
+        p.momentum_buf = self.arena.ptr(L.off_state1) if uses_momentum else None
+        stream = torch.cuda.current_stream(self.arena.device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        _native.check(_native.lib().kml_kavg_merge(ctypes.byref(p), int(stream.cuda_stream)),
+                      "kml_kavg_merge")
+        e1.record(stream)
+        self._events.append((e0, e1))
+        self.merges += 1
+
+    def close(self) -> None:
+        if self.arena is not None:
+            self.arena.close()
+            self.arena = None
+
+
+class DeviceSyncGroup:
+    exportable = False
+
+    def register(self, rs: RankSync) -> None: ...
+    def set_reference_holder(self, rank: int) -> None: ...
+    def copy_reference_into(self, rs: RankSync) -> None: ...
+    def epoch_barrier(self, rs: RankSync, n: int, key) -> None: ...
+
+
+class ThreadedDeviceSyncGroup(DeviceSyncGroup):
+    """All workers are threads of one process (the in-process Cluster on a multi-GPU host, tests).
+    `services.device_sync` is this object; `KubeModel` asks it for the rank engine of its func id."""
+
+    _by_job: Dict[str, "ThreadedDeviceSyncGroup"] = {}
+    _cls_lock = threading.Lock()
+
+    def __init__(self, max_ranks: int):
+        self.max_ranks = max_ranks
+        self.ranks: Dict[int, RankSync] = {}
+        self._lock = threading.RLock()
+        self._barriers: Dict[tuple, threading.Barrier] = {}
+        self._holder = 0
+
+    @classmethod
+    def for_job(cls, job_id: str, max_ranks: int) -> "ThreadedDeviceSyncGroup":
+        with cls._cls_lock:
+            g = cls._by_job.get(job_id)
+            if g is None:
+                g = cls(max_ranks)
+                cls._by_job[job_id] = g
+            return g
+
+    @classmethod
+    def drop_job(cls, job_id: str) -> None:
+        with cls._cls_lock:
+            g = cls._by_job.pop(job_id, None)
+        if g is not None:
+            g.close()
+
+    def rank_sync(self, rank: int) -> RankSync:
+        with self._lock:
+            rs = self.ranks.get(rank)
+            if rs is None:
+                rs = RankSync(self, rank)
+                self.ranks[rank] = rs
+            return rs
+
+    def register(self, rs: RankSync) -> None:
+        lib = _native.lib()
+        with self._lock:
+            ndev = torch.cuda.device_count()
+            for d in range(ndev):
+                if d != rs.arena.device.index:
+                    _native.check(lib.kml_arena_grant_access(rs.arena.handle, d), "kml_arena_grant_access")
+            rs.peers.add(rs.rank, rs.arena.base, rs.layout)
+            for other in self.ranks.values():
+                if other is rs:
+                    continue
+                if other.arena is None:
+                    continue
+                other.peers.add(rs.rank, rs.arena.base, rs.layout)
+                rs.peers.add(other.rank, other.arena.base, other.layout)
+
+    def set_reference_holder(self, rank: int) -> None:
+        self._holder = rank
+
+    def copy_reference_into(self, rs: RankSync) -> None:
+        with self._lock:
+            src = self.ranks.get(self._holder)
+        if src is None or src.arena is None or src is rs:
+            return
+        torch.cuda.current_stream(src.arena.device).synchronize()
+        rs.arena.weights.copy_(src.arena.weights)
+        rs.arena.counters.copy_(src.arena.counters)
+        torch.cuda.current_stream(rs.arena.device).synchronize()
+
+    def epoch_barrier(self, rs: RankSync, n: int, key) -> None:
+        if n <= 1:
+            return
+        with self._lock:
+            b = self._barriers.get(key)
+            if b is None:
+                b = threading.Barrier(n)
+                self._barriers = {key: b}
+        try:
+            b.wait(timeout=float(os.environ.get("KUBEML_EPOCH_BARRIER_S", "120")))
+        except threading.BrokenBarrierError:
+            raise WorkerFault("a worker did not reach the epoch barrier")
+
+    # `services.device_sync` verbs are per rank: KubeModel resolves the rank engine here
+    def for_func(self, func_id: int) -> RankSync:
+        return self.rank_sync(func_id)
+
+    def close(self) -> None:
+        for rs in list(self.ranks.values()):
+            rs.close()
+        self.ranks.clear()
+
+
+class SpmdDeviceSyncGroup(DeviceSyncGroup):
+    """One process per GPU (torchrun, or the control plane's process pool).  Each process holds one
+    `RankSync`; arenas are exported as POSIX fds and mapped by every peer (csrc/arena.cpp), and,
+    where the fabric supports it, bound to one NVSwitch multicast object so the merge can use
+    `multimem.ld_reduce` / `multimem.st`.
+
+    Registration is collective: every rank of the world must reach `register()` for the same job
+    (idle ranks of a small-N epoch run the function with task `join`)."""
+
+    exportable = True
+
+    def __init__(self, rank: int, world: int, sock_dir: Optional[str] = None, job_tag: int = 0):
+        from .peer import FdExchange
+        self.rank, self.world = rank, world
+        self.fdx = FdExchange(rank, world, sock_dir)
+        self.rs = RankSync(self, rank)
+        self._imported: List = []
+        self._mcast = None
+        self._tag = 1000 * (job_tag + 1)
+        self._holder = 0
+
+    def for_func(self, func_id: int) -> RankSync:
+        if func_id != self.rank:
+            raise MergeError(RuntimeError(f"function {func_id} scheduled on rank {self.rank}"))
+        return self.rs
+
+    def _next_tag(self) -> int:
+        self._tag += 1
+        return self._tag
+
+    def register(self, rs: RankSync) -> None:
+        lib = _native.lib()
+        dev = rs.arena.device.index or 0
+        rs.peers.add(rs.rank, rs.arena.base, rs.layout)
+        if self.world == 1:
+            return
+        fd = ctypes.c_int(-1)
+        _native.check(lib.kml_arena_export_fd(rs.arena.handle, ctypes.byref(fd)), "kml_arena_export_fd")
+        got = self.fdx.all_gather_fds([fd.value], self._next_tag())
+        os.close(fd.value)
+        for peer in range(self.world):
+            if peer == self.rank:
+                continue
+            h = ctypes.c_void_p()
+            _native.check(lib.kml_arena_import_fd(dev, got[peer][0], rs.arena.nbytes, ctypes.byref(h)),
+                          f"kml_arena_import_fd(rank {peer})")
+            os.close(got[peer][0])
+            self._imported.append(h)
+            rs.peers.add(peer, int(lib.kml_arena_ptr(h)), rs.layout)
+        self._setup_multicast(rs, dev)
+
+    def _setup_multicast(self, rs: RankSync, dev: int) -> None:
+        if os.environ.get("KUBEML_MERGE_NVLS", "1") == "0":
+            self.fdx.barrier(self._next_tag())
+            return
+        lib = _native.lib()
+        sup = ctypes.c_int(0)
+        ok = lib.kml_mcast_supported(dev, ctypes.byref(sup)) == 0 and sup.value != 0
+        m = ctypes.c_void_p()
+        fds: List[int] = []
+        if self.rank == 0 and ok:
+            if lib.kml_mcast_create(self.world, rs.arena.nbytes, ctypes.byref(m)) == 0:
+                fd = ctypes.c_int(-1)
+                if lib.kml_mcast_export_fd(m, ctypes.byref(fd)) == 0:
+                    fds = [fd.value]
+            else:
+                log.warning("multicast create failed: %s", lib.kml_last_error().decode())
+        got = self.fdx.broadcast_fds(fds, 0, self._next_tag())
+        for f in fds:
+            os.close(f)
+        have = bool(got) and ok
+        if have and self.rank != 0:
+            if lib.kml_mcast_import_fd(got[0], self.world, rs.arena.nbytes, ctypes.byref(m)) != 0:
+                have = False
+            os.close(got[0])
+        if have and lib.kml_mcast_add_device(m, dev) != 0:
+            log.warning("multicast add_device failed: %s", lib.kml_last_error().decode())
+            have = False
+        # everyone must have added its device before anyone binds
+        self.fdx.barrier(self._next_tag())
+        mc_ptr = ctypes.c_void_p()
+        if have and lib.kml_mcast_bind(m, dev, rs.arena.handle, ctypes.byref(mc_ptr)) != 0:
+            log.warning("multicast bind failed: %s", lib.kml_last_error().decode())
+            have = False
+        have = self.fdx.all_agree(have, self._next_tag())
+        if have:
+            self._mcast = m
+            rs.peers.mcast = int(mc_ptr.value) + rs.layout.off_f32
+            rs.peers.mcast_ranks = frozenset(range(self.world))
+            log.info("rank %d: NVLS multicast mapping ready", self.rank)
+
+    def set_reference_holder(self, rank: int) -> None:
+        self._holder = rank
+
+    def copy_reference_into(self, rs: RankSync) -> None:
+        if self.world == 1 or rs.rank == self._holder:
+            return
+        src = rs.peers.weights.get(self._holder)
+        if src is None:
+            return
+        from .arena import _DeviceSpan
+        L = rs.layout
+        w = torch.as_tensor(_DeviceSpan(src, (L.n_f32,), "<f4", self), device=rs.arena.device)
+        rs.arena.weights.copy_(w)
+        if L.n_i64:
+            c = torch.as_tensor(_DeviceSpan(rs.peers.counters[self._holder], (L.n_i64,), "<i8", self),
+                                device=rs.arena.device)
+            rs.arena.counters[: L.n_i64].copy_(c)
+        torch.cuda.current_stream(rs.arena.device).synchronize()
+
+    def epoch_barrier(self, rs: RankSync, n: int, key) -> None:
+        if self.world > 1:
+            self.fdx.barrier(self._next_tag())
+
+    def close(self) -> None:
+        lib = _native.lib()
+        self.rs.close()
+        for h in self._imported:
+            lib.kml_arena_destroy(h)
+        self._imported = []
+        if self._mcast is not None:
+            lib.kml_mcast_destroy(self._mcast)
+            self._mcast = None
+        self.fdx.close()

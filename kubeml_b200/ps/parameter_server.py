@@ -46,7 +46,7 @@ class ParameterServer:
         t = threading.Thread(target=job.train, daemon=True, name=f"job-{task.job.id}")
         with self._mu:
             self._threads[task.job.id] = t
-        t.start()
+            t.start()
 
     def update_task(self, task: TrainTask) -> None:
         """POST /update/{jobId} (api.go:72-119): relay the new parallelism to the job."""
@@ -93,10 +93,19 @@ class ParameterServer:
     def wait(self, job_id: str, timeout: Optional[float] = None) -> Optional[str]:
         """Block until a job's thread ended; returns its error text or None (no reference
         counterpart; the CLI there polls `task list`)."""
-        with self._mu:
-            t = self._threads.get(job_id)
+        import time
+        deadline = None if timeout is None else time.monotonic() + timeout
+        while True:
+            with self._mu:
+                t = self._threads.get(job_id)
+                known = t is not None or job_id in self._finished
+            if known:
+                break
+            if deadline is not None and time.monotonic() > deadline:
+                raise TimeoutError(job_id)
+            time.sleep(0.005)
         if t is not None:
-            t.join(timeout)
+            t.join(None if deadline is None else max(0.0, deadline - time.monotonic()))
             if t.is_alive():
                 raise TimeoutError(job_id)
         with self._mu:

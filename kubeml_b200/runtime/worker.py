@@ -31,7 +31,7 @@ class Worker:
     def invoke(self, function_name: str, query: Dict[str, Any], body: Any = None
                ) -> Tuple[Dict[str, Any] | list, int]:
         if self.gpu_id is not None:
-            os.environ["GPU_ID"] = str(self.gpu_id)
+            self.state["gpu_id"] = self.gpu_id
         inv = Invocation(query=dict(query), body=body, services=self.services,
                          logger=self.log, worker_state=self.state)
         try:

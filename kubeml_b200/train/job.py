@@ -37,7 +37,8 @@ class TrainJob:
                  scheduler: Any = None, ps: Any = None,
                  logger: Optional[logging.Logger] = None,
                  device_mode: bool = False,
-                 checkpoint_dir: Optional[str] = None):
+                 checkpoint_dir: Optional[str] = None,
+                 skip_final_validation: bool = False):
         self.task = task
         self.job_id = task.job.id
         self.invoker = invoker
@@ -48,6 +49,7 @@ class TrainJob:
         self.log = logger or logging.getLogger(f"kubeml.job.{self.job_id}")
         self.device_mode = device_mode
         self.checkpoint_dir = checkpoint_dir
+        self.skip_final_validation = skip_final_validation
 
         opts = task.request.options
         self.parallelism = self._clamp(task.job.state.parallelism or opts.default_parallelism or 1)
@@ -70,6 +72,7 @@ class TrainJob:
         self._barrier: Optional[MergeBarrier] = None
         self._barrier_lock = threading.Lock()
         self.merge_log: List[Dict[str, Any]] = []   # (epoch, participants, seconds) per merge
+        self.epoch_stats: List[Dict[str, Any]] = []  # per epoch: device-timed seconds, steps, bytes
 
     # ------------------------------------------------------------------ external API
     def next_iteration(self, job_id: str, func_id: int) -> None:
@@ -131,7 +134,7 @@ class TrainJob:
                 break
             self.epoch += 1
 
-        if not self.accuracy_reached:
+        if not self.accuracy_reached and not self.skip_final_validation:
             try:
                 self._validate()
             except KubeMLException as e:
@@ -193,6 +196,14 @@ class TrainJob:
         self.history.epoch_duration.append(time.time() - self.start_time)   # cumulative (job.go:327)
         self.history.train_loss.append(loss)
         self.history.merge_seconds.append(merge_s)
+        self.epoch_stats.append({
+            "epoch": self.epoch, "parallelism": n, "wall_seconds": elapsed,
+            "train_seconds": max(float(p.get("train_seconds", 0.0)) for _, p, _ in ok),
+            "merge_seconds": merge_s,
+            "steps": max(int(p.get("steps", 0)) for _, p, _ in ok),
+            "h2d_bytes": sum(int(p.get("h2d_bytes", 0)) for _, p, _ in ok),
+            "d2h_bytes": sum(int(p.get("d2h_bytes", 0)) for _, p, _ in ok),
+            "gpu_launches": sum(int(p.get("gpu_launches", 0)) for _, p, _ in ok)})
         samples = self._epoch_samples()
         self.history.images_per_second.append(samples / elapsed if elapsed > 0 and samples else 0.0)
         self._push_metrics()

@@ -22,6 +22,14 @@ __all__ = ["STORAGE_SUBSET_SIZE", "get_gpu", "split_minibatches", "get_subset_pe
 def get_gpu(func_id: int) -> int:
     """Round-robin worker -> GPU, sticky through the GPU_ID env var (util.py:13-34): a warm
     worker process keeps the device it first ran on."""
+    try:   # workers that are threads of one process carry their device in the invocation
+        from .runtime.context import current_invocation, has_invocation
+        if has_invocation():
+            ws = current_invocation().worker_state
+            if ws is not None and ws.get("gpu_id") is not None:
+                return int(ws["gpu_id"])
+    except ImportError:
+        pass
     pinned = os.environ.get("GPU_ID")
     if pinned is not None:
         return int(pinned)

@@ -1,0 +1,65 @@
+"""GPU end-to-end: the job lifecycle with device-resident weights (arena + merge kernel)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _mnist(store, n=512, nt=128):
+    rng = np.random.default_rng(0)
+    store.create("mnist", rng.integers(0, 255, (n, 28, 28), dtype=np.uint8), rng.integers(0, 10, (n,)),
+                 rng.integers(0, 255, (nt, 28, 28), dtype=np.uint8), rng.integers(0, 10, (nt,)))
+
+
+def _run(cluster, req):
+    from kubeml_b200.controller import make_kubeml_client
+    cl = make_kubeml_client(cluster)
+    jid = cl.v1().networks().train(req)
+    err = cluster.wait(jid, 300)
+    assert err is None, err
+    return cl.v1().histories().get(jid), cluster.jobs[jid]
+
+
+def test_lenet_device_sync_matches_host_sync(kube_home):
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    req = TrainRequest(model_type="lenet", batch_size=64, epochs=2, dataset="mnist", lr=0.01,
+                       function_name="lenet",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=2))
+    hist = {}
+    for mode in ("host", "device"):
+        c = Cluster(home=kube_home + "/" + mode, max_parallelism=1,
+                    options={"force_host_sync": mode == "host"})
+        _mnist(c.shard_store)
+        h, job = _run(c, req)
+        hist[mode] = h.data
+        assert job.device_mode == (mode == "device")
+        c.shutdown()
+    assert len(hist["device"].train_loss) == 2 and len(hist["device"].accuracy) == 2
+    np.testing.assert_allclose(hist["device"].train_loss, hist["host"].train_loss, rtol=2e-3)
+    np.testing.assert_allclose(hist["device"].validation_loss, hist["host"].validation_loss, rtol=2e-3)
+
+
+def test_resnet34_function_one_round(kube_home, monkeypatch):
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    monkeypatch.setenv("KUBEML_RESNET_CLASSES", "10")
+    c = Cluster(home=kube_home, max_parallelism=1)
+    rng = np.random.default_rng(0)
+    c.shard_store.create("cifar10", rng.integers(0, 255, (256, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (256,)),
+                         rng.integers(0, 255, (64, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (64,)))
+    req = TrainRequest(model_type="resnet34", batch_size=32, epochs=1, dataset="cifar10", lr=0.05,
+                       function_name="resnet34",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=0, k=4))
+    h, job = _run(c, req)
+    assert np.isfinite(h.data.train_loss[0]) and 0.5 < h.data.train_loss[0] < 10
+    assert len(h.data.accuracy) == 1
+    st = job.epoch_stats[0]
+    assert st["steps"] == 8 and st["h2d_bytes"] > 0 and st["d2h_bytes"] == 4 * 8 and st["gpu_launches"] > 0
+    c.shutdown()
+
+
+def test_smoke_entry():
+    import __graft_entry__ as g
+    g.smoke()

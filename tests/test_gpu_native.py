@@ -1,0 +1,256 @@
+"""GPU numerics: every hand-written kernel against a plain PyTorch fp32 restatement of the same op."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    d = torch.device("cuda", 0)
+    torch.cuda.set_device(d)
+    from kubeml_b200 import _native
+    _native.lib()           # the extension must be the thing under test: fail loudly if absent
+    return d
+
+
+def test_native_library_loaded(dev):
+    from kubeml_b200 import _native
+    assert _native.lib().kml_version() >= 100
+
+
+# ------------------------------------------------------------------------------------- optimizers
+@pytest.mark.parametrize("momentum,nesterov,wd", [(0.0, False, 1e-4), (0.9, False, 1e-4), (0.9, True, 0.0)])
+def test_sgd_matches_torch(dev, momentum, nesterov, wd):
+    from kubeml_b200 import ops
+    torch.manual_seed(0)
+    n = 1 << 16
+    w0 = torch.randn(n, device=dev)
+    p = torch.nn.Parameter(w0.clone())
+    opt = torch.optim.SGD([p], lr=0.05, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    w = w0.clone()
+    mb = torch.zeros(n, device=dev)
+    wb = torch.empty(n, device=dev, dtype=torch.bfloat16)
+    for _ in range(3):
+        g = torch.randn(n, device=dev)
+        p.grad = g.clone()
+        opt.step()
+        ops.sgd_step_(w, g, mb if momentum else None, 0.05, wd, momentum, nesterov, w_bf16=wb)
+    torch.testing.assert_close(w, p.data, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(wb.float(), w.bfloat16().float(), rtol=0, atol=0)
+
+
+def test_adam_matches_torch(dev):
+    from kubeml_b200 import ops
+    torch.manual_seed(0)
+    n = 1 << 14
+    w0 = torch.randn(n, device=dev)
+    p = torch.nn.Parameter(w0.clone())
+    opt = torch.optim.Adam([p], lr=1e-2, weight_decay=1e-4)
+    w, m, v = w0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    for t in range(1, 4):
+        g = torch.randn(n, device=dev)
+        p.grad = g.clone()
+        opt.step()
+        ops.adam_step_(w, g, m, v, t, 1e-2, (0.9, 0.999), 1e-8, 1e-4)
+    torch.testing.assert_close(w, p.data, rtol=2e-5, atol=2e-6)
+
+
+# ------------------------------------------------------------------------------------- softmax-CE
+@pytest.mark.parametrize("rows,classes,dtype", [(128, 1000, torch.float32), (64, 10, torch.float32),
+                                                (37, 100, torch.bfloat16), (1, 10, torch.float32)])
+def test_softmax_ce(dev, rows, classes, dtype):
+    from kubeml_b200 import ops
+    torch.manual_seed(1)
+    x = (torch.randn(rows, classes, device=dev) * 3).to(dtype)
+    y = torch.randint(0, classes, (rows,), device=dev)
+    xr = x.float().clone().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(xr, y)
+    ref.backward()
+    for _ in range(2):      # twice: the kernel must leave its scratch reusable
+        loss, dl, corr = ops.softmax_ce_raw(x, y, want_grad=True, want_correct=True)
+        tol = 1e-5 if dtype == torch.float32 else 2e-2
+        torch.testing.assert_close(loss.view(()), ref.detach(), rtol=tol, atol=tol)
+        torch.testing.assert_close(dl.float(), xr.grad, rtol=tol, atol=tol if dtype == torch.float32 else 1e-3)
+        assert int(corr.item()) == int(x.float().argmax(1).eq(y).sum().item())
+
+
+def test_cross_entropy_autograd(dev):
+    from kubeml_b200 import ops
+    torch.manual_seed(2)
+    x = torch.randn(32, 10, device=dev, requires_grad=True)
+    y = torch.randint(0, 10, (32,), device=dev)
+    ops.cross_entropy(x, y).backward()
+    g = x.grad.clone()
+    x.grad = None
+    torch.nn.functional.cross_entropy(x, y).backward()
+    torch.testing.assert_close(g, x.grad, rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------- K-AVG merge
+def _merge_single_gpu(dev, replicas_f, replicas_i, parts, write, fuse=None):
+    """All 'ranks' live on one GPU; one launch with generation 0 reduces the whole buffer."""
+    from kubeml_b200 import _native
+    lib = _native.lib()
+    p = _native.MergeParams()
+    for r, t in enumerate(replicas_f):
+        p.replica[r] = t.data_ptr()
+        if replicas_i is not None:
+            p.ireplica[r] = replicas_i[r].data_ptr()
+    p.n_f32 = replicas_f[0].numel()
+    p.n_i64 = replicas_i[0].numel() if replicas_i is not None else 0
+    p.my_rank = parts[0]
+    p.participants = sum(1 << r for r in parts)
+    p.write_mask = sum(1 << r for r in write)
+    p.generation = 0
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    p.status = status.data_ptr()
+    if fuse is not None:
+        p.fuse_sgd = 1
+        p.grad = fuse["grad"].data_ptr()
+        p.n_sgd = fuse["n"]
+        p.lr, p.weight_decay, p.momentum = fuse["lr"], fuse["wd"], fuse["mom"]
+        p.momentum_buf = fuse["mbuf"].data_ptr() if fuse.get("mbuf") is not None else None
+    _native.check(lib.kml_kavg_merge(ctypes.byref(p), _native.stream_ptr()), "kml_kavg_merge")
+    torch.cuda.synchronize()
+    assert int(status.item()) == 0
+
+
+@pytest.mark.parametrize("nranks,parts", [(2, [0, 1]), (4, [0, 1, 2, 3]), (8, list(range(8))), (4, [0, 2]), (3, [1])])
+def test_merge_matches_cpu_oracle(dev, nranks, parts):
+    from kubeml_b200.model.model import kavg_oracle
+    torch.manual_seed(3)
+    n = 4 * 12345
+    reps = [torch.randn(n, device=dev) for _ in range(nranks)]
+    ints = [torch.randint(0, 1000, (7,), device=dev, dtype=torch.int64) for _ in range(nranks)]
+    want = kavg_oracle([{"w": reps[r].cpu().numpy(), "c": ints[r].cpu().numpy()} for r in parts])
+    untouched = {r: reps[r].clone() for r in range(nranks)}
+    write = list(range(nranks)) if len(parts) > 1 else parts
+    _merge_single_gpu(dev, reps, ints, parts, write)
+    for r in write:
+        # same summation order (ascending rank) and a true division: bit-exact
+        np.testing.assert_array_equal(reps[r].cpu().numpy(), want["w"])
+        np.testing.assert_array_equal(ints[r].cpu().numpy(), want["c"])
+    for r in set(range(nranks)) - set(write):
+        torch.testing.assert_close(reps[r], untouched[r], rtol=0, atol=0)
+
+
+def test_merge_fused_last_sgd_step_and_reset(dev):
+    torch.manual_seed(4)
+    n, npar = 4 * 4096, 4 * 3000
+    w = [torch.randn(n, device=dev) for _ in range(2)]
+    g = torch.randn(npar, device=dev)
+    mb = torch.randn(npar, device=dev)
+    w0 = w[0].clone()
+    lr, wd, mom = 0.1, 1e-4, 0.9
+    d = g + wd * w0[:npar]
+    buf = mom * mb + d
+    stepped = w0.clone()
+    stepped[:npar] -= lr * buf
+    want = (stepped + w[1]) / 2
+    _merge_single_gpu(dev, w, None, [0, 1], [0, 1],
+                      fuse=dict(grad=g, n=npar, lr=lr, wd=wd, mom=mom, mbuf=mb))
+    torch.testing.assert_close(w[0], want, rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(w[1], want, rtol=1e-6, atol=1e-6)
+    assert float(mb.abs().max()) == 0.0       # optimizer state reset in the same pass
+
+
+# ------------------------------------------------------------------------------------- tcgen05 GEMM
+def _rel_err(got, want):
+    return float((got.float() - want).abs().max() / want.abs().max().clamp_min(1e-6))
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (128, 128, 256), (256, 512, 512), (100, 72, 200),
+                                   (1024, 1000, 512), (128, 10, 512)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True)])
+def test_gemm_bf16(dev, M, N, K, a_mn, b_mn):
+    from kubeml_b200 import ops
+    if (a_mn and M % 8) or (b_mn and N % 8) or K % 8 or ((not b_mn) and K % 8):
+        pytest.skip("leading dimension not a multiple of 8")
+    torch.manual_seed(5)
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = torch.randn(N, K, device=dev).bfloat16()
+    want = A.float() @ B.float().t()
+    a = A.t().contiguous() if a_mn else A
+    b = B.t().contiguous() if b_mn else B
+    got = ops.gemm_bf16(a, b, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    assert _rel_err(got, want) < 2e-3
+
+
+def test_gemm_bias_relu_bf16_out_and_splitk(dev):
+    from kubeml_b200 import ops
+    torch.manual_seed(6)
+    M, N, K = 256, 192, 1024
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = torch.randn(N, K, device=dev).bfloat16()
+    bias = torch.randn(N, device=dev)
+    want = torch.relu(A.float() @ B.float().t() + bias)
+    got = ops.gemm_bf16(A, B, bias=bias, relu=True)
+    assert got.dtype == torch.bfloat16 and _rel_err(got, want) < 1e-2
+    got2 = ops.gemm_bf16(A, B, out_dtype=torch.float32, splits=4)
+    assert _rel_err(got2, A.float() @ B.float().t()) < 2e-3
+
+
+@pytest.mark.parametrize("N,H,C,Co,k,pad", [(4, 8, 64, 64, 3, 1), (16, 4, 128, 128, 3, 1), (64, 2, 256, 256, 3, 1),
+                                            (128, 1, 512, 512, 3, 1), (2, 16, 64, 128, 3, 1), (8, 8, 64, 64, 1, 0),
+                                            (3, 8, 128, 72, 3, 1)])
+def test_conv2d_fprop(dev, N, H, C, Co, k, pad):
+    from kubeml_b200 import ops
+    torch.manual_seed(7)
+    x = torch.randn(N, H, H, C, device=dev).bfloat16()
+    w = (torch.randn(Co, k, k, C, device=dev) / (k * k * C) ** 0.5).bfloat16()
+    want = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2),
+                                      padding=pad).permute(0, 2, 3, 1)
+    got = ops.conv2d_fprop(x, w, pad, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape
+    assert _rel_err(got, want) < 2e-3
+
+
+@pytest.mark.parametrize("N,H,C,Co,k,pad,splits", [(4, 8, 64, 64, 3, 1, 1), (16, 4, 128, 128, 3, 1, 2),
+                                                   (128, 1, 512, 512, 3, 1, 1), (32, 8, 64, 64, 3, 1, 8),
+                                                   (8, 8, 64, 128, 1, 0, 1), (6, 2, 256, 72, 3, 1, 1)])
+def test_conv2d_wgrad(dev, N, H, C, Co, k, pad, splits):
+    from kubeml_b200 import ops
+    torch.manual_seed(8)
+    x = torch.randn(N, H, H, C, device=dev).bfloat16()
+    Ho = H + 2 * pad - k + 1
+    dy = torch.randn(N, Ho, Ho, Co, device=dev).bfloat16()
+    want = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (Co, C, k, k),
+                                       dy.float().permute(0, 3, 1, 2), padding=pad).permute(0, 2, 3, 1)
+    got = ops.conv2d_wgrad(x, dy, k, k, pad, splits=splits)
+    torch.cuda.synchronize()
+    assert _rel_err(got, want) < 2e-3
+
+
+# ------------------------------------------------------------------------------------- arena
+def test_arena_bind_and_flat_optimizer(dev):
+    from kubeml_b200.optim import SGD
+    from kubeml_b200.parallel.arena import ArenaLayout, WeightArena
+
+    def mk():
+        torch.manual_seed(1)
+        return torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3), torch.nn.BatchNorm2d(8), torch.nn.Flatten(),
+                                   torch.nn.Linear(8 * 36, 10)).to(dev)
+    m1, m2 = mk(), mk()
+    arena = WeightArena(ArenaLayout(m2), dev)
+    arena.bind(m2)
+    o1 = torch.optim.SGD(m1.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    o2 = SGD(m2.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    o2.attach_arena(arena)
+    x = torch.randn(4, 3, 8, 8, device=dev)
+    y = torch.randint(0, 10, (4,), device=dev)
+    for _ in range(3):
+        for m, o in ((m1, o1), (m2, o2)):
+            o.zero_grad()
+            torch.nn.functional.cross_entropy(m(x), y).backward()
+            o.step()
+    assert o2._flat_views() is not None
+    for a, b in zip(m1.state_dict().values(), m2.state_dict().values()):
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5)
+    assert int(arena.counters[0].item()) == 3
+    arena.close()
