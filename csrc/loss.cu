@@ -7,6 +7,7 @@
 // counter in the same scratch) adds the rows up in index order, so the mean is deterministic.
 #include "common.cuh"
 #include "../include/kubeml_b200.h"
+#include <mutex>
 
 namespace {
 
@@ -109,6 +110,75 @@ int kml_softmax_ce(const void* logits, int logits_bf16, const long long* labels,
   KML_CHECK((reinterpret_cast<uintptr_t>(scratch) & 15u) == 0, "kml_softmax_ce: scratch must be 16-byte aligned");
   const int grid = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
   auto s = static_cast<cudaStream_t>(stream);
+  if (logits_bf16)
+    softmax_ce_kernel<__nv_bfloat16><<<grid, kWarpsPerBlock * 32, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(logits), labels, rows, classes, loss, static_cast<__nv_bfloat16*>(dlogits),
+        correct, static_cast<CeScratch*>(scratch));
+  else
+    softmax_ce_kernel<float><<<grid, kWarpsPerBlock * 32, 0, s>>>(static_cast<const float*>(logits), labels, rows,
+                                                                 classes, loss, static_cast<float*>(dlogits), correct,
+                                                                 static_cast<CeScratch*>(scratch));
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant (see include/kubeml_b200.h: kml_softmax_ce_noalloc).
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+// The scratch of kml_softmax_ce (ticket + correct counter + one float per row), but owned by the
+// library instead of the caller.  Every GPU that loads this library carries these bytes until the
+// process exits, which is why the row limit is kept modest.
+static __device__ __align__(256) unsigned char g_ce_noalloc_scratch[sizeof(CeScratch) +
+                                                                    KML_SOFTMAX_CE_NOALLOC_MAX_ROWS * sizeof(float)];
+
+constexpr int kMaxDevices = 64;
+void* g_ce_noalloc_ptr[kMaxDevices] = {};   // per device: device address of the array above
+std::mutex g_ce_noalloc_mu;
+
+// In host code `g_ce_noalloc_scratch` is only a handle for the symbol, not an address a kernel can
+// use; the device address has to be asked for, per device, with that device current.
+int ce_noalloc_scratch_for_current_device(void** out) {
+  int dev = -1;
+  KML_CUDA(cudaGetDevice(&dev));
+  KML_CHECK(dev >= 0 && dev < kMaxDevices, "kml_softmax_ce_noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_ce_noalloc_mu);
+  if (g_ce_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    KML_CUDA(cudaGetSymbolAddress(&p, g_ce_noalloc_scratch));
+    KML_CHECK(p != nullptr, "kml_softmax_ce_noalloc: cudaGetSymbolAddress returned a null address");
+    g_ce_noalloc_ptr[dev] = p;
+  }
+  *out = g_ce_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int kml_softmax_ce_noalloc_max_rows(void) { return KML_SOFTMAX_CE_NOALLOC_MAX_ROWS; }
+
+int kml_softmax_ce_noalloc(const void* logits, int logits_bf16, const long long* labels, int rows, int classes,
+                           float* loss, void* dlogits, int* correct, void* stream) {
+  KML_CHECK(logits && labels && loss, "kml_softmax_ce_noalloc: null pointer");
+  KML_CHECK(rows > 0 && classes > 0, "kml_softmax_ce_noalloc: empty problem (%d x %d)", rows, classes);
+  KML_CHECK(rows <= KML_SOFTMAX_CE_NOALLOC_MAX_ROWS,
+            "kml_softmax_ce_noalloc: %d rows exceed the built-in scratch (max %d rows); use kml_softmax_ce with "
+            "caller-provided scratch for larger batches", rows, KML_SOFTMAX_CE_NOALLOC_MAX_ROWS);
+  void* scratch = nullptr;
+  int rc = ce_noalloc_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  auto s = static_cast<cudaStream_t>(stream);
+  // The array is shared by every call and keeps what the previous one left behind.  Row losses are
+  // fully rewritten before they are read; the ticket and the hit counter must start from zero, so
+  // they are cleared here in stream order (a call that was cut short cannot poison the next one).
+  KML_CUDA(cudaMemsetAsync(scratch, 0, sizeof(CeScratch), s));
+  const int grid = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
   if (logits_bf16)
     softmax_ce_kernel<__nv_bfloat16><<<grid, kWarpsPerBlock * 32, 0, s>>>(
         static_cast<const __nv_bfloat16*>(logits), labels, rows, classes, loss, static_cast<__nv_bfloat16*>(dlogits),

@@ -117,6 +117,34 @@ int kml_softmax_ce(const void* logits, int logits_bf16, const long long* labels,
                    int classes, float* loss, void* dlogits, int* correct, void* scratch,
                    void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * kml_softmax_ce_noalloc — the same fused softmax-cross-entropy, for callers that may not allocate.
+ * (No counterpart in the reference; it exists for integrators, see below.)
+ *
+ * Who this is for: code that has to run the loss without ever asking the CUDA allocator for
+ * memory — a host that has handed all of its HBM to pre-planned arenas and must not fail or
+ * fragment on a late cudaMalloc, a latency-critical loop that cannot afford the device-wide
+ * synchronisation a cudaMalloc/cudaFree can imply, or an embedding where another component owns
+ * the allocator.  kml_softmax_ce needs a caller-provided scratch buffer; this variant keeps that
+ * scratch inside the library, in a fixed `static __device__` array, so the caller passes only
+ * inputs and outputs.  It calls no cudaMalloc, cudaFree or other allocating routine.
+ *
+ * Limits and rules:
+ *  - rows <= KML_SOFTMAX_CE_NOALLOC_MAX_ROWS (kml_softmax_ce_noalloc_max_rows()); larger batches
+ *    are rejected with an error message, use kml_softmax_ce for those.  The array costs
+ *    16 + 4*MAX_ROWS bytes on every GPU that loads the library, until the process exits.
+ *  - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *    that device current) and caches it; make that first call before any stream capture begins.
+ *  - All calls on a device share the one array.  Calls are safe back to back on one stream (or
+ *    otherwise ordered); two calls that can overlap on the GPU (different streams, no dependency)
+ *    race on it and give wrong results.
+ *  - Arguments and results are exactly those of kml_softmax_ce, minus `scratch`.
+ * ---------------------------------------------------------------------------------------------- */
+#define KML_SOFTMAX_CE_NOALLOC_MAX_ROWS 16384
+int kml_softmax_ce_noalloc_max_rows(void);
+int kml_softmax_ce_noalloc(const void* logits, int logits_bf16, const long long* labels, int rows,
+                           int classes, float* loss, void* dlogits, int* correct, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
