@@ -33,6 +33,7 @@ static void load() {
   SYM(cuDeviceGet, "cuDeviceGet")
   SYM(cuDeviceGetAttribute, "cuDeviceGetAttribute")
   SYM(cuGetErrorString, "cuGetErrorString")
+  SYM(cuCtxGetCurrent, "cuCtxGetCurrent")
   SYM(cuTensorMapEncodeTiled, "cuTensorMapEncodeTiled")
 #undef SYM
   g_ok = ok;

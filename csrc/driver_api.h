@@ -23,6 +23,7 @@ struct DriverApi {
   CUresult (*cuDeviceGet)(CUdevice*, int);
   CUresult (*cuDeviceGetAttribute)(int*, CUdevice_attribute, CUdevice);
   CUresult (*cuGetErrorString)(CUresult, const char**);
+  CUresult (*cuCtxGetCurrent)(CUcontext*);
   CUresult (*cuTensorMapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);

@@ -37,6 +37,7 @@ enum OperandKind : int {
   kMatMN = 1,    // matrix, M/N dim contiguous:         coords (mn, k, 0, 0)
   kConvK = 2,    // NHWC activation, tile walks pixels, chunks walk (tap, channel block)
   kConvMN = 3,   // NHWC activation, tile walks channels, chunks walk pixel boxes (+ fixed tap shift)
+  kWgtMN = 4,    // filter [Cout][taps*Cin] read as B[n=cin][k=cout] of the *flipped* tap (data gradient)
 };
 
 struct Geometry {       // how a linear index becomes a (w, h, n) box origin
@@ -59,7 +60,9 @@ struct GemmArgs {
   long long z_col_stride;                // column offset added per tap (weight gradients)
   int m_valid, n_valid;                  // rows / columns actually present
   const float* bias;                     // per output column, may be null
+  const __nv_bfloat16* addend;           // bf16 [rows][ldo] added before ReLU (residual gradient), may be null
   int relu, out_f32, atomic_add;
+  int wgt_taps, wgt_cin;                 // kWgtMN: taps in the filter, input channels per tap
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -229,11 +232,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
         // ---- B ----
         if (args.b_kind == kMatK) {
-          tma_load_4d(&map_b, full_bar + s, sb, kc * kBlockK, nt * BLOCK_N, 0, 0);
+          // with a convolution A operand the filter column is addressed by the *real* tap, so
+          // skipped (all-padding) taps need no repacking of the weights
+          const int bcol = args.a_kind == kConvK
+                               ? (tap_list[kc / args.cblocks] * args.cblocks + kc % args.cblocks) * kBlockK
+                               : kc * kBlockK;
+          tma_load_4d(&map_b, full_bar + s, sb, bcol, nt * BLOCK_N, 0, 0);
         } else if (args.b_kind == kMatMN) {
 #pragma unroll
           for (int hb = 0; hb < BLOCK_N / 64; ++hb)
             tma_load_4d(&map_b, full_bar + s, sb + hb * kHalfBytes, nt * BLOCK_N + hb * 64, kc * kBlockK, 0, 0);
+        } else if (args.b_kind == kWgtMN) {
+          // chunk = (tap' of the dY window, block of 64 output channels); the filter tap is the
+          // point reflection of tap' (dX = dY * flip(W))
+          const int tap = args.wgt_taps - 1 - tap_list[kc / args.cblocks];
+          const int cb = kc % args.cblocks;
+#pragma unroll
+          for (int hb = 0; hb < BLOCK_N / 64; ++hb)
+            tma_load_4d(&map_b, full_bar + s, sb + hb * kHalfBytes, tap * args.wgt_cin + nt * BLOCK_N + hb * 64,
+                        cb * kBlockK, 0, 0);
         } else {
 #pragma unroll
           for (int hb = 0; hb < BLOCK_N / 64; ++hb)
@@ -301,14 +318,37 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       }
       if (!row_ok) continue;
       const int ncol0 = nt * BLOCK_N + c0;                // column within the (per-tap) N range
+      const long long off = static_cast<long long>(row) * args.ldo + col_base + c0;
       float f[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         f[j] = __uint_as_float(v[j]);
         if (args.bias != nullptr && split == 0 && ncol0 + j < args.n_valid) f[j] += __ldg(args.bias + ncol0 + j);
-        if (args.relu) f[j] = fmaxf(f[j], 0.f);
       }
-      const long long off = static_cast<long long>(row) * args.ldo + col_base + c0;
+      if (args.addend != nullptr && split == 0) {
+        const __nv_bfloat16* ad = args.addend + off;
+        if (ncol0 + 32 <= args.n_valid && (off & 7) == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const uint4 u = __ldg(reinterpret_cast<const uint4*>(ad + j));
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float2 v2 = __bfloat1622float2(h[t]);
+              f[j + 2 * t] += v2.x;
+              f[j + 2 * t + 1] += v2.y;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (ncol0 + j < args.n_valid) f[j] += __bfloat162float(ad[j]);
+        }
+      }
+      if (args.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
       if (args.out_f32) {
         float* o = static_cast<float*>(args.out) + off;
         if (args.atomic_add) {
@@ -368,6 +408,10 @@ struct TensorSpec {          // rank-4 view, dim 0 innermost (contiguous)
 int encode_map(CUtensorMap* map, const TensorSpec& t) {
   const kml::DriverApi* d = kml::driver();
   if (!d) return 4;
+  // Driver calls need a context current on *this* thread.  A thread that has not yet made a runtime
+  // call (e.g. autograd's backward thread running us as its first op) has none: bind the primary one.
+  CUcontext ctx = nullptr;
+  if (d->cuCtxGetCurrent(&ctx) != CUDA_SUCCESS || ctx == nullptr) KML_CUDA(cudaFree(0));
   cuuint64_t dims[4] = {t.dim[0], t.dim[1], t.dim[2], t.dim[3]};
   cuuint64_t strides[3] = {t.stride_bytes[0], t.stride_bytes[1], t.stride_bytes[2]};
   cuuint32_t box[4] = {t.box[0], t.box[1], t.box[2], t.box[3]};
@@ -409,7 +453,7 @@ int launch(const TensorSpec& ta, const TensorSpec& tb, const GemmArgs& a, int bl
   rc = encode_map(&mb, tb);
   if (rc) return rc;
   const bool amn = a.a_kind == kMatMN || a.a_kind == kConvMN;
-  const bool bmn = a.b_kind == kMatMN || a.b_kind == kConvMN;
+  const bool bmn = a.b_kind == kMatMN || a.b_kind == kConvMN || a.b_kind == kWgtMN;
   KML_CHECK(block_n == 64 || block_n == 128, "block_n must be 64 or 128");
   KML_CHECK(!(amn && !bmn), "A MN-major with B K-major is not instantiated");
   if (block_n == 64) {
@@ -441,8 +485,12 @@ bool make_geometry(int W, int H, int target, Geometry* g) {
 extern "C" {
 
 int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* out,
-                  long long ldo, int M, int N, int K, const float* bias, int relu, int out_f32, int splits,
-                  int block_n, void* stream) {
+                  long long ldo, int M, int N, int K, const kml_epilogue* epi, void* stream) {
+  const kml_epilogue dflt = {};
+  if (!epi) epi = &dflt;
+  const float* bias = epi->bias;
+  const int relu = epi->relu, out_f32 = epi->out_f32;
+  int splits = epi->splits, block_n = epi->block_n;
   KML_CHECK(A && B && out && M > 0 && N > 0 && K > 0, "kml_gemm_bf16: bad arguments");
   KML_CHECK(lda % 8 == 0 && ldb % 8 == 0, "kml_gemm_bf16: leading dimensions must be multiples of 8 elements");
   if (block_n == 0) block_n = (N > 64) ? 128 : 64;
@@ -468,13 +516,38 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
   g.z_taps = 1; g.kw = 1; g.cblocks = 1;
   g.out = out; g.ldo = ldo; g.m_valid = M; g.n_valid = N;
   g.bias = bias; g.relu = relu; g.out_f32 = out_f32;
+  g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);
   g.atomic_add = g.splits > 1;
   KML_CHECK(!g.atomic_add || (out_f32 && !relu), "split-K needs an fp32 output (pre-zeroed) and no ReLU");
   return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
 }
 
+static int conv_like(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                     int pad, const kml_epilogue* epi, bool dgrad, void* stream);
+
 int kml_conv2d_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
-                     int pad, const float* bias, int relu, int out_f32, int splits, int block_n, void* stream) {
+                     int pad, const kml_epilogue* epi, void* stream) {
+  return conv_like(x, w, y, N, H, W, Cin, Cout, KH, KW, pad, epi, false, stream);
+}
+
+// Data gradient of the stride-1 convolution y = conv(x, w, pad): dx[N,H,W,Cin] from dy[N,Ho,Wo,Cout]
+// and the *forward* filter w[Cout][KH][KW][Cin] (read MN-major through the reflected tap, so no
+// transposed copy of the weights exists).
+int kml_conv2d_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                     int pad, const kml_epilogue* epi, void* stream) {
+  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  // as a forward conv: input dy [N,Ho,Wo,Cout], output dx [N,H,W,Cin], padding K-1-pad
+  KML_CHECK(KH == KW, "kml_conv2d_dgrad: square filters only");
+  return conv_like(dy, w, dx, N, Ho, Wo, Cout, Cin, KH, KW, KH - 1 - pad, epi, true, stream);
+}
+
+static int conv_like(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                     int pad, const kml_epilogue* epi, bool dgrad, void* stream) {
+  const kml_epilogue dflt = {};
+  if (!epi) epi = &dflt;
+  const float* bias = epi->bias;
+  const int relu = epi->relu, out_f32 = epi->out_f32;
+  int splits = epi->splits, block_n = epi->block_n;
   KML_CHECK(x && w && y, "kml_conv2d_fprop: null pointer");
   KML_CHECK(Cin % 64 == 0, "kml_conv2d_fprop: Cin (%d) must be a multiple of 64 (use the im2col path otherwise)", Cin);
   KML_CHECK(Cout % 8 == 0, "kml_conv2d_fprop: Cout (%d) must be a multiple of 8", Cout);
@@ -518,27 +591,16 @@ int kml_conv2d_fprop(const void* x, const void* w, void* y, int N, int H, int W,
   g.out = y; g.ldo = Cout; g.m_valid = static_cast<int>(Mtot); g.n_valid = Cout;
   g.bias = bias; g.relu = relu; g.out_f32 = out_f32; g.atomic_add = g.splits > 1;
   KML_CHECK(!g.atomic_add || (out_f32 && !relu), "split-K needs an fp32 output (pre-zeroed) and no ReLU");
-  // B chunk index must address [tap][cblock] of the *full* filter: remap through a dense weight
-  // view is not possible when taps are skipped, so skipped taps are only allowed when the kernel
-  // can index B by the real tap.  The kernel uses kc*64 as the B column, therefore present B to it
-  // as the concatenation of the live taps.
-  if (ntaps != KH * KW) {
-    // live taps form a contiguous rectangle [kh0,kh1] x [kw0,kw1]; when it is a single row segment
-    // the B columns are contiguous and a pointer offset is enough.
-    int first = -1, last = -1;
-    for (int t = 0; t < KH * KW; ++t) if ((mask >> t) & 1ull) { if (first < 0) first = t; last = t; }
-    if (last - first + 1 == ntaps) {
-      tb.ptr = static_cast<const __nv_bfloat16*>(w) + static_cast<long long>(first) * Cin;
-      tb.dim[0] = Kt - static_cast<long long>(first) * Cin;
-    } else {
-      // fall back to all taps (zeros are loaded, results identical)
-      mask = 0;
-      for (int t = 0; t < KH * KW; ++t) mask |= 1ull << t;
-      g.tap_mask = mask;
-      g.k_chunks = KH * KW * g.cblocks;
-      g.splits = splits > g.k_chunks ? g.k_chunks : splits;
-      g.atomic_add = g.splits > 1;
-    }
+  g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);
+  if (dgrad) {
+    // B = forward filter [rows = real Cout][cols = taps * real Cin], consumed MN-major
+    tb.dim[0] = static_cast<uint64_t>(KH) * KW * Cout; tb.dim[1] = Cin;
+    tb.stride_bytes[0] = tb.dim[0] * 2; tb.stride_bytes[1] = tb.stride_bytes[0] * Cin;
+    tb.stride_bytes[2] = tb.stride_bytes[1];
+    tb.box[0] = 64; tb.box[1] = kBlockK;
+    g.b_kind = kWgtMN;
+    g.wgt_taps = KH * KW;
+    g.wgt_cin = Cout;
   }
   return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
 }

@@ -185,6 +185,23 @@ kavg_merge_kernel(const kml_merge_params p) {
     grid.sync();
     if (tid == 0) rank_barrier(p, 1, p.generation);
     grid.sync();
+  } else if (p.w_bf16) {
+    grid.sync();
+  }
+
+  // ---- phase 3: refresh the local bf16 tensor-core copy of the merged parameters ---------------
+  if (p.w_bf16) {
+    const float4* w = reinterpret_cast<const float4*>(p.replica[p.my_rank]);
+    uint2* wb = reinterpret_cast<uint2*>(p.w_bf16);
+    for (size_t i = tid; i < nsgd4; i += nthreads) {
+      const float4 v = ld_cg_f4(w + i);
+      __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y);
+      __nv_bfloat162 b = __floats2bfloat162_rn(v.z, v.w);
+      uint2 r;
+      r.x = *reinterpret_cast<uint32_t*>(&a);
+      r.y = *reinterpret_cast<uint32_t*>(&b);
+      wb[i] = r;
+    }
   }
 }
 

@@ -1,0 +1,333 @@
+// Small NHWC bf16 layers and data-movement kernels around the tcgen05 GEMMs:
+//   max-pool (any k/stride/pad) forward with saved arg-max + backward as a gather,
+//   global average pool forward/backward,
+//   im2col / col2im for the convolutions the shifted-TMA path cannot express (stride 2, Cin < 64,
+//   non power-of-two grids), column sums (bias gradients), padded fp32->bf16 packing, uint8 image
+//   normalisation.  The reference reaches all of these through ATen/cuDNN.
+#include "common.cuh"
+#include "../include/kubeml_b200.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+inline int grid_for(size_t work, int per_block = kThreads) {
+  size_t want = (work + per_block - 1) / per_block;
+  const size_t cap = static_cast<size_t>(kml::num_sms()) * 16;
+  if (want < 1) want = 1;
+  return static_cast<int>(want < cap ? want : cap);
+}
+
+// ---------------------------------------------------------------------------------- max pool
+__global__ void __launch_bounds__(kThreads)
+maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ idx,
+                   int N, int H, int W, int C, int Ho, int Wo, int k, int stride, int pad) {
+  const size_t total = static_cast<size_t>(N) * Ho * Wo * C;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    size_t p = i / C;
+    const int wo = static_cast<int>(p % Wo); p /= Wo;
+    const int ho = static_cast<int>(p % Ho);
+    const int n = static_cast<int>(p / Ho);
+    float best = -INFINITY;
+    int arg = 0;
+    for (int kh = 0; kh < k; ++kh) {
+      const int h = ho * stride - pad + kh;
+      if (h < 0 || h >= H) continue;
+      for (int kw = 0; kw < k; ++kw) {
+        const int w = wo * stride - pad + kw;
+        if (w < 0 || w >= W) continue;
+        const float v = __bfloat162float(x[((static_cast<size_t>(n) * H + h) * W + w) * C + c]);
+        if (v > best) { best = v; arg = kh * k + kw; }      // first maximum wins, like ATen
+      }
+    }
+    y[i] = __float2bfloat16_rn(best);
+    if (idx) idx[i] = static_cast<unsigned char>(arg);
+  }
+}
+
+// dx[n,h,w,c] = sum of dy over the windows whose saved arg-max is (h,w): a gather, no atomics
+__global__ void __launch_bounds__(kThreads)
+maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char* __restrict__ idx,
+                   __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int stride,
+                   int pad) {
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    size_t p = i / C;
+    const int w = static_cast<int>(p % W); p /= W;
+    const int h = static_cast<int>(p % H);
+    const int n = static_cast<int>(p / H);
+    float acc = 0.f;
+    for (int kh = 0; kh < k; ++kh) {
+      const int hn = h + pad - kh;
+      if (hn < 0 || hn % stride) continue;
+      const int ho = hn / stride;
+      if (ho >= Ho) continue;
+      for (int kw = 0; kw < k; ++kw) {
+        const int wn = w + pad - kw;
+        if (wn < 0 || wn % stride) continue;
+        const int wo = wn / stride;
+        if (wo >= Wo) continue;
+        const size_t o = ((static_cast<size_t>(n) * Ho + ho) * Wo + wo) * C + c;
+        if (idx[o] == kh * k + kw) acc += __bfloat162float(dy[o]);
+      }
+    }
+    dx[i] = __float2bfloat16_rn(acc);
+  }
+}
+
+// ---------------------------------------------------------------------------------- avg pool
+__global__ void __launch_bounds__(kThreads)
+avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C) {
+  const size_t total = static_cast<size_t>(N) * C;
+  const float inv = 1.f / static_cast<float>(HW);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    const size_t n = i / C;
+    float acc = 0.f;
+    for (int p = 0; p < HW; ++p) acc += __bfloat162float(x[(n * HW + p) * C + c]);
+    y[i] = __float2bfloat16_rn(acc * inv);
+  }
+}
+__global__ void __launch_bounds__(kThreads)
+avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
+  const size_t total = static_cast<size_t>(N) * HW * C;
+  const float inv = 1.f / static_cast<float>(HW);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    const size_t n = i / (static_cast<size_t>(HW) * C);
+    dx[i] = __float2bfloat16_rn(__bfloat162float(dy[n * C + c]) * inv);
+  }
+}
+
+// ---------------------------------------------------------------------------------- im2col / col2im
+// cols[m][(kh*KW + kw)*C + c], m = (n, ho, wo); row length ldk >= KH*KW*C, tail zero-filled.
+__global__ void __launch_bounds__(kThreads)
+im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int N, int H, int W, int C, int Ho,
+              int Wo, int KH, int KW, int stride, int pad, int ldk) {
+  const size_t total = static_cast<size_t>(N) * Ho * Wo * ldk;
+  const int K = KH * KW * C;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int kk = static_cast<int>(i % ldk);
+    size_t m = i / ldk;
+    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+    if (kk < K) {
+      const int c = kk % C;
+      const int tap = kk / C;
+      const int kw = tap % KW, kh = tap / KW;
+      const int wo = static_cast<int>(m % Wo); m /= Wo;
+      const int ho = static_cast<int>(m % Ho);
+      const int n = static_cast<int>(m / Ho);
+      const int h = ho * stride - pad + kh, w = wo * stride - pad + kw;
+      if (h >= 0 && h < H && w >= 0 && w < W) v = x[((static_cast<size_t>(n) * H + h) * W + w) * C + c];
+    }
+    cols[i] = v;
+  }
+}
+
+// dx[n,h,w,c] = sum over taps of dcols[m(n,ho,wo)][tap*C + c] (+ addend), a gather over <= KH*KW terms
+__global__ void __launch_bounds__(kThreads)
+col2im_kernel(const __nv_bfloat16* __restrict__ dcols, const __nv_bfloat16* __restrict__ addend,
+              __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int KH, int KW, int stride,
+              int pad, int ldk) {
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    size_t p = i / C;
+    const int w = static_cast<int>(p % W); p /= W;
+    const int h = static_cast<int>(p % H);
+    const int n = static_cast<int>(p / H);
+    float acc = addend ? __bfloat162float(addend[i]) : 0.f;
+    for (int kh = 0; kh < KH; ++kh) {
+      const int hn = h + pad - kh;
+      if (hn < 0 || hn % stride) continue;
+      const int ho = hn / stride;
+      if (ho >= Ho) continue;
+      for (int kw = 0; kw < KW; ++kw) {
+        const int wn = w + pad - kw;
+        if (wn < 0 || wn % stride) continue;
+        const int wo = wn / stride;
+        if (wo >= Wo) continue;
+        const size_t m = (static_cast<size_t>(n) * Ho + ho) * Wo + wo;
+        acc += __bfloat162float(dcols[m * ldk + (kh * KW + kw) * C + c]);
+      }
+    }
+    dx[i] = __float2bfloat16_rn(acc);
+  }
+}
+
+// ---------------------------------------------------------------------------------- misc
+// out[c] = sum_r x[r][c]  (bias gradient); one block per 32 columns, rows strided over warps
+__global__ void __launch_bounds__(kThreads)
+colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int rows, int cols, long long ld) {
+  __shared__ float part[kThreads / 32][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  float acc = 0.f;
+  if (c < cols)
+    for (int r = warp; r < rows; r += kThreads / 32) acc += __bfloat162float(x[static_cast<size_t>(r) * ld + c]);
+  part[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) t += part[w][lane];
+    out[c] = t;
+  }
+}
+
+// dst bf16 [rows][ld] <- src fp32 [rows][cols], zero padded
+__global__ void __launch_bounds__(kThreads)
+pack_rows_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows, int cols, int ld) {
+  const size_t total = static_cast<size_t>(rows) * ld;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % ld);
+    const size_t r = i / ld;
+    dst[i] = __float2bfloat16_rn(c < cols ? src[r * cols + c] : 0.f);
+  }
+}
+
+// uint8 HWC image batch -> normalised bf16 NHWC, optional per-sample horizontal flip and crop offset
+// (RandomHorizontalFlip + RandomCrop(size, padding) of the reference's CIFAR pipeline,
+// ml/experiments/kubeml/function_resnet34.py:17-30, done on whole batches on the GPU)
+__global__ void __launch_bounds__(kThreads)
+image_prep_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict__ y, const int* __restrict__ aug, int N,
+                  int H, int W, int C, int pad, float m0, float m1, float m2, float s0, float s1, float s2) {
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    size_t p = i / C;
+    int w = static_cast<int>(p % W); p /= W;
+    int h = static_cast<int>(p % H);
+    const int n = static_cast<int>(p / H);
+    float v = 0.f;
+    bool inside = true;
+    if (aug) {
+      const int a = aug[n];                 // bit 0: flip, bits 8..15: dy, bits 16..23: dx (0..2*pad)
+      h += ((a >> 8) & 0xff) - pad;
+      w += ((a >> 16) & 0xff) - pad;
+      inside = h >= 0 && h < H && w >= 0 && w < W;
+      if (a & 1) w = W - 1 - w;
+    }
+    const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2);
+    const float istd = c == 0 ? s0 : (c == 1 ? s1 : s2);
+    if (inside) v = static_cast<float>(x[((static_cast<size_t>(n) * H + h) * W + w) * C + c]) * (1.f / 255.f);
+    // padding pixels are zeros *before* normalisation in the reference pipeline (crop pads the PIL image)
+    y[i] = __float2bfloat16_rn((v - mean) * istd);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int kml_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride, int pad,
+                    void* stream) {
+  KML_CHECK(x && y && k * k <= 255, "kml_maxpool_fwd: bad arguments");
+  const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+  const size_t total = static_cast<size_t>(N) * Ho * Wo * C;
+  maxpool_fwd_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(idx), N, H, W,
+      C, Ho, Wo, k, stride, pad);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int k, int stride, int pad,
+                    void* stream) {
+  KML_CHECK(dy && idx && dx, "kml_maxpool_bwd: null pointer");
+  const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  maxpool_bwd_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx),
+      N, H, W, C, Ho, Wo, k, stride, pad);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
+  KML_CHECK(x && y && HW > 0, "kml_avgpool_fwd: bad arguments");
+  avgpool_fwd_kernel<<<grid_for(static_cast<size_t>(N) * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), N, HW, C);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
+  KML_CHECK(dy && dx && HW > 0, "kml_avgpool_bwd: bad arguments");
+  avgpool_bwd_kernel<<<grid_for(static_cast<size_t>(N) * HW * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, HW, C);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_im2col(const void* x, void* cols, int N, int H, int W, int C, int KH, int KW, int stride, int pad, int ldk,
+               void* stream) {
+  KML_CHECK(x && cols && ldk >= KH * KW * C, "kml_im2col: bad arguments");
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+  const size_t total = static_cast<size_t>(N) * Ho * Wo * ldk;
+  im2col_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride, pad,
+      ldk);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, int W, int C, int KH, int KW, int stride,
+               int pad, int ldk, void* stream) {
+  KML_CHECK(dcols && dx && ldk >= KH * KW * C, "kml_col2im: bad arguments");
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  col2im_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dcols), static_cast<const __nv_bfloat16*>(addend),
+      static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld, void* stream) {
+  KML_CHECK(x && out && rows > 0 && cols > 0, "kml_colsum_bf16: bad arguments");
+  colsum_kernel<<<(cols + 31) / 32, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), out, rows, cols, ld);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_pack_rows_bf16(const float* src, void* dst, int rows, int cols, int ld, void* stream) {
+  KML_CHECK(src && dst && ld >= cols, "kml_pack_rows_bf16: bad arguments");
+  pack_rows_kernel<<<grid_for(static_cast<size_t>(rows) * ld), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst), rows, cols, ld);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_image_prep(const void* x_u8, void* y_bf16, const int* aug, int N, int H, int W, int C, int pad,
+                   const float* mean3, const float* std3, void* stream) {
+  KML_CHECK(x_u8 && y_bf16 && mean3 && std3 && C <= 3, "kml_image_prep: bad arguments");
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  image_prep_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const unsigned char*>(x_u8), static_cast<__nv_bfloat16*>(y_bf16), aug, N, H, W, C, pad, mean3[0],
+      mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2]);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+}  // extern "C"

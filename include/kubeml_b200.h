@@ -84,6 +84,8 @@ typedef struct {
   const float* grad;
   float* momentum_buf;                /* zeroed after the merge when non-NULL (optimizer reset)   */
   float lr, weight_decay, momentum;
+  void* w_bf16;                       /* if non-NULL: bf16 copy of the first n_sgd merged floats,
+                                         refreshed by this rank after the final barrier           */
   unsigned long long timeout_cycles;  /* spin limit for the cross-rank barrier; 0 = default       */
   int* status;                        /* device int, set non-zero if the barrier timed out        */
 } kml_merge_params;
@@ -116,6 +118,73 @@ size_t kml_softmax_ce_scratch_bytes(int rows);
 int kml_softmax_ce(const void* logits, int logits_bf16, const long long* labels, int rows,
                    int classes, float* loss, void* dlogits, int* correct, void* scratch,
                    void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * tcgen05 / TMEM / TMA GEMM family (csrc/gemm_tcgen05.cu).  The reference reaches these shapes
+ * through cuDNN / cuBLAS inside torch 1.7.1 (ml/environment/Dockerfile:3,20); SURVEY 2.4 lists them.
+ * All operands bf16, fp32 accumulation in TMEM.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  const float* bias;        /* per output column, added by K-split 0; may be NULL                   */
+  const void* addend_bf16;  /* bf16 tensor shaped like the output, added before ReLU; may be NULL   */
+  int relu;
+  int out_f32;              /* 0: bf16 output, 1: fp32 output                                       */
+  int splits;               /* K-splits combined with red.add (needs a zeroed fp32 output); 0/1 = off */
+  int block_n;              /* 64, 128, or 0 = choose                                               */
+} kml_epilogue;
+
+/* out[M,N] = A * B^T.  a_mn = 0: A is [M][K] (lda = row stride); a_mn = 1: A is [K][M].  Same for B
+ * with N.  Leading dimensions in elements, multiples of 8.  (A MN-major with B K-major is not built.) */
+int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb,
+                  void* out, long long ldo, int M, int N, int K, const kml_epilogue* epi, void* stream);
+/* Stride-1 NHWC convolution as implicit GEMM: x[N,H,W,Cin], w[Cout,KH,KW,Cin] -> y[N,Ho,Wo,Cout].
+ * Needs Cin % 64 == 0, Cout % 8 == 0 and a power-of-two output grid (else use im2col + gemm). */
+int kml_conv2d_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout,
+                     int KH, int KW, int pad, const kml_epilogue* epi, void* stream);
+/* Data gradient of the same convolution from the forward filter (no transposed weight copy). */
+int kml_conv2d_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                     int KH, int KW, int pad, const kml_epilogue* epi, void* stream);
+/* Weight gradient dw[Cout,KH,KW,Cin] (fp32; zero it first when splits > 1). */
+int kml_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout,
+                     int KH, int KW, int pad, int splits, int block_n, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * NHWC bf16 layers around the GEMMs (csrc/norm.cu, csrc/nn_misc.cu); ATen/cuDNN in the reference
+ * (BatchNorm2d, MaxPool2d, AdaptiveAvgPool2d, accuracy, data augmentation).
+ * ---------------------------------------------------------------------------------------------- */
+size_t kml_bn_scratch_bytes(int C);
+/* y = relu?(bn(x) + res?) with batch statistics; updates running stats and num_batches_tracked.
+ * x, res, y: bf16 [M][C]; scratch: kml_bn_scratch_bytes(C) bytes (contents irrelevant). */
+int kml_bn_fwd_train(const void* x, const void* res, void* y, const float* gamma, const float* beta,
+                     float* running_mean, float* running_var, long long* num_batches_tracked,
+                     float* save_mean, float* save_invstd, float* scratch, int M, int C, int relu,
+                     float eps, float momentum, void* stream);
+int kml_bn_fwd_eval(const void* x, const void* res, void* y, const float* gamma, const float* beta,
+                    const float* running_mean, const float* running_var, int M, int C, int relu,
+                    float eps, void* stream);
+/* dy: grad of the block output; y: block output (ReLU mask) or NULL; x: saved conv output.
+ * Writes dx, optionally dres (masked grad for the residual branch), dgamma, dbeta. */
+int kml_bn_bwd(const void* dy, const void* y, const void* x, const float* gamma, const float* save_mean,
+               const float* save_invstd, void* dx, void* dres, float* dgamma, float* dbeta,
+               float* scratch, int M, int C, void* stream);
+int kml_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int k, int stride,
+                    int pad, void* stream);
+int kml_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N, int H, int W, int C, int k,
+                    int stride, int pad, void* stream);
+int kml_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int kml_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+/* cols[m][(kh*KW+kw)*C + c], row stride ldk (zero padded): for convolutions the shifted-TMA path
+ * cannot express (stride 2, Cin < 64, non power-of-two grids). */
+int kml_im2col(const void* x, void* cols, int N, int H, int W, int C, int KH, int KW, int stride, int pad,
+               int ldk, void* stream);
+int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, int W, int C, int KH, int KW,
+               int stride, int pad, int ldk, void* stream);
+int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld, void* stream);
+int kml_pack_rows_bf16(const float* src, void* dst_bf16, int rows, int cols, int ld, void* stream);
+/* uint8 NHWC images -> normalised bf16 NHWC; aug[n] = flip | dy<<8 | dx<<16 (crop offsets in
+ * [0, 2*pad]) or NULL (function_resnet34.py:17-30 on the GPU). mean3/std3 are host arrays. */
+int kml_image_prep(const void* x_u8, void* y_bf16, const int* aug, int N, int H, int W, int C, int pad,
+                   const float* mean3, const float* std3, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * kml_softmax_ce_noalloc — the same fused softmax-cross-entropy, for callers that may not allocate.

@@ -43,9 +43,15 @@ class MergeParams(Structure):
         ("lr", c_float),
         ("weight_decay", c_float),
         ("momentum", c_float),
+        ("w_bf16", c_void_p),
         ("timeout_cycles", c_ulonglong),
         ("status", c_void_p),
     ]
+
+
+class Epilogue(Structure):
+    _fields_ = [("bias", c_void_p), ("addend_bf16", c_void_p), ("relu", c_int), ("out_f32", c_int),
+                ("splits", c_int), ("block_n", c_int)]
 
 
 def _declare(lib) -> None:
@@ -86,11 +92,35 @@ def _declare(lib) -> None:
         c_void_p, c_void_p, c_void_p)
     # tcgen05 GEMM family
     sig("kml_gemm_bf16", c_int, c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong, c_void_p,
-        c_longlong, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p)
+        c_longlong, c_int, c_int, c_int, POINTER(Epilogue), c_void_p)
     sig("kml_conv2d_fprop", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
-        c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p)
+        c_int, c_int, c_int, POINTER(Epilogue), c_void_p)
+    sig("kml_conv2d_dgrad", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_int, c_int, POINTER(Epilogue), c_void_p)
     sig("kml_conv2d_wgrad", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
         c_int, c_int, c_int, c_int, c_int, c_void_p)
+    # NHWC layers
+    sig("kml_bn_scratch_bytes", c_size_t, c_int)
+    sig("kml_bn_fwd_train", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p)
+    sig("kml_bn_fwd_eval", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_int, c_int, c_int, c_float, c_void_p)
+    sig("kml_bn_bwd", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p)
+    sig("kml_maxpool_fwd", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_void_p)
+    sig("kml_maxpool_bwd", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_void_p)
+    sig("kml_avgpool_fwd", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
+    sig("kml_avgpool_bwd", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
+    sig("kml_im2col", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_void_p)
+    sig("kml_col2im", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_int, c_void_p)
+    sig("kml_colsum_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_longlong, c_void_p)
+    sig("kml_pack_rows_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
+    sig("kml_image_prep", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+        POINTER(c_float), POINTER(c_float), c_void_p)
     for name, s in _EXTRA_SIGS.items():
         if hasattr(lib, name):
             sig(name, *s)

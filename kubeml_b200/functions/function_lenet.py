@@ -54,6 +54,7 @@ class MnistDataset(KubeDataset):
 
 
 class KubeLeNet(KubeModel):
+    graph_safe = True
     def __init__(self, network: nn.Module, dataset: MnistDataset, gpu: bool = False):
         super().__init__(network, dataset, gpu=gpu)
 

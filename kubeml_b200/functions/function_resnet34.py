@@ -30,6 +30,7 @@ class Cifar10Dataset(KubeDataset):
     def __init__(self, name: str = "cifar10"):
         super().__init__(name)
         self._consts = {}
+        self.native = False
 
     def _norm(self, device):
         c = self._consts.get(device)
@@ -41,8 +42,17 @@ class Cifar10Dataset(KubeDataset):
         return c
 
     def transform_batch(self, x: torch.Tensor, y: torch.Tensor):
-        """x: uint8 [B,32,32,3] (HWC, as CIFAR is stored) -> float NHWC-in-memory NCHW view."""
+        """x: uint8 [B,32,32,3] (HWC, as CIFAR is stored).  Native models get normalised bf16 NHWC
+        from one fused kernel (flip + crop + normalise); stock modules get the float NCHW view."""
         B = x.shape[0]
+        if self.native and x.is_cuda:
+            aug = None
+            if self.is_training():
+                r = torch.randint(0, 2 * 9 * 9, (B,), device=x.device, dtype=torch.int32)
+                aug = (r % 2) | (((r // 2) % 9) << 8) | ((r // 18) << 16)
+            out = torch.empty((B, 32, 32, 3), dtype=torch.bfloat16, device=x.device)
+            ops.nn.image_prep(x, out, aug, 4, _MEAN, _STD)
+            return out, y.to(torch.int64)
         if self.is_training():
             # RandomHorizontalFlip + RandomCrop(32, padding=4), vectorised over the batch
             flip = torch.rand(B, device=x.device) < 0.5
@@ -68,6 +78,8 @@ class Cifar10Dataset(KubeDataset):
 
 
 class KubeResnet34(KubeModel):
+    graph_safe = True      # train() below never syncs with the host
+
     def __init__(self, network, dataset: Cifar10Dataset, gpu: bool = True):
         super().__init__(network, dataset, gpu=gpu)
         self._amp = os.environ.get("KUBEML_AMP", "1") != "0"
@@ -86,14 +98,16 @@ class KubeResnet34(KubeModel):
     def train(self, batch, batch_index):
         x, y = batch
         self.optimizer.zero_grad()
-        loss = ops.cross_entropy(self._forward(x).float(), y)
+        out = self._forward(x)
+        loss = ops.cross_entropy(out if out.dtype == torch.bfloat16 else out.float(), y)
         loss.backward()
         self.optimizer.step()
         return loss.detach()
 
     def validate(self, batch, batch_index) -> Tuple[torch.Tensor, torch.Tensor]:
         x, y = batch
-        loss, correct = ops.accuracy_count(self._forward(x).float(), y)
+        out = self._forward(x)
+        loss, correct = ops.accuracy_count(out if out.dtype == torch.bfloat16 else out.float(), y)
         return correct * (100.0 / self.batch_size), loss
 
     def infer(self, data):
@@ -120,4 +134,5 @@ def build_network(num_classes: int = 1000):
 def main():
     net = build_network(int(os.environ.get("KUBEML_RESNET_CLASSES", "1000")))
     ds = Cifar10Dataset(os.environ.get("KUBEML_RESNET_DATASET", "cifar10"))
+    ds.native = bool(getattr(net, "native", False))
     return KubeResnet34(net, ds, gpu=torch.cuda.is_available()).start()

@@ -1,0 +1,155 @@
+"""ResNet-18/34 (BasicBlock) with torchvision's topology, parameter names and initialisation —
+the network `torchvision.models.resnet.resnet34()` that the reference's function instantiates
+(ml/experiments/kubeml/function_resnet34.py:101), executed by the hand-written kernels.
+
+Per step on a [N,32,32,3] batch the program is, in kernels:
+  stem      im2col -> tcgen05 GEMM -> BN+ReLU (coop) -> max-pool
+  block     conv (shifted-TMA implicit GEMM, or im2col+GEMM when stride 2) -> BN+ReLU ->
+            conv -> BN + residual + ReLU        [+ 1x1/2 conv -> BN on the identity when downsampling]
+  head      (avg-pool) -> GEMM+bias
+and the mirror image backwards (BN backward produces the masked residual gradient, the first
+convolution's data gradient adds it in its epilogue, weight gradients land in the arena).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..ops import nn as K
+from .native import (Buffers, NativeNet, NBatchNorm2d, NConv2d, NLinear, bn_backward, bn_forward,
+                     conv_backward, conv_forward, linear_backward, linear_forward)
+
+
+class NBasicBlock(nn.Module):
+    expansion = 1
+
+    def __init__(self, cin: int, cout: int, stride: int):
+        super().__init__()
+        self.conv1 = NConv2d(cin, cout, 3, stride, 1)
+        self.bn1 = NBatchNorm2d(cout)
+        self.conv2 = NConv2d(cout, cout, 3, 1, 1)
+        self.bn2 = NBatchNorm2d(cout)
+        self.downsample = None
+        if stride != 1 or cin != cout:
+            self.downsample = nn.Sequential(NConv2d(cin, cout, 1, stride, 0), NBatchNorm2d(cout))
+
+
+class NativeResNet(NativeNet):
+    def __init__(self, layers: List[int], num_classes: int = 1000):
+        super().__init__()
+        self.conv1 = NConv2d(3, 64, 7, 2, 3)
+        self.bn1 = NBatchNorm2d(64)
+        cin = 64
+        for i, (n, c) in enumerate(zip(layers, (64, 128, 256, 512)), start=1):
+            blocks = []
+            for b in range(n):
+                blocks.append(NBasicBlock(cin, c, 2 if (b == 0 and i > 1) else 1))
+                cin = c
+            setattr(self, f"layer{i}", nn.Sequential(*blocks))
+        self.fc = NLinear(512, num_classes)
+        self.num_classes = num_classes
+        self._blocks = [(f"layer{i}.{j}", blk) for i in range(1, 5)
+                        for j, blk in enumerate(getattr(self, f"layer{i}"))]
+        self._saved: Optional[dict] = None
+
+    # wgrad reduces over N*Ho*Wo pixels: shallow-and-wide early layers need K-splits to fill the GPU
+    @staticmethod
+    def _wgrad_splits(pixels: int, cout: int, cin_cols: int) -> int:
+        tiles = ((cout + 127) // 128) * max(1, cin_cols // 64)
+        chunks = max(1, pixels // 64)
+        want = max(1, min(chunks // 4, 148 // max(tiles, 1)))
+        return want
+
+    def _after_bound(self, arena) -> None:
+        # gradients produced with split-K are accumulated with red.add and must start from zero:
+        # remember the flat range that covers them (the early, small layers)
+        self._zero_names = []
+
+    # ---------------------------------------------------------------------------------- forward
+    def _to_nhwc_bf16(self, x: torch.Tensor) -> torch.Tensor:
+        from .native import act_dtype
+        if x.dim() == 4 and x.shape[-1] == 3 and x.shape[1] != 3:
+            return x.contiguous().to(act_dtype())
+        if x.dim() == 4 and x.shape[1] == 3:          # NCHW float (reference-style pipeline)
+            return x.permute(0, 2, 3, 1).contiguous().to(act_dtype())
+        raise ValueError(f"unexpected input shape {tuple(x.shape)}")
+
+    def _forward_impl(self, x: torch.Tensor, train: bool) -> torch.Tensor:
+        x = self._to_nhwc_bf16(x)
+        N = x.shape[0]
+        B = self.buffers_for(N, train)
+        S = {"x": x, "blocks": []}
+        c1 = conv_forward(self.conv1, x, B, "stem")
+        a1 = bn_forward(self.bn1, c1, B, "stem.bn", train, relu=True)
+        _, H1, W1, _ = a1.shape
+        Hp, Wp = (H1 + 2 - 3) // 2 + 1, (W1 + 2 - 3) // 2 + 1
+        p1 = B.get("pool.y", (N, Hp, Wp, 64))
+        idx = B.get("pool.idx", (N, Hp, Wp, 64), torch.uint8)
+        K.maxpool_fwd(a1, p1, idx, 3, 2, 1)
+        S.update(c1=c1, a1=a1, p1=p1)
+        h = p1
+        for tag, blk in self._blocks:
+            t1 = conv_forward(blk.conv1, h, B, tag + ".c1")
+            a = bn_forward(blk.bn1, t1, B, tag + ".bn1", train, relu=True)
+            t2 = conv_forward(blk.conv2, a, B, tag + ".c2")
+            idn, td = h, None
+            if blk.downsample is not None:
+                td = conv_forward(blk.downsample[0], h, B, tag + ".cd")
+                idn = bn_forward(blk.downsample[1], td, B, tag + ".bnd", train, relu=False)
+            out = bn_forward(blk.bn2, t2, B, tag + ".bn2", train, relu=True, res=idn)
+            S["blocks"].append((h, t1, a, t2, td, out))
+            h = out
+        Nn, Hh, Ww, C = h.shape
+        if Hh * Ww == 1:
+            pooled = h.view(Nn, C)
+        else:
+            pooled = B.get("avg.y", (Nn, C))
+            K.avgpool_fwd(h, pooled)
+        logits = linear_forward(self.fc, pooled, B, "fc")
+        S.update(last=h, pooled=pooled, B=B)
+        if train:
+            self._saved = S
+        return logits
+
+    # ---------------------------------------------------------------------------------- backward
+    def _backward_impl(self, dlogits: torch.Tensor) -> None:
+        S = self._saved
+        B: Buffers = S["B"]
+        from .native import act_dtype
+        if dlogits.dtype != act_dtype():
+            dlogits = dlogits.to(act_dtype())
+        dpooled = linear_backward(self.fc, S["pooled"], dlogits, B, "fc")
+        last = S["last"]
+        Nn, Hh, Ww, C = last.shape
+        if Hh * Ww == 1:
+            dh = dpooled.view(Nn, 1, 1, C)
+        else:
+            dh = B.get("avg.dx", tuple(last.shape))
+            K.avgpool_bwd(dpooled, dh)
+        for (tag, blk), (h, t1, a, t2, td, out) in zip(reversed(self._blocks), reversed(S["blocks"])):
+            # out = relu(bn2(t2) + idn)
+            dt2, g = bn_backward(blk.bn2, dh, out, t2, B, tag + ".bn2", want_dres=True)
+            da = conv_backward(blk.conv2, a, dt2, B, tag + ".c2")
+            dt1, _ = bn_backward(blk.bn1, da, a, t1, B, tag + ".bn1")
+            if blk.downsample is None:
+                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=g)
+            else:
+                dtd, _ = bn_backward(blk.downsample[1], g, None, td, B, tag + ".bnd")
+                did = conv_backward(blk.downsample[0], h, dtd, B, tag + ".cd")
+                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=did)
+        # stem
+        da1 = B.get("pool.dx", tuple(S["a1"].shape))
+        K.maxpool_bwd(dh, B["pool.idx"], da1, 3, 2, 1)
+        dc1, _ = bn_backward(self.bn1, da1, S["a1"], S["c1"], B, "stem.bn")
+        conv_backward(self.conv1, S["x"], dc1, B, "stem", need_dx=False)
+
+
+def resnet34(num_classes: int = 1000) -> NativeResNet:
+    return NativeResNet([3, 4, 6, 3], num_classes)
+
+
+def resnet18(num_classes: int = 1000) -> NativeResNet:
+    return NativeResNet([2, 2, 2, 2], num_classes)

@@ -35,6 +35,11 @@ Number = Union[float, torch.Tensor]
 
 
 class KubeModel(ABC):
+    # A subclass whose train() neither synchronises with the host (.item(), prints of tensor
+    # values) nor changes shape-dependent control flow between batches may set this: the worker then
+    # captures one training step in a CUDA graph and replays it (launch-bound small models).
+    graph_safe = False
+
     def __init__(self, network: nn.Module, dataset: KubeDataset, gpu: bool = False):
         self._network = network
         self._dataset = dataset
@@ -195,6 +200,7 @@ class KubeModel(ABC):
         # after the round's merge was queued: one sync per round, not one `.item()` per batch
         stage = _LossStage(self.device) if on_cuda else None
         launches0 = _native_launches()
+        graph_l0 = (self._inv.worker_state or {}).get("graph_launches", 0)
         t_ev0 = t_ev1 = None
         if on_cuda:
             torch.cuda.synchronize(self.device)
@@ -208,8 +214,9 @@ class KubeModel(ABC):
             num_iterations += len(batches)
 
             self._on_iteration_start()
+            graphing = self._graphs_enabled()
             begin_round = getattr(self._sync, "begin_round", None)
-            if begin_round is not None:
+            if begin_round is not None and not graphing:
                 begin_round(len(batches), self.optimizer)
             sliced = isinstance(batches, _sliced_type())
             for idx, batch in enumerate(batches):
@@ -217,7 +224,7 @@ class KubeModel(ABC):
                     raise KubeMLException(f"injected fault in function {a._func_id}", 500)
                 if not sliced:
                     batch = self._batch_to_device(batch)
-                step_loss = self.train(batch, idx)
+                step_loss = self._graphed_step(batch, idx) if graphing else self.train(batch, idx)
                 if stage is not None and isinstance(step_loss, torch.Tensor) and step_loss.is_cuda:
                     stage.push(step_loss)
                 elif isinstance(step_loss, torch.Tensor):
@@ -241,7 +248,8 @@ class KubeModel(ABC):
         else:
             self.train_seconds = _time.perf_counter() - t_wall
         self.steps = num_iterations
-        self.gpu_launches = _native_launches() - launches0
+        ws = self._inv.worker_state or {}
+        self.gpu_launches = _native_launches() - launches0 + ws.get("graph_launches", 0) - graph_l0
         if stage is not None:
             self.d2h_bytes = stage.bytes
         self.merge_seconds = float(getattr(self._sync, "merge_seconds", 0.0))
@@ -249,6 +257,61 @@ class KubeModel(ABC):
         if num_iterations == 0:
             return 0.0
         return (loss_host + float(self._sync.drain_losses(loss_dev))) / num_iterations
+
+    # ---- CUDA-graph replay of the user's train() ---------------------------------------------------
+    def _graphs_enabled(self) -> bool:
+        if self.device is None or self.device.type != "cuda" or not self.graph_safe:
+            return False
+        return os.environ.get("KUBEML_CUDA_GRAPH", "1") != "0"
+
+    def _graphed_step(self, batch, idx):
+        """First two calls per (shapes, hyper-parameters) run eagerly (allocations, lazy inits), the
+        third is captured, later ones replay.  The captured program only touches arena memory and
+        buffers owned by the capturing KubeModel, which the cache keeps alive, so it stays valid for
+        later invocations (epochs) whose fresh module objects alias the same arena."""
+        ws = self._inv.worker_state if self._inv.worker_state is not None else {}
+        cache = ws.setdefault("step_graphs", {})
+        tensors = [t for t in (batch if isinstance(batch, (tuple, list)) else (batch,))
+                   if isinstance(t, torch.Tensor)]
+        opt = self.optimizer
+        hyper = tuple(sorted((k, v) for k, v in getattr(opt, "defaults", {}).items()
+                             if isinstance(v, (int, float, bool))))
+        lr_now = tuple(g.get("lr") for g in getattr(opt, "param_groups", []))
+        key = (self.args._job_id, type(self).__name__, tuple((tuple(t.shape), t.dtype) for t in tensors),
+               hyper, lr_now, id(getattr(self._sync, "arena", None)))
+        ent = cache.get(key)
+        if ent is None:
+            ent = {"calls": 0, "graph": None, "failed": False}
+            cache[key] = ent
+        if ent["graph"] is not None:
+            for s_t, t in zip(ent["static"], tensors):
+                s_t.copy_(t, non_blocking=True)
+            ent["graph"].replay()
+            self._graph_replays = getattr(self, "_graph_replays", 0) + 1
+            ws["graph_launches"] = ws.get("graph_launches", 0) + ent["kernels"]
+            return ent["out"]
+        ent["calls"] += 1
+        if ent["failed"] or ent["calls"] <= 2:
+            return self.train(batch, idx)
+        try:
+            static = [t.clone() for t in tensors]
+            it = iter(static)
+            sbatch = type(batch)(next(it) if isinstance(t, torch.Tensor) else t for t in batch) \
+                if isinstance(batch, (tuple, list)) else static[0]
+            torch.cuda.synchronize(self.device)
+            k0 = _native_launches()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                out = ent["owner_train"](sbatch, idx) if "owner_train" in ent else self.train(sbatch, idx)
+            ent.update(graph=g, static=static, out=out, owner=self, kernels=_native_launches() - k0)
+            g.replay()            # the capture itself did not execute: run this batch now
+            ws["graph_launches"] = ws.get("graph_launches", 0) + ent["kernels"]
+            return out
+        except Exception as e:  # noqa: BLE001 - fall back to eager for this signature
+            ent["failed"] = True
+            self.logger.warning("CUDA graph capture of train() failed (%s); running eagerly", e)
+            torch.cuda.synchronize(self.device)
+            return self.train(batch, idx)
 
     # ---- task: val (network.py:312-360) ----------------------------------------------------------
     def _on_validation_start(self) -> None:

@@ -15,10 +15,18 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
     return 0 if t is None else t.data_ptr()
 
 
+def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0):
+    e = _native.Epilogue()
+    e.bias = _ptr(bias) or None
+    e.addend_bf16 = _ptr(addend) or None
+    e.relu, e.out_f32, e.splits, e.block_n = int(relu), int(out_f32), int(splits), int(block_n)
+    return e
+
+
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
               bias: Optional[torch.Tensor] = None, relu: bool = False,
               out_dtype: torch.dtype = torch.bfloat16, out: Optional[torch.Tensor] = None,
-              splits: int = 1, block_n: int = 0) -> torch.Tensor:
+              splits: int = 1, block_n: int = 0, addend: Optional[torch.Tensor] = None) -> torch.Tensor:
     """out[M,N] = A · B^T (+bias, ReLU) with fp32 accumulation.
 
     a: [M,K] (a_mn=False, K contiguous) or [K,M] (a_mn=True, M contiguous), bf16
@@ -28,12 +36,16 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     M = a.shape[1] if a_mn else a.shape[0]
     K = a.shape[0] if a_mn else a.shape[1]
     N = b.shape[1] if b_mn else b.shape[0]
+    if out is not None:
+        out_dtype = out.dtype
     if not a.is_cuda:
         A = (a.t() if a_mn else a).float()
         B = (b.t() if b_mn else b).float()
         r = A @ B.t()
         if bias is not None:
             r = r + bias.float()
+        if addend is not None:
+            r = r + addend.float()
         if relu:
             r = torch.relu(r)
         r = r.to(out_dtype)
@@ -42,14 +54,15 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
             return out
         return r
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "gemm_bf16 wants bf16 operands"
-    assert a.stride(-1) == 1 and b.stride(-1) == 1
+    assert a.stride(-1) == 1 and b.stride(-1) == 1 and (out is None or out.stride(-1) == 1)
     out_f32 = out_dtype == torch.float32
     if out is None:
         out = (torch.zeros if splits > 1 else torch.empty)((M, N), dtype=out_dtype, device=a.device)
+    import ctypes
+    e = _epi(bias, addend, relu, out_f32, splits, block_n)
     _native.check(_native.lib().kml_gemm_bf16(
         a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(),
-        out.stride(0), M, N, K, _ptr(bias), int(relu), int(out_f32), int(splits), int(block_n),
-        _native.stream_ptr()), "kml_gemm_bf16")
+        out.stride(0), M, N, K, ctypes.byref(e), _native.stream_ptr()), "kml_gemm_bf16")
     return out
 
 
@@ -61,26 +74,62 @@ def conv2d_fprop_supported(H: int, W: int, Cin: int, Cout: int, KH: int, KW: int
 
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[torch.Tensor] = None,
                  relu: bool = False, out_dtype: torch.dtype = torch.bfloat16, splits: int = 1,
-                 block_n: int = 0) -> torch.Tensor:
+                 block_n: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Stride-1 convolution, NHWC.  x: [N,H,W,Cin] bf16; w: [Cout,KH,KW,Cin] bf16 -> [N,Ho,Wo,Cout].
     The data gradient of a stride-1 convolution is this same op applied to dY with the flipped,
     channel-transposed filter and pad' = K-1-pad."""
     N, H, W, Cin = x.shape
     Cout, KH, KW, _ = w.shape
     Ho, Wo = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+    if out is not None:
+        out_dtype = out.dtype
     if not x.is_cuda:
         y = F.conv2d(x.permute(0, 3, 1, 2).float(), w.permute(0, 3, 1, 2).float(),
                      None if bias is None else bias.float(), padding=pad)
         if relu:
             y = torch.relu(y)
-        return y.permute(0, 2, 3, 1).contiguous().to(out_dtype)
+        y = y.permute(0, 2, 3, 1).contiguous().to(out_dtype)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
     assert x.is_contiguous() and w.is_contiguous()
     out_f32 = out_dtype == torch.float32
-    y = (torch.zeros if splits > 1 else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
+    import ctypes
+    y = out if out is not None else \
+        (torch.zeros if splits > 1 else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
+    e = _epi(bias, None, relu, out_f32, splits, block_n)
     _native.check(_native.lib().kml_conv2d_fprop(
-        x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, _ptr(bias),
-        int(relu), int(out_f32), int(splits), int(block_n), _native.stream_ptr()), "kml_conv2d_fprop")
+        x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
+        _native.stream_ptr()), "kml_conv2d_fprop")
     return y
+
+
+def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
+                 addend: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                 block_n: int = 0) -> torch.Tensor:
+    """Data gradient of `conv2d_fprop`: dy [N,Ho,Wo,Cout] bf16, w the *forward* filter
+    [Cout,KH,KW,Cin] bf16 -> dx [N,H,W,Cin] bf16 (+ addend, the residual branch's gradient)."""
+    N, Ho, Wo, Cout = dy.shape
+    _, KH, KW, Cin = w.shape
+    if not dy.is_cuda:
+        dx = torch.nn.grad.conv2d_input((N, Cin, H, W), w.permute(0, 3, 1, 2).float(),
+                                        dy.permute(0, 3, 1, 2).float(), padding=pad).permute(0, 2, 3, 1)
+        if addend is not None:
+            dx = dx + addend.float()
+        dx = dx.contiguous().to(dy.dtype)
+        if out is not None:
+            out.copy_(dx)
+            return out
+        return dx
+    import ctypes
+    assert dy.is_contiguous() and w.is_contiguous()
+    dx = out if out is not None else torch.empty((N, H, W, Cin), dtype=torch.bfloat16, device=dy.device)
+    e = _epi(None, addend, False, False, 1, block_n)
+    _native.check(_native.lib().kml_conv2d_dgrad(
+        dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
+        _native.stream_ptr()), "kml_conv2d_dgrad")
+    return dx
 
 
 def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, KH: int, KW: int, pad: int, *,

@@ -1,0 +1,224 @@
+"""Python entry points of the NHWC bf16 layer kernels (csrc/norm.cu, csrc/nn_misc.cu).  Raw,
+stateless calls on preallocated tensors — the native models (kubeml_b200.models) own the buffers
+and the order of calls; CPU tensors take an fp32 PyTorch restatement (test oracle)."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+_bn_scratch = {}
+
+
+def bn_scratch(device: torch.device, C: int) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    need = int(_native.lib().kml_bn_scratch_bytes(C)) // 4
+    buf = _bn_scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(max(need, 1 << 16), dtype=torch.float32, device=device)
+        _bn_scratch[key] = buf
+    return buf
+
+
+def bn_fwd_train(x, res, y, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd,
+                 relu: bool, eps: float = 1e-5, momentum: float = 0.1) -> None:
+    """y = relu?(bn(x) + res?) with batch statistics.  x/res/y: bf16 [..., C] viewed as [M, C]."""
+    C = x.shape[-1]
+    M = x.numel() // C
+    if x.is_cuda:
+        _native.check(_native.lib().kml_bn_fwd_train(
+            x.data_ptr(), _ptr(res), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), _ptr(running_mean),
+            _ptr(running_var), _ptr(nbt), save_mean.data_ptr(), save_invstd.data_ptr(),
+            bn_scratch(x.device, C).data_ptr(), M, C, int(relu), eps, momentum, _native.stream_ptr()),
+            "kml_bn_fwd_train")
+        return
+    xf = x.float().reshape(M, C)
+    mean = xf.mean(0)
+    var = xf.var(0, unbiased=False)
+    invstd = torch.rsqrt(var + eps)
+    out = (xf - mean) * invstd * gamma + beta
+    if res is not None:
+        out = out + res.float().reshape(M, C)
+    if relu:
+        out = torch.relu(out)
+    y.copy_(out.reshape(y.shape))
+    save_mean.copy_(mean)
+    save_invstd.copy_(invstd)
+    if running_mean is not None:
+        running_mean.mul_(1 - momentum).add_(momentum * mean)
+        running_var.mul_(1 - momentum).add_(momentum * var * (M / max(M - 1, 1)))
+    if nbt is not None:
+        nbt.add_(1)
+
+
+def bn_fwd_eval(x, res, y, gamma, beta, running_mean, running_var, relu: bool, eps: float = 1e-5) -> None:
+    C = x.shape[-1]
+    M = x.numel() // C
+    if x.is_cuda:
+        _native.check(_native.lib().kml_bn_fwd_eval(
+            x.data_ptr(), _ptr(res), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), running_mean.data_ptr(),
+            running_var.data_ptr(), M, C, int(relu), eps, _native.stream_ptr()), "kml_bn_fwd_eval")
+        return
+    out = (x.float().reshape(M, C) - running_mean) * torch.rsqrt(running_var + eps) * gamma + beta
+    if res is not None:
+        out = out + res.float().reshape(M, C)
+    if relu:
+        out = torch.relu(out)
+    y.copy_(out.reshape(y.shape))
+
+
+def bn_bwd(dy, y, x, gamma, save_mean, save_invstd, dx, dres, dgamma, dbeta) -> None:
+    """dy: grad of the block output; y: block output for the ReLU mask (None = no ReLU)."""
+    C = x.shape[-1]
+    M = x.numel() // C
+    if x.is_cuda:
+        _native.check(_native.lib().kml_bn_bwd(
+            dy.data_ptr(), _ptr(y), x.data_ptr(), gamma.data_ptr(), save_mean.data_ptr(),
+            save_invstd.data_ptr(), dx.data_ptr(), _ptr(dres), dgamma.data_ptr(), dbeta.data_ptr(),
+            bn_scratch(x.device, C).data_ptr(), M, C, _native.stream_ptr()), "kml_bn_bwd")
+        return
+    g = dy.float().reshape(M, C)
+    if y is not None:
+        g = g * (y.float().reshape(M, C) > 0)
+    xhat = (x.float().reshape(M, C) - save_mean) * save_invstd
+    s1, s2 = g.sum(0), (g * xhat).sum(0)
+    dbeta.copy_(s1)
+    dgamma.copy_(s2)
+    if dres is not None:
+        dres.copy_(g.reshape(dres.shape))
+    dx.copy_((gamma * save_invstd * (g - s1 / M - xhat * s2 / M)).reshape(dx.shape))
+
+
+def maxpool_fwd(x, y, idx, k: int, stride: int, pad: int) -> None:
+    N, H, W, C = x.shape
+    if x.is_cuda:
+        _native.check(_native.lib().kml_maxpool_fwd(x.data_ptr(), y.data_ptr(), _ptr(idx), N, H, W, C, k, stride,
+                                                    pad, _native.stream_ptr()), "kml_maxpool_fwd")
+        return
+    out, ind = F.max_pool2d(x.float().permute(0, 3, 1, 2), k, stride, pad, return_indices=True)
+    y.copy_(out.permute(0, 2, 3, 1))
+    if idx is not None:       # convert flat input index -> tap index within the window
+        Ho, Wo = out.shape[2], out.shape[3]
+        ih, iw = ind // W, ind % W
+        ho = torch.arange(Ho).view(1, 1, Ho, 1)
+        wo = torch.arange(Wo).view(1, 1, 1, Wo)
+        tap = (ih - (ho * stride - pad)) * k + (iw - (wo * stride - pad))
+        idx.copy_(tap.permute(0, 2, 3, 1).to(torch.uint8))
+
+
+def maxpool_bwd(dy, idx, dx, k: int, stride: int, pad: int) -> None:
+    N, H, W, C = dx.shape
+    if dy.is_cuda:
+        _native.check(_native.lib().kml_maxpool_bwd(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, C, k,
+                                                    stride, pad, _native.stream_ptr()), "kml_maxpool_bwd")
+        return
+    Ho, Wo = dy.shape[1], dy.shape[2]
+    out = torch.zeros(N, H, W, C)
+    t = idx.long()
+    kh, kw = t // k, t % k
+    ho = torch.arange(Ho).view(1, Ho, 1, 1)
+    wo = torch.arange(Wo).view(1, 1, Wo, 1)
+    h = ho * stride - pad + kh
+    w = wo * stride - pad + kw
+    n = torch.arange(N).view(N, 1, 1, 1).expand_as(h)
+    c = torch.arange(C).view(1, 1, 1, C).expand_as(h)
+    out.index_put_((n, h, w, c), dy.float(), accumulate=True)
+    dx.copy_(out)
+
+
+def avgpool_fwd(x, y) -> None:
+    N, H, W, C = x.shape
+    if x.is_cuda:
+        _native.check(_native.lib().kml_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, H * W, C,
+                                                    _native.stream_ptr()), "kml_avgpool_fwd")
+        return
+    y.copy_(x.float().mean(dim=(1, 2)))
+
+
+def avgpool_bwd(dy, dx) -> None:
+    N, H, W, C = dx.shape
+    if dy.is_cuda:
+        _native.check(_native.lib().kml_avgpool_bwd(dy.data_ptr(), dx.data_ptr(), N, H * W, C,
+                                                    _native.stream_ptr()), "kml_avgpool_bwd")
+        return
+    dx.copy_((dy.float() / (H * W)).view(N, 1, 1, C).expand(N, H, W, C))
+
+
+def im2col(x, cols, KH: int, KW: int, stride: int, pad: int) -> None:
+    """cols: bf16 [M, ldk] with ldk >= KH*KW*C; column order (kh, kw, c)."""
+    N, H, W, C = x.shape
+    ldk = cols.shape[1]
+    if x.is_cuda:
+        _native.check(_native.lib().kml_im2col(x.data_ptr(), cols.data_ptr(), N, H, W, C, KH, KW, stride, pad, ldk,
+                                               _native.stream_ptr()), "kml_im2col")
+        return
+    u = F.unfold(x.float().permute(0, 3, 1, 2), (KH, KW), padding=pad, stride=stride)   # [N, C*KH*KW, L]
+    L = u.shape[2]
+    u = u.view(N, C, KH * KW, L).permute(0, 3, 2, 1).reshape(N * L, KH * KW * C)
+    cols.zero_()
+    cols[:, :KH * KW * C].copy_(u)
+
+
+def col2im(dcols, addend, dx, KH: int, KW: int, stride: int, pad: int) -> None:
+    N, H, W, C = dx.shape
+    ldk = dcols.shape[1]
+    if dcols.is_cuda:
+        _native.check(_native.lib().kml_col2im(dcols.data_ptr(), _ptr(addend), dx.data_ptr(), N, H, W, C, KH, KW,
+                                               stride, pad, ldk, _native.stream_ptr()), "kml_col2im")
+        return
+    Ho, Wo = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+    u = dcols[:, :KH * KW * C].float().view(N, Ho * Wo, KH * KW, C).permute(0, 3, 2, 1).reshape(N, C * KH * KW, Ho * Wo)
+    out = F.fold(u, (H, W), (KH, KW), padding=pad, stride=stride).permute(0, 2, 3, 1)
+    if addend is not None:
+        out = out + addend.float()
+    dx.copy_(out)
+
+
+def colsum(x, out) -> None:
+    if x.is_cuda:
+        _native.check(_native.lib().kml_colsum_bf16(x.data_ptr(), out.data_ptr(), x.shape[0], x.shape[1], x.stride(0),
+                                                    _native.stream_ptr()), "kml_colsum_bf16")
+        return
+    out.copy_(x.float().sum(0))
+
+
+def pack_rows(src, dst) -> None:
+    """dst bf16 [rows, ld] <- src fp32 [rows, cols], zero padded."""
+    rows, cols = src.shape
+    if src.is_cuda:
+        _native.check(_native.lib().kml_pack_rows_bf16(src.data_ptr(), dst.data_ptr(), rows, cols, dst.shape[1],
+                                                       _native.stream_ptr()), "kml_pack_rows_bf16")
+        return
+    dst.zero_()
+    dst[:, :cols].copy_(src)
+
+
+def image_prep(x_u8, y, aug, pad: int, mean: Tuple[float, float, float], std: Tuple[float, float, float]) -> None:
+    """uint8 NHWC -> normalised bf16 NHWC with optional per-sample flip/crop codes (see header)."""
+    N, H, W, C = x_u8.shape
+    if x_u8.is_cuda:
+        m = (ctypes.c_float * 3)(*mean)
+        s = (ctypes.c_float * 3)(*std)
+        _native.check(_native.lib().kml_image_prep(x_u8.data_ptr(), y.data_ptr(), _ptr(aug), N, H, W, C, pad, m, s,
+                                                   _native.stream_ptr()), "kml_image_prep")
+        return
+    xf = x_u8.float() / 255.0
+    if aug is not None:
+        out = torch.zeros_like(xf)
+        for n in range(N):
+            a = int(aug[n])
+            dy, dxo = ((a >> 8) & 0xff) - pad, ((a >> 16) & 0xff) - pad
+            img = xf[n].flip(1) if a & 1 else xf[n]
+            padded = F.pad(img.permute(2, 0, 1), (pad, pad, pad, pad)).permute(1, 2, 0)
+            out[n] = padded[pad + dy: pad + dy + H, pad + dxo: pad + dxo + W]
+        xf = out
+    y.copy_((xf - torch.tensor(mean)) / torch.tensor(std))

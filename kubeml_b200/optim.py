@@ -133,7 +133,7 @@ class SGD(_FlatOptimizer):
                 self._defer_at = 0
                 return
             mb = self._arena.state1[: w.numel()] if mom else None
-            ops.sgd_step_(w, gr, mb, lr, wd, mom, nes)
+            ops.sgd_step_(w, gr, mb, lr, wd, mom, nes, w_bf16=getattr(self._arena, "wbf16", None))
             return
         if mom and self._bufs is None:
             self._bufs = [torch.zeros_like(p) for p in self.params]
@@ -180,7 +180,7 @@ class Adam(_FlatOptimizer):
             w, gr = flat
             n = w.numel()
             ops.adam_step_(w, gr, self._arena.state1[:n], self._arena.state2[:n], self._t, g["lr"],
-                           g["betas"], g["eps"], g["weight_decay"])
+                           g["betas"], g["eps"], g["weight_decay"], w_bf16=getattr(self._arena, "wbf16", None))
             return
         if self._m is None:
             self._m = [torch.zeros_like(p) for p in self.params]

@@ -27,7 +27,7 @@ import torch
 
 from ..model.store import weight_key
 
-_F32_ALIGN = 4          # elements: every tensor starts on a 16-byte boundary (float4 kernels)
+_F32_ALIGN = 64         # elements: tensors start on 256-byte (fp32) / 128-byte (bf16 copy) boundaries
 _REGION_ALIGN = 256     # bytes
 SIGNAL_WORDS = 64       # uint32 words of the signal pad (2 phases x 8 ranks used)
 
@@ -40,6 +40,11 @@ class Entry:
     offset: int               # elements from the start of its region
     numel: int
     is_param: bool
+    # Physical order of the elements when it differs from the logical (state_dict) shape: the
+    # native convolutions keep filters as [Cout][KH][KW][Cin]; the parameter the user sees is the
+    # permuted view with torch's [Cout][Cin][KH][KW] shape, so checkpoints keep the reference layout.
+    phys_shape: Optional[Tuple[int, ...]] = None
+    perm: Optional[Tuple[int, ...]] = None
 
 
 def _round_up(x: int, a: int) -> int:
@@ -52,7 +57,8 @@ class ArenaLayout:
 
     def __init__(self, module: torch.nn.Module):
         sd = module.state_dict()
-        param_names = {n for n, _ in module.named_parameters()}
+        params = dict(module.named_parameters())
+        param_names = set(params)
         self.order: List[str] = list(sd.keys())          # state_dict order = reference layer list
         self.entries: "OrderedDict[str, Entry]" = OrderedDict()
         off = 0
@@ -60,9 +66,14 @@ class ArenaLayout:
             t = sd[name]
             if not t.is_floating_point():
                 raise TypeError(f"parameter {name} is not floating point")
-            self.entries[name] = Entry(name, "f32", tuple(t.shape), off, t.numel(), True)
+            e = Entry(name, "f32", tuple(t.shape), off, t.numel(), True)
+            if getattr(params[name], "_kml_layout", None) == "OHWI" and t.dim() == 4:
+                O, I, KH, KW = t.shape
+                e.phys_shape, e.perm = (O, KH, KW, I), (0, 3, 1, 2)
+            self.entries[name] = e
             off += _round_up(max(t.numel(), 1), _F32_ALIGN)
         self.n_param = _round_up(off, 64)
+        self.want_bf16 = bool(getattr(module, "native", False))
         off = self.n_param
         ioff = 0
         for name in [n for n in self.order if n not in param_names]:
@@ -83,10 +94,11 @@ class ArenaLayout:
         self.off_grad = _round_up(self.off_status + 64, _REGION_ALIGN)
         self.off_state1 = _round_up(self.off_grad + self.n_param * 4, _REGION_ALIGN)
         self.off_state2 = _round_up(self.off_state1 + self.n_param * 4, _REGION_ALIGN)
-        self.nbytes = _round_up(self.off_state2 + self.n_param * 4, _REGION_ALIGN)
+        self.off_bf16 = _round_up(self.off_state2 + self.n_param * 4, _REGION_ALIGN)
+        self.nbytes = _round_up(self.off_bf16 + (self.n_param * 2 if self.want_bf16 else 0), _REGION_ALIGN)
 
     def signature(self) -> Tuple:
-        return tuple((e.name, e.kind, e.shape) for e in self.entries.values())
+        return tuple((e.name, e.kind, e.shape, e.phys_shape) for e in self.entries.values())
 
     def index(self, job_id: str, func_id: int = -1) -> List[dict]:
         """Key -> slice table in the reference's naming (for checkpoints / debugging)."""
@@ -131,6 +143,7 @@ class WeightArena:
         self.grads = self._view(L.off_grad, (max(L.n_param, 4),), torch.float32)
         self.state1 = self._view(L.off_state1, (max(L.n_param, 4),), torch.float32)
         self.state2 = self._view(L.off_state2, (max(L.n_param, 4),), torch.float32)
+        self.wbf16 = (self._view(L.off_bf16, (L.n_param,), torch.bfloat16) if L.want_bf16 else None)
 
     # ---- raw views -----------------------------------------------------------------------
     def _view(self, byte_off: int, shape: Tuple[int, ...], dtype: torch.dtype) -> torch.Tensor:
@@ -147,6 +160,9 @@ class WeightArena:
             return torch.frombuffer(buf, dtype=dtype, count=n, offset=byte_off).view(shape)
         if n == 0:
             return torch.empty(shape, dtype=dtype, device=self.device)
+        if dtype == torch.bfloat16:      # no bf16 in the array interface: view int16 bits
+            span = _DeviceSpan(self.base + byte_off, tuple(shape), "<i2", self)
+            return torch.as_tensor(span, device=self.device).view(torch.bfloat16)
         typestr = {torch.float32: "<f4", torch.int64: "<i8", torch.int32: "<i4"}[dtype]
         span = _DeviceSpan(self.base + byte_off, tuple(shape), typestr, self)
         return torch.as_tensor(span, device=self.device)
@@ -157,13 +173,29 @@ class WeightArena:
     def tensor(self, name: str) -> torch.Tensor:
         e = self.layout.entries[name]
         if e.kind == "f32":
-            return self._view(self.layout.off_f32 + e.offset * 4, e.shape, torch.float32)
+            return self._logical(e, self.layout.off_f32 + e.offset * 4, torch.float32)
         return self._view(self.layout.off_i64 + e.offset * 8, e.shape, torch.int64)
+
+    def _logical(self, e: Entry, byte_off: int, dtype: torch.dtype) -> torch.Tensor:
+        if e.phys_shape is not None:
+            return self._view(byte_off, e.phys_shape, dtype).permute(*e.perm)
+        return self._view(byte_off, e.shape, dtype)
 
     def grad(self, name: str) -> torch.Tensor:
         e = self.layout.entries[name]
         assert e.is_param
-        return self._view(self.layout.off_grad + e.offset * 4, e.shape, torch.float32)
+        return self._logical(e, self.layout.off_grad + e.offset * 4, torch.float32)
+
+    def physical(self, name: str, region: str = "weights") -> torch.Tensor:
+        """The entry in its physical element order (what the native kernels read):
+        region in {"weights", "grads", "bf16"}."""
+        e = self.layout.entries[name]
+        shape = e.phys_shape or e.shape
+        if region == "weights":
+            return self._view(self.layout.off_f32 + e.offset * 4, shape, torch.float32)
+        if region == "grads":
+            return self._view(self.layout.off_grad + e.offset * 4, shape, torch.float32)
+        return self._view(self.layout.off_bf16 + e.offset * 2, shape, torch.bfloat16)
 
     # ---- module binding ------------------------------------------------------------------
     def bind(self, module: torch.nn.Module, copy_in: bool = True, bind_grads: bool = True) -> None:
@@ -187,11 +219,23 @@ class WeightArena:
                     if copy_in:
                         view.copy_(mod._buffers[leaf].detach().to(view.device, non_blocking=True))
                     mod._buffers[leaf] = view
+        self.refresh_bf16()
+        hook = getattr(module, "_on_arena_bound", None)
+        if callable(hook):
+            hook(self)
+
+    def refresh_bf16(self) -> None:
+        """Re-derive the bf16 tensor-core copy of the parameters from the fp32 masters (after a
+        bind, a checkpoint load or a peer copy; the optimizer and the merge keep it current)."""
+        if self.wbf16 is not None and self.layout.n_param:
+            from .. import ops
+            ops.cast_bf16_(self.wbf16, self.weights[: self.layout.n_param])
 
     def load_state_dict(self, state: Dict[str, torch.Tensor]) -> None:
         with torch.no_grad():
             for name in self.layout.entries:
                 self.tensor(name).copy_(state[name].to(self.device))
+        self.refresh_bf16()
 
     def state_dict(self) -> "OrderedDict[str, torch.Tensor]":
         return OrderedDict((n, self.tensor(n).detach().clone()) for n in self.layout.order)
@@ -199,7 +243,7 @@ class WeightArena:
     def close(self) -> None:
         if self.handle is not None:
             from .. import _native
-            for name in ("weights", "counters", "flags", "status", "grads", "state1", "state2"):
+            for name in ("weights", "counters", "flags", "status", "grads", "state1", "state2", "wbf16"):
                 setattr(self, name, None)
             _native.lib().kml_arena_destroy(self.handle)
             self.handle = None

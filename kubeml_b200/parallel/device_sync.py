@@ -100,7 +100,7 @@ class RankSync:
         self._ensure_arena(net, kube_model.device, copy_in=False)
         if joined:
             self.group.copy_reference_into(self)
-        self.arena.bind(net, copy_in=False)
+        self.arena.bind(net, copy_in=False)      # also refreshes the bf16 operand copy
         if a._task in ("train", "join"):
             self._epoch = int(a.epoch)
             self._schedule = (round_schedule(kube_model._dataset.num_docs, a._N, a._K, a.batch_size)
@@ -197,6 +197,7 @@ class RankSync:
             self._fused_steps += 1
         uses_momentum = opt is not None and bool(getattr(opt, "defaults", {}).get("momentum", 0))
         p.momentum_buf = self.arena.ptr(L.off_state1) if uses_momentum else None
+        p.w_bf16 = self.arena.ptr(L.off_bf16) if self.arena.wbf16 is not None else None
         stream = torch.cuda.current_stream(self.arena.device)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
