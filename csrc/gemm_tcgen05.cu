@@ -28,7 +28,9 @@ namespace {
 
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;            // bf16 elements = one 128-byte swizzle row
-constexpr int kStages = 4;
+// 4 stages: split-K keeps the per-CTA K loop short, and <= 128 KB lets two CTAs share an SM so that
+// independent GEMMs (weight gradient next to the data-gradient chain) overlap.
+template <int BLOCK_N> struct Stages { static constexpr int value = 4; };
 constexpr int kNumThreads = 192;       // producer warp, MMA warp, 4 epilogue warps
 constexpr int kUmmaK = 16;
 
@@ -63,6 +65,7 @@ struct GemmArgs {
   const __nv_bfloat16* addend;           // bf16 [rows][ldo] added before ReLU (residual gradient), may be null
   int relu, out_f32, atomic_add;
   int wgt_taps, wgt_cin;                 // kWgtMN: taps in the filter, input channels per tap
+  long long slab_stride;                 // != 0: split s stores its partial tile at out + s*slab_stride (no atomics)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -149,13 +152,14 @@ __device__ __forceinline__ void box_origin(const Geometry& g, int idx, int& w0, 
 }
 
 template <int BLOCK_N, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kNumThreads, 1)
+__global__ void __launch_bounds__(kNumThreads, 2)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const GemmArgs args) {
   constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
   constexpr uint32_t kBBytes = BLOCK_N * kBlockK * 2;
   constexpr uint32_t kHalfBytes = 64 * kBlockK * 2;   // one 64-wide MN block of an MN-major operand
   constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+  constexpr int kStages = Stages<BLOCK_N>::value;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -318,7 +322,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       }
       if (!row_ok) continue;
       const int ncol0 = nt * BLOCK_N + c0;                // column within the (per-tap) N range
-      const long long off = static_cast<long long>(row) * args.ldo + col_base + c0;
+      const long long off = static_cast<long long>(row) * args.ldo + col_base + c0 +
+                            static_cast<long long>(split) * args.slab_stride;
       float f[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
@@ -352,9 +357,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       if (args.out_f32) {
         float* o = static_cast<float*>(args.out) + off;
         if (args.atomic_add) {
+          if (ncol0 + 32 <= args.n_valid && (off & 3) == 0) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (ncol0 + j < args.n_valid) atomicAdd(o + j, f[j]);
+            for (int j = 0; j < 32; j += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(f[j]), "f"(f[j + 1]),
+                           "f"(f[j + 2]), "f"(f[j + 3]) : "memory");
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (ncol0 + j < args.n_valid) atomicAdd(o + j, f[j]);
+          }
         } else if (ncol0 + 32 <= args.n_valid && (off & 3) == 0) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
@@ -432,7 +444,7 @@ int encode_map(CUtensorMap* map, const TensorSpec& t) {
 
 template <int BLOCK_N, bool A_MN, bool B_MN>
 int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& a, cudaStream_t s) {
-  constexpr size_t smem = kStages * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 /*align*/ + 512 /*barriers+taps*/;
+  constexpr size_t smem = Stages<BLOCK_N>::value * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 /*align*/ + 640 /*barriers+taps*/;
   auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN>;
   static bool configured = false;
   if (!configured) {
@@ -517,8 +529,9 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
   g.out = out; g.ldo = ldo; g.m_valid = M; g.n_valid = N;
   g.bias = bias; g.relu = relu; g.out_f32 = out_f32;
   g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);
-  g.atomic_add = g.splits > 1;
-  KML_CHECK(!g.atomic_add || (out_f32 && !relu), "split-K needs an fp32 output (pre-zeroed) and no ReLU");
+  g.atomic_add = g.splits > 1 && !epi->slabs;
+  g.slab_stride = (g.splits > 1 && epi->slabs) ? static_cast<long long>(M) * ldo : 0;
+  KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
   return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
 }
 
@@ -589,8 +602,10 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
   g.splits = splits > g.k_chunks ? g.k_chunks : splits;
   g.z_taps = 1;
   g.out = y; g.ldo = Cout; g.m_valid = static_cast<int>(Mtot); g.n_valid = Cout;
-  g.bias = bias; g.relu = relu; g.out_f32 = out_f32; g.atomic_add = g.splits > 1;
-  KML_CHECK(!g.atomic_add || (out_f32 && !relu), "split-K needs an fp32 output (pre-zeroed) and no ReLU");
+  g.bias = bias; g.relu = relu; g.out_f32 = out_f32;
+  g.atomic_add = g.splits > 1 && !epi->slabs;
+  g.slab_stride = (g.splits > 1 && epi->slabs) ? Mtot * Cout : 0;
+  KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
   g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);
   if (dgrad) {
     // B = forward filter [rows = real Cout][cols = taps * real Cin], consumed MN-major

@@ -80,9 +80,46 @@ __device__ void rank_barrier(const kml_merge_params& p, int phase, uint32_t gen)
   __threadfence_system();
 }
 
+// Reduce [begin, end) of NP source replicas (compact list, ascending rank) and store the average
+// to ND destinations.  U elements per thread are loaded before any is used: NP*U 16-byte loads in
+// flight per thread hide the ~2 us NVLink round trip.  Sum in list order, true division: bit-parity
+// with the CPU oracle (ml/pkg/model/model.go:286-296, parallelSGD.go:31-50).
+template <int NP, int U>
+__device__ __forceinline__ void reduce_range(const float4* const* src, float4* const* dst, int nd, size_t begin,
+                                             size_t end, size_t tid, size_t nthreads, float fn) {
+  const float4* s_[NP];
+#pragma unroll
+  for (int j = 0; j < NP; ++j) s_[j] = src[j];
+  auto finish = [&](size_t idx, const float4 (&v)[NP]) {
+    float4 a = v[0];
+#pragma unroll
+    for (int j = 1; j < NP; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+    a.x = a.x / fn; a.y = a.y / fn; a.z = a.z / fn; a.w = a.w / fn;
+    for (int d = 0; d < nd; ++d) st_cg_f4(dst[d] + idx, a);
+  };
+  size_t i = begin + tid;
+  for (; i + (U - 1) * nthreads < end; i += U * nthreads) {
+    float4 v[U][NP];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int j = 0; j < NP; ++j) v[u][j] = ld_cg_f4(s_[j] + i + u * nthreads);
+#pragma unroll
+    for (int u = 0; u < U; ++u) finish(i + u * nthreads, v[u]);
+  }
+  for (; i < end; i += nthreads) {
+    float4 v[NP];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) v[j] = ld_cg_f4(s_[j] + i);
+    finish(i, v);
+  }
+}
+
 template <bool kMcast>
 __global__ void __launch_bounds__(kThreads)
 kavg_merge_kernel(const kml_merge_params p) {
+  __shared__ const float4* s_src[KML_MAX_RANKS];
+  __shared__ float4* s_dst[KML_MAX_RANKS];
   cg::grid_group grid = cg::this_grid();
   const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
@@ -132,31 +169,44 @@ kavg_merge_kernel(const kml_merge_params p) {
 
   if constexpr (kMcast) {
     float4* mc = reinterpret_cast<float4*>(p.mcast);
-    for (size_t i = begin + tid; i < end; i += nthreads) {
+    constexpr int U = 4;                       // loads in flight per thread: NVLink round trips are ~2 us
+    size_t i = begin + tid;
+    for (; i + (U - 1) * nthreads < end; i += U * nthreads) {
+      float4 s[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) s[u] = mc_ld_reduce_f4(mc + i + u * nthreads);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        s[u].x *= inv; s[u].y *= inv; s[u].z *= inv; s[u].w *= inv;
+        mc_st_f4(mc + i + u * nthreads, s[u]);
+      }
+    }
+    for (; i < end; i += nthreads) {
       float4 s = mc_ld_reduce_f4(mc + i);
       s.x *= inv; s.y *= inv; s.z *= inv; s.w *= inv;
       mc_st_f4(mc + i, s);
     }
   } else {
-    for (size_t i = begin + tid; i < end; i += nthreads) {
-      float4 v[KML_MAX_RANKS];
-#pragma unroll
-      for (int r = 0; r < KML_MAX_RANKS; ++r)
-        if ((p.participants >> r) & 1u) v[r] = ld_cg_f4(reinterpret_cast<const float4*>(p.replica[r]) + i);
-      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-      bool first = true;
-#pragma unroll
+    const float fn = static_cast<float>(nparts);
+    int nd = 0;
+    if (threadIdx.x == 0) {
+      int ns = 0, ndl = 0;
       for (int r = 0; r < KML_MAX_RANKS; ++r) {
-        if (!((p.participants >> r) & 1u)) continue;
-        if (first) { s = v[r]; first = false; }
-        else { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+        if ((p.participants >> r) & 1u) s_src[ns++] = reinterpret_cast<const float4*>(p.replica[r]);
+        if ((p.write_mask >> r) & 1u) s_dst[ndl++] = reinterpret_cast<float4*>(p.replica[r]);
       }
-      // true division keeps bit-parity with the CPU oracle (sum then divide)
-      s.x = s.x / static_cast<float>(nparts); s.y = s.y / static_cast<float>(nparts);
-      s.z = s.z / static_cast<float>(nparts); s.w = s.w / static_cast<float>(nparts);
-#pragma unroll
-      for (int r = 0; r < KML_MAX_RANKS; ++r)
-        if ((p.write_mask >> r) & 1u) st_cg_f4(reinterpret_cast<float4*>(p.replica[r]) + i, s);
+    }
+    nd = __popc(p.write_mask);
+    __syncthreads();
+    switch (nparts) {
+      case 1: reduce_range<1, 8>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
+      case 2: reduce_range<2, 4>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
+      case 3: reduce_range<3, 2>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
+      case 4: reduce_range<4, 2>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
+      case 5: reduce_range<5, 1>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
+      case 6: reduce_range<6, 1>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
+      case 7: reduce_range<7, 1>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
+      default: reduce_range<8, 1>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
     }
   }
 

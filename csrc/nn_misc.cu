@@ -163,6 +163,200 @@ col2im_kernel(const __nv_bfloat16* __restrict__ dcols, const __nv_bfloat16* __re
   }
 }
 
+
+// ---------------------------------------------------------------------------------- 8-channel vector variants
+__device__ __forceinline__ void ld8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 v = __bfloat1622float2(h[i]); f[2 * i] = v.x; f[2 * i + 1] = v.y; }
+}
+__device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&f)[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+__global__ void __launch_bounds__(kThreads)
+maxpool_fwd_vec_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ idx,
+                       int N, int H, int W, int C, int Ho, int Wo, int k, int stride, int pad) {
+  const int C8 = C / 8;
+  const size_t total = static_cast<size_t>(N) * Ho * Wo * C8;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C8) * 8;
+    size_t p = i / C8;
+    const int wo = static_cast<int>(p % Wo); p /= Wo;
+    const int ho = static_cast<int>(p % Ho);
+    const int n = static_cast<int>(p / Ho);
+    float best[8];
+    int arg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = 0; }
+    for (int kh = 0; kh < k; ++kh) {
+      const int h = ho * stride - pad + kh;
+      if (h < 0 || h >= H) continue;
+      for (int kw = 0; kw < k; ++kw) {
+        const int w = wo * stride - pad + kw;
+        if (w < 0 || w >= W) continue;
+        float v[8];
+        ld8(x + ((static_cast<size_t>(n) * H + h) * W + w) * C + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (v[j] > best[j]) { best[j] = v[j]; arg[j] = kh * k + kw; }
+      }
+    }
+    const size_t o = (i / C8) * C + c;
+    st8(y + o, best);
+    if (idx) {
+      uint2 u;
+      u.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+      u.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+      *reinterpret_cast<uint2*>(idx + o) = u;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+maxpool_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char* __restrict__ idx,
+                       __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int stride,
+                       int pad) {
+  const int C8 = C / 8;
+  const size_t total = static_cast<size_t>(N) * H * W * C8;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C8) * 8;
+    size_t p = i / C8;
+    const int w = static_cast<int>(p % W); p /= W;
+    const int h = static_cast<int>(p % H);
+    const int n = static_cast<int>(p / H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int kh = 0; kh < k; ++kh) {
+      const int hn = h + pad - kh;
+      if (hn < 0 || hn % stride) continue;
+      const int ho = hn / stride;
+      if (ho >= Ho) continue;
+      for (int kw = 0; kw < k; ++kw) {
+        const int wn = w + pad - kw;
+        if (wn < 0 || wn % stride) continue;
+        const int wo = wn / stride;
+        if (wo >= Wo) continue;
+        const size_t o = ((static_cast<size_t>(n) * Ho + ho) * Wo + wo) * C + c;
+        const uint2 u = __ldg(reinterpret_cast<const uint2*>(idx + o));
+        float g[8];
+        ld8(dy + o, g);
+        const int tap = kh * k + kw;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int a = ((j < 4 ? u.x : u.y) >> (8 * (j & 3))) & 0xff;
+          if (a == tap) acc[j] += g[j];
+        }
+      }
+    }
+    st8(dx + (i / C8) * C + c, acc);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+im2col_vec_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int N, int H, int W, int C,
+                  int Ho, int Wo, int KH, int KW, int stride, int pad, int ldk) {
+  const int L8 = ldk / 8, C8 = C / 8, K8 = KH * KW * C8;
+  const size_t total = static_cast<size_t>(N) * Ho * Wo * L8;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int k8 = static_cast<int>(i % L8);
+    size_t m = i / L8;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (k8 < K8) {
+      const int c = (k8 % C8) * 8;
+      const int tap = k8 / C8;
+      const int kw = tap % KW, kh = tap / KW;
+      const int wo = static_cast<int>(m % Wo); m /= Wo;
+      const int ho = static_cast<int>(m % Ho);
+      const int n = static_cast<int>(m / Ho);
+      const int h = ho * stride - pad + kh, w = wo * stride - pad + kw;
+      if (h >= 0 && h < H && w >= 0 && w < W)
+        v = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<size_t>(n) * H + h) * W + w) * C + c));
+    }
+    *reinterpret_cast<uint4*>(cols + i * 8) = v;
+  }
+}
+
+// any C (the 3-channel stem): one thread gathers 8 consecutive columns and stores them as one vector
+__global__ void __launch_bounds__(kThreads)
+im2col_gather8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int N, int H, int W, int C,
+                      int Ho, int Wo, int KH, int KW, int stride, int pad, int ldk) {
+  const int L8 = ldk / 8, K = KH * KW * C;
+  const size_t total = static_cast<size_t>(N) * Ho * Wo * L8;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int k0 = static_cast<int>(i % L8) * 8;
+    size_t m = i / L8;
+    const int wo = static_cast<int>(m % Wo); m /= Wo;
+    const int ho = static_cast<int>(m % Ho);
+    const int n = static_cast<int>(m / Ho);
+    const __nv_bfloat16* img = x + static_cast<size_t>(n) * H * W * C;
+    __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int kk = k0 + j;
+      __nv_bfloat16 e = __float2bfloat16_rn(0.f);
+      if (kk < K) {
+        const int c = kk % C, tap = kk / C;
+        const int h = ho * stride - pad + tap / KW, w = wo * stride - pad + tap % KW;
+        if (h >= 0 && h < H && w >= 0 && w < W) e = img[(static_cast<size_t>(h) * W + w) * C + c];
+      }
+      v[j] = e;
+    }
+    *reinterpret_cast<uint4*>(cols + i * 8) = *reinterpret_cast<const uint4*>(v);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+col2im_vec_kernel(const __nv_bfloat16* __restrict__ dcols, const __nv_bfloat16* __restrict__ addend,
+                  __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int KH, int KW, int stride,
+                  int pad, int ldk) {
+  const int C8 = C / 8;
+  const size_t total = static_cast<size_t>(N) * H * W * C8;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C8) * 8;
+    size_t p = i / C8;
+    const int w = static_cast<int>(p % W); p /= W;
+    const int h = static_cast<int>(p % H);
+    const int n = static_cast<int>(p / H);
+    const size_t o = (i / C8) * C + c;
+    float acc[8];
+    if (addend) ld8(addend + o, acc);
+    else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    }
+    for (int kh = 0; kh < KH; ++kh) {
+      const int hn = h + pad - kh;
+      if (hn < 0 || hn % stride) continue;
+      const int ho = hn / stride;
+      if (ho >= Ho) continue;
+      for (int kw = 0; kw < KW; ++kw) {
+        const int wn = w + pad - kw;
+        if (wn < 0 || wn % stride) continue;
+        const int wo = wn / stride;
+        if (wo >= Wo) continue;
+        const size_t m = (static_cast<size_t>(n) * Ho + ho) * Wo + wo;
+        float g[8];
+        ld8(dcols + m * ldk + (kh * KW + kw) * C + c, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += g[j];
+      }
+    }
+    st8(dx + o, acc);
+  }
+}
+
 // ---------------------------------------------------------------------------------- misc
 // out[c] = sum_r x[r][c]  (bias gradient); one block per 32 columns, rows strided over warps
 __global__ void __launch_bounds__(kThreads)
@@ -235,6 +429,11 @@ int kml_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int 
   KML_CHECK(x && y && k * k <= 255, "kml_maxpool_fwd: bad arguments");
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = static_cast<size_t>(N) * Ho * Wo * C;
+  if (C % 8 == 0)
+    maxpool_fwd_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(idx), N, H,
+        W, C, Ho, Wo, k, stride, pad);
+  else
   maxpool_fwd_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(idx), N, H, W,
       C, Ho, Wo, k, stride, pad);
@@ -248,6 +447,11 @@ int kml_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int
   KML_CHECK(dy && idx && dx, "kml_maxpool_bwd: null pointer");
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = static_cast<size_t>(N) * H * W * C;
+  if (C % 8 == 0)
+    maxpool_bwd_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx),
+        N, H, W, C, Ho, Wo, k, stride, pad);
+  else
   maxpool_bwd_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx),
       N, H, W, C, Ho, Wo, k, stride, pad);
@@ -279,6 +483,15 @@ int kml_im2col(const void* x, void* cols, int N, int H, int W, int C, int KH, in
   KML_CHECK(x && cols && ldk >= KH * KW * C, "kml_im2col: bad arguments");
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const size_t total = static_cast<size_t>(N) * Ho * Wo * ldk;
+  if (C % 8 == 0 && ldk % 8 == 0)
+    im2col_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride,
+        pad, ldk);
+  else if (ldk % 8 == 0)
+    im2col_gather8_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride,
+        pad, ldk);
+  else
   im2col_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride, pad,
       ldk);
@@ -292,6 +505,11 @@ int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, in
   KML_CHECK(dcols && dx && ldk >= KH * KW * C, "kml_col2im: bad arguments");
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const size_t total = static_cast<size_t>(N) * H * W * C;
+  if (C % 8 == 0 && ldk % 8 == 0)
+    col2im_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dcols), static_cast<const __nv_bfloat16*>(addend),
+        static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk);
+  else
   col2im_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dcols), static_cast<const __nv_bfloat16*>(addend),
       static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk);

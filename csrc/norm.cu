@@ -1,32 +1,59 @@
-// BatchNorm2d for NHWC bf16 activations, training and inference, with ReLU and the residual add of
-// a ResNet block fused in.  The reference gets these through cuDNN/ATen inside torch 1.7.1
+// BatchNorm2d for NHWC activations, training and inference, with ReLU and the residual add of a
+// ResNet block fused in.  The reference gets these through cuDNN/ATen inside torch 1.7.1
 // (torchvision resnet34 in ml/experiments/kubeml/function_resnet34.py:101; SURVEY 2.4 "BatchNorm2d
 // fwd/bwd (train: batch stats + running-stat update + num_batches_tracked++)").
 //
-// Training forward, one cooperative launch:
-//   phase 1  every CTA sums x and x^2 per channel over its rows -> partial[cta][2][C]
-//   grid.sync
-//   phase 2  every CTA folds the partials in the same fixed order (deterministic, no atomics, nothing
-//            to zero), normalises its rows, adds the residual, applies ReLU, stores bf16;
-//            CTA 0 also stores mean / inv-std for backward, updates the running statistics
-//            (momentum, unbiased variance) and bumps num_batches_tracked.
-// Backward has the same shape: phase 1 sums g and g*xhat (g = dy masked by the ReLU output),
-// phase 2 writes dx (and g itself for the residual branch); CTA 0 writes dgamma / dbeta.
+// The layers are tiny (64 K .. 2 M elements) and sit between latency-bound GEMMs, so the design goal
+// is the fewest dependent memory round trips:
+//   * one launch per direction with a software grid barrier (not a cooperative launch, see grid_barrier); each thread owns <= 4 rows x 8 channels which it keeps
+//     in registers across the grid barrier, so the tensor is read exactly once;
+//   * the input may be the split-K *slabs* of the producing GEMM (fp32 [S][M][C]): the partial sums
+//     are folded here, on the fly, instead of by a reduction kernel or atomics in the GEMM;
+//   * per-channel statistics are combined across CTAs with red.add into a double-buffered
+//     accumulator: launch k uses buffer k&1 and clears buffer (k+1)&1 for its successor, the launch
+//     counter lives in device memory, so nothing has to be zeroed by the host and the kernel is
+//     safe to replay from a CUDA graph.
+// Forward (training): y = relu?(gamma*(x-mean)*invstd + beta + res?), saves mean/invstd, x (bf16)
+// when it came as slabs, updates running stats (momentum, unbiased variance) and num_batches_tracked.
+// Backward: g = dy * (y > 0); dbeta = sum g; dgamma = sum g*xhat;
+//           dx = gamma*invstd*(g - dbeta/M - xhat*dgamma/M); optionally stores g for the residual branch.
 #include "common.cuh"
 #include "../include/kubeml_b200.h"
-#include <cooperative_groups.h>
-
-namespace cg = cooperative_groups;
 
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kVec = 8;   // channels per thread (one 16-byte bf16 vector)
+constexpr int kVec = 8;        // channels per thread (one 16-byte bf16 vector)
+constexpr int kRows = 4;       // rows a thread keeps in registers
+constexpr int kMaxC = 2048;
 
-struct alignas(16) Bf16x8 { __nv_bfloat162 h[4]; };
+struct BnScratch {             // device-resident launch state, zero-initialised once
+  unsigned int launches;       // parity selects the statistics buffer of this launch
+  unsigned int bar;            // grid barrier: arrivals, monotonically increasing
+  unsigned int bar_base;       // value of `bar` when the current launch started
+  unsigned int pad;
+  float acc[2][2 * kMaxC];
+};
 
-__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
-  const uint4 u = *reinterpret_cast<const uint4*>(p);
+// Grid-wide barrier for a *regular* launch.  A cooperative launch costs ~7 us on this part (measured:
+// 9.3 us vs 1.9 us for an 8-row problem), which is more than the whole layer; the grid is sized to
+// fit the GPU at once (<= SMs x resident CTAs), the stream serialises launches, so every CTA becomes
+// resident and the spin cannot deadlock.
+__device__ __forceinline__ void grid_barrier(BnScratch* sc, unsigned base) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(&sc->bar, 1u);
+    unsigned v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&sc->bar) : "memory");
+    } while (v - base < gridDim.x);
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void cvt8(const uint4& u, float (&f)[8]) {
   const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -35,78 +62,160 @@ __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
     f[2 * i + 1] = v.y;
   }
 }
-__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   uint4 u;
   __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
 #pragma unroll
   for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-  *reinterpret_cast<uint4*>(p) = u;
+  return u;
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+  cvt8(__ldcg(reinterpret_cast<const uint4*>(p)), f);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+  *reinterpret_cast<uint4*>(p) = pack8(f);
+}
+// 8 channels of one row from either a bf16 tensor or the sum of S fp32 slabs
+__device__ __forceinline__ void load_row(const __nv_bfloat16* xb, const float* xs, int nslabs, size_t slab_stride,
+                                         size_t off, float (&f)[8]) {
+  if (xs == nullptr) {
+    load8(xb + off, f);
+    return;
+  }
+  float4 a = __ldcg(reinterpret_cast<const float4*>(xs + off));
+  float4 b = __ldcg(reinterpret_cast<const float4*>(xs + off + 4));
+  for (int s = 1; s < nslabs; ++s) {
+    const float4 c = __ldcg(reinterpret_cast<const float4*>(xs + s * slab_stride + off));
+    const float4 d = __ldcg(reinterpret_cast<const float4*>(xs + s * slab_stride + off + 4));
+    a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w;
+    b.x += d.x; b.y += d.y; b.z += d.z; b.w += d.w;
+  }
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+// Block-level then grid-level combination of two per-channel sums.  On return sm[0..2C) holds the
+// grid totals.  `sm` needs 2C floats.
+__device__ __forceinline__ void combine_stats(BnScratch* sc, int C, int c0, bool active,
+                                              const float (&s1)[kVec], const float (&s2)[kVec], float* sm) {
+  const unsigned par = sc->launches & 1u;          // read before anyone can bump it (bump is after the sync)
+  const unsigned base = sc->bar_base;
+  for (int i = threadIdx.x; i < 2 * C; i += kThreads) sm[i] = 0.f;
+  __syncthreads();
+  {
+    // threads of a warp that own the same channel group are `groups` lanes apart: fold them with
+    // shuffles first (power-of-two group counts), then one shared-memory atomic per warp and channel
+    const int groups = C / kVec;
+    float r1[kVec], r2[kVec];
+#pragma unroll
+    for (int i = 0; i < kVec; ++i) { r1[i] = active ? s1[i] : 0.f; r2[i] = active ? s2[i] : 0.f; }
+    bool writer = active;
+    if (groups < 32 && (groups & (groups - 1)) == 0) {
+      for (int off = groups; off < 32; off <<= 1) {
+#pragma unroll
+        for (int i = 0; i < kVec; ++i) {
+          r1[i] += __shfl_xor_sync(0xffffffffu, r1[i], off);
+          r2[i] += __shfl_xor_sync(0xffffffffu, r2[i], off);
+        }
+      }
+      writer = (threadIdx.x & 31) < groups;
+    }
+    if (writer) {
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) { atomicAdd(&sm[c0 + i], r1[i]); atomicAdd(&sm[C + c0 + i], r2[i]); }
+    }
+  }
+  __syncthreads();
+  float* acc = sc->acc[par];
+  for (int i = threadIdx.x; i < 2 * C; i += kThreads) atomicAdd(acc + i, sm[i]);
+  if (blockIdx.x == gridDim.x - 1) {               // clear the buffer of the *next* launch: all of it,
+    float4* nxt = reinterpret_cast<float4*>(sc->acc[par ^ 1u]);   // the next layer may be wider than this one
+    for (int i = threadIdx.x; i < 2 * kMaxC / 4; i += kThreads) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  grid_barrier(sc, base);
+  for (int i = threadIdx.x; i < 2 * C; i += kThreads) sm[i] = __ldcg(acc + i);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {       // everyone has arrived: publish the next launch's state
+    sc->launches += 1;
+    sc->bar_base = base + gridDim.x;
+  }
+  __syncthreads();
 }
 
 struct BnFwdArgs {
-  const __nv_bfloat16* x;       // [M][C] convolution output
+  const __nv_bfloat16* x;       // [M][C] convolution output (bf16), or null when xs is given
+  const float* xs;              // [S][M][C] split-K slabs of the convolution output, or null
+  int nslabs;
+  long long slab_stride;
+  __nv_bfloat16* x_out;         // [M][C] bf16 copy of the folded input (needed by backward) or null
   const __nv_bfloat16* res;     // [M][C] residual added before ReLU, or null
   __nv_bfloat16* y;             // [M][C]
   const float* gamma;
   const float* beta;
   float* running_mean;
   float* running_var;
-  long long* num_batches_tracked;   // may be null
-  float* save_mean;             // [C]
-  float* save_invstd;           // [C]
-  float* partial;               // [grid][2][C] scratch
+  long long* num_batches_tracked;
+  float* save_mean;
+  float* save_invstd;
+  BnScratch* scratch;
   int M, C, relu;
   float eps, momentum;
 };
 
-// thread layout: groups = C/8 channel vectors, lanes = kThreads/groups rows in flight per CTA
 __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs a) {
-  cg::grid_group grid = cg::this_grid();
-  extern __shared__ float sm[];              // [2][C] block sums, then [2][C] scale/shift
+  extern __shared__ float sm[];                    // [2C] totals, then reused as scale/shift
   const int groups = a.C / kVec;
   const int lanes = kThreads / groups;
   const int g = threadIdx.x % groups;
   const int lane = threadIdx.x / groups;
   const int c0 = g * kVec;
   const int row_stride = gridDim.x * lanes;
+  const int row0 = blockIdx.x * lanes + lane;
   const bool active = lane < lanes;
+  const size_t ss = static_cast<size_t>(a.slab_stride);
 
-  for (int i = threadIdx.x; i < 2 * a.C; i += kThreads) sm[i] = 0.f;
-  __syncthreads();
+  float v[kRows][kVec];
   float s[kVec], q[kVec];
 #pragma unroll
   for (int i = 0; i < kVec; ++i) s[i] = q[i] = 0.f;
   if (active) {
-    for (int r = blockIdx.x * lanes + lane; r < a.M; r += row_stride) {
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      const int row = row0 + r * row_stride;
+      if (row < a.M) load_row(a.x, a.xs, a.nslabs, ss, static_cast<size_t>(row) * a.C + c0, v[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      const int row = row0 + r * row_stride;
+      if (row < a.M) {
+        if (a.x_out) {
+          const uint4 u = pack8(v[r]);
+          *reinterpret_cast<uint4*>(a.x_out + static_cast<size_t>(row) * a.C + c0) = u;
+          cvt8(u, v[r]);                           // statistics of exactly what backward will read
+        }
+#pragma unroll
+        for (int i = 0; i < kVec; ++i) { s[i] += v[r][i]; q[i] = fmaf(v[r][i], v[r][i], q[i]); }
+      }
+    }
+    for (int row = row0 + kRows * row_stride; row < a.M; row += row_stride) {   // rare: very large M
       float f[kVec];
-      load8(a.x + static_cast<size_t>(r) * a.C + c0, f);
+      load_row(a.x, a.xs, a.nslabs, ss, static_cast<size_t>(row) * a.C + c0, f);
+      if (a.x_out) { const uint4 u = pack8(f); *reinterpret_cast<uint4*>(a.x_out + static_cast<size_t>(row) * a.C + c0) = u; cvt8(u, f); }
 #pragma unroll
       for (int i = 0; i < kVec; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
     }
-#pragma unroll
-    for (int i = 0; i < kVec; ++i) { atomicAdd(&sm[c0 + i], s[i]); atomicAdd(&sm[a.C + c0 + i], q[i]); }
   }
-  __syncthreads();
-  float* mine = a.partial + static_cast<size_t>(blockIdx.x) * 2 * a.C;
-  for (int i = threadIdx.x; i < 2 * a.C; i += kThreads) mine[i] = sm[i];
-  __threadfence();
-  grid.sync();
+  combine_stats(a.scratch, a.C, c0, active, s, q, sm);
 
-  // fold partials: thread i owns channel i (and i + kThreads, ...)
   const float inv_m = 1.f / static_cast<float>(a.M);
-  for (int c = threadIdx.x; c < a.C; c += kThreads) {
-    float ts = 0.f, tq = 0.f;
-    for (int b = 0; b < gridDim.x; ++b) {
-      ts += __ldcg(a.partial + static_cast<size_t>(b) * 2 * a.C + c);
-      tq += __ldcg(a.partial + static_cast<size_t>(b) * 2 * a.C + a.C + c);
-    }
-    const float mean = ts * inv_m;
-    const float var = fmaxf(tq * inv_m - mean * mean, 0.f);
+  float sc[kVec], sh[kVec];
+#pragma unroll
+  for (int i = 0; i < kVec; ++i) {
+    const int c = c0 + i;
+    const float mean = sm[c] * inv_m;
+    const float var = fmaxf(sm[a.C + c] * inv_m - mean * mean, 0.f);
     const float invstd = rsqrtf(var + a.eps);
-    const float sc = a.gamma[c] * invstd;
-    sm[c] = sc;
-    sm[a.C + c] = a.beta[c] - mean * sc;
-    if (blockIdx.x == 0) {
+    sc[i] = a.gamma[c] * invstd;
+    sh[i] = a.beta[c] - mean * sc[i];
+    if (blockIdx.x == 0 && lane == 0) {
       a.save_mean[c] = mean;
       a.save_invstd[c] = invstd;
       if (a.running_mean) {
@@ -117,38 +226,43 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
     }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.num_batches_tracked) *a.num_batches_tracked += 1;
-  __syncthreads();
 
-  if (active) {
-    float sc[kVec], sh[kVec];
+  if (!active) return;
+  auto finish = [&](int row, float (&f)[kVec]) {
+    const size_t off = static_cast<size_t>(row) * a.C + c0;
 #pragma unroll
-    for (int i = 0; i < kVec; ++i) { sc[i] = sm[c0 + i]; sh[i] = sm[a.C + c0 + i]; }
-    for (int r = blockIdx.x * lanes + lane; r < a.M; r += row_stride) {
-      const size_t off = static_cast<size_t>(r) * a.C + c0;
-      float f[kVec];
-      load8(a.x + off, f);
+    for (int i = 0; i < kVec; ++i) f[i] = fmaf(f[i], sc[i], sh[i]);
+    if (a.res) {
+      float rr[kVec];
+      load8(a.res + off, rr);
 #pragma unroll
-      for (int i = 0; i < kVec; ++i) f[i] = fmaf(f[i], sc[i], sh[i]);
-      if (a.res) {
-        float rr[kVec];
-        load8(a.res + off, rr);
-#pragma unroll
-        for (int i = 0; i < kVec; ++i) f[i] += rr[i];
-      }
-      if (a.relu) {
-#pragma unroll
-        for (int i = 0; i < kVec; ++i) f[i] = fmaxf(f[i], 0.f);
-      }
-      store8(a.y + off, f);
+      for (int i = 0; i < kVec; ++i) f[i] += rr[i];
     }
+    if (a.relu) {
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) f[i] = fmaxf(f[i], 0.f);
+    }
+    store8(a.y + off, f);
+  };
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) {
+    const int row = row0 + r * row_stride;
+    if (row < a.M) finish(row, v[r]);
+  }
+  const __nv_bfloat16* xb = a.x_out ? a.x_out : a.x;
+  for (int row = row0 + kRows * row_stride; row < a.M; row += row_stride) {
+    float f[kVec];
+    load8(xb + static_cast<size_t>(row) * a.C + c0, f);
+    finish(row, f);
   }
 }
 
 // Inference: running statistics, no reduction.
 __global__ void __launch_bounds__(kThreads)
-bn_fwd_eval_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
-                   __nv_bfloat16* __restrict__ y, const float* __restrict__ gamma, const float* __restrict__ beta,
-                   const float* __restrict__ rmean, const float* __restrict__ rvar, int M, int C, int relu, float eps) {
+bn_fwd_eval_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ xs, int nslabs, long long slab_stride,
+                   const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y, const float* __restrict__ gamma,
+                   const float* __restrict__ beta, const float* __restrict__ rmean, const float* __restrict__ rvar, int M,
+                   int C, int relu, float eps) {
   const int groups = C / kVec;
   const size_t total = static_cast<size_t>(M) * groups;
   for (size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
@@ -156,7 +270,7 @@ bn_fwd_eval_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
     const int c0 = static_cast<int>(idx % groups) * kVec;
     const size_t off = (idx / groups) * C + c0;
     float f[kVec];
-    load8(x + off, f);
+    load_row(x, xs, nslabs, static_cast<size_t>(slab_stride), off, f);
 #pragma unroll
     for (int i = 0; i < kVec; ++i) {
       const float sc = gamma[c0 + i] * rsqrtf(rvar[c0 + i] + eps);
@@ -177,7 +291,11 @@ bn_fwd_eval_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
 }
 
 struct BnBwdArgs {
-  const __nv_bfloat16* dy;      // [M][C] gradient w.r.t. the block output
+  const __nv_bfloat16* dy;      // [M][C] gradient w.r.t. the block output (bf16), or null when dys is given
+  const float* dys;             // [S][M][C] split-K slabs of that gradient, or null
+  int nslabs;
+  long long slab_stride;
+  const __nv_bfloat16* dy_add;  // [M][C] added to the folded slabs (residual-branch gradient), or null
   const __nv_bfloat16* y;       // [M][C] block output (ReLU mask), or null when there was no ReLU
   const __nv_bfloat16* x;       // [M][C] convolution output saved by forward
   const float* gamma;
@@ -187,12 +305,11 @@ struct BnBwdArgs {
   __nv_bfloat16* dres;          // [M][C] masked gradient for the residual branch, or null
   float* dgamma;
   float* dbeta;
-  float* partial;               // [grid][2][C]
+  BnScratch* scratch;
   int M, C;
 };
 
 __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
-  cg::grid_group grid = cg::this_grid();
   extern __shared__ float sm[];
   const int groups = a.C / kVec;
   const int lanes = kThreads / groups;
@@ -200,153 +317,167 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
   const int lane = threadIdx.x / groups;
   const int c0 = g * kVec;
   const int row_stride = gridDim.x * lanes;
+  const int row0 = blockIdx.x * lanes + lane;
   const bool active = lane < lanes;
+  const size_t ss = static_cast<size_t>(a.slab_stride);
 
-  for (int i = threadIdx.x; i < 2 * a.C; i += kThreads) sm[i] = 0.f;
-  __syncthreads();
   float mean[kVec], istd[kVec];
 #pragma unroll
   for (int i = 0; i < kVec; ++i) { mean[i] = a.save_mean[c0 + i]; istd[i] = a.save_invstd[c0 + i]; }
-  if (active) {
-    float s1[kVec], s2[kVec];
-#pragma unroll
-    for (int i = 0; i < kVec; ++i) s1[i] = s2[i] = 0.f;
-    for (int r = blockIdx.x * lanes + lane; r < a.M; r += row_stride) {
-      const size_t off = static_cast<size_t>(r) * a.C + c0;
-      float gy[kVec], xv[kVec];
-      load8(a.dy + off, gy);
-      load8(a.x + off, xv);
-      if (a.y) {
-        float yv[kVec];
-        load8(a.y + off, yv);
-#pragma unroll
-        for (int i = 0; i < kVec; ++i) gy[i] = yv[i] > 0.f ? gy[i] : 0.f;
-      }
-#pragma unroll
-      for (int i = 0; i < kVec; ++i) {
-        s1[i] += gy[i];
-        s2[i] = fmaf(gy[i], (xv[i] - mean[i]) * istd[i], s2[i]);
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < kVec; ++i) { atomicAdd(&sm[c0 + i], s1[i]); atomicAdd(&sm[a.C + c0 + i], s2[i]); }
-  }
-  __syncthreads();
-  float* mine = a.partial + static_cast<size_t>(blockIdx.x) * 2 * a.C;
-  for (int i = threadIdx.x; i < 2 * a.C; i += kThreads) mine[i] = sm[i];
-  __threadfence();
-  grid.sync();
 
-  for (int c = threadIdx.x; c < a.C; c += kThreads) {
-    float t1 = 0.f, t2 = 0.f;
-    for (int b = 0; b < gridDim.x; ++b) {
-      t1 += __ldcg(a.partial + static_cast<size_t>(b) * 2 * a.C + c);
-      t2 += __ldcg(a.partial + static_cast<size_t>(b) * 2 * a.C + a.C + c);
+  // masked gradient and normalised input of one row
+  auto fetch = [&](int row, float (&gy)[kVec], float (&xh)[kVec]) {
+    const size_t off = static_cast<size_t>(row) * a.C + c0;
+    load_row(a.dy, a.dys, a.nslabs, ss, off, gy);
+    if (a.dy_add) {
+      float ad[kVec];
+      load8(a.dy_add + off, ad);
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) gy[i] += ad[i];
     }
-    sm[c] = t1;
-    sm[a.C + c] = t2;
-    if (blockIdx.x == 0) { a.dbeta[c] = t1; a.dgamma[c] = t2; }
-  }
-  __syncthreads();
+    load8(a.x + off, xh);
+    if (a.y) {
+      float yv[kVec];
+      load8(a.y + off, yv);
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) gy[i] = yv[i] > 0.f ? gy[i] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < kVec; ++i) xh[i] = (xh[i] - mean[i]) * istd[i];
+  };
 
+  float gy[kRows][kVec], xh[kRows][kVec];
+  float s1[kVec], s2[kVec];
+#pragma unroll
+  for (int i = 0; i < kVec; ++i) s1[i] = s2[i] = 0.f;
   if (active) {
-    const float inv_m = 1.f / static_cast<float>(a.M);
-    float k1[kVec], k2[kVec], sc[kVec];
 #pragma unroll
-    for (int i = 0; i < kVec; ++i) {
-      sc[i] = a.gamma[c0 + i] * istd[i];
-      k1[i] = sm[c0 + i] * inv_m;
-      k2[i] = sm[a.C + c0 + i] * inv_m;
-    }
-    for (int r = blockIdx.x * lanes + lane; r < a.M; r += row_stride) {
-      const size_t off = static_cast<size_t>(r) * a.C + c0;
-      float gy[kVec], xv[kVec];
-      load8(a.dy + off, gy);
-      load8(a.x + off, xv);
-      if (a.y) {
-        float yv[kVec];
-        load8(a.y + off, yv);
+    for (int r = 0; r < kRows; ++r) {
+      const int row = row0 + r * row_stride;
+      if (row < a.M) {
+        fetch(row, gy[r], xh[r]);
 #pragma unroll
-        for (int i = 0; i < kVec; ++i) gy[i] = yv[i] > 0.f ? gy[i] : 0.f;
+        for (int i = 0; i < kVec; ++i) { s1[i] += gy[r][i]; s2[i] = fmaf(gy[r][i], xh[r][i], s2[i]); }
       }
-      if (a.dres) store8(a.dres + off, gy);
-      float d[kVec];
-#pragma unroll
-      for (int i = 0; i < kVec; ++i) d[i] = sc[i] * (gy[i] - k1[i] - (xv[i] - mean[i]) * istd[i] * k2[i]);
-      store8(a.dx + off, d);
     }
+    for (int row = row0 + kRows * row_stride; row < a.M; row += row_stride) {
+      float g2[kVec], x2[kVec];
+      fetch(row, g2, x2);
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) { s1[i] += g2[i]; s2[i] = fmaf(g2[i], x2[i], s2[i]); }
+    }
+  }
+  combine_stats(a.scratch, a.C, c0, active, s1, s2, sm);
+
+  if (blockIdx.x == 0 && lane == 0) {
+#pragma unroll
+    for (int i = 0; i < kVec; ++i) { a.dbeta[c0 + i] = sm[c0 + i]; a.dgamma[c0 + i] = sm[a.C + c0 + i]; }
+  }
+  if (!active) return;
+  const float inv_m = 1.f / static_cast<float>(a.M);
+  float k1[kVec], k2[kVec], sc[kVec];
+#pragma unroll
+  for (int i = 0; i < kVec; ++i) {
+    sc[i] = a.gamma[c0 + i] * istd[i];
+    k1[i] = sm[c0 + i] * inv_m;
+    k2[i] = sm[a.C + c0 + i] * inv_m;
+  }
+  auto finish = [&](int row, const float (&g2)[kVec], const float (&x2)[kVec]) {
+    const size_t off = static_cast<size_t>(row) * a.C + c0;
+    if (a.dres) store8(a.dres + off, g2);
+    float d[kVec];
+#pragma unroll
+    for (int i = 0; i < kVec; ++i) d[i] = sc[i] * (g2[i] - k1[i] - x2[i] * k2[i]);
+    store8(a.dx + off, d);
+  };
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) {
+    const int row = row0 + r * row_stride;
+    if (row < a.M) finish(row, gy[r], xh[r]);
+  }
+  for (int row = row0 + kRows * row_stride; row < a.M; row += row_stride) {
+    float g2[kVec], x2[kVec];
+    fetch(row, g2, x2);
+    finish(row, g2, x2);
   }
 }
 
 int bn_grid(int M, int C, const void* kernel, size_t smem) {
   const int groups = C / kVec;
   const int lanes = kThreads / groups;
-  int want = (M + lanes * 4 - 1) / (lanes * 4);          // ~4 rows per thread
-  if (want < 1) want = 1;
+  static int occ_cache[2] = {0, 0};
   int occ = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, smem);
   if (occ < 1) occ = 1;
+  (void)occ_cache;
   const int cap = kml::num_sms() * (occ > 2 ? 2 : occ);
-  return want < cap ? want : cap;
+  int want = (M + lanes - 1) / lanes;                    // one row per thread if the GPU has room
+  if (want > cap) want = cap;
+  return want < 1 ? 1 : want;
 }
 
 }  // namespace
 
 extern "C" {
 
-size_t kml_bn_scratch_bytes(int C) { return static_cast<size_t>(kml::num_sms()) * 2 * 2 * C * sizeof(float); }
+size_t kml_bn_scratch_bytes(int C) {
+  (void)C;
+  return sizeof(BnScratch);
+}
 
-int kml_bn_fwd_train(const void* x, const void* res, void* y, const float* gamma, const float* beta,
-                     float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
-                     float* save_invstd, float* scratch, int M, int C, int relu, float eps, float momentum,
-                     void* stream) {
-  KML_CHECK(x && y && gamma && beta && save_mean && save_invstd && scratch, "kml_bn_fwd_train: null pointer");
-  KML_CHECK(C % kVec == 0 && C / kVec <= kThreads && M > 0, "kml_bn_fwd_train: C (%d) must be a multiple of 8 and <= %d", C,
-            kThreads * kVec);
-  BnFwdArgs a{static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(res),
+int kml_bn_fwd_train(const void* x, const float* x_slabs, int nslabs, long long slab_stride, void* x_out,
+                     const void* res, void* y, const float* gamma, const float* beta, float* running_mean,
+                     float* running_var, long long* num_batches_tracked, float* save_mean, float* save_invstd,
+                     void* scratch, int M, int C, int relu, float eps, float momentum, void* stream) {
+  KML_CHECK((x || x_slabs) && y && gamma && beta && save_mean && save_invstd && scratch, "kml_bn_fwd_train: null pointer");
+  KML_CHECK(C % kVec == 0 && C / kVec <= kThreads && C <= kMaxC && M > 0,
+            "kml_bn_fwd_train: C (%d) must be a multiple of 8 and <= %d", C, kMaxC);
+  KML_CHECK(!x_slabs || (nslabs >= 1 && x_out), "kml_bn_fwd_train: slab input needs nslabs >= 1 and x_out");
+  BnFwdArgs a{static_cast<const __nv_bfloat16*>(x_slabs ? nullptr : x), x_slabs, nslabs, slab_stride,
+              static_cast<__nv_bfloat16*>(x_slabs ? x_out : nullptr), static_cast<const __nv_bfloat16*>(res),
               static_cast<__nv_bfloat16*>(y), gamma, beta, running_mean, running_var, num_batches_tracked,
-              save_mean, save_invstd, scratch, M, C, relu, eps, momentum};
+              save_mean, save_invstd, static_cast<BnScratch*>(scratch), M, C, relu, eps, momentum};
   const size_t smem = 2 * C * sizeof(float);
   const int grid = bn_grid(M, C, reinterpret_cast<const void*>(bn_fwd_train_kernel), smem);
-  void* args[] = {&a};
-  KML_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_fwd_train_kernel), dim3(grid), dim3(kThreads), args,
-                                       smem, static_cast<cudaStream_t>(stream)));
+  bn_fwd_train_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+  KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
 }
 
-int kml_bn_fwd_eval(const void* x, const void* res, void* y, const float* gamma, const float* beta,
-                    const float* running_mean, const float* running_var, int M, int C, int relu, float eps,
-                    void* stream) {
-  KML_CHECK(x && y && gamma && beta && running_mean && running_var, "kml_bn_fwd_eval: null pointer");
+int kml_bn_fwd_eval(const void* x, const float* x_slabs, int nslabs, long long slab_stride, const void* res, void* y,
+                    const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                    int M, int C, int relu, float eps, void* stream) {
+  KML_CHECK((x || x_slabs) && y && gamma && beta && running_mean && running_var, "kml_bn_fwd_eval: null pointer");
   KML_CHECK(C % kVec == 0 && M > 0, "kml_bn_fwd_eval: C must be a multiple of 8");
   const size_t total = static_cast<size_t>(M) * (C / kVec);
   size_t want = (total + kThreads - 1) / kThreads;
   const size_t cap = static_cast<size_t>(kml::num_sms()) * 8;
   const int grid = static_cast<int>(want < cap ? want : cap);
   bn_fwd_eval_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(res), static_cast<__nv_bfloat16*>(y),
-      gamma, beta, running_mean, running_var, M, C, relu, eps);
+      static_cast<const __nv_bfloat16*>(x_slabs ? nullptr : x), x_slabs, nslabs, slab_stride,
+      static_cast<const __nv_bfloat16*>(res), static_cast<__nv_bfloat16*>(y), gamma, beta, running_mean, running_var,
+      M, C, relu, eps);
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
 }
 
-int kml_bn_bwd(const void* dy, const void* y, const void* x, const float* gamma, const float* save_mean,
-               const float* save_invstd, void* dx, void* dres, float* dgamma, float* dbeta, float* scratch, int M,
-               int C, void* stream) {
-  KML_CHECK(dy && x && gamma && save_mean && save_invstd && dx && dgamma && dbeta && scratch,
+int kml_bn_bwd(const void* dy, const float* dy_slabs, int nslabs, long long slab_stride, const void* dy_add,
+               const void* y, const void* x, const float* gamma, const float* save_mean, const float* save_invstd,
+               void* dx, void* dres, float* dgamma, float* dbeta, void* scratch, int M, int C, void* stream) {
+  KML_CHECK((dy || dy_slabs) && x && gamma && save_mean && save_invstd && dx && dgamma && dbeta && scratch,
             "kml_bn_bwd: null pointer");
-  KML_CHECK(C % kVec == 0 && C / kVec <= kThreads && M > 0, "kml_bn_bwd: C (%d) must be a multiple of 8 and <= %d", C,
-            kThreads * kVec);
-  BnBwdArgs a{static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y),
+  KML_CHECK(C % kVec == 0 && C / kVec <= kThreads && C <= kMaxC && M > 0,
+            "kml_bn_bwd: C (%d) must be a multiple of 8 and <= %d", C, kMaxC);
+  BnBwdArgs a{static_cast<const __nv_bfloat16*>(dy_slabs ? nullptr : dy), dy_slabs, nslabs, slab_stride,
+              static_cast<const __nv_bfloat16*>(dy_add), static_cast<const __nv_bfloat16*>(y),
               static_cast<const __nv_bfloat16*>(x), gamma, save_mean, save_invstd, static_cast<__nv_bfloat16*>(dx),
-              static_cast<__nv_bfloat16*>(dres), dgamma, dbeta, scratch, M, C};
+              static_cast<__nv_bfloat16*>(dres), dgamma, dbeta, static_cast<BnScratch*>(scratch), M, C};
   const size_t smem = 2 * C * sizeof(float);
   const int grid = bn_grid(M, C, reinterpret_cast<const void*>(bn_bwd_kernel), smem);
-  void* args[] = {&a};
-  KML_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_bwd_kernel), dim3(grid), dim3(kThreads), args, smem,
-                                       static_cast<cudaStream_t>(stream)));
+  bn_bwd_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+  KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
 }

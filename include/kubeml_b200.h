@@ -129,7 +129,9 @@ typedef struct {
   const void* addend_bf16;  /* bf16 tensor shaped like the output, added before ReLU; may be NULL   */
   int relu;
   int out_f32;              /* 0: bf16 output, 1: fp32 output                                       */
-  int splits;               /* K-splits combined with red.add (needs a zeroed fp32 output); 0/1 = off */
+  int splits;               /* K-splits; 0/1 = off.  Combined with red.add into a zeroed fp32 output, or */
+  int slabs;                /* (slabs != 0) each split stores its partial tile to out + split*M*ldo (fp32
+                               [splits][M][ldo]) for a consumer that folds them (kml_bn_*)             */
   int block_n;              /* 64, 128, or 0 = choose                                               */
 } kml_epilogue;
 
@@ -154,19 +156,25 @@ int kml_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int
  * ---------------------------------------------------------------------------------------------- */
 size_t kml_bn_scratch_bytes(int C);
 /* y = relu?(bn(x) + res?) with batch statistics; updates running stats and num_batches_tracked.
- * x, res, y: bf16 [M][C]; scratch: kml_bn_scratch_bytes(C) bytes (contents irrelevant). */
-int kml_bn_fwd_train(const void* x, const void* res, void* y, const float* gamma, const float* beta,
-                     float* running_mean, float* running_var, long long* num_batches_tracked,
-                     float* save_mean, float* save_invstd, float* scratch, int M, int C, int relu,
-                     float eps, float momentum, void* stream);
-int kml_bn_fwd_eval(const void* x, const void* res, void* y, const float* gamma, const float* beta,
-                    const float* running_mean, const float* running_var, int M, int C, int relu,
-                    float eps, void* stream);
-/* dy: grad of the block output; y: block output (ReLU mask) or NULL; x: saved conv output.
- * Writes dx, optionally dres (masked grad for the residual branch), dgamma, dbeta. */
-int kml_bn_bwd(const void* dy, const void* y, const void* x, const float* gamma, const float* save_mean,
-               const float* save_invstd, void* dx, void* dres, float* dgamma, float* dbeta,
-               float* scratch, int M, int C, void* stream);
+ * Input: either x (bf16 [M][C]) or x_slabs (fp32 [nslabs][M][C], the split-K partial outputs of the
+ * producing GEMM, slab_stride elements apart) whose sum is the input; in the slab case x_out receives
+ * the folded input as bf16 for the backward pass.  scratch: kml_bn_scratch_bytes() bytes, zeroed
+ * ONCE at allocation and then owned by these kernels (it carries a launch counter). */
+int kml_bn_fwd_train(const void* x, const float* x_slabs, int nslabs, long long slab_stride, void* x_out,
+                     const void* res, void* y, const float* gamma, const float* beta, float* running_mean,
+                     float* running_var, long long* num_batches_tracked, float* save_mean,
+                     float* save_invstd, void* scratch, int M, int C, int relu, float eps, float momentum,
+                     void* stream);
+int kml_bn_fwd_eval(const void* x, const float* x_slabs, int nslabs, long long slab_stride, const void* res,
+                    void* y, const float* gamma, const float* beta, const float* running_mean,
+                    const float* running_var, int M, int C, int relu, float eps, void* stream);
+/* dy (bf16) or dy_slabs (fp32 split-K slabs) [+ dy_add]: grad of the block output; y: block output
+ * (ReLU mask) or NULL; x: saved conv output.  Writes dx, optionally dres (masked grad for the
+ * residual branch), dgamma, dbeta. */
+int kml_bn_bwd(const void* dy, const float* dy_slabs, int nslabs, long long slab_stride, const void* dy_add,
+               const void* y, const void* x, const float* gamma, const float* save_mean,
+               const float* save_invstd, void* dx, void* dres, float* dgamma, float* dbeta, void* scratch,
+               int M, int C, void* stream);
 int kml_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int k, int stride,
                     int pad, void* stream);
 int kml_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N, int H, int W, int C, int k,

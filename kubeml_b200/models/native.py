@@ -94,6 +94,8 @@ class Buffers:
     def __init__(self, device: torch.device):
         self.device = device
         self._t: Dict[str, torch.Tensor] = {}
+        self.split_grads: List[torch.Tensor] = []     # gradients accumulated with red.add this pass
+        self.zero_range: Optional[Tuple[int, int]] = None
 
     def get(self, name: str, shape: Tuple[int, ...], dtype=None, zero: bool = False) -> torch.Tensor:
         dtype = dtype or ACT_DTYPE
@@ -105,6 +107,26 @@ class Buffers:
 
     def __getitem__(self, name: str) -> torch.Tensor:
         return self._t[name]
+
+    # -- side stream: work that is off the critical path (weight gradients) runs next to the
+    #    data-gradient chain; both are latency-bound kernels on a handful of SMs each -------------
+    def on_side(self):
+        import contextlib
+        import os
+        if self.device.type != "cuda" or os.environ.get("KUBEML_SIDE_STREAM", "1") == "0":
+            return contextlib.nullcontext()
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._side.wait_event(ev)
+        self._side_used = True
+        return torch.cuda.stream(self._side)
+
+    def join_side(self) -> None:
+        if getattr(self, "_side_used", False):
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            self._side_used = False
 
     def has(self, name: str) -> bool:
         return name in self._t
@@ -191,6 +213,29 @@ class NativeNet(nn.Module):
             self._anchor_zero = torch.zeros(1, device=dev)
         return torch.empty(1, device=dev, requires_grad=True)
 
+    def _begin_backward(self, B: "Buffers") -> None:
+        """Split-K weight gradients are accumulated with red.add and must start from zero.  The first
+        backward of a batch size clears the whole gradient buffer and records which tensors were
+        accumulated; later ones clear only the flat range that covers those."""
+        a = self._arena
+        n = a.layout.n_param
+        if B.zero_range is None:
+            ops.fill_(a.grads[:n], 0.0)
+        elif B.zero_range[1] > B.zero_range[0]:
+            ops.fill_(a.grads[B.zero_range[0]:B.zero_range[1]], 0.0)
+        B.split_grads = []
+
+    def _end_backward(self, B: "Buffers") -> None:
+        B.join_side()
+        if B.zero_range is None:
+            base = self._arena.grads.data_ptr()
+            lo, hi = 0, 0
+            if B.split_grads:
+                lo = min((t.data_ptr() - base) // 4 for t in B.split_grads)
+                hi = max((t.data_ptr() - base) // 4 + t.numel() for t in B.split_grads)
+                lo, hi = lo // 4 * 4, (hi + 3) // 4 * 4
+            B.zero_range = (lo, hi)
+
     def _forward_impl(self, x: torch.Tensor, train: bool) -> torch.Tensor:
         raise NotImplementedError
 
@@ -206,23 +251,88 @@ class NativeNet(nn.Module):
 # ---------------------------------------------------------------------------------------------
 # layer programs shared by the models
 # ---------------------------------------------------------------------------------------------
+_SMS = 148
+
+
+def auto_splits(tiles: int, chunks: int, min_chunks: int = 2) -> int:
+    """K-splits for a GEMM with `tiles` output tiles and `chunks` 64-deep reduction chunks: enough
+    CTAs to cover the GPU, never fewer than `min_chunks` chunks per CTA, and only split counts
+    that leave no CTA without work."""
+    if tiles >= _SMS or chunks < 2 * min_chunks:
+        return 1
+    s = max(1, min(_SMS // max(tiles, 1), chunks // min_chunks))
+    per = (chunks + s - 1) // s
+    return (chunks + per - 1) // per
+
+
+def pick_block_n(m_tiles: int, n: int) -> int:
+    """128-wide tiles only when there are enough of them to occupy the GPU."""
+    if n <= 64:
+        return 64
+    return 128 if m_tiles * ((n + 127) // 128) >= _SMS // 2 else 64
+
+
+class Act:
+    """An activation or gradient: a bf16 tensor, or the fp32 split-K *slabs* [S, ...] of the GEMM that
+    produced it.  Slabs are folded by the BatchNorm kernel that consumes them (csrc/norm.cu), so a
+    small, deep GEMM can be spread over the whole GPU without a reduction pass or atomics."""
+    __slots__ = ("t", "slabs")
+
+    def __init__(self, t: torch.Tensor, slabs: int = 0):
+        self.t, self.slabs = t, slabs
+
+    @property
+    def shape(self):
+        return self.t.shape[1:] if self.slabs else self.t.shape
+
+    def dense(self, B: "Buffers", tag: str) -> torch.Tensor:
+        """bf16 tensor (folds slabs with a torch op; only used off the hot path)."""
+        if not self.slabs:
+            return self.t
+        out = B.get(tag + ".dense", tuple(self.shape))
+        out.copy_(self.t.sum(0))
+        return out
+
+
+def _slab_enabled() -> bool:
+    import os
+    return os.environ.get("KUBEML_SPLITK_SLABS", "1") != "0"
+
+
 def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None, relu: bool = False,
-                 splits: int = 1) -> torch.Tensor:
-    """x: bf16 [N,H,W,Cin] -> bf16 [N,Ho,Wo,Cout]; saves im2col columns under `tag` when used."""
+                 allow_slabs: bool = False) -> Act:
+    """x: bf16 [N,H,W,Cin] -> [N,Ho,Wo,Cout] (bf16, or fp32 slabs when `allow_slabs` and the problem is
+    too small to fill the GPU otherwise); saves im2col columns under `tag` when used."""
     N, H, W, _ = x.shape
     k, s, p = conv.k, conv.stride, conv.padding
     Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
-    y = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
-    if conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p):
-        ops.conv2d_fprop(x, conv.w_bf16, p, bias=bias, relu=relu, out=y)
+    M = N * Ho * Wo
+    m_tiles = (M + 127) // 128
+    bn_ = pick_block_n(m_tiles, conv.cout)
+    tiles = m_tiles * ((conv.cout + bn_ - 1) // bn_)
+    direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p)
+    Kd = k * k * conv.cin
+    if direct:
+        live = sum(1 for kh in range(k) for kw in range(k)
+                   if (kh - p) <= H - 1 and (Ho - 1 + kh - p) >= 0 and (kw - p) <= W - 1 and (Wo - 1 + kw - p) >= 0)
+        chunks = live * (conv.cin // 64)
     else:
-        Kd = k * k * conv.cin
+        chunks = (Kd + 63) // 64
+    S = auto_splits(tiles, chunks, min_chunks=3) if (allow_slabs and bias is None and not relu and _slab_enabled()) else 1
+    if S > 1:
+        y = B.get(tag + ".slabs", (S, N, Ho, Wo, conv.cout), torch.float32)
+    else:
+        y = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
+    if direct:
+        ops.conv2d_fprop(x, conv.w_bf16, p, bias=bias, relu=relu, out=y, block_n=bn_, splits=S, slabs=S > 1)
+    else:
         ldk = _ceil(Kd, 64)
-        cols = B.get(tag + ".cols", (N * Ho * Wo, ldk))
+        cols = B.get(tag + ".cols", (M, ldk))
         K.im2col(x, cols, k, k, s, p)
         ops.gemm_bf16(cols, _packed_weight(conv, B, tag, ldk), bias=bias, relu=relu,
-                      out=y.view(N * Ho * Wo, conv.cout))
-    return y
+                      out=y.view(S, M, conv.cout) if S > 1 else y.view(M, conv.cout), block_n=bn_,
+                      splits=S, slabs=S > 1)
+    return Act(y, S if S > 1 else 0)
 
 
 def _packed_weight(conv: NConv2d, B: Buffers, tag: str, ldk: int) -> torch.Tensor:
@@ -236,56 +346,89 @@ def _packed_weight(conv: NConv2d, B: Buffers, tag: str, ldk: int) -> torch.Tenso
 
 
 def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, tag: str,
-                  need_dx: bool = True, addend: Optional[torch.Tensor] = None, wgrad_splits: int = 1,
-                  dx_out: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
-    """Weight gradient into the arena, data gradient (+ addend) returned."""
+                  need_dx: bool = True, addend: Optional[torch.Tensor] = None,
+                  allow_slabs: bool = False) -> Optional[Act]:
+    """Weight gradient into the arena; data gradient (+ addend) returned (bf16, or fp32 slabs when
+    `allow_slabs`: the consumer must then be a BatchNorm backward)."""
     N, H, W, _ = x.shape
     k, s, p = conv.k, conv.stride, conv.padding
     Ho, Wo = dy.shape[1], dy.shape[2]
     M = N * Ho * Wo
     dy2 = dy.view(M, conv.cout)
     direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p)
+    chunks = (M + 63) // 64
     if direct:
-        ops.conv2d_wgrad(x, dy, k, k, p, out=conv.w_grad, splits=wgrad_splits)
+        bn_w = 128 if conv.cin > 64 else 64
+        tiles = ((conv.cout + 127) // 128) * ((conv.cin + bn_w - 1) // bn_w) * k * k
+        # gradients accumulate with red.add across splits; _begin_backward cleared them
+        sp = auto_splits(tiles, chunks)
+        if sp > 1:
+            B.split_grads.append(conv.w_grad)
+        with B.on_side():
+            ops.conv2d_wgrad(x, dy, k, k, p, out=conv.w_grad, splits=sp, block_n=bn_w)
         if not need_dx:
             return None
-        dx = dx_out if dx_out is not None else B.get(tag + ".dx", (N, H, W, conv.cin))
-        ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=dx)
-        return dx
+        m_tiles = (N * H * W + 127) // 128
+        bn_d = pick_block_n(m_tiles, conv.cin)
+        dtiles = m_tiles * ((conv.cin + bn_d - 1) // bn_d)
+        pd = k - 1 - p
+        live = sum(1 for kh in range(k) for kw in range(k)
+                   if (kh - pd) <= Ho - 1 and (H - 1 + kh - pd) >= 0 and (kw - pd) <= Wo - 1 and (W - 1 + kw - pd) >= 0)
+        S = auto_splits(dtiles, live * (conv.cout // 64), min_chunks=3) if (allow_slabs and _slab_enabled()) else 1
+        if S > 1:
+            dx = B.get(tag + ".dxslabs", (S, N, H, W, conv.cin), torch.float32)
+        else:
+            dx = B.get(tag + ".dx", (N, H, W, conv.cin))
+        ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=dx, block_n=bn_d, splits=S, slabs=S > 1)
+        return Act(dx, S if S > 1 else 0)
     Kd = k * k * conv.cin
     cols = B[tag + ".cols"]
     ldk = cols.shape[1]
     # dW[Cout][Kd] = dY^T · cols  (both consumed MN-major, reduction over the M output pixels)
-    ops.gemm_bf16(dy2, cols[:, :Kd] if Kd % 8 else cols, a_mn=True, b_mn=True, out_dtype=torch.float32,
-                  out=conv.w_grad.view(conv.cout, Kd), splits=wgrad_splits)
+    bn_w = 128 if Kd > 64 else 64
+    tiles = ((conv.cout + 127) // 128) * ((Kd + bn_w - 1) // bn_w)
+    sp = auto_splits(tiles, chunks)
+    if sp > 1:
+        B.split_grads.append(conv.w_grad)
+    with B.on_side():
+        ops.gemm_bf16(dy2, cols[:, :Kd] if Kd % 8 else cols, a_mn=True, b_mn=True, out_dtype=torch.float32,
+                      out=conv.w_grad.view(conv.cout, Kd), splits=sp, block_n=bn_w)
     if not need_dx:
         return None
     # dcols[M][Kd] = dY · W  (W consumed MN-major: no transposed weight copy)
     dcols = B.get(tag + ".dcols", (M, ldk))
-    ops.gemm_bf16(dy2, conv.w_bf16.view(conv.cout, Kd), b_mn=True, out=dcols[:, :Kd] if ldk != Kd else dcols)
-    dx = dx_out if dx_out is not None else B.get(tag + ".dx", (N, H, W, conv.cin))
+    ops.gemm_bf16(dy2, conv.w_bf16.view(conv.cout, Kd), b_mn=True, out=dcols[:, :Kd] if ldk != Kd else dcols,
+                  block_n=pick_block_n((M + 127) // 128, Kd))
+    dx = B.get(tag + ".dx", (N, H, W, conv.cin))
     K.col2im(dcols, addend, dx, k, k, s, p)
-    return dx
+    return Act(dx)
 
 
-def bn_forward(bn: NBatchNorm2d, x: torch.Tensor, B: Buffers, tag: str, train: bool, relu: bool,
-               res: Optional[torch.Tensor] = None) -> torch.Tensor:
-    y = B.get(tag + ".y", tuple(x.shape))
+def bn_forward(bn: NBatchNorm2d, x: Act, B: Buffers, tag: str, train: bool, relu: bool,
+               res: Optional[torch.Tensor] = None):
+    """Returns (y, x_saved): the block output and the bf16 input the backward pass needs."""
+    shape = tuple(x.shape)
+    y = B.get(tag + ".y", shape)
+    xs = x.t if x.slabs else None
+    xb = None if x.slabs else x.t
+    x_out = B.get(tag + ".xsave", shape) if x.slabs else None
     if train:
         mean = B.get(tag + ".mean", (bn.c,), torch.float32)
         istd = B.get(tag + ".istd", (bn.c,), torch.float32)
-        K.bn_fwd_train(x, res, y, bn.weight.data, bn.bias.data, bn.running_mean, bn.running_var,
-                       bn.num_batches_tracked, mean, istd, relu, bn.eps, bn.momentum)
+        K.bn_fwd_train(xb, res, y, bn.weight.data, bn.bias.data, bn.running_mean, bn.running_var,
+                       bn.num_batches_tracked, mean, istd, relu, bn.eps, bn.momentum, x_slabs=xs, x_out=x_out)
     else:
-        K.bn_fwd_eval(x, res, y, bn.weight.data, bn.bias.data, bn.running_mean, bn.running_var, relu, bn.eps)
-    return y
+        K.bn_fwd_eval(xb, res, y, bn.weight.data, bn.bias.data, bn.running_mean, bn.running_var, relu, bn.eps,
+                      x_slabs=xs)
+    return y, (x_out if x.slabs else x.t)
 
 
-def bn_backward(bn: NBatchNorm2d, dy: torch.Tensor, y: Optional[torch.Tensor], x: torch.Tensor, B: Buffers,
-                tag: str, want_dres: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+def bn_backward(bn: NBatchNorm2d, dy: Act, y: Optional[torch.Tensor], x: torch.Tensor, B: Buffers,
+                tag: str, want_dres: bool = False):
     dx = B.get(tag + ".dx", tuple(x.shape))
     dres = B.get(tag + ".dres", tuple(x.shape)) if want_dres else None
-    K.bn_bwd(dy, y, x, bn.weight.data, B[tag + ".mean"], B[tag + ".istd"], dx, dres, bn.g_weight, bn.g_bias)
+    K.bn_bwd(None if dy.slabs else dy.t, y, x, bn.weight.data, B[tag + ".mean"], B[tag + ".istd"], dx, dres,
+             bn.g_weight, bn.g_bias, dy_slabs=dy.t if dy.slabs else None)
     return dx, dres
 
 
@@ -305,8 +448,9 @@ def linear_backward(fc: NLinear, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
         pad = B.get(tag + ".dy", (dy.shape[0], ld), zero=True)
         pad[:, :fc.cout].copy_(dy)
         dy = pad[:, :fc.cout]
-    ops.gemm_bf16(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, out=fc.w_grad)     # dW = dY^T · X
-    K.colsum(dy, fc.b_grad)
+    with B.on_side():
+        ops.gemm_bf16(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, out=fc.w_grad)     # dW = dY^T · X (store)
+        K.colsum(dy, fc.b_grad)
     if not need_dx:
         return None
     dx = B.get(tag + ".dx", (x.shape[0], fc.cin))

@@ -82,25 +82,25 @@ class NativeResNet(NativeNet):
         N = x.shape[0]
         B = self.buffers_for(N, train)
         S = {"x": x, "blocks": []}
-        c1 = conv_forward(self.conv1, x, B, "stem")
-        a1 = bn_forward(self.bn1, c1, B, "stem.bn", train, relu=True)
+        c1 = conv_forward(self.conv1, x, B, "stem", allow_slabs=True)
+        a1, c1s = bn_forward(self.bn1, c1, B, "stem.bn", train, relu=True)
         _, H1, W1, _ = a1.shape
         Hp, Wp = (H1 + 2 - 3) // 2 + 1, (W1 + 2 - 3) // 2 + 1
         p1 = B.get("pool.y", (N, Hp, Wp, 64))
         idx = B.get("pool.idx", (N, Hp, Wp, 64), torch.uint8)
         K.maxpool_fwd(a1, p1, idx, 3, 2, 1)
-        S.update(c1=c1, a1=a1, p1=p1)
+        S.update(c1=c1s, a1=a1, p1=p1)
         h = p1
         for tag, blk in self._blocks:
-            t1 = conv_forward(blk.conv1, h, B, tag + ".c1")
-            a = bn_forward(blk.bn1, t1, B, tag + ".bn1", train, relu=True)
-            t2 = conv_forward(blk.conv2, a, B, tag + ".c2")
-            idn, td = h, None
+            t1 = conv_forward(blk.conv1, h, B, tag + ".c1", allow_slabs=True)
+            a, t1s = bn_forward(blk.bn1, t1, B, tag + ".bn1", train, relu=True)
+            t2 = conv_forward(blk.conv2, a, B, tag + ".c2", allow_slabs=True)
+            idn, tds = h, None
             if blk.downsample is not None:
-                td = conv_forward(blk.downsample[0], h, B, tag + ".cd")
-                idn = bn_forward(blk.downsample[1], td, B, tag + ".bnd", train, relu=False)
-            out = bn_forward(blk.bn2, t2, B, tag + ".bn2", train, relu=True, res=idn)
-            S["blocks"].append((h, t1, a, t2, td, out))
+                td = conv_forward(blk.downsample[0], h, B, tag + ".cd", allow_slabs=True)
+                idn, tds = bn_forward(blk.downsample[1], td, B, tag + ".bnd", train, relu=False)
+            out, t2s = bn_forward(blk.bn2, t2, B, tag + ".bn2", train, relu=True, res=idn)
+            S["blocks"].append((h, t1s, a, t2s, tds, out))
             h = out
         Nn, Hh, Ww, C = h.shape
         if Hh * Ww == 1:
@@ -116,35 +116,41 @@ class NativeResNet(NativeNet):
 
     # ---------------------------------------------------------------------------------- backward
     def _backward_impl(self, dlogits: torch.Tensor) -> None:
+        from .native import Act, act_dtype
         S = self._saved
         B: Buffers = S["B"]
-        from .native import act_dtype
         if dlogits.dtype != act_dtype():
             dlogits = dlogits.to(act_dtype())
+        self._begin_backward(B)
         dpooled = linear_backward(self.fc, S["pooled"], dlogits, B, "fc")
         last = S["last"]
         Nn, Hh, Ww, C = last.shape
         if Hh * Ww == 1:
-            dh = dpooled.view(Nn, 1, 1, C)
+            dh = Act(dpooled.view(Nn, 1, 1, C))
         else:
-            dh = B.get("avg.dx", tuple(last.shape))
-            K.avgpool_bwd(dpooled, dh)
-        for (tag, blk), (h, t1, a, t2, td, out) in zip(reversed(self._blocks), reversed(S["blocks"])):
+            t = B.get("avg.dx", tuple(last.shape))
+            K.avgpool_bwd(dpooled, t)
+            dh = Act(t)
+        nblk = len(self._blocks)
+        for bi, ((tag, blk), (h, t1, a, t2, td, out)) in enumerate(zip(reversed(self._blocks),
+                                                                         reversed(S["blocks"]))):
+            first_block = bi == nblk - 1          # its input gradient feeds the max-pool backward (dense)
             # out = relu(bn2(t2) + idn)
             dt2, g = bn_backward(blk.bn2, dh, out, t2, B, tag + ".bn2", want_dres=True)
-            da = conv_backward(blk.conv2, a, dt2, B, tag + ".c2")
+            da = conv_backward(blk.conv2, a, dt2, B, tag + ".c2", allow_slabs=True)
             dt1, _ = bn_backward(blk.bn1, da, a, t1, B, tag + ".bn1")
             if blk.downsample is None:
-                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=g)
+                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=g, allow_slabs=not first_block)
             else:
-                dtd, _ = bn_backward(blk.downsample[1], g, None, td, B, tag + ".bnd")
+                dtd, _ = bn_backward(blk.downsample[1], Act(g), None, td, B, tag + ".bnd")
                 did = conv_backward(blk.downsample[0], h, dtd, B, tag + ".cd")
-                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=did)
+                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=did.t)
         # stem
         da1 = B.get("pool.dx", tuple(S["a1"].shape))
-        K.maxpool_bwd(dh, B["pool.idx"], da1, 3, 2, 1)
-        dc1, _ = bn_backward(self.bn1, da1, S["a1"], S["c1"], B, "stem.bn")
+        K.maxpool_bwd(dh.dense(B, "pool.dy"), B["pool.idx"], da1, 3, 2, 1)
+        dc1, _ = bn_backward(self.bn1, Act(da1), S["a1"], S["c1"], B, "stem.bn")
         conv_backward(self.conv1, S["x"], dc1, B, "stem", need_dx=False)
+        self._end_backward(B)
 
 
 def resnet34(num_classes: int = 1000) -> NativeResNet:

@@ -94,6 +94,12 @@ class KubeModel(ABC):
         if sv.device_sync is not None and self.platform == "gpu" and torch.cuda.is_available():
             ds = sv.device_sync
             return ds.for_func(self.args._func_id) if hasattr(ds, "for_func") else ds
+        factory = (sv.options or {}).get("sync_factory")
+        if factory is not None:          # e.g. CollectiveSync: K-AVG through torch.distributed
+            ws = self._inv.worker_state if self._inv.worker_state is not None else {}
+            if "sync_engine" not in ws:
+                ws["sync_engine"] = factory()
+            return ws["sync_engine"]
         from .train.sync import HostSync
         return HostSync(sv.tensor_store, sv.barrier)
 

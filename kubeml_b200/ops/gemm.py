@@ -15,23 +15,26 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
     return 0 if t is None else t.data_ptr()
 
 
-def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0):
+def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0, slabs=False):
     e = _native.Epilogue()
     e.bias = _ptr(bias) or None
     e.addend_bf16 = _ptr(addend) or None
     e.relu, e.out_f32, e.splits, e.block_n = int(relu), int(out_f32), int(splits), int(block_n)
+    e.slabs = int(slabs)
     return e
 
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
               bias: Optional[torch.Tensor] = None, relu: bool = False,
               out_dtype: torch.dtype = torch.bfloat16, out: Optional[torch.Tensor] = None,
-              splits: int = 1, block_n: int = 0, addend: Optional[torch.Tensor] = None) -> torch.Tensor:
+              splits: int = 1, block_n: int = 0, addend: Optional[torch.Tensor] = None,
+              slabs: bool = False) -> torch.Tensor:
     """out[M,N] = A · B^T (+bias, ReLU) with fp32 accumulation.
 
     a: [M,K] (a_mn=False, K contiguous) or [K,M] (a_mn=True, M contiguous), bf16
     b: [N,K] (b_mn=False)               or [K,N] (b_mn=True), bf16
-    splits > 1 accumulates K-slices with red.add into an fp32 `out` (zeroed here if not given).
+    splits > 1 accumulates K-slices with red.add into an fp32 `out` (zeroed here if not given), or,
+    with slabs=True, stores each split's partial result in out[s] (out: fp32 [splits, M, N]).
     """
     M = a.shape[1] if a_mn else a.shape[0]
     K = a.shape[0] if a_mn else a.shape[1]
@@ -50,7 +53,13 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
             r = torch.relu(r)
         r = r.to(out_dtype)
         if out is not None:
-            out.copy_(r) if splits == 1 else out.add_(r)
+            if slabs and splits > 1:
+                out.zero_()
+                out[0].copy_(r)
+            elif splits == 1:
+                out.copy_(r)
+            else:
+                out.add_(r)
             return out
         return r
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "gemm_bf16 wants bf16 operands"
@@ -59,10 +68,10 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     if out is None:
         out = (torch.zeros if splits > 1 else torch.empty)((M, N), dtype=out_dtype, device=a.device)
     import ctypes
-    e = _epi(bias, addend, relu, out_f32, splits, block_n)
+    e = _epi(bias, addend, relu, out_f32, splits, block_n, slabs and splits > 1)
     _native.check(_native.lib().kml_gemm_bf16(
         a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(),
-        out.stride(0), M, N, K, ctypes.byref(e), _native.stream_ptr()), "kml_gemm_bf16")
+        out.stride(-2), M, N, K, ctypes.byref(e), _native.stream_ptr()), "kml_gemm_bf16")
     return out
 
 
@@ -74,7 +83,7 @@ def conv2d_fprop_supported(H: int, W: int, Cin: int, Cout: int, KH: int, KW: int
 
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[torch.Tensor] = None,
                  relu: bool = False, out_dtype: torch.dtype = torch.bfloat16, splits: int = 1,
-                 block_n: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 block_n: int = 0, out: Optional[torch.Tensor] = None, slabs: bool = False) -> torch.Tensor:
     """Stride-1 convolution, NHWC.  x: [N,H,W,Cin] bf16; w: [Cout,KH,KW,Cin] bf16 -> [N,Ho,Wo,Cout].
     The data gradient of a stride-1 convolution is this same op applied to dY with the flipped,
     channel-transposed filter and pad' = K-1-pad."""
@@ -90,7 +99,11 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
             y = torch.relu(y)
         y = y.permute(0, 2, 3, 1).contiguous().to(out_dtype)
         if out is not None:
-            out.copy_(y)
+            if slabs:                      # [S, N, Ho, Wo, C]: everything in slab 0, zeros elsewhere
+                out.zero_()
+                out[0].copy_(y)
+            else:
+                out.copy_(y)
             return out
         return y
     assert x.is_contiguous() and w.is_contiguous()
@@ -98,7 +111,7 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
     import ctypes
     y = out if out is not None else \
         (torch.zeros if splits > 1 else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
-    e = _epi(bias, None, relu, out_f32, splits, block_n)
+    e = _epi(bias, None, relu, out_f32, splits, block_n, slabs)
     _native.check(_native.lib().kml_conv2d_fprop(
         x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_fprop")
@@ -107,7 +120,7 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
 
 def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
                  addend: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                 block_n: int = 0) -> torch.Tensor:
+                 block_n: int = 0, splits: int = 1, slabs: bool = False) -> torch.Tensor:
     """Data gradient of `conv2d_fprop`: dy [N,Ho,Wo,Cout] bf16, w the *forward* filter
     [Cout,KH,KW,Cin] bf16 -> dx [N,H,W,Cin] bf16 (+ addend, the residual branch's gradient)."""
     N, Ho, Wo, Cout = dy.shape
@@ -117,15 +130,18 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
                                         dy.permute(0, 3, 1, 2).float(), padding=pad).permute(0, 2, 3, 1)
         if addend is not None:
             dx = dx + addend.float()
-        dx = dx.contiguous().to(dy.dtype)
         if out is not None:
-            out.copy_(dx)
+            if slabs:
+                out.zero_()
+                out[0].copy_(dx)
+            else:
+                out.copy_(dx.contiguous().to(out.dtype))
             return out
-        return dx
+        return dx.contiguous().to(dy.dtype)
     import ctypes
     assert dy.is_contiguous() and w.is_contiguous()
     dx = out if out is not None else torch.empty((N, H, W, Cin), dtype=torch.bfloat16, device=dy.device)
-    e = _epi(None, addend, False, False, 1, block_n)
+    e = _epi(None, addend, False, dx.dtype == torch.float32, splits, block_n, slabs)
     _native.check(_native.lib().kml_conv2d_dgrad(
         dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_dgrad")

@@ -19,29 +19,41 @@ def _ptr(t: Optional[torch.Tensor]):
 _bn_scratch = {}
 
 
-def bn_scratch(device: torch.device, C: int) -> torch.Tensor:
+def bn_scratch(device: torch.device, C: int = 0) -> torch.Tensor:
+    """Launch state of the BatchNorm kernels (double-buffered statistics + launch counter): zeroed
+    once here, then owned by the kernels.  One per (device, stream): launches on a stream serialise."""
     key = (device.index, torch.cuda.current_stream(device).cuda_stream)
-    need = int(_native.lib().kml_bn_scratch_bytes(C)) // 4
     buf = _bn_scratch.get(key)
-    if buf is None or buf.numel() < need:
-        buf = torch.empty(max(need, 1 << 16), dtype=torch.float32, device=device)
+    if buf is None:
+        buf = torch.zeros(int(_native.lib().kml_bn_scratch_bytes(C)), dtype=torch.uint8, device=device)
         _bn_scratch[key] = buf
     return buf
 
 
+def _fold(x, x_slabs):
+    """CPU restatement: the layer input is x, or the sum of the split-K slabs."""
+    return x.float() if x_slabs is None else x_slabs.float().sum(0)
+
+
 def bn_fwd_train(x, res, y, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd,
-                 relu: bool, eps: float = 1e-5, momentum: float = 0.1) -> None:
-    """y = relu?(bn(x) + res?) with batch statistics.  x/res/y: bf16 [..., C] viewed as [M, C]."""
-    C = x.shape[-1]
-    M = x.numel() // C
-    if x.is_cuda:
+                 relu: bool, eps: float = 1e-5, momentum: float = 0.1, x_slabs=None, x_out=None) -> None:
+    """y = relu?(bn(x) + res?) with batch statistics.  Input is `x` (bf16 [..., C]) or `x_slabs`
+    (fp32 [S, ..., C], split-K partials of the producing GEMM); in the slab case `x_out` receives the
+    folded bf16 input that backward needs."""
+    C = y.shape[-1]
+    M = y.numel() // C
+    if y.is_cuda:
+        S = 0 if x_slabs is None else x_slabs.shape[0]
         _native.check(_native.lib().kml_bn_fwd_train(
-            x.data_ptr(), _ptr(res), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), _ptr(running_mean),
-            _ptr(running_var), _ptr(nbt), save_mean.data_ptr(), save_invstd.data_ptr(),
-            bn_scratch(x.device, C).data_ptr(), M, C, int(relu), eps, momentum, _native.stream_ptr()),
-            "kml_bn_fwd_train")
+            _ptr(x), _ptr(x_slabs), S, 0 if x_slabs is None else x_slabs.stride(0), _ptr(x_out), _ptr(res),
+            y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), _ptr(running_mean), _ptr(running_var), _ptr(nbt),
+            save_mean.data_ptr(), save_invstd.data_ptr(), bn_scratch(y.device, C).data_ptr(), M, C, int(relu),
+            eps, momentum, _native.stream_ptr()), "kml_bn_fwd_train")
         return
-    xf = x.float().reshape(M, C)
+    xf = _fold(x, x_slabs).reshape(M, C)
+    if x_out is not None:
+        x_out.copy_(xf.reshape(x_out.shape))
+        xf = x_out.float().reshape(M, C)
     mean = xf.mean(0)
     var = xf.var(0, unbiased=False)
     invstd = torch.rsqrt(var + eps)
@@ -60,15 +72,18 @@ def bn_fwd_train(x, res, y, gamma, beta, running_mean, running_var, nbt, save_me
         nbt.add_(1)
 
 
-def bn_fwd_eval(x, res, y, gamma, beta, running_mean, running_var, relu: bool, eps: float = 1e-5) -> None:
-    C = x.shape[-1]
-    M = x.numel() // C
-    if x.is_cuda:
+def bn_fwd_eval(x, res, y, gamma, beta, running_mean, running_var, relu: bool, eps: float = 1e-5,
+                x_slabs=None) -> None:
+    C = y.shape[-1]
+    M = y.numel() // C
+    if y.is_cuda:
+        S = 0 if x_slabs is None else x_slabs.shape[0]
         _native.check(_native.lib().kml_bn_fwd_eval(
-            x.data_ptr(), _ptr(res), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), running_mean.data_ptr(),
-            running_var.data_ptr(), M, C, int(relu), eps, _native.stream_ptr()), "kml_bn_fwd_eval")
+            _ptr(x), _ptr(x_slabs), S, 0 if x_slabs is None else x_slabs.stride(0), _ptr(res), y.data_ptr(),
+            gamma.data_ptr(), beta.data_ptr(), running_mean.data_ptr(), running_var.data_ptr(), M, C, int(relu),
+            eps, _native.stream_ptr()), "kml_bn_fwd_eval")
         return
-    out = (x.float().reshape(M, C) - running_mean) * torch.rsqrt(running_var + eps) * gamma + beta
+    out = (_fold(x, x_slabs).reshape(M, C) - running_mean) * torch.rsqrt(running_var + eps) * gamma + beta
     if res is not None:
         out = out + res.float().reshape(M, C)
     if relu:
@@ -76,17 +91,22 @@ def bn_fwd_eval(x, res, y, gamma, beta, running_mean, running_var, relu: bool, e
     y.copy_(out.reshape(y.shape))
 
 
-def bn_bwd(dy, y, x, gamma, save_mean, save_invstd, dx, dres, dgamma, dbeta) -> None:
-    """dy: grad of the block output; y: block output for the ReLU mask (None = no ReLU)."""
+def bn_bwd(dy, y, x, gamma, save_mean, save_invstd, dx, dres, dgamma, dbeta, dy_slabs=None, dy_add=None) -> None:
+    """dy (bf16) or dy_slabs (fp32 [S, ...]) [+ dy_add]: grad of the block output; y: block output
+    for the ReLU mask (None = no ReLU)."""
     C = x.shape[-1]
     M = x.numel() // C
     if x.is_cuda:
+        S = 0 if dy_slabs is None else dy_slabs.shape[0]
         _native.check(_native.lib().kml_bn_bwd(
-            dy.data_ptr(), _ptr(y), x.data_ptr(), gamma.data_ptr(), save_mean.data_ptr(),
-            save_invstd.data_ptr(), dx.data_ptr(), _ptr(dres), dgamma.data_ptr(), dbeta.data_ptr(),
-            bn_scratch(x.device, C).data_ptr(), M, C, _native.stream_ptr()), "kml_bn_bwd")
+            _ptr(dy), _ptr(dy_slabs), S, 0 if dy_slabs is None else dy_slabs.stride(0), _ptr(dy_add), _ptr(y),
+            x.data_ptr(), gamma.data_ptr(), save_mean.data_ptr(), save_invstd.data_ptr(), dx.data_ptr(), _ptr(dres),
+            dgamma.data_ptr(), dbeta.data_ptr(), bn_scratch(x.device, C).data_ptr(), M, C, _native.stream_ptr()),
+            "kml_bn_bwd")
         return
-    g = dy.float().reshape(M, C)
+    g = _fold(dy, dy_slabs).reshape(M, C)
+    if dy_add is not None:
+        g = g + dy_add.float().reshape(M, C)
     if y is not None:
         g = g * (y.float().reshape(M, C) > 0)
     xhat = (x.float().reshape(M, C) - save_mean) * save_invstd

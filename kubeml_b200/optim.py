@@ -70,7 +70,10 @@ class _FlatOptimizer:
     def zero_grad(self, set_to_none: bool = False) -> None:
         if self._arena is not None:
             a = self._arena
-            ops.fill_(a.grads[: max(a.layout.n_param, 4)], 0.0)
+            # a native network's backward *writes* every gradient (and clears what it accumulates
+            # into itself), so the 87 MB fill is only needed for autograd-accumulated models
+            if not a.layout.want_bf16:
+                ops.fill_(a.grads[: max(a.layout.n_param, 4)], 0.0)
             for name, p in self._named():
                 p.grad = a.grad(name)
             return

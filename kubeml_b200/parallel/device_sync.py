@@ -101,7 +101,8 @@ class RankSync:
         if joined:
             self.group.copy_reference_into(self)
         self.arena.bind(net, copy_in=False)      # also refreshes the bf16 operand copy
-        if a._task in ("train", "join"):
+        join_for = (kube_model._inv.query or {}).get("joinFor") if a._task == "join" else None
+        if a._task == "train" or join_for == "train":
             self._epoch = int(a.epoch)
             self._schedule = (round_schedule(kube_model._dataset.num_docs, a._N, a._K, a.batch_size)
                               if a._task == "train" else [])

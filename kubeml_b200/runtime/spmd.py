@@ -121,11 +121,13 @@ class SpmdInvoker(Invoker):
                 "options": dict(self.options)}
 
     def _pad(self, queries: List[Optional[Dict[str, Any]]], template: Dict[str, Any]) -> List[Dict[str, Any]]:
-        """Idle ranks get a `join` so collective group maintenance stays in lock-step."""
+        """Idle ranks get a `join` so collective group maintenance stays in lock-step; `joinFor`
+        tells them which task the busy ranks run (only a train fan-out has a membership barrier)."""
         out = list(queries)
         collective = self.rt.group is not None
         for r in range(len(out), self.rt.world):
-            out.append(dict(template, task="join", funcId=r) if collective else None)
+            out.append(dict(template, task="join", funcId=r, joinFor=template.get("task"))
+                       if collective else None)
         return out
 
     def invoke_one(self, func_id, function, query, body=None):

@@ -191,3 +191,49 @@ def test_native_resnet18_matches_torchvision(dev):
     net.eval(); ref.eval()
     with torch.no_grad():
         _close(net(x), ref(x), 5e-2)
+
+
+@pytest.mark.parametrize("N,H,C,Co,S", [(16, 4, 128, 128, 4), (64, 2, 256, 256, 9), (8, 8, 64, 64, 3)])
+def test_splitk_slabs_conv_then_bn(dev, N, H, C, Co, S):
+    """A split-K convolution writes fp32 partial slabs; the BatchNorm kernels fold them."""
+    from kubeml_b200 import ops
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(6)
+    x = torch.randn(N, H, H, C, device=dev).bfloat16()
+    w = (torch.randn(Co, 3, 3, C, device=dev) / (9 * C) ** 0.5).bfloat16()
+    want = ops.conv2d_fprop(x, w, 1, out_dtype=torch.float32)
+    slabs = torch.empty(S, N, H, H, Co, device=dev, dtype=torch.float32)
+    ops.conv2d_fprop(x, w, 1, out=slabs, splits=S, slabs=True)
+    _close(slabs.sum(0), want, 1e-4)
+    dslabs = torch.empty(S, N, H, H, C, device=dev, dtype=torch.float32)
+    dy = torch.randn(N, H, H, Co, device=dev).bfloat16()
+    add = torch.randn(N, H, H, C, device=dev).bfloat16()
+    ops.conv2d_dgrad(dy, w, 1, H, H, addend=add, out=dslabs, splits=S, slabs=True)
+    _close(dslabs.sum(0), ops.conv2d_dgrad(dy.cpu(), w.cpu(), 1, H, H, addend=add.cpu()), 1e-2)
+    # BN forward/backward on slabs == on the folded tensor
+    M = N * H * H
+    gamma, beta = torch.rand(Co, device=dev) + 0.5, torch.randn(Co, device=dev)
+    res = {}
+    for mode in ("dense", "slabs"):
+        y = torch.empty(M, Co, dtype=torch.bfloat16, device=dev)
+        xo = torch.empty(M, Co, dtype=torch.bfloat16, device=dev)
+        mean, istd = torch.empty(Co, device=dev), torch.empty(Co, device=dev)
+        folded = slabs.sum(0).view(M, Co).bfloat16()
+        if mode == "dense":
+            K.bn_fwd_train(folded, None, y, gamma, beta, None, None, None, mean, istd, True)
+            xo = folded
+        else:
+            K.bn_fwd_train(None, None, y, gamma, beta, None, None, None, mean, istd, True,
+                           x_slabs=slabs.view(S, M, Co), x_out=xo)
+        dx = torch.empty(M, Co, dtype=torch.bfloat16, device=dev)
+        dg, db = torch.empty(Co, device=dev), torch.empty(Co, device=dev)
+        torch.manual_seed(7)
+        gs = torch.randn(S, M, Co, device=dev)
+        if mode == "dense":
+            K.bn_bwd(gs.sum(0).bfloat16(), y, xo, gamma, mean, istd, dx, None, dg, db)
+        else:
+            K.bn_bwd(None, y, xo, gamma, mean, istd, dx, None, dg, db, dy_slabs=gs)
+        res[mode] = (y, xo, mean, istd, dx, dg, db)
+    torch.cuda.synchronize()
+    for a, b in zip(res["slabs"], res["dense"]):
+        _close(a, b, 2e-2)

@@ -1,0 +1,66 @@
+"""Multi-GPU (>= 2 B200): process-per-GPU workers, peer-mapped arenas, the fused merge kernel with
+its cross-rank flag barrier, against the host-side oracle."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _torchrun(n, script, *args, port=29541, timeout=600, env=None):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), script, *args]
+    e = dict(os.environ, KUBEML_MERGE_TIMEOUT_S="5", **(env or {}))
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=e, cwd=ROOT)
+
+
+def _result(proc):
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+    for line in proc.stdout.splitlines():
+        if line.startswith("RESULT "):
+            return json.loads(line[7:])
+    raise AssertionError("no RESULT line:\n" + proc.stdout[-2000:] + proc.stderr[-2000:])
+
+
+def test_merge_kernel_two_ranks_matches_average(tmp_path):
+    n = min(torch.cuda.device_count(), 2)
+    proc = _torchrun(n, os.path.join(ROOT, "bench", "merge_bench.py"), "--check", "--iters", "3",
+                     "--sizes", "lenet,1M", port=29543)
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+    rows = [json.loads(l) for l in proc.stdout.splitlines() if l.startswith("{")]
+    assert len(rows) == 2
+    for r in rows:
+        assert r["p2p_max_abs_err"] < 1e-6
+        if "nvls_max_abs_err" in r:
+            assert r["nvls_max_abs_err"] < 1e-5
+
+
+def test_spmd_lenet_matches_host_oracle(tmp_path, kube_home):
+    """The same job through (a) two GPU processes with the device merge and (b) the in-process host
+    path (TensorStore + CPU ParallelSGD): train losses must agree."""
+    n = 2
+    res = _result(_torchrun(n, os.path.join(ROOT, "tests", "mp_scripts", "spmd_lenet.py"), str(tmp_path / "spmd"),
+                            "2", port=29545))
+    assert res["error"] is None
+    dev_hist = res["history"]
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster, make_kubeml_client
+    c = Cluster(home=str(tmp_path / "host"), max_parallelism=2, options={"force_host_sync": True})
+    rng = np.random.default_rng(0)
+    c.shard_store.create("mnist", rng.integers(0, 255, (1024 + 64, 28, 28), dtype=np.uint8), rng.integers(0, 10, (1024 + 64,)),
+                         rng.integers(0, 255, (256, 28, 28), dtype=np.uint8), rng.integers(0, 10, (256,)))
+    req = TrainRequest(model_type="lenet", batch_size=64, epochs=2, dataset="mnist", lr=0.01, function_name="lenet",
+                       options=TrainOptions(default_parallelism=2, static_parallelism=True, validate_every=1, k=2))
+    jid = make_kubeml_client(c).v1().networks().train(req)
+    assert c.wait(jid, 300) is None
+    host_hist = c.histories.get(jid).data
+    c.shutdown()
+    np.testing.assert_allclose(dev_hist["train_loss"], host_hist.train_loss, rtol=5e-3)
+    np.testing.assert_allclose(dev_hist["validation_loss"], host_hist.validation_loss, rtol=5e-3)
+    assert dev_hist["parallelism"] == [2.0, 2.0]

@@ -1,0 +1,111 @@
+"""The native model *programs* (forward + hand-ordered backward) against torchvision, run through
+the CPU fp32 restatement of every kernel: exact agreement here + per-kernel GPU numerics
+(tests/test_gpu_layers.py) is what pins the GPU path."""
+import numpy as np
+import pytest
+import torch
+
+from kubeml_b200 import ops
+from kubeml_b200.models import native as nv
+
+
+@pytest.fixture()
+def fp32_activations():
+    nv.set_activation_dtype(torch.float32)
+    yield
+    nv.set_activation_dtype(torch.bfloat16)
+
+
+def test_resnet18_program_matches_torchvision(fp32_activations):
+    import torchvision
+    from kubeml_b200.models import resnet18
+    torch.manual_seed(0)
+    net = resnet18(num_classes=10)
+    net._ensure_arena()
+    with torch.no_grad():
+        for p in net.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.bfloat16().float())        # the tensor-core copy is bf16: make it lossless
+    net._arena.refresh_bf16()
+    ref = torchvision.models.resnet18(num_classes=10)
+    assert list(net.state_dict().keys()) == list(ref.state_dict().keys())
+    assert all(a.shape == b.shape for a, b in zip(net.state_dict().values(), ref.state_dict().values()))
+    ref.load_state_dict(net.state_dict())
+    net.train(); ref.train()
+    x = torch.randn(8, 3, 32, 32)
+    y = torch.randint(0, 10, (8,))
+    out = net(x)
+    ops.cross_entropy(out, y).backward()
+    out_r = ref(x)
+    torch.nn.functional.cross_entropy(out_r, y).backward()
+    torch.testing.assert_close(out, out_r, rtol=1e-4, atol=1e-4)
+    for n, p in ref.named_parameters():
+        g = net._arena.grad(n)
+        scale = p.grad.abs().max().item() + 1e-12
+        assert (g - p.grad).abs().max().item() / scale < 1e-3, n
+    torch.testing.assert_close(net.bn1.running_mean, ref.bn1.running_mean, rtol=1e-5, atol=1e-6)
+    assert int(net.layer4[1].bn2.num_batches_tracked) == 1
+    # a second step accumulates nothing stale (split-K gradients are cleared by the backward itself)
+    net(x).float().sum().backward()
+    ref(x).sum().backward()
+    net.eval(); ref.eval()
+    with torch.no_grad():
+        torch.testing.assert_close(net(x), ref(x), rtol=1e-3, atol=1e-3)
+
+
+def test_filter_is_stored_ohwi_but_exposed_oihw():
+    from kubeml_b200.models import resnet18
+    net = resnet18(num_classes=10)
+    net._ensure_arena()
+    w = net.layer1[0].conv1.weight
+    assert tuple(w.shape) == (64, 64, 3, 3) and not w.is_contiguous()
+    phys = net._arena.physical("layer1.0.conv1.weight")
+    assert tuple(phys.shape) == (64, 3, 3, 64)
+    with torch.no_grad():
+        w[5, 7, 1, 2] = 42.0
+    assert float(phys[5, 1, 2, 7]) == 42.0
+    sd = net.state_dict()
+    assert tuple(sd["layer1.0.conv1.weight"].shape) == (64, 64, 3, 3)
+    net2 = resnet18(num_classes=10)
+    net2.load_state_dict(sd)
+    torch.testing.assert_close(net2.layer1[0].conv1.weight, w)
+
+
+def test_arena_layout_flat_optimizer_and_bf16_copy():
+    from kubeml_b200.optim import SGD
+    from kubeml_b200.parallel.arena import ArenaLayout, WeightArena
+
+    def mk():
+        torch.manual_seed(1)
+        return torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3), torch.nn.BatchNorm2d(8), torch.nn.Flatten(),
+                                   torch.nn.Linear(8 * 36, 10))
+    m1, m2 = mk(), mk()
+    lay = ArenaLayout(m2)
+    assert lay.n_i64 == 1 and lay.n_param % 64 == 0 and lay.n_f32 >= lay.n_param
+    idx = lay.index("job1")
+    assert idx[0]["key"] == "job1:0.weight" and lay.index("job1", 3)[0]["key"] == "job1:0.weight/3"
+    arena = WeightArena(lay, torch.device("cpu"))
+    arena.bind(m2)
+    o1 = torch.optim.SGD(m1.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    o2 = SGD(m2.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    o2.attach_arena(arena)
+    x, y = torch.randn(4, 3, 8, 8), torch.randint(0, 10, (4,))
+    for _ in range(3):
+        for m, o in ((m1, o1), (m2, o2)):
+            o.zero_grad()
+            torch.nn.functional.cross_entropy(m(x), y).backward()
+            o.step()
+    assert o2._flat_views() is not None
+    for a, b in zip(m1.state_dict().values(), m2.state_dict().values()):
+        torch.testing.assert_close(a, b)
+    assert int(arena.counters[0]) == 3
+    o2.reset_state()
+    assert float(arena.state1.abs().max()) == 0.0
+
+
+def test_auto_splits_never_leaves_an_empty_split():
+    for tiles in (1, 2, 9, 16, 64, 144):
+        for chunks in range(1, 600, 7):
+            s = nv.auto_splits(tiles, chunks)
+            per = -(-chunks // s)
+            assert s >= 1 and (s - 1) * per < chunks
