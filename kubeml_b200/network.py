@@ -268,6 +268,8 @@ class KubeModel(ABC):
     def _graphs_enabled(self) -> bool:
         if self.device is None or self.device.type != "cuda" or not self.graph_safe:
             return False
+        if (self._inv.services.options or {}).get("cuda_graphs") is False:
+            return False
         return os.environ.get("KUBEML_CUDA_GRAPH", "1") != "0"
 
     def _graphed_step(self, batch, idx):
@@ -307,7 +309,8 @@ class KubeModel(ABC):
             torch.cuda.synchronize(self.device)
             k0 = _native_launches()
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            # thread_local: workers may be threads of one process, each capturing on its own GPU
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 out = ent["owner_train"](sbatch, idx) if "owner_train" in ent else self.train(sbatch, idx)
             ent.update(graph=g, static=static, out=out, owner=self, kernels=_native_launches() - k0)
             g.replay()            # the capture itself did not execute: run this batch now

@@ -55,6 +55,10 @@ class ThreadInvoker(Invoker):
         self.max_parallelism = max_parallelism
         self.gpu_ids = gpu_ids
         self._workers: Dict[int, Worker] = {}
+        if gpu_ids is not None and len(gpu_ids) > 1:
+            # several GPU workers as threads of one process: stream capture is per-process state in
+            # practice (allocator, generators), so step graphs are left to the process-per-GPU runtime
+            self.services.options["cuda_graphs"] = False
 
     def _worker(self, func_id: int) -> Worker:
         w = self._workers.get(func_id)
