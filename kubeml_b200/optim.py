@@ -143,13 +143,14 @@ class SGD(_FlatOptimizer):
         for i, p in enumerate(self.params):
             if p.grad is None:
                 continue
-            w, gr = p.data.view(-1), p.grad.view(-1)
-            mb = self._bufs[i].view(-1) if mom else None
-            ok = w.is_cuda and w.numel() % 4 == 0 and w.data_ptr() % 16 == 0 and gr.data_ptr() % 16 == 0 \
+            dense = p.data.is_contiguous() and p.grad.is_contiguous()
+            w, gr = (p.data.view(-1), p.grad.view(-1)) if dense else (p.data, p.grad)
+            mb = (self._bufs[i].view(-1) if dense else self._bufs[i]) if mom else None
+            ok = dense and w.is_cuda and w.numel() % 4 == 0 and w.data_ptr() % 16 == 0 and gr.data_ptr() % 16 == 0 \
                 and (mb is None or mb.data_ptr() % 16 == 0)
-            if ok or not w.is_cuda:
+            if ok or (dense and not w.is_cuda):
                 ops.sgd_step_(w, gr, mb, lr, wd, mom, nes)
-            else:   # odd-sized CUDA tensor outside an arena: same math with torch ops
+            else:   # odd-sized or strided (channels-last) tensor outside an arena: same math with torch ops
                 d = gr.add(w, alpha=wd) if wd else gr
                 if mom:
                     mb.mul_(mom).add_(d)
@@ -191,10 +192,11 @@ class Adam(_FlatOptimizer):
         for i, p in enumerate(self.params):
             if p.grad is None:
                 continue
-            w, gr = p.data.view(-1), p.grad.view(-1)
-            m, v = self._m[i].view(-1), self._v[i].view(-1)
-            aligned = all(t.data_ptr() % 16 == 0 for t in (w, gr, m, v)) and w.numel() % 4 == 0
-            if not w.is_cuda or aligned:
+            dense = p.data.is_contiguous() and p.grad.is_contiguous()
+            w, gr = (p.data.view(-1), p.grad.view(-1)) if dense else (p.data, p.grad)
+            m, v = (self._m[i].view(-1), self._v[i].view(-1)) if dense else (self._m[i], self._v[i])
+            aligned = dense and all(t.data_ptr() % 16 == 0 for t in (w, gr, m, v)) and w.numel() % 4 == 0
+            if (dense and not w.is_cuda) or aligned:
                 ops.adam_step_(w, gr, m, v, self._t, g["lr"], g["betas"], g["eps"], g["weight_decay"])
             else:
                 d = gr.add(w, alpha=g["weight_decay"]) if g["weight_decay"] else gr

@@ -328,9 +328,9 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
         from .peer import FdExchange
         self.rank, self.world = rank, world
         self.fdx = FdExchange(rank, world, sock_dir)
-        self.rs = RankSync(self, rank)
-        self._imported: List = []
-        self._mcast = None
+        self._jobs: Dict[str, RankSync] = {}
+        self.rs = RankSync(self, rank)          # engine of the most recent job (benchmarks use one job at a time)
+        self.rs._imported, self.rs._mcast = [], None
         self._tag = 1000 * (job_tag + 1)
         self._holder = 0
 
@@ -338,6 +338,24 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
         if func_id != self.rank:
             raise MergeError(RuntimeError(f"function {func_id} scheduled on rank {self.rank}"))
         return self.rs
+
+    def for_job(self, job_id: str, func_id: int) -> RankSync:
+        """One engine (arena, peer mappings, multicast object) per job: a control plane may run
+        several jobs with different models over the same worker processes."""
+        if func_id != self.rank:
+            raise MergeError(RuntimeError(f"function {func_id} scheduled on rank {self.rank}"))
+        rs = self._jobs.get(job_id)
+        if rs is None:
+            rs = RankSync(self, self.rank)
+            rs._imported, rs._mcast = [], None
+            self._jobs[job_id] = rs
+            self.rs = rs
+        return rs
+
+    def release(self, job_id: str) -> None:
+        rs = self._jobs.pop(job_id, None)
+        if rs is not None:
+            self._close_rank(rs)
 
     def _next_tag(self) -> int:
         self._tag += 1
@@ -360,7 +378,7 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
             _native.check(lib.kml_arena_import_fd(dev, got[peer][0], rs.arena.nbytes, ctypes.byref(h)),
                           f"kml_arena_import_fd(rank {peer})")
             os.close(got[peer][0])
-            self._imported.append(h)
+            rs._imported.append(h)
             rs.peers.add(peer, int(lib.kml_arena_ptr(h)), rs.layout)
         self._setup_multicast(rs, dev)
 
@@ -399,7 +417,7 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
             have = False
         have = self.fdx.all_agree(have, self._next_tag())
         if have:
-            self._mcast = m
+            rs._mcast = m
             rs.peers.mcast = int(mc_ptr.value) + rs.layout.off_f32
             rs.peers.mcast_ranks = frozenset(range(self.world))
             log.info("rank %d: NVLS multicast mapping ready", self.rank)
@@ -427,13 +445,20 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
         if self.world > 1:
             self.fdx.barrier(self._next_tag())
 
-    def close(self) -> None:
+    def _close_rank(self, rs: RankSync) -> None:
         lib = _native.lib()
-        self.rs.close()
-        for h in self._imported:
+        if rs.arena is not None:
+            torch.cuda.synchronize(rs.arena.device)
+        if getattr(rs, "_mcast", None) is not None:
+            lib.kml_mcast_destroy(rs._mcast)
+            rs._mcast = None
+        for h in getattr(rs, "_imported", []):
             lib.kml_arena_destroy(h)
-        self._imported = []
-        if self._mcast is not None:
-            lib.kml_mcast_destroy(self._mcast)
-            self._mcast = None
+        rs._imported = []
+        rs.close()
+
+    def close(self) -> None:
+        for jid in list(self._jobs):
+            self.release(jid)
+        self._close_rank(self.rs)
         self.fdx.close()

@@ -56,6 +56,8 @@ class SpmdRuntime:
                                  barrier=None, device_sync=self.group, options=dict(options or {}))
         self.worker = Worker(self.services, self.registry,
                              gpu_id=self.local_rank if cuda else None, name=f"rank{self.rank}")
+        import threading
+        self._lock = threading.Lock()       # fan-outs of concurrent jobs are serialised
 
     # ---- collective helpers --------------------------------------------------------------
     def _bcast(self, obj: Any) -> Any:
@@ -73,6 +75,11 @@ class SpmdRuntime:
         return out
 
     def _execute(self, msg: dict) -> Any:
+        if msg.get("release"):
+            if self.group is not None:
+                self.group.release(msg["release"])
+            (self.worker.state.get("step_graphs") or {}).clear()
+            return None
         for k, v in (msg.get("env") or {}).items():
             os.environ[k] = str(v)
         for k, v in (msg.get("options") or {}).items():
@@ -93,8 +100,9 @@ class SpmdRuntime:
 
     # ---- rank 0 ----------------------------------------------------------------------------
     def run(self, msg: dict) -> List[Any]:
-        self._bcast(msg)
-        return self._gather(self._execute(msg)) or []
+        with self._lock:
+            self._bcast(msg)
+            return self._gather(self._execute(msg)) or []
 
     def stop(self) -> None:
         if self.rank == 0 and self.world > 1:
@@ -129,6 +137,10 @@ class SpmdInvoker(Invoker):
             out.append(dict(template, task="join", funcId=r, joinFor=template.get("task"))
                        if collective else None)
         return out
+
+    def release_job(self, job_id: str) -> None:
+        """Free the job's arenas, peer mappings and captured step graphs on every rank."""
+        self.rt.run({"release": job_id})
 
     def invoke_one(self, func_id, function, query, body=None):
         assert func_id == 0, "single invocations run on rank 0"

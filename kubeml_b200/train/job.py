@@ -50,6 +50,7 @@ class TrainJob:
         self.device_mode = device_mode
         self.checkpoint_dir = checkpoint_dir
         self.skip_final_validation = skip_final_validation
+        self.release_on_finish = True
 
         opts = task.request.options
         self.parallelism = self._clamp(task.job.state.parallelism or opts.default_parallelism or 1)
@@ -298,6 +299,12 @@ class TrainJob:
                                 getattr(self, "layer_names", []), self.task.request, self.history)
             except Exception as e:  # noqa: BLE001
                 self.log.error("checkpoint failed: %s", e)
+        release = getattr(self.invoker, "release_job", None)
+        if callable(release) and self.release_on_finish:
+            try:
+                release(self.job_id)
+            except Exception as e:  # noqa: BLE001
+                self.log.error("could not release worker state: %s", e)
         if self.ps is not None:
             try:
                 self.ps.job_finished(self.job_id, self.exit_err)

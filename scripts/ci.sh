@@ -1,0 +1,10 @@
+#!/bin/sh
+# What CI runs (the reference's workflows only build images, .github/workflows/*.yml).
+set -e
+cd "$(dirname "$0")/.."
+python -c "import __graft_entry__ as g; g.build()"
+python -m pytest tests -x -q -m "not gpu"
+if python -c "import torch,sys; sys.exit(0 if torch.cuda.is_available() else 1)"; then
+  python -m pytest tests -x -q -m gpu
+  python bench.py --steps 16 --warmup 4
+fi

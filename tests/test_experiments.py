@@ -1,0 +1,65 @@
+import math
+import os
+
+import numpy as np
+
+from kubeml_b200.experiments import analysis
+from kubeml_b200.experiments.harness import (KubemlExperiment, grid_points, point_title, retry, run_grid,
+                                             to_dataframe)
+from kubeml_b200.experiments.sysmetrics import MetricsCollector
+
+
+def test_tta_definitions():
+    acc = [50, 69, 71, 68, 72, 73, 74]
+    t = [1, 2, 3, 4, 5, 6, 7]
+    assert analysis.tta(acc, t, 70) == 3
+    assert analysis.tta_crossbow(acc, t, 70) == 6            # median of the last five first reaches 70 at epoch 6
+    assert math.isnan(analysis.tta(acc, t, 99))
+    assert analysis.total_time(t) == 7 and analysis.mean_parallelism([2, 4]) == 3
+
+
+def test_retry_backoff():
+    calls = {"n": 0}
+
+    @retry(ValueError, total_tries=3, initial_wait=0.001)
+    def flaky():
+        calls["n"] += 1
+        if calls["n"] < 3:
+            raise ValueError
+        return "ok"
+    assert flaky() == "ok" and calls["n"] == 3
+
+
+def test_grid_resume_and_dataframe(kube_home, monkeypatch, tmp_path):
+    from kubeml_b200.controller import Cluster, make_kubeml_client
+    monkeypatch.setenv("KUBEML_CUDA_GRAPH", "0")
+    c = Cluster(home=kube_home, max_parallelism=2, options={"force_host_sync": True})
+    rng = np.random.default_rng(0)
+    c.shard_store.create("mnist", rng.integers(0, 255, (256, 28, 28), dtype=np.uint8), rng.integers(0, 10, (256,)),
+                         rng.integers(0, 255, (64, 28, 28), dtype=np.uint8), rng.integers(0, 10, (64,)))
+    grid = {"batch": [64], "k": [-1, 2], "parallelism": [1, 2]}
+    assert len(grid_points(grid)) == 4 and point_title("lenet", grid_points(grid)[0]) == "lenet-b64-k-1-p1"
+    mc = MetricsCollector(interval=0.05)
+    recs = run_grid(make_kubeml_client(c), "lenet", "mnist", 0.01, grid, str(tmp_path / "out"), epochs=1,
+                    metrics=mc, timeout=300)
+    assert len(recs) == 4 and all(r.error is None for r in recs)
+    assert "cpu" in recs[0].system_metrics and len(recs[0].system_metrics["cpu"]) >= 1
+    n_files = len(os.listdir(tmp_path / "out"))
+    again = run_grid(make_kubeml_client(c), "lenet", "mnist", 0.01, grid, str(tmp_path / "out"), epochs=1)
+    assert len(again) == 4 and len(os.listdir(tmp_path / "out")) == n_files
+    assert [r.task_id for r in again] == [r.task_id for r in recs]          # nothing was re-run
+    df = to_dataframe(recs)
+    assert list(df["k"]) == [-1, -1, 2, 2] and len(df["train_loss"][0]) == 1
+    c.shutdown()
+    assert KubemlExperiment._fake_history(3).data.accuracy == [10.0, 20.0, 30.0]
+
+
+def test_k_optimizer_learns_a_trend():
+    ko = analysis.KOptimizer()
+    for _ in range(30):
+        for k, t in ((8, 1480.0), (16, 925.0), (32, 665.0), (-1, 450.0)):      # BASELINE.md, batch 128
+            ko.update(128, 0.1, 4, k, t, 70.0)
+    assert ko.best_k(128, 0.1, 4) == -1
+    t8, _ = ko.predict(128, 0.1, 4, 8)
+    tinf, _ = ko.predict(128, 0.1, 4, -1)
+    assert t8 > tinf
