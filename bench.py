@@ -139,6 +139,10 @@ def run_own(args) -> int:
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
+    # stage both datasets in page-locked host memory up front (set-up, not part of a step): the timed
+    # region then copies each step's batch host->device from pinned memory
+    for name in (f"cifar10_w{args.warmup}", f"cifar10_t{args.steps}"):
+        store.pinned(name, "train")
 
     if rank != 0:
         rt.serve()
@@ -172,8 +176,8 @@ def run_own(args) -> int:
     run_job(f"cifar10_w{args.warmup}", resident=True)
 
     sampler = ClockSampler(0).start()
-    job_dev = run_job(f"cifar10_t{args.steps}", resident=True)
     job_e2e = run_job(f"cifar10_t{args.steps}", resident=False)
+    job_dev = run_job(f"cifar10_t{args.steps}", resident=True)
     clocks = sampler.stop()
     rt.stop()
 

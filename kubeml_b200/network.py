@@ -93,9 +93,9 @@ class KubeModel(ABC):
             raise KubeMLException("invocation carries no services", 500)
         if sv.device_sync is not None and self.platform == "gpu" and torch.cuda.is_available():
             ds = sv.device_sync
-            if hasattr(ds, "for_job"):
-                return ds.for_job(self.args._job_id, self.args._func_id)
-            return ds.for_func(self.args._func_id) if hasattr(ds, "for_func") else ds
+            if hasattr(ds, "engine_for"):
+                return ds.engine_for(self.args._job_id, self.args._func_id)
+            return ds
         factory = (sv.options or {}).get("sync_factory")
         if factory is not None:          # e.g. CollectiveSync: K-AVG through torch.distributed
             ws = self._inv.worker_state if self._inv.worker_state is not None else {}
@@ -126,6 +126,13 @@ class KubeModel(ABC):
             return {"loss": loss, "accuracy": acc, "length": length}, 200
         if self.task == "infer":
             return {"predictions": self.__infer()}, 200
+        if self.task == "checkpoint":
+            # framework-internal: persist the device-resident reference model
+            self._set_device()
+            self._sync.attach(self)
+            from .utils.checkpoint import save_state_dict
+            path = save_state_dict(self._inv.query["ckptDir"], self.args._job_id, self._network.state_dict())
+            return {"path": path}, 200
         if self.task == "join":
             # framework-internal: an idle rank of a process-per-GPU group keeps its arena mapped
             # into the peers and takes part in the epoch's membership barrier

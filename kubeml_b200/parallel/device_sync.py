@@ -307,6 +307,9 @@ class ThreadedDeviceSyncGroup(DeviceSyncGroup):
     def for_func(self, func_id: int) -> RankSync:
         return self.rank_sync(func_id)
 
+    def engine_for(self, job_id: str, func_id: int) -> RankSync:
+        return self.rank_sync(func_id)          # this group object already belongs to one job
+
     def close(self) -> None:
         for rs in list(self.ranks.values()):
             rs.close()
@@ -339,7 +342,7 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
             raise MergeError(RuntimeError(f"function {func_id} scheduled on rank {self.rank}"))
         return self.rs
 
-    def for_job(self, job_id: str, func_id: int) -> RankSync:
+    def engine_for(self, job_id: str, func_id: int) -> RankSync:
         """One engine (arena, peer mappings, multicast object) per job: a control plane may run
         several jobs with different models over the same worker processes."""
         if func_id != self.rank:

@@ -292,11 +292,21 @@ class TrainJob:
             self.tensor_store.delete(self.tensor_store.keys(f"{self.job_id}:*/*"))
         except Exception:  # noqa: BLE001
             pass
-        if self.checkpoint_dir and self.exit_err is None and not self.device_mode:
+        if self.checkpoint_dir and self.exit_err is None:
             try:
-                from ..utils.checkpoint import save_checkpoint
-                save_checkpoint(self.checkpoint_dir, self.job_id, self.tensor_store,
-                                getattr(self, "layer_names", []), self.task.request, self.history)
+                if self.device_mode:       # rank 0 writes its arena; history goes next to it
+                    q = dict(self._query("checkpoint", 0, 1), ckptDir=self.checkpoint_dir)
+                    payload, status = self.invoker.invoke_one(0, self.task.request.function_name, q)
+                    if status != 200:
+                        raise KubeMLException(str(payload), status)
+                    import json
+                    import os
+                    with open(os.path.join(self.checkpoint_dir, self.job_id, "history.json"), "w") as f:
+                        json.dump(History(id=self.job_id, task=self.task.request, data=self.history).to_dict(), f)
+                else:
+                    from ..utils.checkpoint import save_checkpoint
+                    save_checkpoint(self.checkpoint_dir, self.job_id, self.tensor_store,
+                                    getattr(self, "layer_names", []), self.task.request, self.history)
             except Exception as e:  # noqa: BLE001
                 self.log.error("checkpoint failed: %s", e)
         release = getattr(self.invoker, "release_job", None)

@@ -35,6 +35,10 @@ def test_lenet_device_sync_matches_host_sync(kube_home):
         h, job = _run(c, req)
         hist[mode] = h.data
         assert job.device_mode == (mode == "device")
+        from kubeml_b200.utils.checkpoint import load_checkpoint
+        sd, ck_hist = load_checkpoint(c.checkpoint_dir, job.job_id)          # both modes leave a checkpoint
+        assert "fc3.weight" in sd and tuple(sd["conv1.weight"].shape) == (6, 1, 5, 5)
+        assert ck_hist.data.train_loss == h.data.train_loss
         c.shutdown()
     assert len(hist["device"].train_loss) == 2 and len(hist["device"].accuracy) == 2
     np.testing.assert_allclose(hist["device"].train_loss, hist["host"].train_loss, rtol=2e-3)

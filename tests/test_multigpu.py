@@ -64,3 +64,14 @@ def test_spmd_lenet_matches_host_oracle(tmp_path, kube_home):
     np.testing.assert_allclose(dev_hist["train_loss"], host_hist.train_loss, rtol=5e-3)
     np.testing.assert_allclose(dev_hist["validation_loss"], host_hist.validation_loss, rtol=5e-3)
     assert dev_hist["parallelism"] == [2.0, 2.0]
+
+
+def test_elastic_parallelism_grows_between_epochs(tmp_path):
+    """Scheduler policy: 1 worker, then +1 on second sight; the joining rank maps the peers' arenas,
+    copies the merged model and takes part in the next epoch's merges."""
+    res = _result(_torchrun(2, os.path.join(ROOT, "tests", "mp_scripts", "spmd_elastic.py"), str(tmp_path), port=29547))
+    assert res["error"] is None
+    h = res["history"]
+    assert h["parallelism"][0] == 1.0 and h["parallelism"][1] == 2.0
+    assert len(h["train_loss"]) == 3 and all(np.isfinite(h["train_loss"]))
+    assert len(h["accuracy"]) == 3
