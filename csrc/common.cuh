@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdarg>
 #include <atomic>
+#include <cstdlib>
 
 namespace kml {
 
@@ -43,6 +44,16 @@ inline int num_sms() {
   return n;
 }
 
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------
+// Kernels launched with launch_pdl() may start while the previous kernel in the stream is still
+// running: everything before pdl_wait() (barrier init, TMEM allocation, descriptor prefetch, smem
+// zeroing) overlaps the predecessor's tail; pdl_wait() returns once the predecessor has completed
+// and its writes are visible, so no global memory may be touched before it.  Each kernel calls
+// pdl_launch_dependents() at its start so that its own successor can be scheduled early.  A kernel
+// launched normally after a PDL kernel simply waits for full completion, so mixing is safe.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -52,6 +63,37 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
+}
+
+inline bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("KUBEML_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
+
+// Every kernel of this library asks for the same shared-memory carve-out (maximum shared memory).
+// Consecutive kernels with different carve-outs cannot overlap on an SM and force a drain between
+// them; the training step alternates 100-130 KB GEMM CTAs with tiny element-wise CTAs ~200 times.
+void note_kernel(const void* fn);
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  note_kernel(reinterpret_cast<const void*>(kernel));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 }  // namespace kml

@@ -171,6 +171,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
   int* tap_list = reinterpret_cast<int*>(tmem_slot + 1);   // up to 64 entries
 
+  kml::pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int mt = blockIdx.x, nt = blockIdx.y;
@@ -197,6 +198,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  kml::pdl_wait();       // the set-up above overlapped the previous kernel; its results are needed from here on
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
@@ -452,8 +454,7 @@ int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs&
     configured = true;
   }
   dim3 grid(a.m_tiles, a.n_tiles, a.z_taps * a.splits);
-  kernel<<<grid, kNumThreads, smem, s>>>(ma, mb, a);
-  KML_CUDA(cudaGetLastError());
+  KML_CUDA(kml::launch_pdl(kernel, grid, dim3(kNumThreads), smem, s, ma, mb, a));
   kml::count_launch();
   return 0;
 }

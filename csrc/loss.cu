@@ -32,6 +32,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 softmax_ce_kernel(const T* __restrict__ logits, const long long* __restrict__ labels, int rows, int classes,
                   float* __restrict__ loss_out, T* __restrict__ dlogits, int* __restrict__ correct_out,
                   CeScratch* __restrict__ scratch) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   float* row_loss = reinterpret_cast<float*>(scratch + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * kWarpsPerBlock + warp;
@@ -111,13 +113,9 @@ int kml_softmax_ce(const void* logits, int logits_bf16, const long long* labels,
   const int grid = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
   auto s = static_cast<cudaStream_t>(stream);
   if (logits_bf16)
-    softmax_ce_kernel<__nv_bfloat16><<<grid, kWarpsPerBlock * 32, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(logits), labels, rows, classes, loss, static_cast<__nv_bfloat16*>(dlogits),
-        correct, static_cast<CeScratch*>(scratch));
+    KML_CUDA(kml::launch_pdl(softmax_ce_kernel<__nv_bfloat16>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, s, static_cast<const __nv_bfloat16*>(logits), labels, rows, classes, loss, static_cast<__nv_bfloat16*>(dlogits), correct, static_cast<CeScratch*>(scratch)));
   else
-    softmax_ce_kernel<float><<<grid, kWarpsPerBlock * 32, 0, s>>>(static_cast<const float*>(logits), labels, rows,
-                                                                 classes, loss, static_cast<float*>(dlogits), correct,
-                                                                 static_cast<CeScratch*>(scratch));
+    KML_CUDA(kml::launch_pdl(softmax_ce_kernel<float>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, s, static_cast<const float*>(logits), labels, rows, classes, loss, static_cast<float*>(dlogits), correct, static_cast<CeScratch*>(scratch)));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -180,13 +178,9 @@ int kml_softmax_ce_noalloc(const void* logits, int logits_bf16, const long long*
   KML_CUDA(cudaMemsetAsync(scratch, 0, sizeof(CeScratch), s));
   const int grid = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
   if (logits_bf16)
-    softmax_ce_kernel<__nv_bfloat16><<<grid, kWarpsPerBlock * 32, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(logits), labels, rows, classes, loss, static_cast<__nv_bfloat16*>(dlogits),
-        correct, static_cast<CeScratch*>(scratch));
+    KML_CUDA(kml::launch_pdl(softmax_ce_kernel<__nv_bfloat16>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, s, static_cast<const __nv_bfloat16*>(logits), labels, rows, classes, loss, static_cast<__nv_bfloat16*>(dlogits), correct, static_cast<CeScratch*>(scratch)));
   else
-    softmax_ce_kernel<float><<<grid, kWarpsPerBlock * 32, 0, s>>>(static_cast<const float*>(logits), labels, rows,
-                                                                 classes, loss, static_cast<float*>(dlogits), correct,
-                                                                 static_cast<CeScratch*>(scratch));
+    KML_CUDA(kml::launch_pdl(softmax_ce_kernel<float>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, s, static_cast<const float*>(logits), labels, rows, classes, loss, static_cast<float*>(dlogits), correct, static_cast<CeScratch*>(scratch)));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;

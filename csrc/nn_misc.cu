@@ -22,6 +22,8 @@ inline int grid_for(size_t work, int per_block = kThreads) {
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ idx,
                    int N, int H, int W, int C, int Ho, int Wo, int k, int stride, int pad) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(N) * Ho * Wo * C;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -52,6 +54,8 @@ __global__ void __launch_bounds__(kThreads)
 maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char* __restrict__ idx,
                    __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int stride,
                    int pad) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(N) * H * W * C;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -82,6 +86,8 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char* __
 // ---------------------------------------------------------------------------------- avg pool
 __global__ void __launch_bounds__(kThreads)
 avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(N) * C;
   const float inv = 1.f / static_cast<float>(HW);
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -95,6 +101,8 @@ avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
 }
 __global__ void __launch_bounds__(kThreads)
 avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(N) * HW * C;
   const float inv = 1.f / static_cast<float>(HW);
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -110,6 +118,8 @@ avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restri
 __global__ void __launch_bounds__(kThreads)
 im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int N, int H, int W, int C, int Ho,
               int Wo, int KH, int KW, int stride, int pad, int ldk) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(N) * Ho * Wo * ldk;
   const int K = KH * KW * C;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -136,6 +146,8 @@ __global__ void __launch_bounds__(kThreads)
 col2im_kernel(const __nv_bfloat16* __restrict__ dcols, const __nv_bfloat16* __restrict__ addend,
               __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int KH, int KW, int stride,
               int pad, int ldk) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(N) * H * W * C;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -182,6 +194,8 @@ __device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&f)[8]) {
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_vec_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ idx,
                        int N, int H, int W, int C, int Ho, int Wo, int k, int stride, int pad) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const int C8 = C / 8;
   const size_t total = static_cast<size_t>(N) * Ho * Wo * C8;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -223,6 +237,8 @@ __global__ void __launch_bounds__(kThreads)
 maxpool_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char* __restrict__ idx,
                        __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int stride,
                        int pad) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const int C8 = C / 8;
   const size_t total = static_cast<size_t>(N) * H * W * C8;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -264,6 +280,8 @@ maxpool_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char
 __global__ void __launch_bounds__(kThreads)
 im2col_vec_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int N, int H, int W, int C,
                   int Ho, int Wo, int KH, int KW, int stride, int pad, int ldk) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const int L8 = ldk / 8, C8 = C / 8, K8 = KH * KW * C8;
   const size_t total = static_cast<size_t>(N) * Ho * Wo * L8;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -290,6 +308,8 @@ im2col_vec_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict
 __global__ void __launch_bounds__(kThreads)
 im2col_gather8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int N, int H, int W, int C,
                       int Ho, int Wo, int KH, int KW, int stride, int pad, int ldk) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const int L8 = ldk / 8, K = KH * KW * C;
   const size_t total = static_cast<size_t>(N) * Ho * Wo * L8;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -320,6 +340,8 @@ __global__ void __launch_bounds__(kThreads)
 col2im_vec_kernel(const __nv_bfloat16* __restrict__ dcols, const __nv_bfloat16* __restrict__ addend,
                   __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int KH, int KW, int stride,
                   int pad, int ldk) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const int C8 = C / 8;
   const size_t total = static_cast<size_t>(N) * H * W * C8;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -361,6 +383,8 @@ col2im_vec_kernel(const __nv_bfloat16* __restrict__ dcols, const __nv_bfloat16* 
 // out[c] = sum_r x[r][c]  (bias gradient); one block per 32 columns, rows strided over warps
 __global__ void __launch_bounds__(kThreads)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int rows, int cols, long long ld) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   __shared__ float part[kThreads / 32][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
@@ -380,6 +404,8 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int 
 // dst bf16 [rows][ld] <- src fp32 [rows][cols], zero padded
 __global__ void __launch_bounds__(kThreads)
 pack_rows_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows, int cols, int ld) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(rows) * ld;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -395,6 +421,8 @@ pack_rows_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
 __global__ void __launch_bounds__(kThreads)
 image_prep_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict__ y, const int* __restrict__ aug, int N,
                   int H, int W, int C, int pad, float m0, float m1, float m2, float s0, float s1, float s2) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t total = static_cast<size_t>(N) * H * W * C;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -430,13 +458,9 @@ int kml_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int 
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = static_cast<size_t>(N) * Ho * Wo * C;
   if (C % 8 == 0)
-    maxpool_fwd_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(idx), N, H,
-        W, C, Ho, Wo, k, stride, pad);
+    KML_CUDA(kml::launch_pdl(maxpool_fwd_vec_kernel, dim3(grid_for(total / 8)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(idx), N, H, W, C, Ho, Wo, k, stride, pad));
   else
-  maxpool_fwd_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(idx), N, H, W,
-      C, Ho, Wo, k, stride, pad);
+  KML_CUDA(kml::launch_pdl(maxpool_fwd_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<unsigned char*>(idx), N, H, W, C, Ho, Wo, k, stride, pad));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -448,13 +472,9 @@ int kml_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = static_cast<size_t>(N) * H * W * C;
   if (C % 8 == 0)
-    maxpool_bwd_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx),
-        N, H, W, C, Ho, Wo, k, stride, pad);
+    KML_CUDA(kml::launch_pdl(maxpool_bwd_vec_kernel, dim3(grid_for(total / 8)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, k, stride, pad));
   else
-  maxpool_bwd_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx),
-      N, H, W, C, Ho, Wo, k, stride, pad);
+  KML_CUDA(kml::launch_pdl(maxpool_bwd_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(idx), static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, k, stride, pad));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -462,8 +482,7 @@ int kml_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int
 
 int kml_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
   KML_CHECK(x && y && HW > 0, "kml_avgpool_fwd: bad arguments");
-  avgpool_fwd_kernel<<<grid_for(static_cast<size_t>(N) * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), N, HW, C);
+  KML_CUDA(kml::launch_pdl(avgpool_fwd_kernel, dim3(grid_for(static_cast<size_t>(N) * C)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), N, HW, C));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -471,8 +490,7 @@ int kml_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) 
 
 int kml_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
   KML_CHECK(dy && dx && HW > 0, "kml_avgpool_bwd: bad arguments");
-  avgpool_bwd_kernel<<<grid_for(static_cast<size_t>(N) * HW * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, HW, C);
+  KML_CUDA(kml::launch_pdl(avgpool_bwd_kernel, dim3(grid_for(static_cast<size_t>(N) * HW * C)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, HW, C));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -484,17 +502,11 @@ int kml_im2col(const void* x, void* cols, int N, int H, int W, int C, int KH, in
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const size_t total = static_cast<size_t>(N) * Ho * Wo * ldk;
   if (C % 8 == 0 && ldk % 8 == 0)
-    im2col_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride,
-        pad, ldk);
+    KML_CUDA(kml::launch_pdl(im2col_vec_kernel, dim3(grid_for(total / 8)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk));
   else if (ldk % 8 == 0)
-    im2col_gather8_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride,
-        pad, ldk);
+    KML_CUDA(kml::launch_pdl(im2col_gather8_kernel, dim3(grid_for(total / 8)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk));
   else
-  im2col_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride, pad,
-      ldk);
+  KML_CUDA(kml::launch_pdl(im2col_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -506,13 +518,9 @@ int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, in
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const size_t total = static_cast<size_t>(N) * H * W * C;
   if (C % 8 == 0 && ldk % 8 == 0)
-    col2im_vec_kernel<<<grid_for(total / 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(dcols), static_cast<const __nv_bfloat16*>(addend),
-        static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk);
+    KML_CUDA(kml::launch_pdl(col2im_vec_kernel, dim3(grid_for(total / 8)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dcols), static_cast<const __nv_bfloat16*>(addend), static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk));
   else
-  col2im_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dcols), static_cast<const __nv_bfloat16*>(addend),
-      static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk);
+  KML_CUDA(kml::launch_pdl(col2im_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dcols), static_cast<const __nv_bfloat16*>(addend), static_cast<__nv_bfloat16*>(dx), N, H, W, C, Ho, Wo, KH, KW, stride, pad, ldk));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -520,8 +528,7 @@ int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, in
 
 int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld, void* stream) {
   KML_CHECK(x && out && rows > 0 && cols > 0, "kml_colsum_bf16: bad arguments");
-  colsum_kernel<<<(cols + 31) / 32, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), out, rows, cols, ld);
+  KML_CUDA(kml::launch_pdl(colsum_kernel, dim3((cols + 31) / 32), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), out, rows, cols, ld));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -529,8 +536,7 @@ int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld,
 
 int kml_pack_rows_bf16(const float* src, void* dst, int rows, int cols, int ld, void* stream) {
   KML_CHECK(src && dst && ld >= cols, "kml_pack_rows_bf16: bad arguments");
-  pack_rows_kernel<<<grid_for(static_cast<size_t>(rows) * ld), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      src, static_cast<__nv_bfloat16*>(dst), rows, cols, ld);
+  KML_CUDA(kml::launch_pdl(pack_rows_kernel, dim3(grid_for(static_cast<size_t>(rows) * ld)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), src, static_cast<__nv_bfloat16*>(dst), rows, cols, ld));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -540,9 +546,7 @@ int kml_image_prep(const void* x_u8, void* y_bf16, const int* aug, int N, int H,
                    const float* mean3, const float* std3, void* stream) {
   KML_CHECK(x_u8 && y_bf16 && mean3 && std3 && C <= 3, "kml_image_prep: bad arguments");
   const size_t total = static_cast<size_t>(N) * H * W * C;
-  image_prep_kernel<<<grid_for(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const unsigned char*>(x_u8), static_cast<__nv_bfloat16*>(y_bf16), aug, N, H, W, C, pad, mean3[0],
-      mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2]);
+  KML_CUDA(kml::launch_pdl(image_prep_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const unsigned char*>(x_u8), static_cast<__nv_bfloat16*>(y_bf16), aug, N, H, W, C, pad, mean3[0], mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2]));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;

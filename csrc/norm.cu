@@ -162,6 +162,8 @@ struct BnFwdArgs {
 
 __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs a) {
   extern __shared__ float sm[];                    // [2C] totals, then reused as scale/shift
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const int groups = a.C / kVec;
   const int lanes = kThreads / groups;
   const int g = threadIdx.x % groups;
@@ -311,6 +313,8 @@ struct BnBwdArgs {
 
 __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
   extern __shared__ float sm[];
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const int groups = a.C / kVec;
   const int lanes = kThreads / groups;
   const int g = threadIdx.x % groups;
@@ -439,8 +443,7 @@ int kml_bn_fwd_train(const void* x, const float* x_slabs, int nslabs, long long 
               save_mean, save_invstd, static_cast<BnScratch*>(scratch), M, C, relu, eps, momentum};
   const size_t smem = 2 * C * sizeof(float);
   const int grid = bn_grid(M, C, reinterpret_cast<const void*>(bn_fwd_train_kernel), smem);
-  bn_fwd_train_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
-  KML_CUDA(cudaGetLastError());
+  KML_CUDA(kml::launch_pdl(bn_fwd_train_kernel, dim3(grid), dim3(kThreads), smem, static_cast<cudaStream_t>(stream), a));
   kml::count_launch();
   return 0;
 }
@@ -476,8 +479,7 @@ int kml_bn_bwd(const void* dy, const float* dy_slabs, int nslabs, long long slab
               static_cast<__nv_bfloat16*>(dres), dgamma, dbeta, static_cast<BnScratch*>(scratch), M, C};
   const size_t smem = 2 * C * sizeof(float);
   const int grid = bn_grid(M, C, reinterpret_cast<const void*>(bn_bwd_kernel), smem);
-  bn_bwd_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
-  KML_CUDA(cudaGetLastError());
+  KML_CUDA(kml::launch_pdl(bn_bwd_kernel, dim3(grid), dim3(kThreads), smem, static_cast<cudaStream_t>(stream), a));
   kml::count_launch();
   return 0;
 }

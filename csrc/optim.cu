@@ -22,6 +22,8 @@ template <bool kMomentum, bool kNesterov, bool kBf16>
 __global__ void __launch_bounds__(kThreads)
 sgd_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __restrict__ mbuf, uint2* __restrict__ wb,
            size_t n4, float lr, float wd, float mom) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 wv = w[i];
@@ -49,6 +51,8 @@ __global__ void __launch_bounds__(kThreads)
 adam_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __restrict__ m1, float4* __restrict__ m2,
             uint2* __restrict__ wb, size_t n4, float lr, float b1, float b2, float eps, float wd, float bc1,
             float bc2_sqrt) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   const float step_size = lr / bc1;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -69,6 +73,8 @@ adam_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __rest
 
 __global__ void __launch_bounds__(kThreads)
 cast_kernel(const float4* __restrict__ src, uint2* __restrict__ dst, size_t n4) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride)
     dst[i] = pack_bf16x4(src[i]);
@@ -76,6 +82,8 @@ cast_kernel(const float4* __restrict__ src, uint2* __restrict__ dst, size_t n4) 
 
 __global__ void __launch_bounds__(kThreads)
 fill_kernel(float4* __restrict__ dst, float v, size_t n4) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   const float4 f = make_float4(v, v, v, v);
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) dst[i] = f;
@@ -106,7 +114,7 @@ int kml_sgd_step(float* w, const float* g, float* mbuf, size_t n, float lr, floa
   auto M = reinterpret_cast<float4*>(mbuf);
   auto B = reinterpret_cast<uint2*>(w_bf16);
   const int grid = grid_for(n4);
-#define LAUNCH(MOM, NES, BF) sgd_kernel<MOM, NES, BF><<<grid, kThreads, 0, s>>>(W, G, M, B, n4, lr, wd, mom)
+#define LAUNCH(MOM, NES, BF) KML_CUDA(kml::launch_pdl(sgd_kernel<MOM, NES, BF>, dim3(grid), dim3(kThreads), 0, s, W, G, M, B, n4, lr, wd, mom))
   const bool m = mom != 0.f, nes = nesterov != 0, bf = w_bf16 != nullptr;
   if (m && nes && bf) LAUNCH(true, true, true);
   else if (m && nes) LAUNCH(true, true, false);
@@ -133,13 +141,9 @@ int kml_adam_step(float* w, const float* g, float* m1, float* m2, size_t n, floa
   auto s = static_cast<cudaStream_t>(stream);
   const int grid = grid_for(n4);
   if (w_bf16)
-    adam_kernel<true><<<grid, kThreads, 0, s>>>(reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g),
-                                               reinterpret_cast<float4*>(m1), reinterpret_cast<float4*>(m2),
-                                               reinterpret_cast<uint2*>(w_bf16), n4, lr, b1, b2, eps, wd, bc1, bc2s);
+    KML_CUDA(kml::launch_pdl(adam_kernel<true>, dim3(grid), dim3(kThreads), 0, s, reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(m1), reinterpret_cast<float4*>(m2), reinterpret_cast<uint2*>(w_bf16), n4, lr, b1, b2, eps, wd, bc1, bc2s));
   else
-    adam_kernel<false><<<grid, kThreads, 0, s>>>(reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g),
-                                                reinterpret_cast<float4*>(m1), reinterpret_cast<float4*>(m2), nullptr,
-                                                n4, lr, b1, b2, eps, wd, bc1, bc2s);
+    KML_CUDA(kml::launch_pdl(adam_kernel<false>, dim3(grid), dim3(kThreads), 0, s, reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(m1), reinterpret_cast<float4*>(m2), nullptr, n4, lr, b1, b2, eps, wd, bc1, bc2s));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -149,8 +153,7 @@ int kml_cast_f32_to_bf16(const float* src, void* dst, size_t n, void* stream) {
   KML_CHECK(src && dst && n % 4 == 0 && aligned16(src) && (reinterpret_cast<uintptr_t>(dst) & 7u) == 0,
             "kml_cast_f32_to_bf16: bad arguments");
   if (n == 0) return 0;
-  cast_kernel<<<grid_for(n / 4), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const float4*>(src), reinterpret_cast<uint2*>(dst), n / 4);
+  KML_CUDA(kml::launch_pdl(cast_kernel, dim3(grid_for(n / 4)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(src), reinterpret_cast<uint2*>(dst), n / 4));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;
@@ -159,8 +162,7 @@ int kml_cast_f32_to_bf16(const float* src, void* dst, size_t n, void* stream) {
 int kml_fill_f32(float* dst, float v, size_t n, void* stream) {
   KML_CHECK(dst && n % 4 == 0 && aligned16(dst), "kml_fill_f32: bad arguments");
   if (n == 0) return 0;
-  fill_kernel<<<grid_for(n / 4), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float4*>(dst), v,
-                                                                                    n / 4);
+  KML_CUDA(kml::launch_pdl(fill_kernel, dim3(grid_for(n / 4)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), reinterpret_cast<float4*>(dst), v, n / 4));
   KML_CUDA(cudaGetLastError());
   kml::count_launch();
   return 0;

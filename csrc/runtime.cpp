@@ -2,10 +2,23 @@
 #include "common.cuh"
 #include "../include/kubeml_b200.h"
 #include <cstring>
+#include <mutex>
+#include <unordered_set>
 
 namespace kml {
 static thread_local char g_err[1024] = "";
 std::atomic<unsigned long long> g_launches{0};
+
+void note_kernel(const void* fn) {
+  static std::mutex mu;
+  static std::unordered_set<const void*> seen;
+  std::lock_guard<std::mutex> lock(mu);
+  if (seen.insert(fn).second) {
+    const char* e = getenv("KUBEML_UNIFORM_CARVEOUT");
+    if (!(e && e[0] == '0'))
+      cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  }
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
