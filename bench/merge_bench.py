@@ -5,9 +5,13 @@ against NCCL all_reduce + divide over the same buffers, for model sizes from LeN
         --master-port 29531 bench/merge_bench.py [--check]
 
 Every number is device time (CUDA events on the launching stream), max over ranks, after warm-up.
-Roofline: each rank must pull (P-1)/P of the buffer from peers and push 1/P of it to each of the
-P-1 peers, i.e. ~B*(P-1)/P bytes each way per GPU over NVLink (770 GB/s measured per direction,
-/opt/skills/guides/B200_PROFILING.md); the NVLS path moves B/P out + B/P*(..) in-switch.
+Rooflines (bytes that must cross each GPU's NVLink ports per direction, over the measured
+770 GB/s per direction, /opt/skills/guides/B200_PROFILING.md):
+  P2P   a rank reads its 1/P slice from the P-1 peers and writes the average back to them, and it
+        serves the same traffic to its peers: 2*(P-1)/P*B out and the same in   -> t >= 2(P-1)/P*B/BW
+  NVLS  the switch reduces and replicates: every byte leaves a GPU once ((P-1)/P*B pulled by
+        multimem.ld_reduce + B/P multicast store) and enters it once            -> t >= B/BW
+(NCCL's ring/tree all-reduce moves the P2P volume.)
 """
 import argparse, ctypes, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -102,10 +106,15 @@ def main():
         def nccl():
             dist.all_reduce(buf); buf.div_(world)
         row["nccl_allreduce_div_ms"] = round(timed(nccl, args.iters), 4)
-        roof_ms = (n * 4 * (world - 1) / world) / (NVLINK_GBS * 1e9) * 1e3 if world > 1 else 0.0
-        row["nvlink_roofline_ms"] = round(roof_ms, 4)
+        B = n * 4
+        p2p_roof = (2 * B * (world - 1) / world) / (NVLINK_GBS * 1e9) * 1e3 if world > 1 else 0.0
+        nvls_roof = B / (NVLINK_GBS * 1e9) * 1e3 if world > 1 else 0.0
+        row["p2p_roofline_ms"] = round(p2p_roof, 4)
+        row["p2p_roofline_fraction"] = round(p2p_roof / row["p2p_ms"], 3)
+        if "nvls_ms" in row:
+            row["nvls_roofline_ms"] = round(nvls_roof, 4)
+            row["nvls_roofline_fraction"] = round(nvls_roof / row["nvls_ms"], 3)
         best = min(row["p2p_ms"], row.get("nvls_ms", 1e9))
-        row["roofline_fraction"] = round(roof_ms / best, 3) if best > 0 else None
         row["speedup_vs_nccl"] = round(row["nccl_allreduce_div_ms"] / best, 2)
         out.append(row)
         if rank == 0:

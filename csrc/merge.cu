@@ -280,18 +280,29 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
   int dev = 0;
   KML_CUDA(cudaGetDevice(&dev));
   auto kernel = use_mc ? kavg_merge_kernel<true> : kavg_merge_kernel<false>;
+  // launch shape: tunable for experiments (KUBEML_MERGE_THREADS in {128,256,512},
+  // KUBEML_MERGE_CTAS_PER_SM); the grid must stay co-resident (cooperative launch checks it)
+  static int threads = 0, ctas_per_sm = 0;
+  if (threads == 0) {
+    const char* e = getenv("KUBEML_MERGE_THREADS");
+    threads = e ? atoi(e) : kThreads;
+    if (threads != 128 && threads != 256 && threads != 512) threads = kThreads;
+    const char* c = getenv("KUBEML_MERGE_CTAS_PER_SM");
+    ctas_per_sm = c ? atoi(c) : 2;
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+  }
   static int occ[2] = {0, 0};
   if (occ[use_mc] == 0) {
     int o = 0;
-    KML_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, kThreads, 0));
+    KML_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, threads, 0));
     occ[use_mc] = o > 0 ? o : 1;
   }
   const size_t n4 = p.n_f32 / 4;
-  int max_blocks = kml::num_sms() * (occ[use_mc] > 2 ? 2 : occ[use_mc]);
-  size_t want = (n4 + kThreads - 1) / kThreads;
+  int max_blocks = kml::num_sms() * (occ[use_mc] > ctas_per_sm ? ctas_per_sm : occ[use_mc]);
+  size_t want = (n4 + threads - 1) / threads;
   int blocks = static_cast<int>(want < static_cast<size_t>(max_blocks) ? (want ? want : 1) : max_blocks);
   void* args[] = {&p};
-  KML_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3(blocks), dim3(kThreads), args, 0,
+  KML_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3(blocks), dim3(threads), args, 0,
                                        static_cast<cudaStream_t>(stream)));
   kml::count_launch();
   return 0;
