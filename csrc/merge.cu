@@ -115,12 +115,61 @@ __device__ __forceinline__ void reduce_range(const float4* const* src, float4* c
   }
 }
 
-template <bool kMcast>
+// Words 16.. of a rank's signal pad: state of the intra-GPU barrier of the regular-launch variant.
+struct LocalBarrier {
+  unsigned count;         // CTA arrivals, monotonically increasing across launches
+  unsigned release;       // barriers completed, monotonically increasing
+  unsigned count_base;    // value of `count` when the current launch started
+  unsigned release_base;  // value of `release` when the current launch started
+};
+
+template <bool kMcast, bool kCoop>
 __global__ void __launch_bounds__(kThreads)
 kavg_merge_kernel(const kml_merge_params p) {
   __shared__ const float4* s_src[KML_MAX_RANKS];
   __shared__ float4* s_dst[KML_MAX_RANKS];
-  cg::grid_group grid = cg::this_grid();
+  __shared__ unsigned s_cbase, s_rbase;
+  // Two ways to synchronise the grid with itself and with the other ranks:
+  //  kCoop  cooperative launch: grid.sync / flag exchange by one thread / grid.sync (used when the
+  //         caller provides no signal pad, i.e. the single-GPU emulation in the tests);
+  //  !kCoop regular launch (a cooperative launch costs several microseconds on this part): CTAs
+  //         arrive on a counter in the rank's own signal pad, the last one to arrive performs the
+  //         cross-rank flag exchange on behalf of the GPU and then releases the others.  The grid
+  //         is sized to be co-resident, so the spin cannot deadlock.
+  LocalBarrier* lb = kCoop ? nullptr : reinterpret_cast<LocalBarrier*>(p.flags[p.my_rank] + 2 * KML_MAX_RANKS);
+  if (!kCoop && threadIdx.x == 0) {
+    s_cbase = *reinterpret_cast<volatile unsigned*>(&lb->count_base);
+    s_rbase = *reinterpret_cast<volatile unsigned*>(&lb->release_base);
+  }
+  unsigned nbar = 0;
+  auto full_barrier = [&](int rank_phase /* -1: this GPU only */) {
+    ++nbar;
+    if constexpr (kCoop) {
+      cg::grid_group grid = cg::this_grid();
+      grid.sync();
+      if (rank_phase >= 0) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) rank_barrier(p, rank_phase, p.generation);
+        grid.sync();
+      }
+    } else {
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned arrived = atomicAdd(&lb->count, 1u) + 1u - s_cbase;
+        if (arrived == nbar * gridDim.x) {
+          if (rank_phase >= 0) rank_barrier(p, rank_phase, p.generation);
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&lb->release), "r"(s_rbase + nbar) : "memory");
+        } else {
+          unsigned v;
+          do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&lb->release) : "memory");
+          } while (v - s_rbase < nbar);
+        }
+        __threadfence_system();
+      }
+      __syncthreads();
+    }
+  };
   const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
   const size_t n4 = p.n_f32 / 4;
@@ -149,13 +198,8 @@ kavg_merge_kernel(const kml_merge_params p) {
     }
   }
 
-  if (sync_ranks) {
-    grid.sync();
-    if (tid == 0) rank_barrier(p, 0, p.generation);
-    grid.sync();
-  } else if (p.fuse_sgd) {
-    grid.sync();
-  }
+  if (sync_ranks) full_barrier(0);
+  else if (p.fuse_sgd) full_barrier(-1);
 
   // ---- phase 1: reduce my slice, write everyone -----------------------------------------------
   int nparts = __popc(p.participants);
@@ -231,13 +275,8 @@ kavg_merge_kernel(const kml_merge_params p) {
     for (size_t i = tid; i < nsgd4; i += nthreads) __stcs(m + i, z);
   }
 
-  if (sync_ranks) {
-    grid.sync();
-    if (tid == 0) rank_barrier(p, 1, p.generation);
-    grid.sync();
-  } else if (p.w_bf16) {
-    grid.sync();
-  }
+  if (sync_ranks) full_barrier(1);
+  else if (p.w_bf16) full_barrier(-1);
 
   // ---- phase 3: refresh the local bf16 tensor-core copy of the merged parameters ---------------
   if (p.w_bf16) {
@@ -252,6 +291,11 @@ kavg_merge_kernel(const kml_merge_params p) {
       r.y = *reinterpret_cast<uint32_t*>(&b);
       wb[i] = r;
     }
+  }
+  if (!kCoop && nbar && blockIdx.x == 0 && threadIdx.x == 0) {
+    // every CTA read the bases before its first arrival and everyone has arrived nbar times
+    lb->count_base = s_cbase + nbar * gridDim.x;
+    lb->release_base = s_rbase + nbar;
   }
 }
 
@@ -279,7 +323,16 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
 
   int dev = 0;
   KML_CUDA(cudaGetDevice(&dev));
-  auto kernel = use_mc ? kavg_merge_kernel<true> : kavg_merge_kernel<false>;
+  static int force_coop = -1;
+  if (force_coop < 0) {
+    // measured on 2xB200: with ~300 CTAs the counter/spin barrier is slower than grid.sync
+    // (LeNet-size merge 34 us vs 23 us), so the cooperative variant stays the default
+    const char* e = getenv("KUBEML_MERGE_COOP");
+    force_coop = (e && e[0] == '0') ? 0 : 1;
+  }
+  const bool coop = force_coop || p.flags[p.my_rank] == nullptr;
+  auto kernel = coop ? (use_mc ? kavg_merge_kernel<true, true> : kavg_merge_kernel<false, true>)
+                     : (use_mc ? kavg_merge_kernel<true, false> : kavg_merge_kernel<false, false>);
   // launch shape: tunable for experiments (KUBEML_MERGE_THREADS in {128,256,512},
   // KUBEML_MERGE_CTAS_PER_SM); the grid must stay co-resident (cooperative launch checks it)
   static int threads = 0, ctas_per_sm = 0;
@@ -291,19 +344,25 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
     ctas_per_sm = c ? atoi(c) : 2;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
-  static int occ[2] = {0, 0};
-  if (occ[use_mc] == 0) {
+  static int occ[4] = {0, 0, 0, 0};
+  const int vi = (use_mc ? 1 : 0) + (coop ? 2 : 0);
+  if (occ[vi] == 0) {
     int o = 0;
     KML_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, threads, 0));
-    occ[use_mc] = o > 0 ? o : 1;
+    occ[vi] = o > 0 ? o : 1;
   }
   const size_t n4 = p.n_f32 / 4;
-  int max_blocks = kml::num_sms() * (occ[use_mc] > ctas_per_sm ? ctas_per_sm : occ[use_mc]);
+  int max_blocks = kml::num_sms() * (occ[vi] > ctas_per_sm ? ctas_per_sm : occ[vi]);
   size_t want = (n4 + threads - 1) / threads;
   int blocks = static_cast<int>(want < static_cast<size_t>(max_blocks) ? (want ? want : 1) : max_blocks);
-  void* args[] = {&p};
-  KML_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3(blocks), dim3(threads), args, 0,
-                                       static_cast<cudaStream_t>(stream)));
+  if (coop) {
+    void* args[] = {&p};
+    KML_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3(blocks), dim3(threads), args, 0,
+                                         static_cast<cudaStream_t>(stream)));
+  } else {
+    kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    KML_CUDA(cudaGetLastError());
+  }
   kml::count_launch();
   return 0;
 }
