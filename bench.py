@@ -217,7 +217,7 @@ def main() -> int:
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=16)
-    ap.add_argument("--impl", default="own", choices=["own", "reference", "ref-torch"])
+    ap.add_argument("--impl", default="own", choices=["own", "reference", "ref-torch", "ddp"])
     ap.add_argument("--model-impl", default=os.environ.get("KUBEML_RESNET_IMPL", "auto"),
                     choices=["auto", "native", "compat"])
     args = ap.parse_args()
@@ -225,9 +225,9 @@ def main() -> int:
         args.warmup = 3
     if args.impl == "reference":
         return run_reference(args)
-    if args.impl == "ref-torch":
+    if args.impl in ("ref-torch", "ddp"):
         from baseline.ref_torch import run_ref_torch
-        return run_ref_torch(args)
+        return run_ref_torch(args, ddp=args.impl == "ddp")
     return run_own(args)
 
 

@@ -113,9 +113,10 @@ class Buffers:
     def on_side(self):
         import contextlib
         import os
-        # measured on B200 (profiles/): inside a CUDA graph the 36 fork/join edges cost more than the
-        # overlap returns (3.04 vs 2.72 ms per ResNet-34 step), so the side stream is opt-in
-        if self.device.type != "cuda" or os.environ.get("KUBEML_SIDE_STREAM", "0") != "1":
+        # measured on B200: a loss while BatchNorm used cooperative launches (which cannot overlap
+        # anything: 3.04 vs 2.72 ms per ResNet-34 step), a gain since it uses a software grid barrier
+        # and launches are programmatic-dependent (1.82 vs 1.95 ms)
+        if self.device.type != "cuda" or os.environ.get("KUBEML_SIDE_STREAM", "1") == "0":
             return contextlib.nullcontext()
         if getattr(self, "_side", None) is None:
             self._side = torch.cuda.Stream(device=self.device)

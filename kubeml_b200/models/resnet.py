@@ -92,13 +92,16 @@ class NativeResNet(NativeNet):
         S.update(c1=c1s, a1=a1, p1=p1)
         h = p1
         for tag, blk in self._blocks:
+            idn, tds = h, None
+            if blk.downsample is not None:       # the projection shortcut runs next to the main branch
+                with B.on_side():
+                    td = conv_forward(blk.downsample[0], h, B, tag + ".cd", allow_slabs=True)
+                    idn, tds = bn_forward(blk.downsample[1], td, B, tag + ".bnd", train, relu=False)
             t1 = conv_forward(blk.conv1, h, B, tag + ".c1", allow_slabs=True)
             a, t1s = bn_forward(blk.bn1, t1, B, tag + ".bn1", train, relu=True)
             t2 = conv_forward(blk.conv2, a, B, tag + ".c2", allow_slabs=True)
-            idn, tds = h, None
             if blk.downsample is not None:
-                td = conv_forward(blk.downsample[0], h, B, tag + ".cd", allow_slabs=True)
-                idn, tds = bn_forward(blk.downsample[1], td, B, tag + ".bnd", train, relu=False)
+                B.join_side()
             out, t2s = bn_forward(blk.bn2, t2, B, tag + ".bn2", train, relu=True, res=idn)
             S["blocks"].append((h, t1s, a, t2s, tds, out))
             h = out
