@@ -448,9 +448,148 @@ image_prep_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict
   }
 }
 
+
+// ---------------------------------------------------------------------------------- VGG-style layers
+// g = scale * dy * (y > 0): gradient through a ReLU that was fused into the producing GEMM's epilogue;
+// with y the *dropped* output and scale = 1/(1-p) it is also the gradient through ReLU -> Dropout
+// (a kept, positive activation is exactly a positive dropped output).
+__global__ void __launch_bounds__(kThreads)
+relu_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ g,
+                float scale, size_t n8) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    float a[8], b[8];
+    ld8(dy + i * 8, a);
+    ld8(y + i * 8, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = b[j] > 0.f ? a[j] * scale : 0.f;
+    st8(g + i * 8, a);
+  }
+}
+
+__device__ __forceinline__ uint32_t mix32(uint64_t z) {        // splitmix64 finaliser
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  return static_cast<uint32_t>((z ^ (z >> 31)) >> 32);
+}
+
+// Inverted dropout.  The keep-mask is drawn in the kernel from (device-resident step counter, layer id,
+// element index), stored as bytes for the backward pass; the counter is bumped on the device so a
+// CUDA-graph replay draws a fresh mask every step.
+__global__ void __launch_bounds__(kThreads)
+dropout_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ mask,
+                   unsigned long long* __restrict__ counter, unsigned int layer, float p, size_t n) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const unsigned long long step = *counter;
+  const float scale = 1.f / (1.f - p);
+  const uint32_t thresh = static_cast<uint32_t>(p * 4294967296.0);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const uint32_t r = mix32((step << 40) ^ (static_cast<unsigned long long>(layer) << 34) ^ i);
+    const bool keep = r >= thresh;
+    if (mask) mask[i] = keep ? 1 : 0;
+    y[i] = __float2bfloat16_rn(keep ? __bfloat162float(x[i]) * scale : 0.f);
+  }
+}
+__global__ void __launch_bounds__(kThreads)
+dropout_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const unsigned char* __restrict__ mask,
+                   __nv_bfloat16* __restrict__ dx, float p, size_t n) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const float scale = 1.f / (1.f - p);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    dx[i] = __float2bfloat16_rn(mask[i] ? __bfloat162float(dy[i]) * scale : 0.f);
+}
+__global__ void bump_counter_kernel(unsigned long long* counter) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  if (threadIdx.x == 0 && blockIdx.x == 0) *counter += 1;
+}
+
+// AdaptiveAvgPool2d((R,R)) on a 1x1 feature map is a broadcast: y[n][c*R2 + r] = x[n][c]
+// (torchvision vgg on 32x32 inputs), and its gradient a sum over the R2 copies.
+__global__ void __launch_bounds__(kThreads)
+replicate_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int C, int R2) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const size_t total = static_cast<size_t>(N) * C * R2;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    y[i] = x[i / R2];
+}
+__global__ void __launch_bounds__(kThreads)
+replicate_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int C, int R2) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const size_t total = static_cast<size_t>(N) * C;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    float acc = 0.f;
+    for (int r = 0; r < R2; ++r) acc += __bfloat162float(dy[i * R2 + r]);
+    dx[i] = __float2bfloat16_rn(acc);
+  }
+}
+
 }  // namespace
 
 extern "C" {
+
+int kml_relu_bwd(const void* dy, const void* y, void* g, float scale, size_t n, void* stream) {
+  KML_CHECK(dy && y && g && n % 8 == 0, "kml_relu_bwd: bad arguments (n must be a multiple of 8)");
+  KML_CUDA(kml::launch_pdl(relu_bwd_kernel, dim3(grid_for(n / 8)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream),
+                           static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y),
+                           static_cast<__nv_bfloat16*>(g), scale, n / 8));
+  kml::count_launch();
+  return 0;
+}
+
+int kml_dropout_fwd(const void* x, void* y, void* mask_u8, unsigned long long* counter, unsigned int layer, float p,
+                    size_t n, void* stream) {
+  KML_CHECK(x && y && counter && p >= 0.f && p < 1.f, "kml_dropout_fwd: bad arguments");
+  KML_CUDA(kml::launch_pdl(dropout_fwd_kernel, dim3(grid_for(n)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream),
+                           static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y),
+                           static_cast<unsigned char*>(mask_u8), counter, layer, p, n));
+  kml::count_launch();
+  return 0;
+}
+
+int kml_dropout_bwd(const void* dy, const void* mask_u8, void* dx, float p, size_t n, void* stream) {
+  KML_CHECK(dy && mask_u8 && dx, "kml_dropout_bwd: null pointer");
+  KML_CUDA(kml::launch_pdl(dropout_bwd_kernel, dim3(grid_for(n)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream),
+                           static_cast<const __nv_bfloat16*>(dy), static_cast<const unsigned char*>(mask_u8),
+                           static_cast<__nv_bfloat16*>(dx), p, n));
+  kml::count_launch();
+  return 0;
+}
+
+int kml_bump_counter(unsigned long long* counter, void* stream) {
+  KML_CHECK(counter, "kml_bump_counter: null pointer");
+  KML_CUDA(kml::launch_pdl(bump_counter_kernel, dim3(1), dim3(32), 0, static_cast<cudaStream_t>(stream), counter));
+  kml::count_launch();
+  return 0;
+}
+
+int kml_replicate_fwd(const void* x, void* y, int N, int C, int R2, void* stream) {
+  KML_CHECK(x && y && R2 > 0, "kml_replicate_fwd: bad arguments");
+  KML_CUDA(kml::launch_pdl(replicate_fwd_kernel, dim3(grid_for(static_cast<size_t>(N) * C * R2)), dim3(kThreads), 0,
+                           static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x),
+                           static_cast<__nv_bfloat16*>(y), N, C, R2));
+  kml::count_launch();
+  return 0;
+}
+
+int kml_replicate_bwd(const void* dy, void* dx, int N, int C, int R2, void* stream) {
+  KML_CHECK(dy && dx && R2 > 0, "kml_replicate_bwd: bad arguments");
+  KML_CUDA(kml::launch_pdl(replicate_bwd_kernel, dim3(grid_for(static_cast<size_t>(N) * C)), dim3(kThreads), 0,
+                           static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dy),
+                           static_cast<__nv_bfloat16*>(dx), N, C, R2));
+  kml::count_launch();
+  return 0;
+}
 
 int kml_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride, int pad,
                     void* stream) {

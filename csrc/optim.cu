@@ -46,13 +46,22 @@ sgd_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __restr
   }
 }
 
+// step_dev == nullptr: bias corrections come from the host (bc1, bc2_sqrt).  Otherwise the step count
+// lives on the device ({count, ticket}): every block reads count at its start, the last block to
+// finish publishes count+1 — so a CUDA-graph replay of the step advances the bias correction.
 template <bool kBf16>
 __global__ void __launch_bounds__(kThreads)
 adam_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __restrict__ m1, float4* __restrict__ m2,
             uint2* __restrict__ wb, size_t n4, float lr, float b1, float b2, float eps, float wd, float bc1,
-            float bc2_sqrt) {
+            float bc2_sqrt, int* __restrict__ step_dev) {
   kml::pdl_launch_dependents();
   kml::pdl_wait();
+  int t = 0;
+  if (step_dev) {
+    t = *reinterpret_cast<volatile int*>(step_dev) + 1;
+    bc1 = 1.f - powf(b1, static_cast<float>(t));
+    bc2_sqrt = sqrtf(1.f - powf(b2, static_cast<float>(t)));
+  }
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   const float step_size = lr / bc1;
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -68,6 +77,16 @@ adam_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __rest
     }
     w[i] = wv; m1[i] = a; m2[i] = b;
     if constexpr (kBf16) wb[i] = pack_bf16x4(wv);
+  }
+  if (step_dev) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(step_dev + 1, 1) == static_cast<int>(gridDim.x) - 1) {
+        step_dev[1] = 0;
+        step_dev[0] = t;
+      }
+    }
   }
 }
 
@@ -128,25 +147,44 @@ int kml_sgd_step(float* w, const float* g, float* mbuf, size_t n, float lr, floa
   return 0;
 }
 
+static int adam_launch(float* w, const float* g, float* m1, float* m2, size_t n, float lr, float b1, float b2,
+                       float eps, float wd, float bc1, float bc2s, int* step_dev, void* w_bf16, void* stream) {
+  if (n == 0) return 0;
+  const size_t n4 = n / 4;
+  auto s = static_cast<cudaStream_t>(stream);
+  const int grid = grid_for(n4);
+  if (w_bf16)
+    KML_CUDA(kml::launch_pdl(adam_kernel<true>, dim3(grid), dim3(kThreads), 0, s, reinterpret_cast<float4*>(w),
+                             reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(m1),
+                             reinterpret_cast<float4*>(m2), reinterpret_cast<uint2*>(w_bf16), n4, lr, b1, b2, eps, wd,
+                             bc1, bc2s, step_dev));
+  else
+    KML_CUDA(kml::launch_pdl(adam_kernel<false>, dim3(grid), dim3(kThreads), 0, s, reinterpret_cast<float4*>(w),
+                             reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(m1),
+                             reinterpret_cast<float4*>(m2), static_cast<uint2*>(nullptr), n4, lr, b1, b2, eps, wd, bc1,
+                             bc2s, step_dev));
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
 int kml_adam_step(float* w, const float* g, float* m1, float* m2, size_t n, float lr, float b1, float b2, float eps,
                   float wd, int step, void* w_bf16, void* stream) {
   KML_CHECK(w && g && m1 && m2, "kml_adam_step: null pointer");
   KML_CHECK(n % 4 == 0 && aligned16(w) && aligned16(g) && aligned16(m1) && aligned16(m2),
             "kml_adam_step: buffers must be 16-byte aligned, n %% 4 == 0");
   KML_CHECK(step >= 1, "kml_adam_step: step starts at 1");
-  if (n == 0) return 0;
-  const size_t n4 = n / 4;
   const float bc1 = 1.f - powf(b1, static_cast<float>(step));
   const float bc2s = sqrtf(1.f - powf(b2, static_cast<float>(step)));
-  auto s = static_cast<cudaStream_t>(stream);
-  const int grid = grid_for(n4);
-  if (w_bf16)
-    KML_CUDA(kml::launch_pdl(adam_kernel<true>, dim3(grid), dim3(kThreads), 0, s, reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(m1), reinterpret_cast<float4*>(m2), reinterpret_cast<uint2*>(w_bf16), n4, lr, b1, b2, eps, wd, bc1, bc2s));
-  else
-    KML_CUDA(kml::launch_pdl(adam_kernel<false>, dim3(grid), dim3(kThreads), 0, s, reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(m1), reinterpret_cast<float4*>(m2), nullptr, n4, lr, b1, b2, eps, wd, bc1, bc2s));
-  KML_CUDA(cudaGetLastError());
-  kml::count_launch();
-  return 0;
+  return adam_launch(w, g, m1, m2, n, lr, b1, b2, eps, wd, bc1, bc2s, nullptr, w_bf16, stream);
+}
+
+int kml_adam_step_dev(float* w, const float* g, float* m1, float* m2, size_t n, float lr, float b1, float b2,
+                      float eps, float wd, int* step_dev, void* w_bf16, void* stream) {
+  KML_CHECK(w && g && m1 && m2 && step_dev, "kml_adam_step_dev: null pointer");
+  KML_CHECK(n % 4 == 0 && aligned16(w) && aligned16(g) && aligned16(m1) && aligned16(m2),
+            "kml_adam_step_dev: buffers must be 16-byte aligned, n %% 4 == 0");
+  return adam_launch(w, g, m1, m2, n, lr, b1, b2, eps, wd, 1.f, 1.f, step_dev, w_bf16, stream);
 }
 
 int kml_cast_f32_to_bf16(const float* src, void* dst, size_t n, void* stream) {

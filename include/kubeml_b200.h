@@ -104,6 +104,11 @@ int kml_sgd_step(float* w, const float* g, float* momentum_buf, size_t n, float 
 int kml_adam_step(float* w, const float* g, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
                   float beta1, float beta2, float eps, float weight_decay, int step, void* w_bf16,
                   void* stream);
+/* Same update with the step count on the device: step_dev = int[2] {steps done, internal ticket},
+ * both zero at (re)set; the kernel advances it, so a CUDA-graph replay keeps the bias correction right. */
+int kml_adam_step_dev(float* w, const float* g, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
+                      float beta1, float beta2, float eps, float weight_decay, int* step_dev, void* w_bf16,
+                      void* stream);
 int kml_cast_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* stream);
 int kml_fill_f32(float* dst, float value, size_t n, void* stream);
 
@@ -189,6 +194,15 @@ int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, in
                int stride, int pad, int ldk, void* stream);
 int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld, void* stream);
 int kml_pack_rows_bf16(const float* src, void* dst_bf16, int rows, int cols, int ld, void* stream);
+/* VGG-style layers (ReLU fused in the producing GEMM, Dropout p=0.5 in the classifier, the
+ * AdaptiveAvgPool2d((7,7)) of torchvision vgg on a 1x1 map; ml/experiments/kubeml/function_vgg11.py). */
+int kml_relu_bwd(const void* dy, const void* y, void* g, float scale, size_t n, void* stream);
+int kml_dropout_fwd(const void* x, void* y, void* mask_u8, unsigned long long* counter, unsigned int layer,
+                    float p, size_t n, void* stream);
+int kml_dropout_bwd(const void* dy, const void* mask_u8, void* dx, float p, size_t n, void* stream);
+int kml_bump_counter(unsigned long long* counter, void* stream);
+int kml_replicate_fwd(const void* x, void* y, int N, int C, int R2, void* stream);
+int kml_replicate_bwd(const void* dy, void* dx, int N, int C, int R2, void* stream);
 /* uint8 NHWC images -> normalised bf16 NHWC; aug[n] = flip | dy<<8 | dx<<16 (crop offsets in
  * [0, 2*pad]) or NULL (function_resnet34.py:17-30 on the GPU). mean3/std3 are host arrays. */
 int kml_image_prep(const void* x_u8, void* y_bf16, const int* aug, int N, int H, int W, int C, int pad,

@@ -85,6 +85,8 @@ def _declare(lib) -> None:
         c_int, c_void_p, c_void_p)
     sig("kml_adam_step", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float,
         c_float, c_float, c_float, c_int, c_void_p, c_void_p)
+    sig("kml_adam_step_dev", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float,
+        c_float, c_float, c_float, c_void_p, c_void_p, c_void_p)
     sig("kml_cast_f32_to_bf16", c_int, c_void_p, c_void_p, c_size_t, c_void_p)
     sig("kml_fill_f32", c_int, c_void_p, c_float, c_size_t, c_void_p)
     sig("kml_softmax_ce_scratch_bytes", c_size_t, c_int)
@@ -120,6 +122,12 @@ def _declare(lib) -> None:
         c_int, c_int, c_void_p)
     sig("kml_colsum_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_longlong, c_void_p)
     sig("kml_pack_rows_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
+    sig("kml_relu_bwd", c_int, c_void_p, c_void_p, c_void_p, c_float, c_size_t, c_void_p)
+    sig("kml_dropout_fwd", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_uint32, c_float, c_size_t, c_void_p)
+    sig("kml_dropout_bwd", c_int, c_void_p, c_void_p, c_void_p, c_float, c_size_t, c_void_p)
+    sig("kml_bump_counter", c_int, c_void_p, c_void_p)
+    sig("kml_replicate_fwd", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
+    sig("kml_replicate_bwd", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
     sig("kml_image_prep", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
         POINTER(c_float), POINTER(c_float), c_void_p)
     for name, s in _EXTRA_SIGS.items():

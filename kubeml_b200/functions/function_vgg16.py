@@ -2,8 +2,10 @@
 function written against an older KubeModel API (`train(self, model, dataset)`, which no longer
 matches KubeModel.__train; ml/experiments/kubeml/function_vgg11.py:50); this is the same
 recipe (torchvision VGG, Adam, CrossEntropy, accuracy = correct/total) against the current API.
-Compute runs on the compatibility path (stock torch modules under bf16 autocast, weights in the
-arena, flat Adam, fused loss, fused K-AVG merge of the 138 M parameters)."""
+The network is `kubeml_b200.models.vgg16` (hand-written kernels, NHWC bf16 activations, weights in
+the arena, one-launch Adam with its step count on the device, fused loss, fused K-AVG merge of the
+138 M parameters); KUBEML_VGG_IMPL=torch selects the stock torchvision module under bf16 autocast
+(the path any user-supplied nn.Module takes)."""
 from __future__ import annotations
 
 import os
@@ -31,7 +33,7 @@ class KubeVGG(KubeModel):
         return Adam(self.parameters(), lr=self.lr)
 
     def _forward(self, x):
-        if x.device.type != "cuda":
+        if getattr(self._network, "native", False) or x.device.type != "cuda":
             return self(x)
         with torch.autocast("cuda", dtype=torch.bfloat16):
             return self(x)
@@ -39,14 +41,16 @@ class KubeVGG(KubeModel):
     def train(self, batch, batch_index):
         x, y = batch
         self.optimizer.zero_grad()
-        loss = ops.cross_entropy(self._forward(x), y)
+        out = self._forward(x)
+        loss = ops.cross_entropy(out if out.dtype == torch.bfloat16 else out.float(), y)
         loss.backward()
         self.optimizer.step()
         return loss.detach()
 
     def validate(self, batch, batch_index) -> Tuple[torch.Tensor, torch.Tensor]:
         x, y = batch
-        loss, correct = ops.accuracy_count(self._forward(x), y)
+        out = self._forward(x)
+        loss, correct = ops.accuracy_count(out if out.dtype == torch.bfloat16 else out.float(), y)
         return correct * (100.0 / max(int(y.shape[0]), 1)), loss       # correct/total, function_vgg11.py:96
 
     def infer(self, data):
@@ -57,6 +61,9 @@ class KubeVGG(KubeModel):
 
 
 def build_network(name: str = "vgg16", num_classes: int = 1000):
+    if os.environ.get("KUBEML_VGG_IMPL", "native") != "torch":
+        from kubeml_b200.models import vgg as native_vgg
+        return getattr(native_vgg, name)(num_classes=num_classes)
     import torchvision.models as tvm
     net = getattr(tvm, name)(num_classes=num_classes)
     return net.to(memory_format=torch.channels_last)
@@ -65,4 +72,5 @@ def build_network(name: str = "vgg16", num_classes: int = 1000):
 def main():
     net = build_network(os.environ.get("KUBEML_VGG_ARCH", "vgg16"), int(os.environ.get("KUBEML_VGG_CLASSES", "1000")))
     ds = Cifar100Dataset(os.environ.get("KUBEML_VGG_DATASET", "cifar100"))
+    ds.native = bool(getattr(net, "native", False))
     return KubeVGG(net, ds, gpu=torch.cuda.is_available()).start()

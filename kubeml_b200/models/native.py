@@ -245,6 +245,14 @@ class NativeNet(nn.Module):
     def _backward_impl(self, dlogits: torch.Tensor) -> None:
         raise NotImplementedError
 
+    def load_state_dict(self, *args, **kwargs):
+        """Host-path syncs (TensorStore / collectives) load merged weights through here: the
+        bf16 tensor-core copy has to follow the fp32 masters."""
+        out = super().load_state_dict(*args, **kwargs)
+        if self._arena is not None:
+            self._arena.refresh_bf16()
+        return out
+
     def _apply(self, fn, recurse=True):
         # moving the module (.to(device)) invalidates arena slices and cached buffers
         out = super()._apply(fn, recurse)

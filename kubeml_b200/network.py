@@ -144,6 +144,13 @@ class KubeModel(ABC):
     # ---- optimizer (network.py:99-138) ---------------------------------------------------------
     def _config_optimizer(self) -> None:
         self.optimizer = self.configure_optimizers()
+        # A native network keeps bf16 tensor-core copies of its weights that only the flat (arena)
+        # optimizers maintain: on the host-sync path give it its private arena up front.
+        net = self._network
+        if getattr(net, "native", False) and hasattr(self.optimizer, "attach_arena") \
+                and getattr(self._sync, "arena", None) is None:
+            net._ensure_arena()
+            self.optimizer.attach_arena(net._arena)
 
     def _reset_optimizer_state(self) -> None:
         """Momentum & co. are discarded at every sync: state carried over from a pre-merge

@@ -44,7 +44,15 @@ def sgd_step_(w: torch.Tensor, g: torch.Tensor, momentum_buf: Optional[torch.Ten
 
 def adam_step_(w: torch.Tensor, g: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor,
                step: int, lr: float, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8,
-               weight_decay: float = 0.0, w_bf16: Optional[torch.Tensor] = None) -> None:
+               weight_decay: float = 0.0, w_bf16: Optional[torch.Tensor] = None,
+               step_dev: Optional[torch.Tensor] = None) -> None:
+    """`step_dev` (int32[2] on the device, zero at reset) replaces the host `step`: the kernel keeps
+    the count itself, which is what a CUDA-graph replay needs."""
+    if w.is_cuda and step_dev is not None:
+        _native.check(_native.lib().kml_adam_step_dev(
+            w.data_ptr(), g.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), w.numel(), lr, betas[0], betas[1],
+            eps, weight_decay, step_dev.data_ptr(), _ptr(w_bf16), _native.stream_ptr()), "kml_adam_step_dev")
+        return
     if w.is_cuda:
         lib = _native.lib()
         _native.check(lib.kml_adam_step(w.data_ptr(), g.data_ptr(), exp_avg.data_ptr(),

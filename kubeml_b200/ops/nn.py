@@ -242,3 +242,58 @@ def image_prep(x_u8, y, aug, pad: int, mean: Tuple[float, float, float], std: Tu
             out[n] = padded[pad + dy: pad + dy + H, pad + dxo: pad + dxo + W]
         xf = out
     y.copy_((xf - torch.tensor(mean)) / torch.tensor(std))
+
+
+def relu_bwd(dy, y, g, scale: float = 1.0) -> None:
+    """g = scale * dy * (y > 0)."""
+    if dy.is_cuda:
+        _native.check(_native.lib().kml_relu_bwd(dy.data_ptr(), y.data_ptr(), g.data_ptr(), scale, dy.numel(),
+                                                 _native.stream_ptr()), "kml_relu_bwd")
+        return
+    g.copy_(dy.float() * (y.float() > 0) * scale)
+
+
+def dropout_fwd(x, y, mask, counter, layer: int, p: float) -> None:
+    """Inverted dropout; `counter` is a device int64 the caller bumps once per step (`bump_counter`)."""
+    if x.is_cuda:
+        _native.check(_native.lib().kml_dropout_fwd(x.data_ptr(), y.data_ptr(), _ptr(mask), counter.data_ptr(), layer,
+                                                    p, x.numel(), _native.stream_ptr()), "kml_dropout_fwd")
+        return
+    keep = torch.rand(x.shape) >= p
+    if mask is not None:
+        mask.copy_(keep.to(torch.uint8))
+    y.copy_(x.float() * keep / (1.0 - p))
+
+
+def dropout_bwd(dy, mask, dx, p: float) -> None:
+    if dy.is_cuda:
+        _native.check(_native.lib().kml_dropout_bwd(dy.data_ptr(), mask.data_ptr(), dx.data_ptr(), p, dy.numel(),
+                                                    _native.stream_ptr()), "kml_dropout_bwd")
+        return
+    dx.copy_(dy.float() * mask.float() / (1.0 - p))
+
+
+def bump_counter(counter) -> None:
+    if counter.is_cuda:
+        _native.check(_native.lib().kml_bump_counter(counter.data_ptr(), _native.stream_ptr()), "kml_bump_counter")
+        return
+    counter.add_(1)
+
+
+def replicate_fwd(x, y, r2: int) -> None:
+    """y[n, c*r2 + r] = x[n, c]: AdaptiveAvgPool2d((R,R)) + flatten of a 1x1 feature map."""
+    N, C = x.shape
+    if x.is_cuda:
+        _native.check(_native.lib().kml_replicate_fwd(x.data_ptr(), y.data_ptr(), N, C, r2, _native.stream_ptr()),
+                      "kml_replicate_fwd")
+        return
+    y.copy_(x.unsqueeze(2).expand(N, C, r2).reshape(N, C * r2))
+
+
+def replicate_bwd(dy, dx, r2: int) -> None:
+    N, C = dx.shape
+    if dy.is_cuda:
+        _native.check(_native.lib().kml_replicate_bwd(dy.data_ptr(), dx.data_ptr(), N, C, r2, _native.stream_ptr()),
+                      "kml_replicate_bwd")
+        return
+    dx.copy_(dy.float().view(N, C, r2).sum(2))

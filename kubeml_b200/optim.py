@@ -81,6 +81,8 @@ class _FlatOptimizer:
             if p.grad is not None:
                 if set_to_none:
                     p.grad = None
+                elif p.grad._is_view():
+                    p.grad.zero_()
                 else:
                     p.grad.detach_().zero_()
 
@@ -166,12 +168,17 @@ class Adam(_FlatOptimizer):
         self._m: Optional[List[torch.Tensor]] = None
         self._v: Optional[List[torch.Tensor]] = None
 
+    def attach_arena(self, arena) -> None:
+        super().attach_arena(arena)
+        arena.opt_step.zero_()          # a fresh optimizer counts from step 1
+
     def reset_state(self) -> None:
         self._t = 0
         if self._arena is not None:
             n = max(self._arena.layout.n_param, 4)
             ops.fill_(self._arena.state1[:n], 0.0)
             ops.fill_(self._arena.state2[:n], 0.0)
+            self._arena.opt_step.zero_()
         self._m = self._v = None
         self.state = {}
 
@@ -184,7 +191,8 @@ class Adam(_FlatOptimizer):
             w, gr = flat
             n = w.numel()
             ops.adam_step_(w, gr, self._arena.state1[:n], self._arena.state2[:n], self._t, g["lr"],
-                           g["betas"], g["eps"], g["weight_decay"], w_bf16=getattr(self._arena, "wbf16", None))
+                           g["betas"], g["eps"], g["weight_decay"], w_bf16=getattr(self._arena, "wbf16", None),
+                           step_dev=self._arena.opt_step if w.is_cuda else None)
             return
         if self._m is None:
             self._m = [torch.zeros_like(p) for p in self.params]

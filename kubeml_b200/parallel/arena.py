@@ -140,6 +140,7 @@ class WeightArena:
         self.counters = self._view(L.off_i64, (max(L.n_i64, 1),), torch.int64)
         self.flags = self._view(L.off_flags, (SIGNAL_WORDS,), torch.int32)
         self.status = self._view(L.off_status, (1,), torch.int32)
+        self.opt_step = self._view(L.off_status + 16, (2,), torch.int32)     # device-side Adam step count
         self.grads = self._view(L.off_grad, (max(L.n_param, 4),), torch.float32)
         self.state1 = self._view(L.off_state1, (max(L.n_param, 4),), torch.float32)
         self.state2 = self._view(L.off_state2, (max(L.n_param, 4),), torch.float32)

@@ -67,3 +67,24 @@ def test_resnet34_function_one_round(kube_home, monkeypatch):
 def test_smoke_entry():
     import __graft_entry__ as g
     g.smoke()
+
+
+def test_vgg_function_native_round(kube_home, monkeypatch):
+    """BASELINE config 3's function (VGG + Adam) on the native model through a job with K=2."""
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    monkeypatch.setenv("KUBEML_VGG_ARCH", "vgg11")
+    monkeypatch.setenv("KUBEML_VGG_CLASSES", "100")
+    c = Cluster(home=kube_home, max_parallelism=1)
+    rng = np.random.default_rng(0)
+    c.shard_store.create("cifar100", rng.integers(0, 255, (512, 32, 32, 3), dtype=np.uint8),
+                         rng.integers(0, 100, (512,)), rng.integers(0, 255, (64, 32, 32, 3), dtype=np.uint8),
+                         rng.integers(0, 100, (64,)))
+    req = TrainRequest(model_type="vgg", batch_size=32, epochs=2, dataset="cifar100", lr=1e-4,
+                       function_name="vgg16",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=4))
+    h, job = _run(c, req)
+    assert all(np.isfinite(v) for v in h.data.train_loss) and 3.0 < h.data.train_loss[0] < 6.0
+    assert h.data.train_loss[1] <= h.data.train_loss[0] + 0.2
+    assert job.epoch_stats[0]["gpu_launches"] > 0
+    c.shutdown()

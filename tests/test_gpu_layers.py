@@ -237,3 +237,120 @@ def test_splitk_slabs_conv_then_bn(dev, N, H, C, Co, S):
     torch.cuda.synchronize()
     for a, b in zip(res["slabs"], res["dense"]):
         _close(a, b, 2e-2)
+
+
+# ----------------------------------------------------------------------------------- VGG-style layers
+def test_relu_bwd_dropout_replicate(dev):
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(0)
+    n = 128 * 4096
+    dy = torch.randn(n, device=dev).bfloat16()
+    y = torch.randn(n, device=dev).relu().bfloat16()
+    g = torch.empty_like(dy)
+    K.relu_bwd(dy, y, g, 2.0)
+    _close(g, dy.float() * (y.float() > 0) * 2.0, 1e-2)
+    # dropout: keep rate, scaling, mask consistency, a fresh mask after the counter moves
+    x = torch.randn(n, device=dev).bfloat16()
+    out, mask = torch.empty_like(x), torch.empty(n, dtype=torch.uint8, device=dev)
+    cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+    K.dropout_fwd(x, out, mask, cnt, 1, 0.5)
+    keep = mask.float().mean().item()
+    assert 0.49 < keep < 0.51
+    _close(out, x.float() * mask.float() * 2.0, 1e-2)
+    out_b, mask_b = torch.empty_like(x), torch.empty_like(mask)
+    K.dropout_fwd(x, out_b, mask_b, cnt, 2, 0.5)              # another layer, same step
+    assert 0.45 < (mask == mask_b).float().mean().item() < 0.55
+    K.bump_counter(cnt)
+    assert int(cnt) == 1
+    mask_c = torch.empty_like(mask)
+    K.dropout_fwd(x, out_b, mask_c, cnt, 1, 0.5)
+    assert 0.45 < (mask == mask_c).float().mean().item() < 0.55
+    dx = torch.empty_like(x)
+    K.dropout_bwd(dy, mask, dx, 0.5)
+    _close(dx, dy.float() * mask.float() * 2.0, 1e-2)
+    # 49x broadcast and its gradient
+    xs = torch.randn(128, 512, device=dev).bfloat16()
+    rep = torch.empty(128, 512 * 49, device=dev, dtype=torch.bfloat16)
+    K.replicate_fwd(xs, rep, 49)
+    assert torch.equal(rep.view(128, 512, 49), xs.unsqueeze(2).expand(128, 512, 49))
+    dr = torch.randn(128, 512 * 49, device=dev).bfloat16()
+    dxs = torch.empty_like(xs)
+    K.replicate_bwd(dr, dxs, 49)
+    _close(dxs, dr.float().view(128, 512, 49).sum(2), 1e-2)
+
+
+def test_native_vgg11_matches_torchvision(dev):
+    import torchvision
+    from kubeml_b200 import ops
+    from kubeml_b200.models import vgg11
+    torch.manual_seed(0)
+    net = vgg11(num_classes=100, dropout=0.0).to(dev)
+    net._ensure_arena()
+    with torch.no_grad():
+        for p in net.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.bfloat16().float())
+            else:
+                p.uniform_(-0.05, 0.05)
+    net._arena.refresh_bf16()
+    ref = torchvision.models.vgg11(num_classes=100, dropout=0.0).to(dev)
+    ref.load_state_dict(net.state_dict())
+    net.train(); ref.train()
+    x = torch.randn(64, 3, 32, 32, device=dev).bfloat16().float()
+    y = torch.randint(0, 100, (64,), device=dev)
+    out = net(x)
+    loss = ops.cross_entropy(out, y)
+    loss.backward()
+    out_r = ref(x)
+    loss_r = torch.nn.functional.cross_entropy(out_r, y)
+    loss_r.backward()
+    torch.cuda.synchronize()
+    _close(out, out_r, 3e-2)
+    assert abs(loss.item() - loss_r.item()) < 0.02
+    table = []
+    for n, p in ref.named_parameters():
+        g = net._arena.grad(n).flatten().float()
+        table.append((torch.nn.functional.cosine_similarity(g, p.grad.flatten(), dim=0).item(), n))
+    print("\n".join(f"{c:.4f} {n}" for c, n in table))
+    worst = min(table)
+    assert worst[0] > 0.95, f"{worst[1]}: cosine {worst[0]:.4f}"
+    # with dropout the step still runs, draws fresh masks and leaves eval deterministic
+    net2 = vgg11(num_classes=100).to(dev)
+    net2.train()
+    a = net2(x).clone()
+    a.float().sum().backward()
+    b = net2(x).clone()
+    assert not torch.equal(a, b) and int(net2._counter) == 1
+    net2.eval()
+    with torch.no_grad():
+        assert torch.equal(net2(x).clone(), net2(x))
+
+
+def test_adam_device_step_count_survives_graph_replay(dev):
+    """The flat Adam keeps its step count on the device, so replaying a captured step advances the
+    bias correction exactly like eager torch.optim.Adam."""
+    from kubeml_b200 import ops
+    torch.manual_seed(0)
+    n = 1 << 14
+    w0 = torch.randn(n, device=dev)
+    p = torch.nn.Parameter(w0.clone())
+    opt = torch.optim.Adam([p], lr=1e-2, weight_decay=1e-4)
+    w, m, v = w0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    g = torch.randn(n, device=dev)
+    step = torch.zeros(2, dtype=torch.int32, device=dev)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        ops.adam_step_(w, g, m, v, 0, 1e-2, (0.9, 0.999), 1e-8, 1e-4, step_dev=step)      # eager step 1
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            ops.adam_step_(w, g, m, v, 0, 1e-2, (0.9, 0.999), 1e-8, 1e-4, step_dev=step)
+        for _ in range(4):
+            graph.replay()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    for _ in range(5):
+        p.grad = g.clone()
+        opt.step()
+    assert step.tolist() == [5, 0]
+    torch.testing.assert_close(w, p.data, rtol=2e-5, atol=2e-6)

@@ -109,3 +109,52 @@ def test_auto_splits_never_leaves_an_empty_split():
             s = nv.auto_splits(tiles, chunks)
             per = -(-chunks // s)
             assert s >= 1 and (s - 1) * per < chunks
+
+
+def test_vgg11_program_matches_torchvision(fp32_activations):
+    import torchvision
+    from kubeml_b200.models import vgg11
+    torch.manual_seed(0)
+    net = vgg11(num_classes=10, dropout=0.0)
+    net._ensure_arena()
+    with torch.no_grad():
+        for p in net.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.bfloat16().float())
+            else:
+                p.uniform_(-0.1, 0.1)               # non-zero biases so their path is exercised
+    net._arena.refresh_bf16()
+    ref = torchvision.models.vgg11(num_classes=10, dropout=0.0)
+    assert list(net.state_dict().keys()) == list(ref.state_dict().keys())
+    assert all(a.shape == b.shape for a, b in zip(net.state_dict().values(), ref.state_dict().values()))
+    ref.load_state_dict(net.state_dict())
+    net.train(); ref.train()
+    x = torch.randn(4, 3, 32, 32)
+    y = torch.randint(0, 10, (4,))
+    out = net(x)
+    ops.cross_entropy(out, y).backward()
+    out_r = ref(x)
+    torch.nn.functional.cross_entropy(out_r, y).backward()
+    torch.testing.assert_close(out, out_r, rtol=1e-4, atol=1e-4)
+    for n, p in ref.named_parameters():
+        g = net._arena.grad(n)
+        scale = p.grad.abs().max().item() + 1e-12
+        assert (g - p.grad).abs().max().item() / scale < 1e-3, n
+
+
+def test_vgg_dropout_train_and_eval(fp32_activations):
+    from kubeml_b200.models import vgg11
+    torch.manual_seed(0)
+    net = vgg11(num_classes=10, dropout=0.5)
+    net._ensure_arena()
+    x = torch.randn(2, 3, 32, 32)
+    net.train()
+    out = net(x)
+    a = out.detach().clone()                          # the logits buffer is reused by the next step
+    out.float().sum().backward()
+    assert int(net._counter) == 1                     # bumped once per step
+    b = net(x)
+    assert not torch.equal(a, b)                      # fresh mask
+    net.eval()
+    with torch.no_grad():
+        assert torch.equal(net(x), net(x))
