@@ -114,6 +114,9 @@ def run_own(args) -> int:
     os.environ["KUBEML_HOME"] = home
     os.environ.setdefault("KUBEML_RESNET_DATASET", "cifar10")
     os.environ.setdefault("KUBEML_RESNET_IMPL", args.model_impl)
+    vgg = args.model == "vgg16"          # BASELINE.md config 3 (secondary; the headline is resnet34)
+    ds_env = "KUBEML_VGG_DATASET" if vgg else "KUBEML_RESNET_DATASET"
+    ds_prefix = "cifar100" if vgg else "cifar10"
 
     from kubeml_b200.api.types import JobInfo, JobState, TrainOptions, TrainRequest, TrainTask
     from kubeml_b200.runtime.spmd import SpmdRuntime
@@ -130,18 +133,18 @@ def run_own(args) -> int:
         if rank == 0 and not store.exists(name):
             rng = np.random.default_rng(1234)
             x = rng.integers(0, 256, size=(n, 32, 32, 3), dtype=np.uint8)
-            y = rng.integers(0, 10, size=(n,), dtype=np.int64)
+            y = rng.integers(0, 100 if vgg else 10, size=(n,), dtype=np.int64)
             store.create(name, x, y, x[:BATCH * N], y[:BATCH * N])
 
     rt = SpmdRuntime(shard_store=store)
-    make_dataset(f"cifar10_w{args.warmup}", args.warmup)
-    make_dataset(f"cifar10_t{args.steps}", args.steps)
+    make_dataset(f"{ds_prefix}_w{args.warmup}", args.warmup)
+    make_dataset(f"{ds_prefix}_t{args.steps}", args.steps)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
     # stage both datasets in page-locked host memory up front (set-up, not part of a step): the timed
     # region then copies each step's batch host->device from pinned memory
-    for name in (f"cifar10_w{args.warmup}", f"cifar10_t{args.steps}"):
+    for name in (f"{ds_prefix}_w{args.warmup}", f"{ds_prefix}_t{args.steps}"):
         store.pinned(name, "train")
 
     if rank != 0:
@@ -152,15 +155,15 @@ def run_own(args) -> int:
     histories = HistoryStore(os.path.join(home, "history"))
 
     def run_job(dataset: str, resident: bool):
-        req = TrainRequest(model_type="resnet34", batch_size=BATCH, epochs=1, dataset=dataset, lr=0.1,
-                           function_name="resnet34",
+        req = TrainRequest(model_type=args.model, batch_size=BATCH, epochs=1, dataset=dataset,
+                           lr=1e-4 if vgg else 0.1, function_name=args.model,
                            options=TrainOptions(default_parallelism=N, static_parallelism=True,
                                                 validate_every=0, k=K_AVG, goal_accuracy=101.0))
         # one job id for the warm-up and the timed jobs: the workers keep the job's arena, peer
         # mappings and captured step graph, so the timed region replays what the warm-up built
         task = TrainTask(request=req, job=JobInfo(id="bench", state=JobState(parallelism=N)))
         inv = rt.invoker()
-        inv.env = {"KUBEML_RESNET_DATASET": dataset, "KUBEML_RESNET_IMPL": args.model_impl}
+        inv.env = {ds_env: dataset, "KUBEML_RESNET_IMPL": args.model_impl}
         inv.options = {"device_resident_data": resident}
         job = TrainJob(task, inv, rt.tensor_store, history_store=histories, device_mode=True,
                        skip_final_validation=True)
@@ -172,12 +175,12 @@ def run_own(args) -> int:
 
     # warm-up: W steps per worker through the same path (compiles nothing, but touches every
     # allocation, cuDNN/cuBLAS heuristics of the compat path, the arena, the peer mappings)
-    run_job(f"cifar10_w{args.warmup}", resident=False)
-    run_job(f"cifar10_w{args.warmup}", resident=True)
+    run_job(f"{ds_prefix}_w{args.warmup}", resident=False)
+    run_job(f"{ds_prefix}_w{args.warmup}", resident=True)
 
     sampler = ClockSampler(0).start()
-    job_e2e = run_job(f"cifar10_t{args.steps}", resident=False)
-    job_dev = run_job(f"cifar10_t{args.steps}", resident=True)
+    job_e2e = run_job(f"{ds_prefix}_t{args.steps}", resident=False)
+    job_dev = run_job(f"{ds_prefix}_t{args.steps}", resident=True)
     clocks = sampler.stop()
     rt.stop()
 
@@ -187,16 +190,18 @@ def run_own(args) -> int:
     value = imgs / sd["train_seconds"]
     e2e = N * int(se["steps"]) * BATCH / se["train_seconds"]
     out = {
-        "metric": "images/sec ResNet-34 K-AVG (K=8, batch 128/worker)",
+        "metric": ("images/sec VGG-16 K-AVG (K=8, batch 128/worker)" if vgg
+                   else "images/sec ResNet-34 K-AVG (K=8, batch 128/worker)"),
         "value": round(value, 1), "unit": "images/s", "n_gpus": N, "steps": steps, "warmup": args.warmup,
         "ms_per_step": round(1e3 * sd["train_seconds"] / max(steps, 1), 4),
         "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": round(value / BASELINE_IMG_S, 2),
+        "vs_baseline": None if vgg else round(value / BASELINE_IMG_S, 2),
         "dtype": "bf16", "data": "synthetic",
         "impl": "own",
-        "config": {"model": "resnet34 (torchvision topology, 1000 logits) on 32x32x3", "global_batch": BATCH * N,
+        "config": {"model": ("vgg16" if vgg else "resnet34") + " (torchvision topology, 1000 logits) on 32x32x3",
+                   "global_batch": BATCH * N,
                    "seq_len": None, "parallelism": f"kavg-dp{N}", "k": K_AVG, "model_impl": args.model_impl,
-                   "optimizer": "SGD lr 0.1 wd 1e-4", "merges_in_timed_region": steps // K_AVG,
+                   "optimizer": "Adam lr 1e-4" if vgg else "SGD lr 0.1 wd 1e-4", "merges_in_timed_region": steps // K_AVG,
                    "l2": "per-step working set (fp32 weights+grads 175 MB, bf16 copies, activations) "
                          "exceeds the 126 MB L2; no explicit flush"},
         "merge_ms_per_sync": round(1e3 * sd["merge_seconds"] / max(steps // K_AVG, 1), 4),
@@ -218,6 +223,7 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=16)
     ap.add_argument("--impl", default="own", choices=["own", "reference", "ref-torch", "ddp"])
+    ap.add_argument("--model", default="resnet34", choices=["resnet34", "vgg16"])
     ap.add_argument("--model-impl", default=os.environ.get("KUBEML_RESNET_IMPL", "auto"),
                     choices=["auto", "native", "compat"])
     args = ap.parse_args()

@@ -1,0 +1,26 @@
+"""One launch of the VGG fc1 weight-gradient GEMM (dW[4096,25088] = dY^T[4096,128] . X[128,25088], fp32 out)
+and of the big square GEMM, for `ncu --set full`."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from kubeml_b200 import ops
+dev = torch.device("cuda", 0); torch.cuda.set_device(dev)
+dy = torch.randn(128, 4096, device=dev).bfloat16()
+x = torch.randn(128, 25088, device=dev).bfloat16()
+dw = torch.empty(4096, 25088, device=dev)
+for _ in range(3):
+    ops.gemm_bf16(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, out=dw)
+torch.cuda.synchronize()
+def timeit(fn, n=20):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    fn(); torch.cuda.synchronize(); e0.record()
+    for _ in range(n): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / n
+print("fc1 wgrad us", timeit(lambda: ops.gemm_bf16(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, out=dw)))
+A = torch.randn(8192, 4096, device=dev).bfloat16(); Bm = torch.randn(4096, 4096, device=dev).bfloat16()
+o = torch.empty(8192, 4096, device=dev, dtype=torch.bfloat16)
+t = timeit(lambda: ops.gemm_bf16(A, Bm, out=o, block_n=128))
+print("gemm 8192x4096x4096 us", t, "TFLOP/s", 2 * 8192 * 4096 * 4096 / t / 1e6)
+ref = dy.float().t() @ x.float()
+print("ok", float((dw - ref).abs().max()))

@@ -30,7 +30,9 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;            // bf16 elements = one 128-byte swizzle row
 // 4 stages: split-K keeps the per-CTA K loop short, and <= 128 KB lets two CTAs share an SM so that
 // independent GEMMs (weight gradient next to the data-gradient chain) overlap.
-template <int BLOCK_N> struct Stages { static constexpr int value = 4; };
+// 96 KB of pipeline per CTA either way (4 x 24 KB / 3 x 32 KB): two CTAs fit on an SM, so one CTA's
+// epilogue overlaps the other's main loop (with 4 x 32 KB the 128-wide tile ran one CTA per SM)
+template <int BLOCK_N> struct Stages { static constexpr int value = BLOCK_N > 64 ? 3 : 4; };
 constexpr int kNumThreads = 192;       // producer warp, MMA warp, 4 epilogue warps
 constexpr int kUmmaK = 16;
 

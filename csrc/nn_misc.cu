@@ -4,6 +4,7 @@
 //   im2col / col2im for the convolutions the shifted-TMA path cannot express (stride 2, Cin < 64,
 //   non power-of-two grids), column sums (bias gradients), padded fp32->bf16 packing, uint8 image
 //   normalisation.  The reference reaches all of these through ATen/cuDNN.
+#include <algorithm>
 #include "common.cuh"
 #include "../include/kubeml_b200.h"
 
@@ -380,7 +381,76 @@ col2im_vec_kernel(const __nv_bfloat16* __restrict__ dcols, const __nv_bfloat16* 
 }
 
 // ---------------------------------------------------------------------------------- misc
-// out[c] = sum_r x[r][c]  (bias gradient); one block per 32 columns, rows strided over warps
+// Column pass over a row-major [M][C] matrix, 8 columns (16 B) per thread, rows split over the grid:
+//   v = dy (bf16) or the sum of S fp32 split-K slabs;  a = (y ? (y > 0 ? v * scale : 0) : v);
+//   g (optional) <- a;   colsum (optional, zeroed by the launcher) += sum over rows of a.
+// One kernel serves the bias gradient (colsum only), the ReLU(+dropout) gradient, both at once, and
+// folds the slabs of a split-K data-gradient GEMM on the way (no reduction pass, no atomics there).
+template <bool kSlabs>
+__global__ void __launch_bounds__(kThreads)
+colpass_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ dys, int S, size_t slab_stride,
+               const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ g, float scale,
+               float* __restrict__ colsum, int M, int C, long long ld, int rows_per_block) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  __shared__ float red[kThreads][9];
+  const int cg = C / 8;
+  const int cgw = cg < kThreads ? cg : kThreads;           // column groups handled by this block
+  const int rpi = kThreads / cgw;                          // rows per iteration
+  const int lane_row = threadIdx.x / cgw;
+  const int cgi = blockIdx.y * kThreads + threadIdx.x % cgw;
+  const bool active = lane_row < rpi && cgi < cg;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(M, r0 + rows_per_block);
+  if (active) {
+    for (int r = r0 + lane_row; r < r1; r += rpi) {
+      const size_t off = static_cast<size_t>(r) * ld + static_cast<size_t>(cgi) * 8;
+      float v[8];
+      if constexpr (kSlabs) {
+        const float4* p = reinterpret_cast<const float4*>(dys + off);
+        float4 a = p[0], b = p[1];
+        for (int s2 = 1; s2 < S; ++s2) {
+          const float4* q = reinterpret_cast<const float4*>(dys + s2 * slab_stride + off);
+          const float4 c = q[0], d = q[1];
+          a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w;
+          b.x += d.x; b.y += d.y; b.z += d.z; b.w += d.w;
+        }
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+      } else {
+        ld8(dy + off, v);
+      }
+      if (y) {
+        float m[8];
+        ld8(y + off, m);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = m[k] > 0.f ? v[k] * scale : 0.f;
+      }
+      if (g) st8(g + off, v);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += v[k];
+    }
+  }
+  if (colsum == nullptr) return;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) red[threadIdx.x][k] = acc[k];
+  __syncthreads();
+  if (active && lane_row == 0) {
+    for (int l = 1; l < rpi; ++l)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += red[threadIdx.x + l * cgw][k];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) atomicAdd(colsum + static_cast<size_t>(cgi) * 8 + k, acc[k]);
+  }
+}
+
+__global__ void zero_f32_kernel(float* __restrict__ p, int n) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = 0.f;
+}
+
+// scalar fallback (columns not a multiple of 8): one block per 32 columns
 __global__ void __launch_bounds__(kThreads)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int rows, int cols, long long ld) {
   kml::pdl_launch_dependents();
@@ -398,6 +468,34 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int 
 #pragma unroll
     for (int w = 0; w < kThreads / 32; ++w) t += part[w][lane];
     out[c] = t;
+  }
+}
+
+// y = relu?(sum of S fp32 split-K slabs + bias) as bf16: the epilogue a split GEMM cannot apply itself
+__global__ void __launch_bounds__(kThreads)
+bias_act_kernel(const float* __restrict__ xs, int S, size_t slab_stride, const float* __restrict__ bias,
+                __nv_bfloat16* __restrict__ y, int relu, size_t M, int C, long long ld_x, long long ld_y) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const int cg = C / 8;
+  const size_t total = M * cg;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t r = i / cg;
+    const int c = static_cast<int>(i % cg) * 8;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = bias ? bias[c + k] : 0.f;
+    for (int s2 = 0; s2 < S; ++s2) {
+      const float4* q = reinterpret_cast<const float4*>(xs + s2 * slab_stride + r * ld_x + c);
+      const float4 a = q[0], b = q[1];
+      v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w; v[4] += b.x; v[5] += b.y; v[6] += b.z; v[7] += b.w;
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+    }
+    st8(y + r * ld_y + c, v);
   }
 }
 
@@ -665,10 +763,61 @@ int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, in
   return 0;
 }
 
+static int colpass_launch(const void* dy, const float* dys, int S, size_t slab_stride, const void* y, void* g, float scale,
+                          float* colsum, int M, int C, long long ld, cudaStream_t s) {
+  const int cg = C / 8;
+  const int cgw = cg < kThreads ? cg : kThreads;
+  const int rpi = kThreads / cgw;
+  const int gy = (cg + kThreads - 1) / kThreads;
+  // enough blocks to fill the GPU, at least 4 iterations of rows each
+  int want = std::max(1, (kml::num_sms() * 4) / gy);
+  int rows_per_block = std::max(rpi * 4, (M + want - 1) / want);
+  rows_per_block = (rows_per_block + rpi - 1) / rpi * rpi;
+  const int gx = (M + rows_per_block - 1) / rows_per_block;
+  if (colsum) {
+    KML_CUDA(kml::launch_pdl(zero_f32_kernel, dim3((C + 255) / 256), dim3(256), 0, s, colsum, C));
+    kml::count_launch();
+  }
+  if (dys)
+    KML_CUDA(kml::launch_pdl(colpass_kernel<true>, dim3(gx, gy), dim3(kThreads), 0, s,
+                             static_cast<const __nv_bfloat16*>(nullptr), dys, S, slab_stride,
+                             static_cast<const __nv_bfloat16*>(y), static_cast<__nv_bfloat16*>(g), scale, colsum, M, C, ld,
+                             rows_per_block));
+  else
+    KML_CUDA(kml::launch_pdl(colpass_kernel<false>, dim3(gx, gy), dim3(kThreads), 0, s,
+                             static_cast<const __nv_bfloat16*>(dy), static_cast<const float*>(nullptr), 0, size_t{0},
+                             static_cast<const __nv_bfloat16*>(y), static_cast<__nv_bfloat16*>(g), scale, colsum, M, C, ld,
+                             rows_per_block));
+  kml::count_launch();
+  return 0;
+}
+
 int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld, void* stream) {
   KML_CHECK(x && out && rows > 0 && cols > 0, "kml_colsum_bf16: bad arguments");
-  KML_CUDA(kml::launch_pdl(colsum_kernel, dim3((cols + 31) / 32), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), out, rows, cols, ld));
+  auto s = static_cast<cudaStream_t>(stream);
+  if (cols % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15u) == 0)
+    return colpass_launch(x, nullptr, 0, 0, nullptr, nullptr, 1.f, out, rows, cols, ld, s);
+  KML_CUDA(kml::launch_pdl(colsum_kernel, dim3((cols + 31) / 32), dim3(kThreads), 0, s,
+                           static_cast<const __nv_bfloat16*>(x), out, rows, cols, ld));
   KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_relu_bwd_cols(const void* dy, const float* dy_slabs, int nslabs, size_t slab_stride, const void* y, void* g,
+                      float scale, float* dbias, int M, int C, void* stream) {
+  KML_CHECK((dy != nullptr) != (dy_slabs != nullptr && nslabs > 0), "kml_relu_bwd_cols: give dy or dy_slabs");
+  KML_CHECK(y && g && M > 0 && C > 0 && C % 8 == 0, "kml_relu_bwd_cols: bad arguments (C must be a multiple of 8)");
+  return colpass_launch(dy, dy_slabs, nslabs, slab_stride, y, g, scale, dbias, M, C, C, static_cast<cudaStream_t>(stream));
+}
+
+int kml_bias_act(const float* x_slabs, int nslabs, size_t slab_stride, const float* bias, void* y, int relu, int M,
+                 int C, long long ld_x, long long ld_y, void* stream) {
+  KML_CHECK(x_slabs && y && nslabs > 0 && M > 0 && C > 0 && C % 8 == 0 && ld_x % 4 == 0 && ld_y % 8 == 0,
+            "kml_bias_act: bad arguments");
+  KML_CUDA(kml::launch_pdl(bias_act_kernel, dim3(grid_for(static_cast<size_t>(M) * (C / 8))), dim3(kThreads), 0,
+                           static_cast<cudaStream_t>(stream), x_slabs, nslabs, slab_stride, bias,
+                           static_cast<__nv_bfloat16*>(y), relu, static_cast<size_t>(M), C, ld_x, ld_y));
   kml::count_launch();
   return 0;
 }

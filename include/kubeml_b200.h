@@ -197,6 +197,13 @@ int kml_pack_rows_bf16(const float* src, void* dst_bf16, int rows, int cols, int
 /* VGG-style layers (ReLU fused in the producing GEMM, Dropout p=0.5 in the classifier, the
  * AdaptiveAvgPool2d((7,7)) of torchvision vgg on a 1x1 map; ml/experiments/kubeml/function_vgg11.py). */
 int kml_relu_bwd(const void* dy, const void* y, void* g, float scale, size_t n, void* stream);
+/* g = scale * v * (y > 0) with v = dy (bf16) or the sum of `nslabs` fp32 split-K slabs; dbias (optional)
+ * receives the column sums of g (the bias gradient) in the same pass. */
+int kml_relu_bwd_cols(const void* dy, const float* dy_slabs, int nslabs, size_t slab_stride, const void* y, void* g,
+                      float scale, float* dbias, int M, int C, void* stream);
+/* y(bf16) = relu?(sum of fp32 slabs + bias): the epilogue of a split-K GEMM. */
+int kml_bias_act(const float* x_slabs, int nslabs, size_t slab_stride, const float* bias, void* y, int relu, int M,
+                 int C, long long ld_x, long long ld_y, void* stream);
 int kml_dropout_fwd(const void* x, void* y, void* mask_u8, unsigned long long* counter, unsigned int layer,
                     float p, size_t n, void* stream);
 int kml_dropout_bwd(const void* dy, const void* mask_u8, void* dx, float p, size_t n, void* stream);

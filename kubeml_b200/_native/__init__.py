@@ -123,6 +123,10 @@ def _declare(lib) -> None:
     sig("kml_colsum_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_longlong, c_void_p)
     sig("kml_pack_rows_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
     sig("kml_relu_bwd", c_int, c_void_p, c_void_p, c_void_p, c_float, c_size_t, c_void_p)
+    sig("kml_relu_bwd_cols", c_int, c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_float, c_void_p,
+        c_int, c_int, c_void_p)
+    sig("kml_bias_act", c_int, c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_int, c_int, c_int, c_longlong,
+        c_longlong, c_void_p)
     sig("kml_dropout_fwd", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_uint32, c_float, c_size_t, c_void_p)
     sig("kml_dropout_bwd", c_int, c_void_p, c_void_p, c_void_p, c_float, c_size_t, c_void_p)
     sig("kml_bump_counter", c_int, c_void_p, c_void_p)

@@ -311,9 +311,10 @@ def _slab_enabled() -> bool:
 
 
 def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None, relu: bool = False,
-                 allow_slabs: bool = False) -> Act:
+                 allow_slabs: bool = False, fold: bool = False) -> Act:
     """x: bf16 [N,H,W,Cin] -> [N,Ho,Wo,Cout] (bf16, or fp32 slabs when `allow_slabs` and the problem is
-    too small to fill the GPU otherwise); saves im2col columns under `tag` when used."""
+    too small to fill the GPU otherwise); saves im2col columns under `tag` when used.  With `fold`
+    a split result is reduced here by the bias+activation kernel (no BatchNorm follows to do it)."""
     N, H, W, _ = x.shape
     k, s, p = conv.k, conv.stride, conv.padding
     Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
@@ -329,20 +330,27 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
         chunks = live * (conv.cin // 64)
     else:
         chunks = (Kd + 63) // 64
-    S = auto_splits(tiles, chunks, min_chunks=3) if (allow_slabs and bias is None and not relu and _slab_enabled()) else 1
+    can_split = allow_slabs and _slab_enabled() and (fold or (bias is None and not relu))
+    S = auto_splits(tiles, chunks, min_chunks=3) if can_split else 1
     if S > 1:
         y = B.get(tag + ".slabs", (S, N, Ho, Wo, conv.cout), torch.float32)
+        ebias, erelu = None, False
     else:
         y = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
+        ebias, erelu = bias, relu
     if direct:
-        ops.conv2d_fprop(x, conv.w_bf16, p, bias=bias, relu=relu, out=y, block_n=bn_, splits=S, slabs=S > 1)
+        ops.conv2d_fprop(x, conv.w_bf16, p, bias=ebias, relu=erelu, out=y, block_n=bn_, splits=S, slabs=S > 1)
     else:
         ldk = _ceil(Kd, 64)
         cols = B.get(tag + ".cols", (M, ldk))
         K.im2col(x, cols, k, k, s, p)
-        ops.gemm_bf16(cols, _packed_weight(conv, B, tag, ldk), bias=bias, relu=relu,
+        ops.gemm_bf16(cols, _packed_weight(conv, B, tag, ldk), bias=ebias, relu=erelu,
                       out=y.view(S, M, conv.cout) if S > 1 else y.view(M, conv.cout), block_n=bn_,
                       splits=S, slabs=S > 1)
+    if S > 1 and fold:
+        yd = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
+        K.bias_act(y.view(S, M, conv.cout), bias, yd.view(M, conv.cout), relu)
+        return Act(yd)
     return Act(y, S if S > 1 else 0)
 
 
@@ -445,15 +453,31 @@ def bn_backward(bn: NBatchNorm2d, dy: Act, y: Optional[torch.Tensor], x: torch.T
 
 def linear_forward(fc: NLinear, x: torch.Tensor, B: Buffers, tag: str, relu: bool = False) -> torch.Tensor:
     """y[N, cout]; the row stride is padded to a multiple of 8 elements (TMA wants 16-byte strides
-    when the gradient GEMMs read it back), the returned tensor is the [:, :cout] view."""
+    when the gradient GEMMs read it back), the returned tensor is the [:, :cout] view.  A deep,
+    narrow product (VGG's 25088 -> 4096 on 128 rows) is split over K into fp32 slabs that the
+    bias+activation kernel folds."""
     ld = _ceil(fc.cout, 8)
-    y = B.get(tag + ".y", (x.shape[0], ld))
-    ops.gemm_bf16(x, fc.w_bf16, bias=fc.bias.data, relu=relu, out=y[:, :fc.cout] if ld != fc.cout else y)
-    return y[:, :fc.cout] if ld != fc.cout else y
+    M = x.shape[0]
+    y = B.get(tag + ".y", (M, ld))
+    yv = y[:, :fc.cout] if ld != fc.cout else y
+    m_tiles = (M + 127) // 128
+    bn_ = pick_block_n(m_tiles, fc.cout)
+    tiles = m_tiles * ((fc.cout + bn_ - 1) // bn_)
+    S = auto_splits(tiles, (fc.cin + 63) // 64, min_chunks=8) if (_slab_enabled() and fc.cout % 8 == 0) else 1
+    if S > 1:
+        slabs = B.get(tag + ".slabs", (S, M, fc.cout), torch.float32)
+        ops.gemm_bf16(x, fc.w_bf16, out=slabs, block_n=bn_, splits=S, slabs=True)
+        K.bias_act(slabs, fc.bias.data, yv, relu)
+    else:
+        ops.gemm_bf16(x, fc.w_bf16, bias=fc.bias.data, relu=relu, out=yv, block_n=bn_)
+    return yv
 
 
 def linear_backward(fc: NLinear, x: torch.Tensor, dy: torch.Tensor, B: Buffers, tag: str,
-                    need_dx: bool = True) -> Optional[torch.Tensor]:
+                    need_dx: bool = True, bias_done: bool = False, allow_slabs: bool = False):
+    """Weight/bias gradients into the arena (`bias_done`: the caller's mask kernel already produced
+    the bias gradient); returns dX as a bf16 tensor, or an `Act` of fp32 split-K slabs when
+    `allow_slabs` (the consumer folds them)."""
     ld = _ceil(fc.cout, 8)
     if ld != fc.cout or dy.stride(0) != ld or not dy.is_contiguous():
         pad = B.get(tag + ".dy", (dy.shape[0], ld), zero=True)
@@ -461,9 +485,19 @@ def linear_backward(fc: NLinear, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
         dy = pad[:, :fc.cout]
     with B.on_side():
         ops.gemm_bf16(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, out=fc.w_grad)     # dW = dY^T · X (store)
-        K.colsum(dy, fc.b_grad)
+        if not bias_done:
+            K.colsum(dy, fc.b_grad)
     if not need_dx:
         return None
-    dx = B.get(tag + ".dx", (x.shape[0], fc.cin))
-    ops.gemm_bf16(dy, fc.w_bf16, b_mn=True, out=dx)                                          # dX = dY · W
-    return dx
+    M = x.shape[0]
+    m_tiles = (M + 127) // 128
+    bn_ = pick_block_n(m_tiles, fc.cin)
+    tiles = m_tiles * ((fc.cin + bn_ - 1) // bn_)
+    S = auto_splits(tiles, (fc.cout + 63) // 64, min_chunks=8) if (allow_slabs and _slab_enabled()) else 1
+    if S > 1:
+        dxs = B.get(tag + ".dxslabs", (S, M, fc.cin), torch.float32)
+        ops.gemm_bf16(dy, fc.w_bf16, b_mn=True, out=dxs, block_n=bn_, splits=S, slabs=True)   # dX = dY · W
+        return Act(dxs, S)
+    dx = B.get(tag + ".dx", (M, fc.cin))
+    ops.gemm_bf16(dy, fc.w_bf16, b_mn=True, out=dx, block_n=bn_)
+    return Act(dx) if allow_slabs else dx

@@ -94,7 +94,7 @@ class NativeVGG(NativeNet):
         h = x
         for i, m in enumerate(self.features):
             if isinstance(m, NConv2d):
-                y = conv_forward(m, h, B, f"f{i}", bias=m.bias.data, relu=True).t
+                y = conv_forward(m, h, B, f"f{i}", bias=m.bias.data, relu=True, allow_slabs=True, fold=True).t
                 tape.append(("conv", m, f"f{i}", h, y))
                 h = y
             elif m.kind == "maxpool2x2":
@@ -141,39 +141,44 @@ class NativeVGG(NativeNet):
         self._begin_backward(B)
         fc1, fc2, fc3 = self.classifier[0], self.classifier[3], self.classifier[6]
         scale = 1.0 / (1.0 - self.p) if S["drop"] else 1.0
-        dd2 = linear_backward(fc3, S["d2"], dlogits, B, "c6")
+        # the ReLU(+dropout) mask kernel also folds split-K slabs and emits the bias gradient
+        dd2 = linear_backward(fc3, S["d2"], dlogits, B, "c6", allow_slabs=True)
         g2 = B.get("c3.g", tuple(dd2.shape))
-        K.relu_bwd(dd2, S["d2"], g2, scale)                   # through dropout and ReLU in one mask
-        dd1 = linear_backward(fc2, S["d1"], g2, B, "c3")
+        self._mask(dd2, S["d2"], g2, scale, fc2.b_grad)
+        dd1 = linear_backward(fc2, S["d1"], g2, B, "c3", bias_done=True, allow_slabs=True)
         g1 = B.get("c0.g", tuple(dd1.shape))
-        K.relu_bwd(dd1, S["d1"], g1, scale)
-        dflat = linear_backward(fc1, S["flat"], g1, B, "c0")
+        self._mask(dd1, S["d1"], g1, scale, fc1.b_grad)
+        dflat = linear_backward(fc1, S["flat"], g1, B, "c0", bias_done=True)
         last = S["last"]
         N, H, W, C = last.shape
         R = self.POOL_OUT
-        dh = B.get("flat.dx", tuple(last.shape))
+        dh_t = B.get("flat.dx", tuple(last.shape))
         if H * W == 1:
-            K.replicate_bwd(dflat, dh.view(N, C), R * R)
+            K.replicate_bwd(dflat, dh_t.view(N, C), R * R)
         else:
-            dh.copy_(dflat.view(N, C, R, R).permute(0, 2, 3, 1))
-        first_conv = next(t for t in S["tape"] if t[0] == "conv")
-        for kind, m, tag, xin, y in reversed(S["tape"]):
+            dh_t.copy_(dflat.view(N, C, R, R).permute(0, 2, 3, 1))
+        dh = Act(dh_t)
+        tape = S["tape"]
+        for ti in range(len(tape) - 1, -1, -1):
+            kind, m, tag, xin, y = tape[ti]
             if kind == "pool":
                 dx = B.get(tag + ".dx", tuple(xin.shape))
-                K.maxpool_bwd(dh, B[tag + ".idx"], dx, 2, 2, 0)
-                dh = dx
+                K.maxpool_bwd(dh.t, B[tag + ".idx"], dx, 2, 2, 0)
+                dh = Act(dx)
             else:
                 g = B.get(tag + ".g", tuple(y.shape))
-                K.relu_bwd(dh, y, g, 1.0)
-                with B.on_side():
-                    K.colsum(g.view(-1, m.cout), m.b_grad)
-                need_dx = m is not first_conv[1]
-                r = conv_backward(m, xin, g, B, tag, need_dx=need_dx)
-                if need_dx:
-                    dh = r.t
+                self._mask(dh, y, g, 1.0, m.b_grad)
+                # slabs only when the consumer is another mask kernel (the previous op is a conv)
+                dh = conv_backward(m, xin, g, B, tag, need_dx=ti > 0,
+                                   allow_slabs=ti > 0 and tape[ti - 1][0] == "conv")
         if S["drop"]:
             K.bump_counter(self._counter)
         self._end_backward(B)
+
+
+NativeVGG._mask = staticmethod(
+    lambda dy, y, g, scale, dbias: K.relu_bwd_cols(None if dy.slabs else dy.t, y, g, scale, dbias,
+                                                   dy_slabs=dy.t if dy.slabs else None))
 
 
 def _vgg(name: str, num_classes: int, dropout: float) -> NativeVGG:

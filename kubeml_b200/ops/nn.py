@@ -297,3 +297,39 @@ def replicate_bwd(dy, dx, r2: int) -> None:
                       "kml_replicate_bwd")
         return
     dx.copy_(dy.float().view(N, C, r2).sum(2))
+
+
+def relu_bwd_cols(dy, y, g, scale: float = 1.0, dbias=None, dy_slabs=None) -> None:
+    """g = scale * v * (y > 0), v = dy (bf16 [M, C]) or the fold of fp32 split-K slabs [S, M, C];
+    `dbias` (fp32 [C]) receives the column sums of g in the same pass."""
+    C = y.shape[-1]
+    M = y.numel() // C
+    if y.is_cuda:
+        S = 0 if dy_slabs is None else dy_slabs.shape[0]
+        _native.check(_native.lib().kml_relu_bwd_cols(
+            _ptr(dy), _ptr(dy_slabs), S, 0 if dy_slabs is None else dy_slabs.stride(0), y.data_ptr(), g.data_ptr(),
+            scale, _ptr(dbias), M, C, _native.stream_ptr()), "kml_relu_bwd_cols")
+        return
+    v = _fold(dy, dy_slabs).reshape(M, C) * (y.float().reshape(M, C) > 0) * scale
+    g.copy_(v.reshape(g.shape))
+    if dbias is not None:
+        dbias.copy_(v.sum(0))
+
+
+def bias_act(x_slabs, bias, y, relu: bool) -> None:
+    """y (bf16 [M, C], row stride may be padded) = relu?(sum_s x_slabs[s] + bias)."""
+    S = x_slabs.shape[0]
+    C = y.shape[-1]
+    M = y.numel() // C if y.is_contiguous() else y.shape[0]
+    if y.is_cuda:
+        xs = x_slabs.view(S, M, -1)
+        _native.check(_native.lib().kml_bias_act(
+            xs.data_ptr(), S, xs.stride(0), _ptr(bias), y.data_ptr(), int(relu), M, C, xs.stride(1),
+            y.stride(0) if y.dim() == 2 else C, _native.stream_ptr()), "kml_bias_act")
+        return
+    out = x_slabs.float().sum(0).reshape(M, -1)[:, :C]
+    if bias is not None:
+        out = out + bias
+    if relu:
+        out = torch.relu(out)
+    y.copy_(out.reshape(y.shape))

@@ -354,3 +354,33 @@ def test_adam_device_step_count_survives_graph_replay(dev):
         opt.step()
     assert step.tolist() == [5, 0]
     torch.testing.assert_close(w, p.data, rtol=2e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("M,C,S", [(131072, 64, 0), (2048, 512, 3), (128, 4096, 2), (100, 24, 0), (512, 4104, 0)])
+def test_relu_bwd_cols_bias_act_colsum(dev, M, C, S):
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(0)
+    y = torch.randn(M, C, device=dev).relu().bfloat16()
+    g = torch.empty_like(y)
+    db = torch.full((C,), 7.0, device=dev)             # must be overwritten, not accumulated into
+    if S:
+        slabs = torch.randn(S, M, C, device=dev)
+        v = slabs.sum(0)
+        K.relu_bwd_cols(None, y, g, 2.0, db, dy_slabs=slabs)
+    else:
+        dy = torch.randn(M, C, device=dev).bfloat16()
+        v = dy.float()
+        K.relu_bwd_cols(dy, y, g, 2.0, db)
+    want = v * (y.float() > 0) * 2.0
+    _close(g, want, 1e-2)
+    torch.testing.assert_close(db, want.sum(0), rtol=1e-3, atol=1e-3 * (M ** 0.5))
+    # plain column sum (row stride padded)
+    xp = torch.randn(M, C + 8, device=dev).bfloat16()
+    out = torch.empty(C, device=dev)
+    K.colsum(xp[:, :C], out)
+    torch.testing.assert_close(out, xp[:, :C].float().sum(0), rtol=1e-3, atol=1e-3 * (M ** 0.5))
+    if S:
+        bias = torch.randn(C, device=dev)
+        yb = torch.empty(M, C, device=dev, dtype=torch.bfloat16)
+        K.bias_act(slabs, bias, yb, True)
+        _close(yb, torch.relu(v + bias), 1e-2)
