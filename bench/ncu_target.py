@@ -7,7 +7,7 @@ from kubeml_b200 import _native, ops
 from kubeml_b200.ops import nn as K
 dev = torch.device("cuda", 0); torch.cuda.set_device(dev)
 Nb = 128
-for it in range(3):
+for it in range(int(sys.argv[1]) if len(sys.argv) > 1 else 3):
     # layer2 conv 3x3 128->128 on 4x4 (M=2048): fprop as split-K slabs, dgrad, wgrad
     x = torch.randn(Nb, 4, 4, 128, device=dev).bfloat16()
     w = torch.randn(128, 3, 3, 128, device=dev).bfloat16()

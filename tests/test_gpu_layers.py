@@ -23,7 +23,8 @@ def _close(a, b, tol):
 
 
 @pytest.mark.parametrize("M,C,relu,res", [(8192, 64, True, False), (2048, 128, True, True), (512, 256, False, False),
-                                          (128, 512, True, True), (32768, 64, True, False), (100, 72, True, True)])
+                                          (128, 512, True, True), (32768, 64, True, False), (100, 72, True, True),
+                                          (1024, 128, True, True), (1000, 256, True, False)])
 def test_bn_fwd_bwd(dev, M, C, relu, res):
     from kubeml_b200.ops import nn as K
     torch.manual_seed(0)
