@@ -22,5 +22,19 @@ A = torch.randn(8192, 4096, device=dev).bfloat16(); Bm = torch.randn(4096, 4096,
 o = torch.empty(8192, 4096, device=dev, dtype=torch.bfloat16)
 t = timeit(lambda: ops.gemm_bf16(A, Bm, out=o, block_n=128))
 print("gemm 8192x4096x4096 us", t, "TFLOP/s", 2 * 8192 * 4096 * 4096 / t / 1e6)
+ref2 = (A[:256].float() @ Bm.float().t())
+for bn in (128, 256):
+    t = timeit(lambda: ops.gemm_bf16(A, Bm, out=o, block_n=bn))
+    print("block_n", bn, "us", t, "TFLOP/s", 2 * 8192 * 4096 * 4096 / t / 1e6, "err", float((o[:256].float() - ref2).abs().max() / ref2.abs().max()))
+A2 = torch.randn(16384, 8192, device=dev).bfloat16(); B2 = torch.randn(8192, 8192, device=dev).bfloat16()
+o2 = torch.empty(16384, 8192, device=dev, dtype=torch.bfloat16)
+for bn in (128, 256):
+    t = timeit(lambda: ops.gemm_bf16(A2, B2, out=o2, block_n=bn), 5)
+    print("16384x8192x8192 block_n", bn, "us", t, "TFLOP/s", 2 * 16384 * 8192 * 8192 / t / 1e6)
+t = timeit(lambda: torch.matmul(A2, B2.t(), out=o2), 5)
+print("cuBLAS 16384x8192x8192 us", t, "TFLOP/s", 2 * 16384 * 8192 * 8192 / t / 1e6)
+for bn in (128, 256):
+    t = timeit(lambda: ops.gemm_bf16(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, out=dw, block_n=bn))
+    print("fc1 wgrad block_n", bn, "us", t)
 ref = dy.float().t() @ x.float()
 print("ok", float((dw - ref).abs().max()))

@@ -32,7 +32,7 @@ constexpr int kBlockK = 64;            // bf16 elements = one 128-byte swizzle r
 // independent GEMMs (weight gradient next to the data-gradient chain) overlap.
 // 96 KB of pipeline per CTA either way (4 x 24 KB / 3 x 32 KB): two CTAs fit on an SM, so one CTA's
 // epilogue overlaps the other's main loop (with 4 x 32 KB the 128-wide tile ran one CTA per SM)
-template <int BLOCK_N> struct Stages { static constexpr int value = BLOCK_N > 64 ? 3 : 4; };
+template <int BLOCK_N> struct Stages { static constexpr int value = BLOCK_N > 128 ? 2 : (BLOCK_N > 64 ? 3 : 4); };
 constexpr int kNumThreads = 192;       // producer warp, MMA warp, 4 epilogue warps
 constexpr int kUmmaK = 16;
 
@@ -68,6 +68,9 @@ struct GemmArgs {
   int relu, out_f32, atomic_add;
   int wgt_taps, wgt_cin;                 // kWgtMN: taps in the filter, input channels per tap
   long long slab_stride;                 // != 0: split s stores its partial tile at out + s*slab_stride (no atomics)
+  int cluster_reduce;                    // the `splits` CTAs of a tile are one cluster: partial tiles are added
+                                         // through distributed shared memory, the epilogue runs once per element
+  float* stats;                          // cluster mode: fp32 [2][n_valid] += column sums / sums of squares
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -105,6 +108,19 @@ __device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* ba
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
       "r"(c3) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// float4 from the shared memory of CTA `rank` of this cluster, at the same offset as local address `laddr`
+__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t laddr, uint32_t rank) {
+  uint32_t raddr;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(laddr), "r"(rank));
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(raddr) : "memory");
+  return v;
 }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -324,6 +340,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = 0u;
       }
+      if (args.cluster_reduce) {
+        // partial tile -> own shared memory (the pipeline ring is idle now); the reduction across the
+        // cluster and the real epilogue follow after the role branches
+        float* part = reinterpret_cast<float*>(smem_a) + (q * 32 + lane) * (BLOCK_N + 4) + c0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(part + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                             __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+        continue;
+      }
       if (!row_ok) continue;
       const int ncol0 = nt * BLOCK_N + c0;                // column within the (per-tap) N range
       const long long off = static_cast<long long>(row) * args.ldo + col_base + c0 +
@@ -404,6 +430,100 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   }
 
   __syncthreads();
+  if (args.cluster_reduce) {
+    // ---- split-K reduction across the cluster through distributed shared memory ----------------
+    // CTA `split` owns rows [rbeg, rend) of the 128-row tile: it adds the partial tiles of all
+    // peers for those rows, applies the epilogue once and writes the final output.  Column sums
+    // for BatchNorm fall out of the same pass (a thread keeps the same 4 columns for all its rows).
+    constexpr int kPartStride = BLOCK_N + 4;
+    constexpr int kGroups = BLOCK_N / 4;                 // float4 groups per row
+    float* part = reinterpret_cast<float*>(smem_a);
+    float* st_sm = part + kBlockM * kPartStride;        // [2][BLOCK_N] block-level column sums
+    for (int i = threadIdx.x; i < 2 * BLOCK_N; i += kNumThreads) st_sm[i] = 0.f;
+    cluster_sync_all();
+    if (warp >= 2) {
+      const int S = args.splits;
+      const int rp = (kBlockM + S - 1) / S;
+      const int rbeg = split * rp;
+      const int rend = min(kBlockM, rbeg + rp);
+      const int et = threadIdx.x - 64;                   // 0..127
+      const int c4 = (et % kGroups) * 4;
+      const int ncol = nt * BLOCK_N + c4;
+      const bool col_ok = ncol + 4 <= args.n_valid;
+      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+      float bv[4] = {0.f, 0.f, 0.f, 0.f};
+      if (args.bias != nullptr) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) bv[t] = __ldg(args.bias + ncol + t);
+      }
+      for (int r = rbeg + et / kGroups; r < rend; r += 128 / kGroups) {
+        const uint32_t laddr = smem_u32(part + r * kPartStride + c4);
+        float4 acc = ld_dsmem_f4(laddr, 0);
+        for (int p = 1; p < S; ++p) {
+          const float4 o = ld_dsmem_f4(laddr, static_cast<uint32_t>(p));
+          acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
+        }
+        const int grow = mt * kBlockM + r;
+        if (grow >= args.m_valid) continue;
+        float f[4] = {acc.x + bv[0], acc.y + bv[1], acc.z + bv[2], acc.w + bv[3]};
+        const long long ro = static_cast<long long>(grow) * args.ldo + ncol;
+        if (args.addend != nullptr) {
+          const __nv_bfloat16* ad = args.addend + ro;
+          if (col_ok && (ro & 3) == 0) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(ad));
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+            f[0] += a0.x; f[1] += a0.y; f[2] += a1.x; f[3] += a1.y;
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) f[t] += __bfloat162float(ad[t]);
+          }
+        }
+        if (args.relu) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
+        }
+        if (args.out_f32) {
+          float* o = static_cast<float*>(args.out) + ro;
+          if (col_ok && (ro & 3) == 0) {
+            *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = f[t];
+          }
+        } else {
+          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + ro;
+          __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
+          __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
+          if (col_ok && (ro & 3) == 0) {
+            uint2 u;
+            u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
+            *reinterpret_cast<uint2*>(o) = u;
+          } else {
+            const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = hv[t];
+          }
+          // statistics of exactly the values the consumer will read back
+          const float2 r0 = __bfloat1622float2(p0), r1 = __bfloat1622float2(p1);
+          f[0] = r0.x; f[1] = r0.y; f[2] = r1.x; f[3] = r1.y;
+        }
+#pragma unroll
+        for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
+      }
+      if (args.stats != nullptr) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) { atomicAdd(st_sm + c4 + t, s1[t]); atomicAdd(st_sm + BLOCK_N + c4 + t, s2[t]); }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+        for (int i = et; i < 2 * BLOCK_N; i += 128) {
+          const int c = i % BLOCK_N, which = i / BLOCK_N;
+          const int gc = nt * BLOCK_N + c;
+          if (gc < args.n_valid) atomicAdd(args.stats + static_cast<size_t>(which) * args.n_valid + gc, st_sm[i]);
+        }
+      }
+    }
+    cluster_sync_all();                                  // peers may still be reading this CTA's partial tile
+  }
   if (warp == 1) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
@@ -456,7 +576,8 @@ int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs&
     configured = true;
   }
   dim3 grid(a.m_tiles, a.n_tiles, a.z_taps * a.splits);
-  KML_CUDA(kml::launch_pdl(kernel, grid, dim3(kNumThreads), smem, s, ma, mb, a));
+  const dim3 cluster(1, 1, a.cluster_reduce ? a.splits : 1);
+  KML_CUDA(kml::launch_pdl_cluster(kernel, grid, dim3(kNumThreads), smem, s, cluster, ma, mb, a));
   kml::count_launch();
   return 0;
 }
@@ -469,7 +590,12 @@ int launch(const TensorSpec& ta, const TensorSpec& tb, const GemmArgs& a, int bl
   if (rc) return rc;
   const bool amn = a.a_kind == kMatMN || a.a_kind == kConvMN;
   const bool bmn = a.b_kind == kMatMN || a.b_kind == kConvMN || a.b_kind == kWgtMN;
-  KML_CHECK(block_n == 64 || block_n == 128, "block_n must be 64 or 128");
+  KML_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "block_n must be 64, 128 or 256");
+  if (block_n == 256) {      // 128x256 tiles: two 48 KB stages, two CTAs per SM use all 512 TMEM columns
+    if (!amn && !bmn) return launch_variant<256, false, false>(ma, mb, a, s);
+    if (!amn && bmn) return launch_variant<256, false, true>(ma, mb, a, s);
+    return launch_variant<256, true, true>(ma, mb, a, s);
+  }
   KML_CHECK(!(amn && !bmn), "A MN-major with B K-major is not instantiated");
   if (block_n == 64) {
     if (!amn && !bmn) return launch_variant<64, false, false>(ma, mb, a, s);
@@ -534,7 +660,13 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
   g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);
   g.atomic_add = g.splits > 1 && !epi->slabs;
   g.slab_stride = (g.splits > 1 && epi->slabs) ? static_cast<long long>(M) * ldo : 0;
-  KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
+  if (epi->cluster) {
+    KML_CHECK(g.splits <= 8 && block_n <= 128, "cluster split-K: at most 8 splits, block_n <= 128");
+    g.cluster_reduce = 1; g.stats = epi->stats; g.atomic_add = 0; g.slab_stride = 0;
+  } else {
+    KML_CHECK(epi->stats == nullptr, "column statistics need cluster mode");
+    KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
+  }
   return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
 }
 
@@ -608,7 +740,13 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
   g.bias = bias; g.relu = relu; g.out_f32 = out_f32;
   g.atomic_add = g.splits > 1 && !epi->slabs;
   g.slab_stride = (g.splits > 1 && epi->slabs) ? Mtot * Cout : 0;
-  KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
+  if (epi->cluster) {
+    KML_CHECK(g.splits <= 8 && block_n <= 128, "cluster split-K: at most 8 splits, block_n <= 128");
+    g.cluster_reduce = 1; g.stats = epi->stats; g.atomic_add = 0; g.slab_stride = 0;
+  } else {
+    KML_CHECK(epi->stats == nullptr, "column statistics need cluster mode");
+    KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
+  }
   g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);
   if (dgrad) {
     // B = forward filter [rows = real Cout][cols = taps * real Cin], consumed MN-major

@@ -406,6 +406,84 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
   }
 }
 
+// Forward with statistics that the producing GEMM already accumulated (cluster split-K epilogue,
+// csrc/gemm_tcgen05.cu): no reduction and no grid barrier are left, the layer is an element-wise
+// pass.  stats = fp32 [2][C] (sum, sum of squares) followed by one ticket word; the last CTA to have
+// read the statistics clears them for the next training step (CUDA-graph replay safe).
+struct BnApplyArgs {
+  const __nv_bfloat16* x;
+  float* stats;
+  const __nv_bfloat16* res;
+  __nv_bfloat16* y;
+  const float* gamma;
+  const float* beta;
+  float* running_mean;
+  float* running_var;
+  long long* num_batches_tracked;
+  float* save_mean;
+  float* save_invstd;
+  int M, C, relu;
+  float eps, momentum;
+};
+
+__global__ void __launch_bounds__(kThreads) bn_apply_train_kernel(const BnApplyArgs a) {
+  extern __shared__ float sm[];                    // [C] scale, [C] shift
+  __shared__ int is_last;
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const float inv_m = 1.f / static_cast<float>(a.M);
+  for (int c = threadIdx.x; c < a.C; c += kThreads) {
+    const float mean = __ldcg(a.stats + c) * inv_m;
+    const float var = fmaxf(__ldcg(a.stats + a.C + c) * inv_m - mean * mean, 0.f);
+    const float invstd = rsqrtf(var + a.eps);
+    const float sc = a.gamma[c] * invstd;
+    sm[c] = sc;
+    sm[a.C + c] = a.beta[c] - mean * sc;
+    if (blockIdx.x == 0) {
+      a.save_mean[c] = mean;
+      a.save_invstd[c] = invstd;
+      if (a.running_mean) {
+        const float unbiased = a.M > 1 ? var * static_cast<float>(a.M) / static_cast<float>(a.M - 1) : var;
+        a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
+        a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * unbiased;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && a.num_batches_tracked) *a.num_batches_tracked += 1;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(a.stats + 2 * a.C);
+    is_last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;     // wraps to 0: self-resetting
+  }
+  __syncthreads();
+  if (is_last)
+    for (int c = threadIdx.x; c < 2 * a.C; c += kThreads) a.stats[c] = 0.f;
+
+  const int groups = a.C / kVec;
+  const size_t total = static_cast<size_t>(a.M) * groups;
+  for (size_t idx = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x; idx < total;
+       idx += static_cast<size_t>(gridDim.x) * kThreads) {
+    const int c0 = static_cast<int>(idx % groups) * kVec;
+    const size_t off = (idx / groups) * a.C + c0;
+    float f[kVec];
+    load8(a.x + off, f);
+#pragma unroll
+    for (int i = 0; i < kVec; ++i) f[i] = fmaf(f[i], sm[c0 + i], sm[a.C + c0 + i]);
+    if (a.res) {
+      float rr[kVec];
+      load8(a.res + off, rr);
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) f[i] += rr[i];
+    }
+    if (a.relu) {
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) f[i] = fmaxf(f[i], 0.f);
+    }
+    store8(a.y + off, f);
+  }
+}
+
 int bn_grid(int M, int C, const void* kernel, size_t smem) {
   const int groups = C / kVec;
   const int lanes = kThreads / groups;
@@ -444,6 +522,26 @@ int kml_bn_fwd_train(const void* x, const float* x_slabs, int nslabs, long long 
   const size_t smem = 2 * C * sizeof(float);
   const int grid = bn_grid(M, C, reinterpret_cast<const void*>(bn_fwd_train_kernel), smem);
   KML_CUDA(kml::launch_pdl(bn_fwd_train_kernel, dim3(grid), dim3(kThreads), smem, static_cast<cudaStream_t>(stream), a));
+  kml::count_launch();
+  return 0;
+}
+
+size_t kml_bn_stats_bytes(int C) { return (2 * static_cast<size_t>(C) + 4) * sizeof(float); }
+
+int kml_bn_apply_train(const void* x, float* stats, const void* res, void* y, const float* gamma, const float* beta,
+                       float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
+                       float* save_invstd, int M, int C, int relu, float eps, float momentum, void* stream) {
+  KML_CHECK(x && stats && y && gamma && beta && save_mean && save_invstd, "kml_bn_apply_train: null pointer");
+  KML_CHECK(C % kVec == 0 && C <= 4 * kMaxC && M > 0, "kml_bn_apply_train: C (%d) must be a multiple of 8", C);
+  BnApplyArgs a{static_cast<const __nv_bfloat16*>(x), stats, static_cast<const __nv_bfloat16*>(res),
+                static_cast<__nv_bfloat16*>(y), gamma, beta, running_mean, running_var, num_batches_tracked,
+                save_mean, save_invstd, M, C, relu, eps, momentum};
+  const size_t total = static_cast<size_t>(M) * (C / kVec);
+  size_t want = (total + kThreads - 1) / kThreads;
+  const size_t cap = static_cast<size_t>(kml::num_sms()) * 2;
+  const int grid = static_cast<int>(want < cap ? (want < 1 ? 1 : want) : cap);
+  KML_CUDA(kml::launch_pdl(bn_apply_train_kernel, dim3(grid), dim3(kThreads), 2 * C * sizeof(float),
+                           static_cast<cudaStream_t>(stream), a));
   kml::count_launch();
   return 0;
 }

@@ -137,7 +137,14 @@ typedef struct {
   int splits;               /* K-splits; 0/1 = off.  Combined with red.add into a zeroed fp32 output, or */
   int slabs;                /* (slabs != 0) each split stores its partial tile to out + split*M*ldo (fp32
                                [splits][M][ldo]) for a consumer that folds them (kml_bn_*)             */
-  int block_n;              /* 64, 128, or 0 = choose                                               */
+  int block_n;              /* 64, 128, 256, or 0 = choose                                          */
+  int cluster;              /* != 0: the `splits` CTAs of a tile form a thread-block cluster (<= 8) and add
+                               their partial tiles through distributed shared memory: the output is complete
+                               (bf16 or fp32, bias/addend/ReLU applied), no slabs, no atomics            */
+  float* stats;             /* cluster mode only, may be NULL: fp32 [2][N], += per-column sum and sum of
+                               squares of the (rounded) output over all rows - the BatchNorm batch
+                               statistics, produced where the data already is (zero it before the GEMM;
+                               kml_bn_apply_train re-zeroes it after use)                                */
 } kml_epilogue;
 
 /* out[M,N] = A * B^T.  a_mn = 0: A is [M][K] (lda = row stride); a_mn = 1: A is [K][M].  Same for B
@@ -165,6 +172,13 @@ size_t kml_bn_scratch_bytes(int C);
  * producing GEMM, slab_stride elements apart) whose sum is the input; in the slab case x_out receives
  * the folded input as bf16 for the backward pass.  scratch: kml_bn_scratch_bytes() bytes, zeroed
  * ONCE at allocation and then owned by these kernels (it carries a launch counter). */
+/* Same forward when the producing GEMM already accumulated the batch statistics (kml_epilogue.stats):
+ * an element-wise pass, no reduction.  stats: kml_bn_stats_bytes(C) bytes = fp32 [2][C] + a ticket word,
+ * zeroed once at allocation; this kernel clears it again after use. */
+size_t kml_bn_stats_bytes(int C);
+int kml_bn_apply_train(const void* x, float* stats, const void* res, void* y, const float* gamma, const float* beta,
+                       float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
+                       float* save_invstd, int M, int C, int relu, float eps, float momentum, void* stream);
 int kml_bn_fwd_train(const void* x, const float* x_slabs, int nslabs, long long slab_stride, void* x_out,
                      const void* res, void* y, const float* gamma, const float* beta, float* running_mean,
                      float* running_var, long long* num_batches_tracked, float* save_mean,

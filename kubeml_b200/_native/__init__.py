@@ -51,7 +51,7 @@ class MergeParams(Structure):
 
 class Epilogue(Structure):
     _fields_ = [("bias", c_void_p), ("addend_bf16", c_void_p), ("relu", c_int), ("out_f32", c_int),
-                ("splits", c_int), ("slabs", c_int), ("block_n", c_int)]
+                ("splits", c_int), ("slabs", c_int), ("block_n", c_int), ("cluster", c_int), ("stats", c_void_p)]
 
 
 def _declare(lib) -> None:
@@ -103,6 +103,9 @@ def _declare(lib) -> None:
         c_int, c_int, c_int, c_int, c_int, c_void_p)
     # NHWC layers
     sig("kml_bn_scratch_bytes", c_size_t, c_int)
+    sig("kml_bn_stats_bytes", c_size_t, c_int)
+    sig("kml_bn_apply_train", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p)
     sig("kml_bn_fwd_train", c_int, c_void_p, c_void_p, c_int, c_longlong, c_void_p, c_void_p, c_void_p,
         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
         c_float, c_float, c_void_p)

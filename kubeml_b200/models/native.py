@@ -286,11 +286,12 @@ def pick_block_n(m_tiles: int, n: int) -> int:
 class Act:
     """An activation or gradient: a bf16 tensor, or the fp32 split-K *slabs* [S, ...] of the GEMM that
     produced it.  Slabs are folded by the BatchNorm kernel that consumes them (csrc/norm.cu), so a
-    small, deep GEMM can be spread over the whole GPU without a reduction pass or atomics."""
-    __slots__ = ("t", "slabs")
+    small, deep GEMM can be spread over the whole GPU without a reduction pass or atomics.
+    `stats`: per-channel sum / sum of squares the producing GEMM accumulated (cluster split-K)."""
+    __slots__ = ("t", "slabs", "stats")
 
-    def __init__(self, t: torch.Tensor, slabs: int = 0):
-        self.t, self.slabs = t, slabs
+    def __init__(self, t: torch.Tensor, slabs: int = 0, stats: Optional[torch.Tensor] = None):
+        self.t, self.slabs, self.stats = t, slabs, stats
 
     @property
     def shape(self):
@@ -310,8 +311,18 @@ def _slab_enabled() -> bool:
     return os.environ.get("KUBEML_SPLITK_SLABS", "1") != "0"
 
 
+_CLUSTER_MAX = 8      # portable thread-block cluster size
+
+
+def _cluster_enabled() -> bool:
+    """Split-K as one thread-block cluster per tile, reduced through distributed shared memory in the
+    GEMM itself (final bf16 output + BatchNorm statistics) instead of fp32 slabs folded by the consumer."""
+    import os
+    return os.environ.get("KUBEML_CLUSTER_SPLITK", "1") != "0"
+
+
 def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None, relu: bool = False,
-                 allow_slabs: bool = False, fold: bool = False) -> Act:
+                 allow_slabs: bool = False, fold: bool = False, want_stats: bool = False) -> Act:
     """x: bf16 [N,H,W,Cin] -> [N,Ho,Wo,Cout] (bf16, or fp32 slabs when `allow_slabs` and the problem is
     too small to fill the GPU otherwise); saves im2col columns under `tag` when used.  With `fold`
     a split result is reduced here by the bias+activation kernel (no BatchNorm follows to do it)."""
@@ -330,6 +341,21 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
         chunks = live * (conv.cin // 64)
     else:
         chunks = (Kd + 63) // 64
+    if allow_slabs and _cluster_enabled() and (want_stats or fold):
+        # cluster split-K: complete output (+ bias/ReLU, + BatchNorm statistics) straight from the GEMM
+        S = min(auto_splits(tiles, chunks, min_chunks=3), _CLUSTER_MAX)
+        y = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
+        stats = B.get(tag + ".stats", (K.bn_stats_numel(conv.cout),), torch.float32, zero=True) if want_stats else None
+        if direct:
+            ops.conv2d_fprop(x, conv.w_bf16, p, bias=bias, relu=relu, out=y, block_n=bn_, splits=S, cluster=True,
+                             stats=stats)
+        else:
+            ldk = _ceil(Kd, 64)
+            cols = B.get(tag + ".cols", (M, ldk))
+            K.im2col(x, cols, k, k, s, p)
+            ops.gemm_bf16(cols, _packed_weight(conv, B, tag, ldk), bias=bias, relu=relu, out=y.view(M, conv.cout),
+                          block_n=bn_, splits=S, cluster=True, stats=stats)
+        return Act(y, 0, stats)
     can_split = allow_slabs and _slab_enabled() and (fold or (bias is None and not relu))
     S = auto_splits(tiles, chunks, min_chunks=3) if can_split else 1
     if S > 1:
@@ -393,6 +419,11 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
         pd = k - 1 - p
         live = sum(1 for kh in range(k) for kw in range(k)
                    if (kh - pd) <= Ho - 1 and (H - 1 + kh - pd) >= 0 and (kw - pd) <= Wo - 1 and (W - 1 + kw - pd) >= 0)
+        if allow_slabs and _cluster_enabled():
+            S = min(auto_splits(dtiles, live * (conv.cout // 64), min_chunks=3), _CLUSTER_MAX)
+            dx = B.get(tag + ".dx", (N, H, W, conv.cin))
+            ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=dx, block_n=bn_d, splits=S, cluster=True)
+            return Act(dx)
         S = auto_splits(dtiles, live * (conv.cout // 64), min_chunks=3) if (allow_slabs and _slab_enabled()) else 1
         if S > 1:
             dx = B.get(tag + ".dxslabs", (S, N, H, W, conv.cin), torch.float32)
@@ -428,6 +459,12 @@ def bn_forward(bn: NBatchNorm2d, x: Act, B: Buffers, tag: str, train: bool, relu
     """Returns (y, x_saved): the block output and the bf16 input the backward pass needs."""
     shape = tuple(x.shape)
     y = B.get(tag + ".y", shape)
+    if train and x.stats is not None:
+        mean = B.get(tag + ".mean", (bn.c,), torch.float32)
+        istd = B.get(tag + ".istd", (bn.c,), torch.float32)
+        K.bn_apply_train(x.t, x.stats, res, y, bn.weight.data, bn.bias.data, bn.running_mean, bn.running_var,
+                         bn.num_batches_tracked, mean, istd, relu, bn.eps, bn.momentum)
+        return y, x.t
     xs = x.t if x.slabs else None
     xb = None if x.slabs else x.t
     x_out = B.get(tag + ".xsave", shape) if x.slabs else None

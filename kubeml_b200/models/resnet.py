@@ -82,7 +82,7 @@ class NativeResNet(NativeNet):
         N = x.shape[0]
         B = self.buffers_for(N, train)
         S = {"x": x, "blocks": []}
-        c1 = conv_forward(self.conv1, x, B, "stem", allow_slabs=True)
+        c1 = conv_forward(self.conv1, x, B, "stem", allow_slabs=True, want_stats=train)
         a1, c1s = bn_forward(self.bn1, c1, B, "stem.bn", train, relu=True)
         _, H1, W1, _ = a1.shape
         Hp, Wp = (H1 + 2 - 3) // 2 + 1, (W1 + 2 - 3) // 2 + 1
@@ -95,11 +95,11 @@ class NativeResNet(NativeNet):
             idn, tds = h, None
             if blk.downsample is not None:       # the projection shortcut runs next to the main branch
                 with B.on_side():
-                    td = conv_forward(blk.downsample[0], h, B, tag + ".cd", allow_slabs=True)
+                    td = conv_forward(blk.downsample[0], h, B, tag + ".cd", allow_slabs=True, want_stats=train)
                     idn, tds = bn_forward(blk.downsample[1], td, B, tag + ".bnd", train, relu=False)
-            t1 = conv_forward(blk.conv1, h, B, tag + ".c1", allow_slabs=True)
+            t1 = conv_forward(blk.conv1, h, B, tag + ".c1", allow_slabs=True, want_stats=train)
             a, t1s = bn_forward(blk.bn1, t1, B, tag + ".bn1", train, relu=True)
-            t2 = conv_forward(blk.conv2, a, B, tag + ".c2", allow_slabs=True)
+            t2 = conv_forward(blk.conv2, a, B, tag + ".c2", allow_slabs=True, want_stats=train)
             if blk.downsample is not None:
                 B.join_side()
             out, t2s = bn_forward(blk.bn2, t2, B, tag + ".bn2", train, relu=True, res=idn)

@@ -15,21 +15,40 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
     return 0 if t is None else t.data_ptr()
 
 
-def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0, slabs=False):
+def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0, slabs=False,
+         cluster=False, stats=None):
     e = _native.Epilogue()
     e.bias = _ptr(bias) or None
     e.addend_bf16 = _ptr(addend) or None
     e.relu, e.out_f32, e.splits, e.block_n = int(relu), int(out_f32), int(splits), int(block_n)
     e.slabs = int(slabs)
+    e.cluster = int(cluster)
+    e.stats = _ptr(stats) or None
     return e
+
+
+def _cpu_stats(stats: Optional[torch.Tensor], y: torch.Tensor) -> None:
+    """CPU restatement of the cluster epilogue's column statistics: stats[0] += sum, stats[1] += sum of
+    squares of the (rounded) output over all rows."""
+    if stats is None:
+        return
+    C = y.shape[-1]
+    v = y.float().reshape(-1, C)
+    st = stats[: 2 * C].view(2, C)
+    st[0] += v.sum(0)
+    st[1] += (v * v).sum(0)
 
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
               bias: Optional[torch.Tensor] = None, relu: bool = False,
               out_dtype: torch.dtype = torch.bfloat16, out: Optional[torch.Tensor] = None,
               splits: int = 1, block_n: int = 0, addend: Optional[torch.Tensor] = None,
-              slabs: bool = False) -> torch.Tensor:
+              slabs: bool = False, cluster: bool = False, stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """out[M,N] = A · B^T (+bias, ReLU) with fp32 accumulation.
+
+    cluster=True: the K-splits (<= 8) of a tile run as one thread-block cluster and are added through
+    distributed shared memory; the output is final (any dtype, bias/addend/ReLU allowed) and `stats`
+    (fp32 [2, N], zeroed) receives per-column sum / sum of squares.
 
     a: [M,K] (a_mn=False, K contiguous) or [K,M] (a_mn=True, M contiguous), bf16
     b: [N,K] (b_mn=False)               or [K,N] (b_mn=True), bf16
@@ -52,8 +71,11 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
         if relu:
             r = torch.relu(r)
         r = r.to(out_dtype)
+        _cpu_stats(stats, r)
         if out is not None:
-            if slabs and splits > 1:
+            if cluster:
+                out.copy_(r)
+            elif slabs and splits > 1:
                 out.zero_()
                 out[0].copy_(r)
             elif splits == 1:
@@ -66,9 +88,9 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     assert a.stride(-1) == 1 and b.stride(-1) == 1 and (out is None or out.stride(-1) == 1)
     out_f32 = out_dtype == torch.float32
     if out is None:
-        out = (torch.zeros if splits > 1 else torch.empty)((M, N), dtype=out_dtype, device=a.device)
+        out = (torch.zeros if splits > 1 and not cluster else torch.empty)((M, N), dtype=out_dtype, device=a.device)
     import ctypes
-    e = _epi(bias, addend, relu, out_f32, splits, block_n, slabs and splits > 1)
+    e = _epi(bias, addend, relu, out_f32, splits, block_n, slabs and splits > 1 and not cluster, cluster, stats)
     _native.check(_native.lib().kml_gemm_bf16(
         a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(),
         out.stride(-2), M, N, K, ctypes.byref(e), _native.stream_ptr()), "kml_gemm_bf16")
@@ -83,7 +105,8 @@ def conv2d_fprop_supported(H: int, W: int, Cin: int, Cout: int, KH: int, KW: int
 
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[torch.Tensor] = None,
                  relu: bool = False, out_dtype: torch.dtype = torch.bfloat16, splits: int = 1,
-                 block_n: int = 0, out: Optional[torch.Tensor] = None, slabs: bool = False) -> torch.Tensor:
+                 block_n: int = 0, out: Optional[torch.Tensor] = None, slabs: bool = False,
+                 cluster: bool = False, stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Stride-1 convolution, NHWC.  x: [N,H,W,Cin] bf16; w: [Cout,KH,KW,Cin] bf16 -> [N,Ho,Wo,Cout].
     The data gradient of a stride-1 convolution is this same op applied to dY with the flipped,
     channel-transposed filter and pad' = K-1-pad."""
@@ -98,8 +121,9 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
         if relu:
             y = torch.relu(y)
         y = y.permute(0, 2, 3, 1).contiguous().to(out_dtype)
+        _cpu_stats(stats, y)
         if out is not None:
-            if slabs:                      # [S, N, Ho, Wo, C]: everything in slab 0, zeros elsewhere
+            if slabs and not cluster:      # [S, N, Ho, Wo, C]: everything in slab 0, zeros elsewhere
                 out.zero_()
                 out[0].copy_(y)
             else:
@@ -110,8 +134,8 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
     out_f32 = out_dtype == torch.float32
     import ctypes
     y = out if out is not None else \
-        (torch.zeros if splits > 1 else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
-    e = _epi(bias, None, relu, out_f32, splits, block_n, slabs)
+        (torch.zeros if splits > 1 and not cluster else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
+    e = _epi(bias, None, relu, out_f32, splits, block_n, slabs and not cluster, cluster, stats)
     _native.check(_native.lib().kml_conv2d_fprop(
         x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_fprop")
@@ -120,7 +144,7 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
 
 def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
                  addend: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                 block_n: int = 0, splits: int = 1, slabs: bool = False) -> torch.Tensor:
+                 block_n: int = 0, splits: int = 1, slabs: bool = False, cluster: bool = False) -> torch.Tensor:
     """Data gradient of `conv2d_fprop`: dy [N,Ho,Wo,Cout] bf16, w the *forward* filter
     [Cout,KH,KW,Cin] bf16 -> dx [N,H,W,Cin] bf16 (+ addend, the residual branch's gradient)."""
     N, Ho, Wo, Cout = dy.shape
@@ -131,7 +155,7 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
         if addend is not None:
             dx = dx + addend.float()
         if out is not None:
-            if slabs:
+            if slabs and not cluster:
                 out.zero_()
                 out[0].copy_(dx)
             else:
@@ -141,7 +165,7 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
     import ctypes
     assert dy.is_contiguous() and w.is_contiguous()
     dx = out if out is not None else torch.empty((N, H, W, Cin), dtype=torch.bfloat16, device=dy.device)
-    e = _epi(None, addend, False, dx.dtype == torch.float32, splits, block_n, slabs)
+    e = _epi(None, addend, False, dx.dtype == torch.float32, splits, block_n, slabs and not cluster, cluster)
     _native.check(_native.lib().kml_conv2d_dgrad(
         dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_dgrad")

@@ -72,6 +72,43 @@ def bn_fwd_train(x, res, y, gamma, beta, running_mean, running_var, nbt, save_me
         nbt.add_(1)
 
 
+def bn_stats_numel(C: int) -> int:
+    """fp32 elements of a statistics buffer for `bn_apply_train` ([2][C] sums + ticket word)."""
+    return 2 * C + 4
+
+
+def bn_apply_train(x, stats, res, y, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd,
+                   relu: bool, eps: float = 1e-5, momentum: float = 0.1) -> None:
+    """BatchNorm forward from statistics the producing GEMM accumulated (`stats`: fp32 [2C+4], sums and
+    sums of squares over the M rows; cleared again here)."""
+    C = y.shape[-1]
+    M = y.numel() // C
+    if y.is_cuda:
+        _native.check(_native.lib().kml_bn_apply_train(
+            x.data_ptr(), stats.data_ptr(), _ptr(res), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+            _ptr(running_mean), _ptr(running_var), _ptr(nbt), save_mean.data_ptr(), save_invstd.data_ptr(), M, C,
+            int(relu), eps, momentum, _native.stream_ptr()), "kml_bn_apply_train")
+        return
+    st = stats[: 2 * C].view(2, C)
+    mean = st[0] / M
+    var = (st[1] / M - mean * mean).clamp_min(0.0)
+    invstd = torch.rsqrt(var + eps)
+    out = (x.float().reshape(M, C) - mean) * invstd * gamma + beta
+    if res is not None:
+        out = out + res.float().reshape(M, C)
+    if relu:
+        out = torch.relu(out)
+    y.copy_(out.reshape(y.shape))
+    save_mean.copy_(mean)
+    save_invstd.copy_(invstd)
+    if running_mean is not None:
+        running_mean.mul_(1 - momentum).add_(momentum * mean)
+        running_var.mul_(1 - momentum).add_(momentum * var * (M / max(M - 1, 1)))
+    if nbt is not None:
+        nbt.add_(1)
+    stats.zero_()
+
+
 def bn_fwd_eval(x, res, y, gamma, beta, running_mean, running_var, relu: bool, eps: float = 1e-5,
                 x_slabs=None) -> None:
     C = y.shape[-1]

@@ -385,3 +385,63 @@ def test_relu_bwd_cols_bias_act_colsum(dev, M, C, S):
         yb = torch.empty(M, C, device=dev, dtype=torch.bfloat16)
         K.bias_act(slabs, bias, yb, True)
         _close(yb, torch.relu(v + bias), 1e-2)
+
+
+@pytest.mark.parametrize("N,H,C,Co,S", [(16, 4, 128, 128, 4), (64, 2, 256, 256, 8), (8, 8, 64, 64, 3), (128, 8, 64, 64, 1),
+                                        (4, 4, 64, 72, 5)])
+def test_cluster_splitk_conv_stats_then_bn_apply(dev, N, H, C, Co, S):
+    """Split-K as a thread-block cluster: partial tiles are added through distributed shared memory, the
+    GEMM writes the final bf16 output and the BatchNorm statistics; BatchNorm is then element-wise."""
+    from kubeml_b200 import ops
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(0)
+    x = torch.randn(N, H, H, C).bfloat16()
+    w = (torch.randn(Co, 3, 3, C) * 0.05).bfloat16()
+    ref = torch.nn.functional.conv2d(x.permute(0, 3, 1, 2).float(), w.permute(0, 3, 1, 2).float(), padding=1)
+    ref = ref.permute(0, 2, 3, 1).contiguous()
+    y = torch.empty(N, H, H, Co, dtype=torch.bfloat16, device=dev)
+    stats = torch.zeros(K.bn_stats_numel(Co), device=dev)
+    for _ in range(2):                                    # twice: bn_apply must leave the statistics cleared
+        ops.conv2d_fprop(x.to(dev), w.to(dev), 1, out=y, block_n=64, splits=S, cluster=True, stats=stats)
+        torch.cuda.synchronize()
+        _close(y, ref, 1e-2)
+        M = N * H * H
+        yf = y.float().reshape(M, Co)
+        torch.testing.assert_close(stats[:Co], yf.sum(0), rtol=1e-3, atol=1e-2)
+        torch.testing.assert_close(stats[Co:2 * Co], (yf * yf).sum(0), rtol=1e-3, atol=1e-2)
+        gamma, beta = torch.rand(Co, device=dev) + 0.5, torch.randn(Co, device=dev)
+        out = torch.empty_like(y)
+        rm, rv = torch.zeros(Co, device=dev), torch.ones(Co, device=dev)
+        nbt = torch.zeros((), dtype=torch.long, device=dev)
+        mean, istd = torch.empty(Co, device=dev), torch.empty(Co, device=dev)
+        K.bn_apply_train(y, stats, None, out, gamma, beta, rm, rv, nbt, mean, istd, True)
+        want = torch.relu(torch.nn.functional.batch_norm(yf, None, None, gamma, beta, True, 0.1, 1e-5))
+        _close(out.reshape(M, Co), want, 2e-2)
+        torch.testing.assert_close(mean, yf.mean(0), rtol=1e-3, atol=1e-3)
+        torch.testing.assert_close(rv, 0.9 + 0.1 * yf.var(0, unbiased=True), rtol=1e-3, atol=1e-3)
+        assert float(stats.abs().max()) == 0.0 and int(nbt) == 1
+
+
+def test_cluster_splitk_gemm_bias_relu_and_dgrad(dev):
+    from kubeml_b200 import ops
+    torch.manual_seed(0)
+    a = torch.randn(200, 1152, device=dev).bfloat16()
+    b = (torch.randn(96, 1152, device=dev) * 0.05).bfloat16()
+    bias = torch.randn(96, device=dev)
+    out = torch.empty(200, 96, device=dev, dtype=torch.bfloat16)
+    ops.gemm_bf16(a, b, bias=bias, relu=True, out=out, block_n=64, splits=6, cluster=True)
+    _close(out, torch.relu(a.float() @ b.float().t() + bias), 1e-2)
+    of = torch.empty(200, 96, device=dev)
+    ops.gemm_bf16(a, b, out=of, block_n=128, splits=2, cluster=True)
+    _close(of, a.float() @ b.float().t(), 2e-3)
+    # data gradient with the residual addend
+    N, H, C, Co = 16, 4, 128, 128
+    dy = torch.randn(N, H, H, Co).bfloat16()
+    w = (torch.randn(Co, 3, 3, C) * 0.05).bfloat16()
+    add = torch.randn(N, H, H, C).bfloat16()
+    want = torch.nn.grad.conv2d_input((N, C, H, H), w.permute(0, 3, 1, 2).float(), dy.permute(0, 3, 1, 2).float(),
+                                      padding=1).permute(0, 2, 3, 1) + add.float()
+    got = torch.empty(N, H, H, C, dtype=torch.bfloat16, device=dev)
+    ops.conv2d_dgrad(dy.to(dev), w.to(dev), 1, H, H, addend=add.to(dev), out=got, block_n=64, splits=7, cluster=True)
+    torch.cuda.synchronize()
+    _close(got, want, 1e-2)
