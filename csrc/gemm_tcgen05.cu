@@ -71,6 +71,10 @@ struct GemmArgs {
   int cluster_reduce;                    // the `splits` CTAs of a tile are one cluster: partial tiles are added
                                          // through distributed shared memory, the epilogue runs once per element
   float* stats;                          // cluster mode: fp32 [2][n_valid] += column sums / sums of squares
+  const __nv_bfloat16* mask_y;           // cluster mode: output *= (mask_y > 0)
+  const __nv_bfloat16* bn_x;             // cluster mode: stats become {sum g, sum g * xhat}, xhat from bn_x/mean/invstd
+  const float* bn_mean;
+  const float* bn_invstd;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -456,6 +460,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll
         for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) bv[t] = __ldg(args.bias + ncol + t);
       }
+      float bm[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {0.f, 0.f, 0.f, 0.f};
+      if (args.bn_x != nullptr) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          if (ncol + t < args.n_valid) { bm[t] = args.bn_mean[ncol + t]; bi[t] = args.bn_invstd[ncol + t]; }
+      }
       for (int r = rbeg + et / kGroups; r < rend; r += 128 / kGroups) {
         const uint32_t laddr = smem_u32(part + r * kPartStride + c4);
         float4 acc = ld_dsmem_f4(laddr, 0);
@@ -483,6 +493,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll
           for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
         }
+        if (args.mask_y != nullptr) {
+          const __nv_bfloat16* my = args.mask_y + ro;
+          if (col_ok && (ro & 3) == 0) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(my));
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+            f[0] = a0.x > 0.f ? f[0] : 0.f; f[1] = a0.y > 0.f ? f[1] : 0.f;
+            f[2] = a1.x > 0.f ? f[2] : 0.f; f[3] = a1.y > 0.f ? f[3] : 0.f;
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+              if (ncol + t < args.n_valid) f[t] = __bfloat162float(my[t]) > 0.f ? f[t] : 0.f;
+          }
+        }
         if (args.out_f32) {
           float* o = static_cast<float*>(args.out) + ro;
           if (col_ok && (ro & 3) == 0) {
@@ -508,8 +532,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           const float2 r0 = __bfloat1622float2(p0), r1 = __bfloat1622float2(p1);
           f[0] = r0.x; f[1] = r0.y; f[2] = r1.x; f[3] = r1.y;
         }
+        if (args.bn_x != nullptr) {                     // BatchNorm-backward sums: g and g * xhat
+          float xh[4] = {0.f, 0.f, 0.f, 0.f};
+          const __nv_bfloat16* bx = args.bn_x + ro;
+          if (col_ok && (ro & 3) == 0) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(bx));
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+            xh[0] = a0.x; xh[1] = a0.y; xh[2] = a1.x; xh[3] = a1.y;
+          } else {
 #pragma unroll
-        for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) xh[t] = __bfloat162float(bx[t]);
+          }
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            s1[t] += f[t];
+            s2[t] = fmaf(f[t], (xh[t] - bm[t]) * bi[t], s2[t]);
+          }
+        } else {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
+        }
       }
       if (args.stats != nullptr) {
 #pragma unroll
@@ -573,6 +616,7 @@ int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs&
   static bool configured = false;
   if (!configured) {
     KML_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    KML_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));   // clusters of 16
     configured = true;
   }
   dim3 grid(a.m_tiles, a.n_tiles, a.z_taps * a.splits);
@@ -661,10 +705,15 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
   g.atomic_add = g.splits > 1 && !epi->slabs;
   g.slab_stride = (g.splits > 1 && epi->slabs) ? static_cast<long long>(M) * ldo : 0;
   if (epi->cluster) {
-    KML_CHECK(g.splits <= 8 && block_n <= 128, "cluster split-K: at most 8 splits, block_n <= 128");
+    KML_CHECK(g.splits <= 16 && block_n <= 128, "cluster split-K: at most 16 splits, block_n <= 128");
     g.cluster_reduce = 1; g.stats = epi->stats; g.atomic_add = 0; g.slab_stride = 0;
+    g.mask_y = static_cast<const __nv_bfloat16*>(epi->mask_y);
+    g.bn_x = static_cast<const __nv_bfloat16*>(epi->bn_x);
+    g.bn_mean = epi->bn_mean; g.bn_invstd = epi->bn_invstd;
+    KML_CHECK(!g.bn_x || (g.bn_mean && g.bn_invstd && g.stats), "bn_x needs bn_mean, bn_invstd and stats");
   } else {
-    KML_CHECK(epi->stats == nullptr, "column statistics need cluster mode");
+    KML_CHECK(epi->stats == nullptr && epi->mask_y == nullptr && epi->bn_x == nullptr,
+              "column statistics / masks need cluster mode");
     KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
   }
   return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
@@ -741,10 +790,15 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
   g.atomic_add = g.splits > 1 && !epi->slabs;
   g.slab_stride = (g.splits > 1 && epi->slabs) ? Mtot * Cout : 0;
   if (epi->cluster) {
-    KML_CHECK(g.splits <= 8 && block_n <= 128, "cluster split-K: at most 8 splits, block_n <= 128");
+    KML_CHECK(g.splits <= 16 && block_n <= 128, "cluster split-K: at most 16 splits, block_n <= 128");
     g.cluster_reduce = 1; g.stats = epi->stats; g.atomic_add = 0; g.slab_stride = 0;
+    g.mask_y = static_cast<const __nv_bfloat16*>(epi->mask_y);
+    g.bn_x = static_cast<const __nv_bfloat16*>(epi->bn_x);
+    g.bn_mean = epi->bn_mean; g.bn_invstd = epi->bn_invstd;
+    KML_CHECK(!g.bn_x || (g.bn_mean && g.bn_invstd && g.stats), "bn_x needs bn_mean, bn_invstd and stats");
   } else {
-    KML_CHECK(epi->stats == nullptr, "column statistics need cluster mode");
+    KML_CHECK(epi->stats == nullptr && epi->mask_y == nullptr && epi->bn_x == nullptr,
+              "column statistics / masks need cluster mode");
     KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
   }
   g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);

@@ -451,14 +451,6 @@ __global__ void __launch_bounds__(kThreads) bn_apply_train_kernel(const BnApplyA
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.num_batches_tracked) *a.num_batches_tracked += 1;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    unsigned int* ticket = reinterpret_cast<unsigned int*>(a.stats + 2 * a.C);
-    is_last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;     // wraps to 0: self-resetting
-  }
-  __syncthreads();
-  if (is_last)
-    for (int c = threadIdx.x; c < 2 * a.C; c += kThreads) a.stats[c] = 0.f;
 
   const int groups = a.C / kVec;
   const size_t total = static_cast<size_t>(a.M) * groups;
@@ -482,6 +474,64 @@ __global__ void __launch_bounds__(kThreads) bn_apply_train_kernel(const BnApplyA
     }
     store8(a.y + off, f);
   }
+  // Off the critical path: the last CTA to get here (all have read the statistics long ago) clears
+  // them for the next step.  atomicInc wraps to 0, so the ticket resets itself.
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(a.stats + 2 * a.C);
+    is_last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (is_last)
+    for (int c = threadIdx.x; c < 2 * a.C; c += kThreads) a.stats[c] = 0.f;
+}
+
+// Backward from the sums the producing data-gradient GEMM accumulated: g is already masked.
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
+                    const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ istd,
+                    float* __restrict__ stats, __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
+                    float* __restrict__ dbeta, int M, int C) {
+  extern __shared__ float sm[];                    // [C] each: k1, k2, scale, mean, invstd
+  __shared__ int is_last;
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const float inv_m = 1.f / static_cast<float>(M);
+  for (int c = threadIdx.x; c < C; c += kThreads) {
+    const float s1 = __ldcg(stats + c), s2 = __ldcg(stats + C + c);
+    const float is = istd[c];
+    sm[c] = s1 * inv_m;
+    sm[C + c] = s2 * inv_m;
+    sm[2 * C + c] = gamma[c] * is;
+    sm[3 * C + c] = mean[c];
+    sm[4 * C + c] = is;
+    if (blockIdx.x == 0) { dbeta[c] = s1; dgamma[c] = s2; }
+  }
+  __syncthreads();
+  const int groups = C / kVec;
+  const size_t total = static_cast<size_t>(M) * groups;
+  for (size_t idx = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x; idx < total;
+       idx += static_cast<size_t>(gridDim.x) * kThreads) {
+    const int c0 = static_cast<int>(idx % groups) * kVec;
+    const size_t off = (idx / groups) * C + c0;
+    float gv[kVec], xv[kVec], d[kVec];
+    load8(g + off, gv);
+    load8(x + off, xv);
+#pragma unroll
+    for (int i = 0; i < kVec; ++i) {
+      const float xh = (xv[i] - sm[3 * C + c0 + i]) * sm[4 * C + c0 + i];
+      d[i] = sm[2 * C + c0 + i] * (gv[i] - sm[c0 + i] - xh * sm[C + c0 + i]);
+    }
+    store8(dx + off, d);
+  }
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(stats + 2 * C);
+    is_last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (is_last)
+    for (int c = threadIdx.x; c < 2 * C; c += kThreads) stats[c] = 0.f;
 }
 
 int bn_grid(int M, int C, const void* kernel, size_t smem) {
@@ -542,6 +592,23 @@ int kml_bn_apply_train(const void* x, float* stats, const void* res, void* y, co
   const int grid = static_cast<int>(want < cap ? (want < 1 ? 1 : want) : cap);
   KML_CUDA(kml::launch_pdl(bn_apply_train_kernel, dim3(grid), dim3(kThreads), 2 * C * sizeof(float),
                            static_cast<cudaStream_t>(stream), a));
+  kml::count_launch();
+  return 0;
+}
+
+int kml_bn_bwd_apply(const void* g, const void* x, const float* gamma, const float* save_mean,
+                     const float* save_invstd, float* stats, void* dx, float* dgamma, float* dbeta, int M, int C,
+                     void* stream) {
+  KML_CHECK(g && x && gamma && save_mean && save_invstd && stats && dx && dgamma && dbeta, "kml_bn_bwd_apply: null pointer");
+  KML_CHECK(C % kVec == 0 && C <= kMaxC && M > 0, "kml_bn_bwd_apply: C (%d) must be a multiple of 8 and <= %d", C, kMaxC);
+  const size_t total = static_cast<size_t>(M) * (C / kVec);
+  size_t want = (total + kThreads - 1) / kThreads;
+  const size_t cap = static_cast<size_t>(kml::num_sms()) * 2;
+  const int grid = static_cast<int>(want < cap ? (want < 1 ? 1 : want) : cap);
+  KML_CUDA(kml::launch_pdl(bn_bwd_apply_kernel, dim3(grid), dim3(kThreads), 5 * C * sizeof(float),
+                           static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(g),
+                           static_cast<const __nv_bfloat16*>(x), gamma, save_mean, save_invstd, stats,
+                           static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, M, C));
   kml::count_launch();
   return 0;
 }

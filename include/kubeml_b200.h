@@ -145,6 +145,13 @@ typedef struct {
                                squares of the (rounded) output over all rows - the BatchNorm batch
                                statistics, produced where the data already is (zero it before the GEMM;
                                kml_bn_apply_train re-zeroes it after use)                                */
+  /* cluster mode, data-gradient GEMMs feeding a BatchNorm backward (all optional): the output becomes the
+     masked gradient g = out * (mask_y > 0), and when bn_x is given `stats` receives the two sums that
+     layer's backward needs, sum g and sum g * (bn_x - bn_mean) * bn_invstd, instead of sum / sum of squares */
+  const void* mask_y;       /* bf16, shaped like the output                                          */
+  const void* bn_x;         /* bf16, shaped like the output: the BatchNorm input saved by forward     */
+  const float* bn_mean;     /* fp32 [N]                                                               */
+  const float* bn_invstd;   /* fp32 [N]                                                               */
 } kml_epilogue;
 
 /* out[M,N] = A * B^T.  a_mn = 0: A is [M][K] (lda = row stride); a_mn = 1: A is [K][M].  Same for B
@@ -179,6 +186,12 @@ size_t kml_bn_stats_bytes(int C);
 int kml_bn_apply_train(const void* x, float* stats, const void* res, void* y, const float* gamma, const float* beta,
                        float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
                        float* save_invstd, int M, int C, int relu, float eps, float momentum, void* stream);
+/* Backward counterpart: g = masked gradient and stats = {sum g, sum g*xhat} come from the producing
+ * data-gradient GEMM (kml_epilogue.mask_y / bn_x); dx = gamma*invstd*(g - s1/M - xhat*s2/M), dgamma = s2,
+ * dbeta = s1.  Element-wise; clears stats after use. */
+int kml_bn_bwd_apply(const void* g, const void* x, const float* gamma, const float* save_mean,
+                     const float* save_invstd, float* stats, void* dx, float* dgamma, float* dbeta, int M, int C,
+                     void* stream);
 int kml_bn_fwd_train(const void* x, const float* x_slabs, int nslabs, long long slab_stride, void* x_out,
                      const void* res, void* y, const float* gamma, const float* beta, float* running_mean,
                      float* running_var, long long* num_batches_tracked, float* save_mean,

@@ -51,7 +51,8 @@ class MergeParams(Structure):
 
 class Epilogue(Structure):
     _fields_ = [("bias", c_void_p), ("addend_bf16", c_void_p), ("relu", c_int), ("out_f32", c_int),
-                ("splits", c_int), ("slabs", c_int), ("block_n", c_int), ("cluster", c_int), ("stats", c_void_p)]
+                ("splits", c_int), ("slabs", c_int), ("block_n", c_int), ("cluster", c_int), ("stats", c_void_p),
+                ("mask_y", c_void_p), ("bn_x", c_void_p), ("bn_mean", c_void_p), ("bn_invstd", c_void_p)]
 
 
 def _declare(lib) -> None:
@@ -106,6 +107,8 @@ def _declare(lib) -> None:
     sig("kml_bn_stats_bytes", c_size_t, c_int)
     sig("kml_bn_apply_train", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
         c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p)
+    sig("kml_bn_bwd_apply", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+        c_void_p, c_int, c_int, c_void_p)
     sig("kml_bn_fwd_train", c_int, c_void_p, c_void_p, c_int, c_longlong, c_void_p, c_void_p, c_void_p,
         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
         c_float, c_float, c_void_p)

@@ -140,10 +140,17 @@ class NativeResNet(NativeNet):
             first_block = bi == nblk - 1          # its input gradient feeds the max-pool backward (dense)
             # out = relu(bn2(t2) + idn)
             dt2, g = bn_backward(blk.bn2, dh, out, t2, B, tag + ".bn2", want_dres=True)
-            da = conv_backward(blk.conv2, a, dt2, B, tag + ".c2", allow_slabs=True)
+            # the data-gradient GEMMs mask and pre-reduce for the BatchNorm backward that follows them
+            da = conv_backward(blk.conv2, a, dt2, B, tag + ".c2", allow_slabs=True,
+                               bn_next=(blk.bn1, tag + ".bn1", a, t1))
             dt1, _ = bn_backward(blk.bn1, da, a, t1, B, tag + ".bn1")
             if blk.downsample is None:
-                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=g, allow_slabs=not first_block)
+                nxt = None
+                if not first_block:              # consumer: bn2 of the block before (its output is `h`)
+                    ptag, pblk = self._blocks[nblk - 2 - bi]
+                    nxt = (pblk.bn2, ptag + ".bn2", h, S["blocks"][nblk - 2 - bi][3])
+                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=g, allow_slabs=not first_block,
+                                   bn_next=nxt)
             else:
                 dtd, _ = bn_backward(blk.downsample[1], Act(g), None, td, B, tag + ".bnd")
                 did = conv_backward(blk.downsample[0], h, dtd, B, tag + ".cd")

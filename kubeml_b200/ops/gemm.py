@@ -16,7 +16,7 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
 
 
 def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0, slabs=False,
-         cluster=False, stats=None):
+         cluster=False, stats=None, mask_y=None, bn=None):
     e = _native.Epilogue()
     e.bias = _ptr(bias) or None
     e.addend_bf16 = _ptr(addend) or None
@@ -24,6 +24,9 @@ def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0,
     e.slabs = int(slabs)
     e.cluster = int(cluster)
     e.stats = _ptr(stats) or None
+    e.mask_y = _ptr(mask_y) or None
+    if bn is not None:                       # (x saved by forward, mean, invstd) of the consuming BatchNorm
+        e.bn_x, e.bn_mean, e.bn_invstd = bn[0].data_ptr(), bn[1].data_ptr(), bn[2].data_ptr()
     return e
 
 
@@ -144,9 +147,14 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
 
 def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
                  addend: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                 block_n: int = 0, splits: int = 1, slabs: bool = False, cluster: bool = False) -> torch.Tensor:
+                 block_n: int = 0, splits: int = 1, slabs: bool = False, cluster: bool = False,
+                 mask_y: Optional[torch.Tensor] = None, bn=None,
+                 stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Data gradient of `conv2d_fprop`: dy [N,Ho,Wo,Cout] bf16, w the *forward* filter
-    [Cout,KH,KW,Cin] bf16 -> dx [N,H,W,Cin] bf16 (+ addend, the residual branch's gradient)."""
+    [Cout,KH,KW,Cin] bf16 -> dx [N,H,W,Cin] bf16 (+ addend, the residual branch's gradient).
+    Cluster mode can hand the result to a BatchNorm backward ready-made: `mask_y` (that layer's
+    output, ReLU mask) is applied, and with `bn` = (x, mean, invstd) `stats` receives
+    [sum g, sum g*xhat] per channel (see `ops.nn.bn_bwd_apply`)."""
     N, Ho, Wo, Cout = dy.shape
     _, KH, KW, Cin = w.shape
     if not dy.is_cuda:
@@ -154,6 +162,14 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
                                         dy.permute(0, 3, 1, 2).float(), padding=pad).permute(0, 2, 3, 1)
         if addend is not None:
             dx = dx + addend.float()
+        if mask_y is not None:
+            dx = dx * (mask_y.float() > 0)
+        if bn is not None:
+            gq = dx.to(out.dtype if out is not None else dy.dtype).float().reshape(-1, Cin)
+            xh = (bn[0].float().reshape(-1, Cin) - bn[1]) * bn[2]
+            st = stats[: 2 * Cin].view(2, Cin)
+            st[0] += gq.sum(0)
+            st[1] += (gq * xh).sum(0)
         if out is not None:
             if slabs and not cluster:
                 out.zero_()
@@ -165,7 +181,8 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
     import ctypes
     assert dy.is_contiguous() and w.is_contiguous()
     dx = out if out is not None else torch.empty((N, H, W, Cin), dtype=torch.bfloat16, device=dy.device)
-    e = _epi(None, addend, False, dx.dtype == torch.float32, splits, block_n, slabs and not cluster, cluster)
+    e = _epi(None, addend, False, dx.dtype == torch.float32, splits, block_n, slabs and not cluster, cluster,
+             stats, mask_y, bn)
     _native.check(_native.lib().kml_conv2d_dgrad(
         dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_dgrad")

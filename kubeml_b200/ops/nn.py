@@ -109,6 +109,27 @@ def bn_apply_train(x, stats, res, y, gamma, beta, running_mean, running_var, nbt
     stats.zero_()
 
 
+def bn_bwd_apply(g, x, gamma, save_mean, save_invstd, stats, dx, dgamma, dbeta) -> None:
+    """BatchNorm backward from the masked gradient `g` and the sums [sum g, sum g*xhat] the producing
+    data-gradient GEMM accumulated in `stats` (cleared again here)."""
+    C = x.shape[-1]
+    M = x.numel() // C
+    if x.is_cuda:
+        _native.check(_native.lib().kml_bn_bwd_apply(
+            g.data_ptr(), x.data_ptr(), gamma.data_ptr(), save_mean.data_ptr(), save_invstd.data_ptr(),
+            stats.data_ptr(), dx.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), M, C, _native.stream_ptr()),
+            "kml_bn_bwd_apply")
+        return
+    st = stats[: 2 * C].view(2, C)
+    s1, s2 = st[0].clone(), st[1].clone()
+    gf = g.float().reshape(M, C)
+    xhat = (x.float().reshape(M, C) - save_mean) * save_invstd
+    dbeta.copy_(s1)
+    dgamma.copy_(s2)
+    dx.copy_((gamma * save_invstd * (gf - s1 / M - xhat * s2 / M)).reshape(dx.shape))
+    stats.zero_()
+
+
 def bn_fwd_eval(x, res, y, gamma, beta, running_mean, running_var, relu: bool, eps: float = 1e-5,
                 x_slabs=None) -> None:
     C = y.shape[-1]

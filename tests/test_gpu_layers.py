@@ -445,3 +445,45 @@ def test_cluster_splitk_gemm_bias_relu_and_dgrad(dev):
     ops.conv2d_dgrad(dy.to(dev), w.to(dev), 1, H, H, addend=add.to(dev), out=got, block_n=64, splits=7, cluster=True)
     torch.cuda.synchronize()
     _close(got, want, 1e-2)
+
+
+@pytest.mark.parametrize("N,H,C,Co,S", [(16, 4, 128, 128, 4), (64, 2, 256, 256, 8), (32, 8, 64, 64, 2)])
+def test_cluster_dgrad_feeds_bn_backward(dev, N, H, C, Co, S):
+    """The data-gradient GEMM masks its output with the consumer's ReLU and accumulates that BatchNorm's
+    two backward sums; bn_bwd_apply is then element-wise.  Oracle: fp32 torch autograd of
+    relu(bn(x)) -> conv."""
+    from kubeml_b200 import ops
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(0)
+    M = N * H * H
+    x = (torch.randn(N, H, H, C) * 1.5 + 0.3).bfloat16()             # BatchNorm input saved by forward
+    gamma, beta = torch.rand(C) + 0.5, torch.randn(C) * 0.2
+    w = (torch.randn(Co, 3, 3, C) * 0.05).bfloat16()
+    dy = torch.randn(N, H, H, Co).bfloat16()
+    add = (torch.randn(N, H, H, C) * 0.5).bfloat16()
+    # fp32 oracle
+    xr = x.float().requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    yb = torch.nn.functional.batch_norm(xr.reshape(M, C), None, None, gr, br, True, 0.1, 1e-5).reshape(N, H, H, C)
+    a = torch.relu(yb)
+    out = torch.nn.functional.conv2d(a.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2).float(), padding=1)
+    (out.permute(0, 2, 3, 1) * dy.float()).sum().backward(retain_graph=True)
+    # the residual gradient enters before the mask: d/da of (a * add).sum()
+    (a * add.float()).sum().backward()
+    # device path
+    xd, gd = x.to(dev), gamma.to(dev)
+    mean = xd.float().reshape(M, C).mean(0)
+    istd = torch.rsqrt(xd.float().reshape(M, C).var(0, unbiased=False) + 1e-5)
+    stats = torch.zeros(K.bn_stats_numel(C), device=dev)
+    g = torch.empty(N, H, H, C, dtype=torch.bfloat16, device=dev)
+    for _ in range(2):
+        ops.conv2d_dgrad(dy.to(dev), w.to(dev), 1, H, H, addend=add.to(dev), out=g, block_n=64, splits=S, cluster=True,
+                         mask_y=a.detach().bfloat16().to(dev), bn=(xd, mean, istd), stats=stats)
+        dx = torch.empty_like(g)
+        dg, db = torch.empty(C, device=dev), torch.empty(C, device=dev)
+        K.bn_bwd_apply(g, xd, gd, mean, istd, stats, dx, dg, db)
+        torch.cuda.synchronize()
+        assert float(stats.abs().max()) == 0.0
+        _close(dx, xr.grad, 3e-2)
+        _close(dg, gr.grad, 2e-2)
+        _close(db, br.grad, 2e-2)

@@ -16,8 +16,10 @@ def fp32_activations():
     nv.set_activation_dtype(torch.bfloat16)
 
 
-def test_resnet18_program_matches_torchvision(fp32_activations):
+@pytest.mark.parametrize("bn_bwd_fusion", ["0", "1"])
+def test_resnet18_program_matches_torchvision(fp32_activations, monkeypatch, bn_bwd_fusion):
     import torchvision
+    monkeypatch.setenv("KUBEML_CLUSTER_BNBWD", bn_bwd_fusion)
     from kubeml_b200.models import resnet18
     torch.manual_seed(0)
     net = resnet18(num_classes=10)
