@@ -442,8 +442,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     constexpr int kPartStride = BLOCK_N + 4;
     constexpr int kGroups = BLOCK_N / 4;                 // float4 groups per row
     float* part = reinterpret_cast<float*>(smem_a);
-    float* st_sm = part + kBlockM * kPartStride;        // [2][BLOCK_N] block-level column sums
-    for (int i = threadIdx.x; i < 2 * BLOCK_N; i += kNumThreads) st_sm[i] = 0.f;
+    float* st_sm = part + kBlockM * kPartStride;        // [4 warps][2][BLOCK_N] per-warp column sums
     cluster_sync_all();
     if (warp >= 2) {
       const int S = args.splits;
@@ -555,13 +554,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
       }
       if (args.stats != nullptr) {
+        // No shared-memory float atomics (they compile to compare-and-swap loops): lanes that share a
+        // column group fold with a shuffle, each warp writes its own row of partials, then 4-way sums.
+        if (kGroups == 16) {
 #pragma unroll
-        for (int t = 0; t < 4; ++t) { atomicAdd(st_sm + c4 + t, s1[t]); atomicAdd(st_sm + BLOCK_N + c4 + t, s2[t]); }
+          for (int t = 0; t < 4; ++t) {
+            s1[t] += __shfl_xor_sync(0xffffffffu, s1[t], 16);
+            s2[t] += __shfl_xor_sync(0xffffffffu, s2[t], 16);
+          }
+        }
+        float* wsm = st_sm + (warp - 2) * 2 * BLOCK_N;    // [4 warps][2][BLOCK_N]
+        if (lane < kGroups) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { wsm[c4 + t] = s1[t]; wsm[BLOCK_N + c4 + t] = s2[t]; }
+        }
         asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
         for (int i = et; i < 2 * BLOCK_N; i += 128) {
           const int c = i % BLOCK_N, which = i / BLOCK_N;
           const int gc = nt * BLOCK_N + c;
-          if (gc < args.n_valid) atomicAdd(args.stats + static_cast<size_t>(which) * args.n_valid + gc, st_sm[i]);
+          const float tot = st_sm[i] + st_sm[2 * BLOCK_N + i] + st_sm[4 * BLOCK_N + i] + st_sm[6 * BLOCK_N + i];
+          if (gc < args.n_valid) atomicAdd(args.stats + static_cast<size_t>(which) * args.n_valid + gc, tot);
         }
       }
     }

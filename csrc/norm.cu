@@ -96,29 +96,49 @@ __device__ __forceinline__ void load_row(const __nv_bfloat16* xb, const float* x
 // Block-level then grid-level combination of two per-channel sums.  On return sm[0..2C) holds the
 // grid totals.  `sm` needs 2C floats.
 __device__ __forceinline__ void combine_stats(BnScratch* sc, int C, int c0, bool active,
-                                              const float (&s1)[kVec], const float (&s2)[kVec], float* sm) {
+                                              const float (&s1)[kVec], const float (&s2)[kVec], float* sm,
+                                              bool wide_smem) {
   const unsigned par = sc->launches & 1u;          // read before anyone can bump it (bump is after the sync)
   const unsigned base = sc->bar_base;
-  for (int i = threadIdx.x; i < 2 * C; i += kThreads) sm[i] = 0.f;
-  __syncthreads();
-  {
-    // threads of a warp that own the same channel group are `groups` lanes apart: fold them with
-    // shuffles first (power-of-two group counts), then one shared-memory atomic per warp and channel
-    const int groups = C / kVec;
-    float r1[kVec], r2[kVec];
+  const int groups = C / kVec;
+  // Shared-memory float atomics compile to compare-and-swap loops, so avoid them where the layout
+  // allows: with a power-of-two group count <= 32 the lanes of a warp that share a channel group fold
+  // with shuffles and every warp covers ALL channel groups, so each warp owns one row of a
+  // [warps][2C] table (wide_smem) that is then summed; otherwise fall back to atomics.
+  // (More than 32 groups: `wpg` consecutive warps cover the groups between them, so warps w and
+  // w + wpg write the same entries and take different rows.)
+  const bool tabled = wide_smem && groups <= kThreads && (groups & (groups - 1)) == 0;
+  const int wpg = groups > 32 ? groups / 32 : 1;
+  const int nrows = (kThreads / 32) / wpg;
+  float r1[kVec], r2[kVec];
 #pragma unroll
-    for (int i = 0; i < kVec; ++i) { r1[i] = active ? s1[i] : 0.f; r2[i] = active ? s2[i] : 0.f; }
-    bool writer = active;
-    if (groups < 32 && (groups & (groups - 1)) == 0) {
-      for (int off = groups; off < 32; off <<= 1) {
+  for (int i = 0; i < kVec; ++i) { r1[i] = active ? s1[i] : 0.f; r2[i] = active ? s2[i] : 0.f; }
+  bool writer = active;
+  if (groups < 32 && (groups & (groups - 1)) == 0) {
+    for (int off = groups; off < 32; off <<= 1) {
 #pragma unroll
-        for (int i = 0; i < kVec; ++i) {
-          r1[i] += __shfl_xor_sync(0xffffffffu, r1[i], off);
-          r2[i] += __shfl_xor_sync(0xffffffffu, r2[i], off);
-        }
+      for (int i = 0; i < kVec; ++i) {
+        r1[i] += __shfl_xor_sync(0xffffffffu, r1[i], off);
+        r2[i] += __shfl_xor_sync(0xffffffffu, r2[i], off);
       }
-      writer = (threadIdx.x & 31) < groups;
     }
+    writer = (threadIdx.x & 31) < groups;
+  }
+  if (tabled) {
+    float* row = sm + 2 * C + ((threadIdx.x >> 5) / wpg) * 2 * C;     // table starts after the totals
+    if (writer) {
+#pragma unroll
+      for (int i = 0; i < kVec; ++i) { row[c0 + i] = r1[i]; row[C + c0 + i] = r2[i]; }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * C; i += kThreads) {
+      float t = 0.f;
+      for (int w = 0; w < nrows; ++w) t += sm[2 * C + w * 2 * C + i];
+      sm[i] = t;
+    }
+  } else {
+    for (int i = threadIdx.x; i < 2 * C; i += kThreads) sm[i] = 0.f;
+    __syncthreads();
     if (writer) {
 #pragma unroll
       for (int i = 0; i < kVec; ++i) { atomicAdd(&sm[c0 + i], r1[i]); atomicAdd(&sm[C + c0 + i], r2[i]); }
@@ -158,6 +178,7 @@ struct BnFwdArgs {
   BnScratch* scratch;
   int M, C, relu;
   float eps, momentum;
+  int wide_smem;                // dynamic smem holds [2C] totals + [warps][2C] table
 };
 
 __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs a) {
@@ -205,7 +226,7 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
       for (int i = 0; i < kVec; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
     }
   }
-  combine_stats(a.scratch, a.C, c0, active, s, q, sm);
+  combine_stats(a.scratch, a.C, c0, active, s, q, sm, a.wide_smem != 0);
 
   const float inv_m = 1.f / static_cast<float>(a.M);
   float sc[kVec], sh[kVec];
@@ -309,6 +330,7 @@ struct BnBwdArgs {
   float* dbeta;
   BnScratch* scratch;
   int M, C;
+  int wide_smem;
 };
 
 __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
@@ -371,7 +393,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
       for (int i = 0; i < kVec; ++i) { s1[i] += g2[i]; s2[i] = fmaf(g2[i], x2[i], s2[i]); }
     }
   }
-  combine_stats(a.scratch, a.C, c0, active, s1, s2, sm);
+  combine_stats(a.scratch, a.C, c0, active, s1, s2, sm, a.wide_smem != 0);
 
   if (blockIdx.x == 0 && lane == 0) {
 #pragma unroll
@@ -568,8 +590,9 @@ int kml_bn_fwd_train(const void* x, const float* x_slabs, int nslabs, long long 
   BnFwdArgs a{static_cast<const __nv_bfloat16*>(x_slabs ? nullptr : x), x_slabs, nslabs, slab_stride,
               static_cast<__nv_bfloat16*>(x_slabs ? x_out : nullptr), static_cast<const __nv_bfloat16*>(res),
               static_cast<__nv_bfloat16*>(y), gamma, beta, running_mean, running_var, num_batches_tracked,
-              save_mean, save_invstd, static_cast<BnScratch*>(scratch), M, C, relu, eps, momentum};
-  const size_t smem = 2 * C * sizeof(float);
+              save_mean, save_invstd, static_cast<BnScratch*>(scratch), M, C, relu, eps, momentum, 0};
+  size_t smem = 2 * C * sizeof(float);
+  if (smem * (1 + kThreads / 32) <= 46 * 1024) { smem *= 1 + kThreads / 32; a.wide_smem = 1; }
   const int grid = bn_grid(M, C, reinterpret_cast<const void*>(bn_fwd_train_kernel), smem);
   KML_CUDA(kml::launch_pdl(bn_fwd_train_kernel, dim3(grid), dim3(kThreads), smem, static_cast<cudaStream_t>(stream), a));
   kml::count_launch();
@@ -641,8 +664,9 @@ int kml_bn_bwd(const void* dy, const float* dy_slabs, int nslabs, long long slab
   BnBwdArgs a{static_cast<const __nv_bfloat16*>(dy_slabs ? nullptr : dy), dy_slabs, nslabs, slab_stride,
               static_cast<const __nv_bfloat16*>(dy_add), static_cast<const __nv_bfloat16*>(y),
               static_cast<const __nv_bfloat16*>(x), gamma, save_mean, save_invstd, static_cast<__nv_bfloat16*>(dx),
-              static_cast<__nv_bfloat16*>(dres), dgamma, dbeta, static_cast<BnScratch*>(scratch), M, C};
-  const size_t smem = 2 * C * sizeof(float);
+              static_cast<__nv_bfloat16*>(dres), dgamma, dbeta, static_cast<BnScratch*>(scratch), M, C, 0};
+  size_t smem = 2 * C * sizeof(float);
+  if (smem * (1 + kThreads / 32) <= 46 * 1024) { smem *= 1 + kThreads / 32; a.wide_smem = 1; }
   const int grid = bn_grid(M, C, reinterpret_cast<const void*>(bn_bwd_kernel), smem);
   KML_CUDA(kml::launch_pdl(bn_bwd_kernel, dim3(grid), dim3(kThreads), smem, static_cast<cudaStream_t>(stream), a));
   kml::count_launch();
