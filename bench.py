@@ -220,7 +220,7 @@ def run_own(args) -> int:
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=128)
     ap.add_argument("--warmup", type=int, default=16)
     ap.add_argument("--impl", default="own", choices=["own", "reference", "ref-torch", "ddp"])
     ap.add_argument("--model", default="resnet34", choices=["resnet34", "vgg16"])
