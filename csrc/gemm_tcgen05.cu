@@ -68,6 +68,8 @@ struct GemmArgs {
   int relu, out_f32, atomic_add;
   int wgt_taps, wgt_cin;                 // kWgtMN: taps in the filter, input channels per tap
   long long slab_stride;                 // != 0: split s stores its partial tile at out + s*slab_stride (no atomics)
+  int persistent;                        // grid = resident CTAs; each walks tiles tile0, tile0+grid, ... with two
+                                         // TMEM accumulators so a tile's epilogue overlaps the next tile's MMAs
   int cluster_reduce;                    // the `splits` CTAs of a tile are one cluster: partial tiles are added
                                          // through distributed shared memory, the epilogue runs once per element
   float* stats;                          // cluster mode: fp32 [2][n_valid] += column sums / sums of squares
@@ -112,6 +114,9 @@ __device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* ba
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
       "r"(c3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
@@ -173,7 +178,10 @@ __device__ __forceinline__ void box_origin(const Geometry& g, int idx, int& w0, 
   n0 = (t2 / g.tiles_h) * g.bn;
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN>
+// LINEAR: tiles are addressed by a linear, band-rasterised index (1-D grid, optionally persistent) -
+// the variant for problems of many tiles.  !LINEAR: one tile per CTA straight from the 3-D block index
+// (no index arithmetic at all) - the variant for the small, latency-bound launches and cluster mode.
+template <int BLOCK_N, bool A_MN, bool B_MN, bool LINEAR>
 __global__ void __launch_bounds__(kNumThreads, 2)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const GemmArgs args) {
@@ -189,31 +197,61 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   uint8_t* smem_b = smem + kStages * kABytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_b + kStages * kBBytes);
   uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tmem_full_bar = empty_bar + kStages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + kStages;        // [2] accumulator ready (MMA -> epilogue)
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;          // [2] accumulator drained (epilogue -> MMA)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
   int* tap_list = reinterpret_cast<int*>(tmem_slot + 1);   // up to 64 entries
 
   kml::pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int mt = blockIdx.x, nt = blockIdx.y;
-  const int z_tap = blockIdx.z / args.splits;
-  const int split = blockIdx.z % args.splits;
+  const int tiles_mn = args.m_tiles * args.n_tiles;
+  const bool persistent = LINEAR && args.persistent != 0;
+  const int total_tiles = LINEAR ? tiles_mn * args.z_taps * args.splits : 1;
+  const int tile0 = LINEAR ? static_cast<int>(blockIdx.x) : 0;
+  const int tstride = persistent ? static_cast<int>(gridDim.x) : total_tiles;
   const int per = (args.k_chunks + args.splits - 1) / args.splits;
-  const int kbeg = split * per;
-  const int kend = min(args.k_chunks, kbeg + per);
-  const int nchunks = max(0, kend - kbeg);
+  const uint32_t tmem_cols = persistent ? 2 * kTmemCols : kTmemCols;
+  struct Tile { int mt, nt, z_tap, split, kbeg, nchunks; };
+  auto decode = [&](int tile) {
+    Tile t;
+    int z;
+    if constexpr (LINEAR) {
+      // Rasterisation: walk the (m, n) tile grid in bands of kGroupM m-tiles, n fastest inside a band,
+      // so that the tiles in flight at any time (~2 per SM) share few A row-blocks and few B
+      // column-blocks (a 16 x 18 patch instead of a 128 x 2 stripe keeps the operands L2-resident).
+      constexpr int kGroupM = 16;
+      const int idx = tile % tiles_mn;
+      const int band = idx / (kGroupM * args.n_tiles);
+      const int band_m0 = band * kGroupM;
+      const int band_rows = min(kGroupM, args.m_tiles - band_m0);
+      const int in_band = idx - band * kGroupM * args.n_tiles;
+      t.mt = band_m0 + in_band % band_rows;
+      t.nt = in_band / band_rows;
+      z = tile / tiles_mn;
+    } else {
+      t.mt = blockIdx.x; t.nt = blockIdx.y; z = blockIdx.z;
+    }
+    t.z_tap = z / args.splits;
+    t.split = z % args.splits;
+    t.kbeg = t.split * per;
+    t.nchunks = max(0, min(args.k_chunks, t.kbeg + per) - t.kbeg);
+    return t;
+  };
+  const Tile T_only = decode(0);      // !LINEAR: the one tile of this CTA, decoded once for all roles
+  auto tile_at = [&](int tile) { return LINEAR ? decode(tile) : T_only; };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
     mbar_init(tmem_full_bar, 1);
+    if (LINEAR) { mbar_init(tmem_full_bar + 1, 1); mbar_init(tmem_empty_bar, 4); mbar_init(tmem_empty_bar + 1, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     int n = 0;
     for (int t = 0; t < 64; ++t) if ((args.tap_mask >> t) & 1ull) tap_list[n++] = t;
   }
   if (warp == 1) {   // this warp owns the TMEM allocation
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(kTmemCols) : "memory");
+                 "r"(tmem_cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tcgen05_fence_before();
@@ -227,14 +265,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     if (elect_one()) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      int it = 0;                                        // chunks issued so far, across tiles
+      for (int tile = tile0; tile < total_tiles; tile += tstride) {
+      const Tile T = tile_at(tile);
+      const int mt = T.mt, nt = T.nt, z_tap = T.z_tap, kbeg = T.kbeg, nchunks = T.nchunks;
       int tw0 = 0, th0 = 0, tn0 = 0;
       if (args.a_kind == kConvK) box_origin(args.tile_geo, mt, tw0, th0, tn0);
       const int z_dw = z_tap % max(args.kw, 1) - args.pad_w;   // kConvMN: fixed shift of this CTA's tap
       const int z_dh = z_tap / max(args.kw, 1) - args.pad_h;
-      for (int i = 0; i < nchunks; ++i) {
+      for (int i = 0; i < nchunks; ++i, ++it) {
         const int kc = kbeg + i;
-        const int s = i % kStages;
-        const uint32_t ph = (i / kStages) & 1;
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1;
         mbar_wait(empty_bar + s, ph ^ 1);
         mbar_expect_tx(full_bar + s, kABytes + kBBytes);
         uint8_t* sa = smem_a + s * kABytes;
@@ -285,13 +327,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             tma_load_4d(&map_b, full_bar + s, sb + hb * kHalfBytes, nt * BLOCK_N + hb * 64, cw + z_dw, ch + z_dh, cn);
         }
       }
+      }   // tiles
     }
   } else if (warp == 1) {
     // ===================================== MMA issuer ========================================
     constexpr uint32_t idesc = make_idesc(kBlockM, BLOCK_N, A_MN, B_MN);
-    for (int i = 0; i < nchunks; ++i) {
-      const int s = i % kStages;
-      const uint32_t ph = (i / kStages) & 1;
+    int it = 0, j = 0;
+    for (int tile = tile0; tile < total_tiles; tile += tstride, ++j) {
+    const int nchunks = tile_at(tile).nchunks;
+    const int acc = persistent ? (j & 1) : 0;
+    const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
+    // the epilogue must have drained this accumulator (tile j-2); passes at once the first time
+    if (persistent) {
+      mbar_wait(tmem_empty_bar + acc, ((j >> 1) & 1) ^ 1);
+      tcgen05_fence_after();
+    }
+    if (nchunks == 0 && elect_one()) mbar_arrive(tmem_full_bar + acc);
+    for (int i = 0; i < nchunks; ++i, ++it) {
+      const int s = it % kStages;
+      const uint32_t ph = (it / kStages) & 1;
       mbar_wait(full_bar + s, ph);
       tcgen05_fence_after();
       if (elect_one()) {
@@ -305,31 +359,36 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                                       : make_smem_desc(a_addr + k * 32, 16, 1024);
           const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * 2048, kHalfBytes, 1024)
                                       : make_smem_desc(b_addr + k * 32, 16, 1024);
-          umma_bf16(tmem_base, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+          umma_bf16(d_tmem, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
         }
       }
       __syncwarp();
       if (elect_one()) {
         umma_commit(empty_bar + s);                     // frees the smem slot when the MMAs retire
-        if (i == nchunks - 1) umma_commit(tmem_full_bar);
+        if (i == nchunks - 1) umma_commit(tmem_full_bar + acc);
       }
       __syncwarp();
     }
+    }   // tiles
   } else {
     // ===================================== epilogue ==========================================
     const int q = warp & 3;                              // TMEM lane quarter this warp may read
+    int j = 0;
+    for (int tile = tile0; tile < total_tiles; tile += tstride, ++j) {
+    const Tile T = tile_at(tile);
+    const int mt = T.mt, nt = T.nt, z_tap = T.z_tap, split = T.split, nchunks = T.nchunks;
+    const int acc = persistent ? (j & 1) : 0;
     const int row = mt * kBlockM + q * 32 + lane;
-    if (nchunks > 0) {
-      mbar_wait(tmem_full_bar, 0);
-      tcgen05_fence_after();
-    }
+    mbar_wait(tmem_full_bar + acc, (j >> 1) & 1);
+    tcgen05_fence_after();
     const bool row_ok = row < args.m_valid;
     const long long col_base = static_cast<long long>(z_tap) * args.z_col_stride + static_cast<long long>(nt) * BLOCK_N;
 #pragma unroll 1
     for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
       uint32_t v[32];
       if (nchunks > 0) {
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                               static_cast<uint32_t>(acc * BLOCK_N + c0);
         asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -343,6 +402,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = 0u;
+      }
+      if (persistent && c0 + 32 >= BLOCK_N) {   // accumulator fully read: hand it back before the stores
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
       }
       if (args.cluster_reduce) {
         // partial tile -> own shared memory (the pipeline ring is idle now); the reduction across the
@@ -430,11 +494,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
       }
     }
+    }   // tiles
     tcgen05_fence_before();
   }
 
   __syncthreads();
   if (args.cluster_reduce) {
+    const Tile T0 = tile_at(tile0);                      // cluster mode is never persistent: one tile
+    const int mt = T0.mt, nt = T0.nt, split = T0.split;
     // ---- split-K reduction across the cluster through distributed shared memory ----------------
     // CTA `split` owns rows [rbeg, rend) of the 128-row tile: it adds the partial tiles of all
     // peers for those rows, applies the epilogue once and writes the final output.  Column sums
@@ -581,7 +648,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   }
   if (warp == 1) {
     tcgen05_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
 }
 
@@ -621,21 +688,40 @@ int encode_map(CUtensorMap* map, const TensorSpec& t) {
   return 0;
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN>
-int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& a, cudaStream_t s) {
+template <int BLOCK_N, bool A_MN, bool B_MN, bool LINEAR>
+int launch_tiles(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& a, dim3 grid, cudaStream_t s) {
   constexpr size_t smem = Stages<BLOCK_N>::value * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 /*align*/ + 640 /*barriers+taps*/;
-  auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN>;
+  auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN, LINEAR>;
   static bool configured = false;
   if (!configured) {
     KML_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     KML_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));   // clusters of 16
     configured = true;
   }
-  dim3 grid(a.m_tiles, a.n_tiles, a.z_taps * a.splits);
   const dim3 cluster(1, 1, a.cluster_reduce ? a.splits : 1);
   KML_CUDA(kml::launch_pdl_cluster(kernel, grid, dim3(kNumThreads), smem, s, cluster, ma, mb, a));
   kml::count_launch();
   return 0;
+}
+
+template <int BLOCK_N, bool A_MN, bool B_MN>
+int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& a, cudaStream_t s) {
+  // Many tiles (more than two waves of resident CTAs): linear, band-rasterised tile index; with
+  // BLOCK_N <= 128 also persistent (2 CTAs per SM stride over the tiles, double-buffered accumulator:
+  // 2 x 2 x BLOCK_N <= 512 TMEM columns per SM).
+  static const bool allow_persistent = [] { const char* e = getenv("KUBEML_GEMM_PERSISTENT"); return !(e && e[0] == '0'); }();
+  const long long tiles = static_cast<long long>(a.m_tiles) * a.n_tiles * a.z_taps * a.splits;
+  const int resident = 2 * kml::num_sms();
+  if (!a.cluster_reduce && tiles > 2LL * resident) {
+    GemmArgs b = a;
+    dim3 grid(static_cast<unsigned>(tiles), 1, 1);
+    if (allow_persistent && BLOCK_N <= 128) {
+      b.persistent = 1;
+      grid = dim3(resident, 1, 1);
+    }
+    return launch_tiles<BLOCK_N, A_MN, B_MN, true>(ma, mb, b, grid, s);
+  }
+  return launch_tiles<BLOCK_N, A_MN, B_MN, false>(ma, mb, a, dim3(a.m_tiles, a.n_tiles, a.z_taps * a.splits), s);
 }
 
 int launch(const TensorSpec& ta, const TensorSpec& tb, const GemmArgs& a, int block_n, cudaStream_t s) {

@@ -13,7 +13,7 @@ from ctypes import (POINTER, Structure, c_char_p, c_float, c_int, c_longlong, c_
                     c_ulonglong, c_void_p)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libkubeml_b200.so")
+LIB_PATH = os.environ.get("KUBEML_NATIVE_LIB") or os.path.join(_HERE, "libkubeml_b200.so")     # override: A/B two builds
 KML_MAX_RANKS = 8
 
 _lib = None
