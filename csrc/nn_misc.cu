@@ -404,7 +404,31 @@ colpass_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ d
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(M, r0 + rows_per_block);
   if (active) {
-    for (int r = r0 + lane_row; r < r1; r += rpi) {
+    int r = r0 + lane_row;
+    if constexpr (!kSlabs) {
+      // four rows in flight per thread: the pass is latency-bound otherwise (2 loads, 1 store per row)
+      for (; r + 3 * rpi < r1; r += 4 * rpi) {
+        float v[4][8], m[4][8];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const size_t off = static_cast<size_t>(r + u * rpi) * ld + static_cast<size_t>(cgi) * 8;
+          ld8(dy + off, v[u]);
+          if (y) ld8(y + off, m[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const size_t off = static_cast<size_t>(r + u * rpi) * ld + static_cast<size_t>(cgi) * 8;
+          if (y) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[u][k] = m[u][k] > 0.f ? v[u][k] * scale : 0.f;
+          }
+          if (g) st8(g + off, v[u]);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += v[u][k];
+        }
+      }
+    }
+    for (; r < r1; r += rpi) {
       const size_t off = static_cast<size_t>(r) * ld + static_cast<size_t>(cgi) * 8;
       float v[8];
       if constexpr (kSlabs) {
@@ -770,7 +794,7 @@ static int colpass_launch(const void* dy, const float* dys, int S, size_t slab_s
   const int rpi = kThreads / cgw;
   const int gy = (cg + kThreads - 1) / kThreads;
   // enough blocks to fill the GPU, at least 4 iterations of rows each
-  int want = std::max(1, (kml::num_sms() * 4) / gy);
+  int want = std::max(1, (kml::num_sms() * 2) / gy);      // fewer, longer blocks: fewer atomics per column
   int rows_per_block = std::max(rpi * 4, (M + want - 1) / want);
   rows_per_block = (rows_per_block + rpi - 1) / rpi * rpi;
   const int gx = (M + rows_per_block - 1) / rows_per_block;

@@ -265,13 +265,13 @@ class NativeNet(nn.Module):
 _SMS = 148
 
 
-def auto_splits(tiles: int, chunks: int, min_chunks: int = 2) -> int:
+def auto_splits(tiles: int, chunks: int, min_chunks: int = 2, budget: int = _SMS) -> int:
     """K-splits for a GEMM with `tiles` output tiles and `chunks` 64-deep reduction chunks: enough
-    CTAs to cover the GPU, never fewer than `min_chunks` chunks per CTA, and only split counts
-    that leave no CTA without work."""
-    if tiles >= _SMS or chunks < 2 * min_chunks:
+    CTAs to cover the GPU (`budget` CTAs), never fewer than `min_chunks` chunks per CTA, and only
+    split counts that leave no CTA without work."""
+    if tiles >= budget or chunks < 2 * min_chunks:
         return 1
-    s = max(1, min(_SMS // max(tiles, 1), chunks // min_chunks))
+    s = max(1, min(budget // max(tiles, 1), chunks // min_chunks))
     per = (chunks + s - 1) // s
     return (chunks + per - 1) // per
 
@@ -281,6 +281,26 @@ def pick_block_n(m_tiles: int, n: int) -> int:
     if n <= 64:
         return 64
     return 128 if m_tiles * ((n + 127) // 128) >= _SMS // 2 else 64
+
+
+def plan_cluster(m_tiles: int, n: int, chunks: int, bn0: int):
+    """(block_n, splits) for a cluster split-K GEMM.  In this regime a CTA's time is its number of K
+    chunks times a TMA round trip, whatever the tile width (measured: 0.42 us per chunk for 128x64 and
+    128x128 alike), so when the default choice leaves long K loops a wider tile - half the tiles, twice
+    the splits - halves the time (VGG 512->512 on 4x4: 72 -> 36 chunks per CTA)."""
+    def plan(bn, budget=_SMS):
+        tiles = m_tiles * ((n + bn - 1) // bn)
+        S = min(auto_splits(tiles, chunks, min_chunks=_CL_MIN_CHUNKS, budget=budget), _CLUSTER_MAX)
+        return -(-chunks // S), S, bn
+    best = plan(bn0)
+    if best[0] > 12:                       # long K loops: consider wider tiles and two CTAs per SM
+        cands = [plan(bn0, 2 * _SMS)]
+        if bn0 == 64 and n >= 128:
+            cands += [plan(128), plan(128, 2 * _SMS)]
+        for c in cands:
+            if c[0] < best[0]:
+                best = c
+    return best[2], best[1]
 
 
 class Act:
@@ -353,18 +373,21 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
         chunks = (Kd + 63) // 64
     if allow_slabs and _cluster_enabled() and (want_stats or fold):
         # cluster split-K: complete output (+ bias/ReLU, + BatchNorm statistics) straight from the GEMM
-        S = min(auto_splits(tiles, chunks, min_chunks=_CL_MIN_CHUNKS), _CLUSTER_MAX)
+        bn_, S = plan_cluster(m_tiles, conv.cout, chunks, bn_)
         y = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
         stats = B.get(tag + ".stats", (K.bn_stats_numel(conv.cout),), torch.float32, zero=True) if want_stats else None
+        # one split and no statistics wanted: the plain epilogue does the same, and a launch without the
+        # cluster attribute may run persistent when it has many tiles
+        cl = S > 1 or stats is not None
         if direct:
-            ops.conv2d_fprop(x, conv.w_bf16, p, bias=bias, relu=relu, out=y, block_n=bn_, splits=S, cluster=True,
+            ops.conv2d_fprop(x, conv.w_bf16, p, bias=bias, relu=relu, out=y, block_n=bn_, splits=S, cluster=cl,
                              stats=stats)
         else:
             ldk = _ceil(Kd, 64)
             cols = B.get(tag + ".cols", (M, ldk))
             K.im2col(x, cols, k, k, s, p)
             ops.gemm_bf16(cols, _packed_weight(conv, B, tag, ldk), bias=bias, relu=relu, out=y.view(M, conv.cout),
-                          block_n=bn_, splits=S, cluster=True, stats=stats)
+                          block_n=bn_, splits=S, cluster=cl, stats=stats)
         return Act(y, 0, stats)
     can_split = allow_slabs and _slab_enabled() and (fold or (bias is None and not relu))
     S = auto_splits(tiles, chunks, min_chunks=3) if can_split else 1
@@ -433,7 +456,7 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
         live = sum(1 for kh in range(k) for kw in range(k)
                    if (kh - pd) <= Ho - 1 and (H - 1 + kh - pd) >= 0 and (kw - pd) <= Wo - 1 and (W - 1 + kw - pd) >= 0)
         if allow_slabs and _cluster_enabled():
-            S = min(auto_splits(dtiles, live * (conv.cout // 64), min_chunks=_CL_MIN_CHUNKS), _CLUSTER_MAX)
+            bn_d, S = plan_cluster(m_tiles, conv.cin, live * (conv.cout // 64), bn_d)
             dx = B.get(tag + ".dx", (N, H, W, conv.cin))
             if bn_next is not None and _bn_bwd_fusion():
                 nbn, ntag, ny, nx = bn_next
@@ -441,7 +464,7 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
                 ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=dx, block_n=bn_d, splits=S,
                                  cluster=True, mask_y=ny, bn=(nx, B[ntag + ".mean"], B[ntag + ".istd"]), stats=stats)
                 return Act(dx, 0, stats)
-            ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=dx, block_n=bn_d, splits=S, cluster=True)
+            ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=dx, block_n=bn_d, splits=S, cluster=S > 1)
             return Act(dx)
         S = auto_splits(dtiles, live * (conv.cout // 64), min_chunks=3) if (allow_slabs and _slab_enabled()) else 1
         if S > 1:
@@ -522,7 +545,8 @@ def linear_forward(fc: NLinear, x: torch.Tensor, B: Buffers, tag: str, relu: boo
     m_tiles = (M + 127) // 128
     bn_ = pick_block_n(m_tiles, fc.cout)
     tiles = m_tiles * ((fc.cout + bn_ - 1) // bn_)
-    S = auto_splits(tiles, (fc.cin + 63) // 64, min_chunks=8) if (_slab_enabled() and fc.cout % 8 == 0) else 1
+    # a long reduction (VGG fc1: 392 chunks) may take two CTAs per SM
+    S = auto_splits(tiles, (fc.cin + 63) // 64, min_chunks=8, budget=2 * _SMS) if (_slab_enabled() and fc.cout % 8 == 0) else 1
     if S > 1:
         slabs = B.get(tag + ".slabs", (S, M, fc.cout), torch.float32)
         ops.gemm_bf16(x, fc.w_bf16, out=slabs, block_n=bn_, splits=S, slabs=True)

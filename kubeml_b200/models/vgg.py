@@ -168,9 +168,11 @@ class NativeVGG(NativeNet):
             else:
                 g = B.get(tag + ".g", tuple(y.shape))
                 self._mask(dh, y, g, 1.0, m.b_grad)
-                # slabs only when the consumer is another mask kernel (the previous op is a conv)
+                # split-K is welcome everywhere: the cluster reduction delivers a dense bf16 gradient
+                # (fp32 slabs, the fallback, only when the consumer is another mask kernel)
+                from .native import _cluster_enabled
                 dh = conv_backward(m, xin, g, B, tag, need_dx=ti > 0,
-                                   allow_slabs=ti > 0 and tape[ti - 1][0] == "conv")
+                                   allow_slabs=ti > 0 and (_cluster_enabled() or tape[ti - 1][0] == "conv"))
         if S["drop"]:
             K.bump_counter(self._counter)
         self._end_backward(B)
