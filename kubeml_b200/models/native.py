@@ -16,6 +16,7 @@ program of kernel launches over NHWC bf16 activations:
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -112,7 +113,6 @@ class Buffers:
     #    data-gradient chain; both are latency-bound kernels on a handful of SMs each -------------
     def on_side(self):
         import contextlib
-        import os
         # measured on B200: a loss while BatchNorm used cooperative launches (which cannot overlap
         # anything: 3.04 vs 2.72 ms per ResNet-34 step), a gain since it uses a software grid barrier
         # and launches are programmatic-dependent (1.82 vs 1.95 ms)
@@ -327,27 +327,23 @@ class Act:
 
 
 def _slab_enabled() -> bool:
-    import os
     return os.environ.get("KUBEML_SPLITK_SLABS", "1") != "0"
 
 
-import os as _os
-_CLUSTER_MAX = int(_os.environ.get("KUBEML_CLUSTER_MAX", "8"))       # 8 = portable cluster size, 16 = B200 maximum
-_CL_MIN_CHUNKS = int(_os.environ.get("KUBEML_CL_MIN_CHUNKS", "1"))
+_CLUSTER_MAX = int(os.environ.get("KUBEML_CLUSTER_MAX", "8"))       # 8 = portable cluster size, 16 = B200 maximum
+_CL_MIN_CHUNKS = int(os.environ.get("KUBEML_CL_MIN_CHUNKS", "1"))   # fewest K chunks per CTA of a cluster split
 
 
 def _bn_bwd_fusion() -> bool:
     """Let the data-gradient GEMM also mask and pre-reduce for the BatchNorm backward behind it.
     Off by default: measured neutral on B200 (ResNet-34 step 1.585 ms without, 1.594 ms with) - the
     heavier GEMM epilogue costs what the barrier-free BatchNorm kernel saves."""
-    import os
     return os.environ.get("KUBEML_CLUSTER_BNBWD", "0") == "1"
 
 
 def _cluster_enabled() -> bool:
     """Split-K as one thread-block cluster per tile, reduced through distributed shared memory in the
     GEMM itself (final bf16 output + BatchNorm statistics) instead of fp32 slabs folded by the consumer."""
-    import os
     return os.environ.get("KUBEML_CLUSTER_SPLITK", "1") != "0"
 
 

@@ -19,8 +19,8 @@ import torch
 import torch.nn as nn
 
 from ..ops import nn as K
-from .native import (Act, Buffers, NativeNet, NConv2d, NLinear, act_dtype, conv_backward, conv_forward,
-                     linear_backward, linear_forward)
+from .native import (Act, Buffers, NativeNet, NConv2d, NLinear, _cluster_enabled, act_dtype, conv_backward,
+                     conv_forward, linear_backward, linear_forward)
 
 CFGS: Dict[str, List[Union[int, str]]] = {
     "vgg11": [64, "M", 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"],
@@ -133,6 +133,11 @@ class NativeVGG(NativeNet):
         return logits
 
     # ---------------------------------------------------------------------------------- backward
+    @staticmethod
+    def _mask(dy: Act, y: torch.Tensor, g: torch.Tensor, scale: float, dbias: torch.Tensor) -> None:
+        """g = scale * dy * (y > 0) and dbias = column sums of g in one pass; `dy` may be split-K slabs."""
+        K.relu_bwd_cols(None if dy.slabs else dy.t, y, g, scale, dbias, dy_slabs=dy.t if dy.slabs else None)
+
     def _backward_impl(self, dlogits: torch.Tensor) -> None:
         S = self._saved
         B: Buffers = S["B"]
@@ -170,17 +175,11 @@ class NativeVGG(NativeNet):
                 self._mask(dh, y, g, 1.0, m.b_grad)
                 # split-K is welcome everywhere: the cluster reduction delivers a dense bf16 gradient
                 # (fp32 slabs, the fallback, only when the consumer is another mask kernel)
-                from .native import _cluster_enabled
                 dh = conv_backward(m, xin, g, B, tag, need_dx=ti > 0,
                                    allow_slabs=ti > 0 and (_cluster_enabled() or tape[ti - 1][0] == "conv"))
         if S["drop"]:
             K.bump_counter(self._counter)
         self._end_backward(B)
-
-
-NativeVGG._mask = staticmethod(
-    lambda dy, y, g, scale, dbias: K.relu_bwd_cols(None if dy.slabs else dy.t, y, g, scale, dbias,
-                                                   dy_slabs=dy.t if dy.slabs else None))
 
 
 def _vgg(name: str, num_classes: int, dropout: float) -> NativeVGG:
