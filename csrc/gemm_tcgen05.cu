@@ -653,6 +653,209 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 }
 
 // --------------------------------------------------------------------------------------------
+// Two-SM variant for large plain GEMMs (both operands K-major): a cluster of two CTAs computes a
+// 256 x 256 tile with tcgen05.mma.cta_group::2.  Each CTA loads its own 128 rows of A and HALF of
+// the B tile (128 of the 256 columns); the pair's MMA reads both halves, so a CTA moves 32 KB per
+// 64-deep chunk for a 128 x 256 output instead of 48 KB - the operand traffic from L2 is what bounds
+// the one-CTA kernel on large problems.  CTA 0 (the leader) issues all MMAs; TMA loads of both
+// CTAs complete on the leader's "full" barrier; tcgen05.commit multicasts to the "empty" /
+// "accumulator ready" barriers of both.  Each CTA then drains its own 128 accumulator lanes.
+// --------------------------------------------------------------------------------------------
+constexpr int k2smN = 256;
+constexpr int k2smStages = 3;            // 3 x (16 + 16) KB: two CTAs (of different pairs) per SM
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;   // shared::cluster address of the same offset in CTA 0 of the pair
+
+__device__ __forceinline__ void tma_load_4d_2sm(const CUtensorMap* map, uint64_t* leader_bar, void* dst, int c0, int c1,
+                                                int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(leader_bar) & kPeerBitMask), "r"(c0),
+      "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
+      "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {      // arrives on `bar` in BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3)) : "memory");
+}
+
+struct Gemm2smArgs {
+  int m_pairs, n_tiles, k_chunks;
+  void* out;
+  long long ldo;
+  int m_valid, n_valid;
+  const float* bias;
+  int relu, out_f32;
+};
+
+__global__ void __launch_bounds__(kNumThreads, 2)
+gemm2sm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               const Gemm2smArgs args) {
+  constexpr uint32_t kABytes = kBlockM * kBlockK * 2;            // this CTA's 128 rows of A
+  constexpr uint32_t kBBytes = (k2smN / 2) * kBlockK * 2;        // this CTA's half of the B tile
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + k2smStages * kABytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_b + k2smStages * kBBytes);
+  uint64_t* empty_bar = full_bar + k2smStages;
+  uint64_t* tmem_full_bar = empty_bar + k2smStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  kml::pdl_launch_dependents();
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  // Band rasterisation over the pair tiles (see the one-CTA kernel): bands of 8 pairs = 16 m-tiles,
+  // n fastest inside a band.  Both CTAs of a pair compute the same mapping.
+  int mt, nt;
+  {
+    constexpr int kGroupP = 8;
+    const int lin = static_cast<int>(blockIdx.x >> 1) + args.m_pairs * static_cast<int>(blockIdx.y);
+    const int band = lin / (kGroupP * args.n_tiles);
+    const int band_p0 = band * kGroupP;
+    const int band_rows = min(kGroupP, args.m_pairs - band_p0);
+    const int in_band = lin - band * kGroupP * args.n_tiles;
+    mt = 2 * (band_p0 + in_band % band_rows) + static_cast<int>(rank);   // 128-row tile of this CTA
+    nt = in_band / band_rows;                                            // 256-column tile of the pair
+  }
+  const int nchunks = args.k_chunks;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < k2smStages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {   // the same warp of both CTAs allocates the pair's accumulator columns
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(static_cast<uint32_t>(k2smN)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();                            // the peer's barriers exist before anything signals them
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  kml::pdl_wait();
+
+  if (warp == 0) {
+    if (elect_one()) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      for (int i = 0; i < nchunks; ++i) {
+        const int s = i % k2smStages;
+        const uint32_t ph = (i / k2smStages) & 1;
+        mbar_wait(empty_bar + s, ph ^ 1);
+        // the leader's barrier counts the bytes of BOTH CTAs of the pair
+        if (rank == 0) mbar_expect_tx(full_bar + s, 2 * (kABytes + kBBytes));
+        tma_load_4d_2sm(&map_a, full_bar + s, smem_a + s * kABytes, i * kBlockK, mt * kBlockM, 0, 0);
+        tma_load_4d_2sm(&map_b, full_bar + s, smem_b + s * kBBytes, i * kBlockK,
+                        nt * k2smN + static_cast<int>(rank) * (k2smN / 2), 0, 0);
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc(2 * kBlockM, k2smN, false, false);
+      for (int i = 0; i < nchunks; ++i) {
+        const int s = i % k2smStages;
+        const uint32_t ph = (i / k2smStages) & 1;
+        mbar_wait(full_bar + s, ph);
+        tcgen05_fence_after();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem_a + s * kABytes);
+          const uint32_t b_addr = smem_u32(smem_b + s * kBBytes);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            umma_bf16_2sm(tmem_base, make_smem_desc(a_addr + k * 32, 16, 1024), make_smem_desc(b_addr + k * 32, 16, 1024),
+                          idesc, (i | k) != 0 ? 1u : 0u);
+        }
+        __syncwarp();
+        if (elect_one()) {
+          umma_commit_2sm(empty_bar + s);
+          if (i == nchunks - 1) umma_commit_2sm(tmem_full_bar);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = mt * kBlockM + q * 32 + lane;
+    mbar_wait(tmem_full_bar, 0);
+    tcgen05_fence_after();
+    const bool row_ok = row < args.m_valid;
+#pragma unroll 1
+    for (int c0 = 0; c0 < k2smN; c0 += 32) {
+      uint32_t v[32];
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+            "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          : "r"(taddr) : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (!row_ok) continue;
+      const int ncol0 = nt * k2smN + c0;
+      if (ncol0 >= args.n_valid) continue;
+      const long long off = static_cast<long long>(row) * args.ldo + ncol0;
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        f[j] = __uint_as_float(v[j]);
+        if (args.bias != nullptr && ncol0 + j < args.n_valid) f[j] += __ldg(args.bias + ncol0 + j);
+        if (args.relu) f[j] = fmaxf(f[j], 0.f);
+      }
+      const bool full = ncol0 + 32 <= args.n_valid;
+      if (args.out_f32) {
+        float* o = static_cast<float*>(args.out) + off;
+        if (full && (off & 3) == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (ncol0 + j < args.n_valid) o[j] = f[j];
+        }
+      } else {
+        __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + off;
+        if (full && (off & 7) == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            __nv_bfloat162 p0 = __floats2bfloat162_rn(f[j], f[j + 1]);
+            __nv_bfloat162 p1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
+            __nv_bfloat162 p2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]);
+            __nv_bfloat162 p3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
+            uint4 u;
+            u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
+            u.z = *reinterpret_cast<uint32_t*>(&p2); u.w = *reinterpret_cast<uint32_t*>(&p3);
+            *reinterpret_cast<uint4*>(o + j) = u;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (ncol0 + j < args.n_valid) o[j] = __float2bfloat16_rn(f[j]);
+        }
+      }
+    }
+    tcgen05_fence_before();
+  }
+  __syncthreads();
+  cluster_sync_all();                            // neither CTA frees the pair's TMEM while the other still reads
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(static_cast<uint32_t>(k2smN)) : "memory");
+  }
+}
+
+// --------------------------------------------------------------------------------------------
 // host side
 // --------------------------------------------------------------------------------------------
 
@@ -749,6 +952,24 @@ int launch(const TensorSpec& ta, const TensorSpec& tb, const GemmArgs& a, int bl
   return launch_variant<128, true, true>(ma, mb, a, s);
 }
 
+int launch_2sm(const TensorSpec& ta, const TensorSpec& tb, const Gemm2smArgs& a, cudaStream_t s) {
+  CUtensorMap ma, mb;
+  int rc = encode_map(&ma, ta);
+  if (rc) return rc;
+  rc = encode_map(&mb, tb);
+  if (rc) return rc;
+  constexpr size_t smem = k2smStages * (kBlockM * kBlockK * 2 + (k2smN / 2) * kBlockK * 2) + 1024 + 256;
+  static bool configured = false;
+  if (!configured) {
+    KML_CUDA(cudaFuncSetAttribute(gemm2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    configured = true;
+  }
+  KML_CUDA(kml::launch_pdl_cluster(gemm2sm_kernel, dim3(2 * a.m_pairs, a.n_tiles, 1), dim3(kNumThreads), smem, s,
+                                   dim3(2, 1, 1), ma, mb, a));
+  kml::count_launch();
+  return 0;
+}
+
 inline int ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
 
@@ -776,8 +997,31 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
   int splits = epi->splits, block_n = epi->block_n;
   KML_CHECK(A && B && out && M > 0 && N > 0 && K > 0, "kml_gemm_bf16: bad arguments");
   KML_CHECK(lda % 8 == 0 && ldb % 8 == 0, "kml_gemm_bf16: leading dimensions must be multiples of 8 elements");
-  if (block_n == 0) block_n = (N > 64) ? 128 : 64;
   if (splits < 1) splits = 1;
+  // Large plain GEMM: the two-SM kernel (256 x 256 tiles per CTA pair, tcgen05.mma.cta_group::2).
+  // block_n == 512 asks for it explicitly; the default takes it from four waves of pair tiles upward.
+  static const bool allow_2sm = [] { const char* e = getenv("KUBEML_GEMM_2SM"); return !(e && e[0] == '0'); }();
+  const long long pair_tiles = static_cast<long long>(ceil_div(M, 256)) * ceil_div(N, 256);
+  const bool plain = !a_mn && !b_mn && splits == 1 && !epi->cluster && !epi->addend_bf16 && !epi->slabs;
+  if (plain && (block_n == 512 || (block_n == 0 && allow_2sm && pair_tiles >= 4LL * kml::num_sms()))) {
+    TensorSpec ta{}, tb{};
+    ta.ptr = A; tb.ptr = B;
+    ta.dim[0] = K; ta.dim[1] = M; ta.dim[2] = ta.dim[3] = 1;
+    ta.stride_bytes[0] = static_cast<uint64_t>(lda) * 2; ta.stride_bytes[1] = ta.stride_bytes[0] * M;
+    ta.stride_bytes[2] = ta.stride_bytes[1];
+    ta.box[0] = 64; ta.box[1] = kBlockM; ta.box[2] = ta.box[3] = 1;
+    tb.dim[0] = K; tb.dim[1] = N; tb.dim[2] = tb.dim[3] = 1;
+    tb.stride_bytes[0] = static_cast<uint64_t>(ldb) * 2; tb.stride_bytes[1] = tb.stride_bytes[0] * N;
+    tb.stride_bytes[2] = tb.stride_bytes[1];
+    tb.box[0] = 64; tb.box[1] = k2smN / 2; tb.box[2] = tb.box[3] = 1;
+    Gemm2smArgs g2{};
+    g2.m_pairs = ceil_div(M, 256); g2.n_tiles = ceil_div(N, k2smN); g2.k_chunks = ceil_div(K, kBlockK);
+    g2.out = out; g2.ldo = ldo; g2.m_valid = M; g2.n_valid = N;
+    g2.bias = bias; g2.relu = relu; g2.out_f32 = out_f32;
+    return launch_2sm(ta, tb, g2, static_cast<cudaStream_t>(stream));
+  }
+  KML_CHECK(block_n != 512, "kml_gemm_bf16: the two-SM kernel takes K-major operands, no split-K, no addend");
+  if (block_n == 0) block_n = (N > 64) ? 128 : 64;
   TensorSpec ta{}, tb{};
   ta.ptr = A; tb.ptr = B;
   // K-major [rows][K]: dim0 = K, dim1 = rows.  MN-major [K][rows]: dim0 = rows, dim1 = K.

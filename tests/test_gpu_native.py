@@ -254,3 +254,24 @@ def test_arena_bind_and_flat_optimizer(dev):
         torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5)
     assert int(arena.counters[0].item()) == 3
     arena.close()
+
+
+# ------------------------------------------------------------------------------------- two-SM GEMM
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (1024, 768, 4096), (640, 304, 200), (128, 256, 128)])
+def test_gemm_two_sm_cta_pair(dev, M, N, K):
+    """tcgen05.mma.cta_group::2 kernel (block_n=512 selects it): bias + ReLU bf16 output and plain fp32
+    output against fp32 torch, including ragged M / N / K and an odd number of 128-row tiles."""
+    from kubeml_b200 import ops
+    torch.manual_seed(0)
+    a = torch.randn(M, K, device=dev).bfloat16()
+    b = (torch.randn(N, K, device=dev) * 0.1).bfloat16()
+    bias = torch.randn(N, device=dev)
+    ref = a.float() @ b.float().t()
+    out = torch.full((M, N), 7.0, device=dev, dtype=torch.bfloat16)
+    ops.gemm_bf16(a, b, bias=bias, relu=True, out=out, block_n=512)
+    want = torch.relu(ref + bias)
+    assert float((out.float() - want).abs().max()) <= 1e-2 * float(want.abs().max())
+    of = torch.empty(M, N, device=dev)
+    ops.gemm_bf16(a, b, out=of, block_n=512)
+    torch.cuda.synchronize()
+    assert float((of - ref).abs().max()) <= 2e-3 * float(ref.abs().max())
