@@ -39,7 +39,10 @@ def run_ref_torch(args, ddp: bool = False) -> int:
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(0)
+    bf16 = os.environ.get("KUBEML_REF_TORCH_BF16") == "1"     # stronger stock baseline: channels-last + bf16 autocast
     net = resnet34().to(dev)
+    if bf16:
+        net = net.to(memory_format=torch.channels_last)
     if ddp and world > 1:
         net = torch.nn.parallel.DistributedDataParallel(net, device_ids=[local])
     opt = torch.optim.SGD(net.parameters(), lr=0.1, weight_decay=1e-4)
@@ -62,7 +65,12 @@ def run_ref_torch(args, ddp: bool = False) -> int:
 
     def step(i):
         opt.zero_grad()
-        loss = F.cross_entropy(net(x[i]), y[i])
+        if bf16:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out = net(x[i].contiguous(memory_format=torch.channels_last))
+            loss = F.cross_entropy(out.float(), y[i])
+        else:
+            loss = F.cross_entropy(net(x[i]), y[i])
         loss.backward()
         opt.step()
         if not ddp and (i + 1) % K_AVG == 0:
@@ -89,7 +97,7 @@ def run_ref_torch(args, ddp: bool = False) -> int:
                           "impl": "ddp" if ddp else "ref-torch", "value": round(value, 1), "unit": "images/s",
                           "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                           "ms_per_step": round(1e3 * float(t.item()) / args.steps, 3), "higher_is_better": True,
-                          "scaling": "weak", "vs_baseline": round(value / BASELINE_IMG_S, 2), "dtype": "fp32",
+                          "scaling": "weak", "vs_baseline": round(value / BASELINE_IMG_S, 2), "dtype": "bf16" if bf16 else "fp32",
                           "data": "synthetic (device-resident)",
                           "config": {"model": "torchvision resnet34() 1000 logits on 32x32x3", "global_batch": BATCH * world,
                                      "seq_len": None, "parallelism": ("ddp" if ddp else "kavg-dp") + str(world), "k": K_AVG}}),

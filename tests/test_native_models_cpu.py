@@ -160,3 +160,22 @@ def test_vgg_dropout_train_and_eval(fp32_activations):
     net.eval()
     with torch.no_grad():
         assert torch.equal(net(x), net(x))
+
+
+def test_plan_cluster_prefers_short_k_loops():
+    """Tile width / split choice of the cluster split-K GEMMs: ResNet-34 shapes keep their tuned
+    choice, long-K VGG shapes get wider tiles or two CTAs per SM, nothing exceeds the cluster size."""
+    cases = {  # (rows, channels, K chunks) -> (block_n, splits)
+        (8192, 64, 9): (64, 2), (2048, 128, 18): (64, 4), (512, 256, 36): (64, 8), (128, 512, 72): (64, 8),
+        (2048, 512, 72): (128, 4), (8192, 256, 36): (128, 2), (131072, 64, 9): (64, 1),
+    }
+    for (M, n, chunks), want in cases.items():
+        mt = (M + 127) // 128
+        got = nv.plan_cluster(mt, n, chunks, nv.pick_block_n(mt, n))
+        assert got == want, ((M, n, chunks), got)
+        assert 1 <= got[1] <= 8
+    for tiles in (1, 9, 64, 144):
+        for chunks in range(1, 400, 13):
+            s = nv.auto_splits(tiles, chunks, min_chunks=1, budget=296)
+            per = -(-chunks // s)
+            assert s >= 1 and (s - 1) * per < chunks and tiles * s <= max(296, tiles)
