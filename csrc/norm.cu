@@ -29,8 +29,8 @@ constexpr int kMaxC = 2048;
 
 struct BnScratch {             // device-resident launch state, zero-initialised once
   unsigned int launches;       // parity selects the statistics buffer of this launch
+  unsigned int bar_base;       // value of `bar` when the current launch started (read with `launches` as one uint2)
   unsigned int bar;            // grid barrier: arrivals, monotonically increasing
-  unsigned int bar_base;       // value of `bar` when the current launch started
   unsigned int pad;
   float acc[2][2 * kMaxC];
 };
@@ -95,11 +95,13 @@ __device__ __forceinline__ void load_row(const __nv_bfloat16* xb, const float* x
 
 // Block-level then grid-level combination of two per-channel sums.  On return sm[0..2C) holds the
 // grid totals.  `sm` needs 2C floats.
-__device__ __forceinline__ void combine_stats(BnScratch* sc, int C, int c0, bool active,
+// `state` = {launches, bar_base} read by the caller at kernel entry, so the round trip overlaps the data
+// loads (nobody can bump them before every CTA has passed the barrier below).
+__device__ __forceinline__ void combine_stats(BnScratch* sc, uint2 state, int C, int c0, bool active,
                                               const float (&s1)[kVec], const float (&s2)[kVec], float* sm,
                                               bool wide_smem) {
-  const unsigned par = sc->launches & 1u;          // read before anyone can bump it (bump is after the sync)
-  const unsigned base = sc->bar_base;
+  const unsigned par = state.x & 1u;
+  const unsigned base = state.y;
   const int groups = C / kVec;
   // Shared-memory float atomics compile to compare-and-swap loops, so avoid them where the layout
   // allows: with a power-of-two group count <= 32 the lanes of a warp that share a channel group fold
@@ -185,6 +187,7 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
   extern __shared__ float sm[];                    // [2C] totals, then reused as scale/shift
   kml::pdl_launch_dependents();
   kml::pdl_wait();
+  const uint2 bn_state = __ldcg(reinterpret_cast<const uint2*>(&a.scratch->launches));
   const int groups = a.C / kVec;
   const int lanes = kThreads / groups;
   const int g = threadIdx.x % groups;
@@ -226,7 +229,7 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
       for (int i = 0; i < kVec; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
     }
   }
-  combine_stats(a.scratch, a.C, c0, active, s, q, sm, a.wide_smem != 0);
+  combine_stats(a.scratch, bn_state, a.C, c0, active, s, q, sm, a.wide_smem != 0);
 
   const float inv_m = 1.f / static_cast<float>(a.M);
   float sc[kVec], sh[kVec];
@@ -337,6 +340,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
   extern __shared__ float sm[];
   kml::pdl_launch_dependents();
   kml::pdl_wait();
+  const uint2 bn_state = __ldcg(reinterpret_cast<const uint2*>(&a.scratch->launches));
   const int groups = a.C / kVec;
   const int lanes = kThreads / groups;
   const int g = threadIdx.x % groups;
@@ -393,7 +397,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_kernel(const BnBwdArgs a) {
       for (int i = 0; i < kVec; ++i) { s1[i] += g2[i]; s2[i] = fmaf(g2[i], x2[i], s2[i]); }
     }
   }
-  combine_stats(a.scratch, a.C, c0, active, s1, s2, sm, a.wide_smem != 0);
+  combine_stats(a.scratch, bn_state, a.C, c0, active, s1, s2, sm, a.wide_smem != 0);
 
   if (blockIdx.x == 0 && lane == 0) {
 #pragma unroll
