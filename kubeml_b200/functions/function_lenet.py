@@ -81,9 +81,20 @@ class KubeLeNet(KubeModel):
         return self(x).argmax(dim=1)
 
 
+def build_network() -> nn.Module:
+    """On a GPU the same network on the hand-written kernels (`kubeml_b200.models.lenet`: identical
+    parameter names, shapes and initialisation); `KUBEML_LENET_IMPL=torch` keeps the stock module above,
+    which is also what runs on the CPU."""
+    import os
+    if torch.cuda.is_available() and os.environ.get("KUBEML_LENET_IMPL", "native") != "torch":
+        from kubeml_b200.models import lenet
+        return lenet()
+    return LeNet()
+
+
 def main():
     torch.manual_seed(42)
     random.seed(42)
     import os
-    return KubeLeNet(LeNet(), MnistDataset(os.environ.get("KUBEML_LENET_DATASET", "mnist")),
+    return KubeLeNet(build_network(), MnistDataset(os.environ.get("KUBEML_LENET_DATASET", "mnist")),
                      gpu=torch.cuda.is_available()).start()

@@ -228,8 +228,18 @@ class NativeNet(nn.Module):
             ops.fill_(a.grads[B.zero_range[0]:B.zero_range[1]], 0.0)
         B.split_grads = []
 
+    def _rebind_grads(self) -> None:
+        """A stock optimizer's `zero_grad()` drops `.grad` (set_to_none): point it back at the arena
+        slices the backward program wrote."""
+        first = next(self.parameters())
+        if first.grad is not None and first.grad.data_ptr() == self._arena.grads.data_ptr():
+            return
+        for name, p in self.named_parameters():
+            p.grad = self._arena.grad(name)
+
     def _end_backward(self, B: "Buffers") -> None:
         B.join_side()
+        self._rebind_grads()
         if B.zero_range is None:
             base = self._arena.grads.data_ptr()
             lo, hi = 0, 0

@@ -487,3 +487,42 @@ def test_cluster_dgrad_feeds_bn_backward(dev, N, H, C, Co, S):
         _close(dx, xr.grad, 3e-2)
         _close(dg, gr.grad, 2e-2)
         _close(db, br.grad, 2e-2)
+
+
+def test_native_lenet_matches_reference_network(dev):
+    from kubeml_b200 import ops
+    from kubeml_b200.functions.function_lenet import LeNet
+    from kubeml_b200.models import lenet
+    torch.manual_seed(0)
+    net = lenet().to(dev)
+    net._ensure_arena()
+    with torch.no_grad():
+        for p in net.parameters():
+            p.copy_((p * 2).bfloat16().float())
+    ref = LeNet().to(dev)
+    ref.load_state_dict(net.state_dict())
+    net.train(); ref.train()
+    x = torch.randn(64, 1, 28, 28, device=dev).bfloat16().float()
+    y = torch.randint(0, 10, (64,), device=dev)
+    out = net(x)
+    loss = ops.cross_entropy(out, y)
+    loss.backward()
+    out_r = ref(x)
+    loss_r = torch.nn.functional.cross_entropy(out_r, y)
+    loss_r.backward()
+    torch.cuda.synchronize()
+    _close(out, out_r, 3e-2)
+    assert abs(loss.item() - loss_r.item()) < 0.02
+    for n, p in ref.named_parameters():
+        g = net._arena.grad(n).flatten().float()
+        cos = torch.nn.functional.cosine_similarity(g, p.grad.flatten(), dim=0).item()
+        assert cos > 0.98, f"{n}: cosine {cos:.4f}"
+    opt = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9)       # the reference function's optimizer
+    first = None
+    for _ in range(8):
+        opt.zero_grad()
+        l = ops.cross_entropy(net(x), y)
+        l.backward()
+        opt.step()
+        first = first if first is not None else l.item()
+    assert l.item() < first

@@ -179,3 +179,41 @@ def test_plan_cluster_prefers_short_k_loops():
             s = nv.auto_splits(tiles, chunks, min_chunks=1, budget=296)
             per = -(-chunks // s)
             assert s >= 1 and (s - 1) * per < chunks and tiles * s <= max(296, tiles)
+
+
+def test_lenet_program_matches_reference_network(fp32_activations):
+    """The padded-operand LeNet program against the reference's torch module (function_lenet.LeNet)."""
+    from kubeml_b200.functions.function_lenet import LeNet
+    from kubeml_b200.models import lenet
+    torch.manual_seed(0)
+    net = lenet()
+    net._ensure_arena()
+    ref = LeNet()
+    assert list(net.state_dict().keys()) == list(ref.state_dict().keys())
+    assert all(a.shape == b.shape for a, b in zip(net.state_dict().values(), ref.state_dict().values()))
+    with torch.no_grad():
+        for p in net.parameters():
+            p.copy_((p * 2).bfloat16().float())          # bf16-exact values, large enough for live ReLUs
+    ref.load_state_dict(net.state_dict())
+    net.train(); ref.train()
+    x = torch.randn(16, 1, 28, 28).bfloat16().float()
+    y = torch.randint(0, 10, (16,))
+    out = net(x)
+    ops.cross_entropy(out, y).backward()
+    out_r = ref(x)
+    torch.nn.functional.cross_entropy(out_r, y).backward()
+    torch.testing.assert_close(out, out_r, rtol=1e-4, atol=1e-4)
+    for n, p in ref.named_parameters():
+        g = net._arena.grad(n)
+        scale = p.grad.abs().max().item() + 1e-12
+        assert (g - p.grad).abs().max().item() / scale < 1e-3, n
+    # trains under the stock optimizer the reference's function uses
+    opt = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9)
+    l0 = None
+    for _ in range(5):
+        opt.zero_grad()
+        loss = ops.cross_entropy(net(x), y)
+        loss.backward()
+        opt.step()
+        l0 = l0 if l0 is not None else float(loss)
+    assert float(loss) < l0
