@@ -40,7 +40,10 @@ if __name__ == "__main__":
     from kubeml_b200.optim import SGD, Adam
     name, steps = sys.argv[1], int(sys.argv[2])
     dev = torch.device("cuda", 0); torch.cuda.set_device(dev)
-    net = getattr(models, name)(num_classes=1000).to(dev)
+    if name.startswith("cifar_"):
+        net = getattr(models.cifar_native, name[6:])(num_classes=10).to(dev)
+    else:
+        net = getattr(models, name)(num_classes=1000).to(dev)
     net._ensure_arena()
     opt = Adam(net.parameters(), lr=1e-4) if name.startswith("vgg") else SGD(net.parameters(), lr=0.1, weight_decay=1e-4)
     opt.attach_arena(net._arena)

@@ -392,7 +392,8 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
             ldk = _ceil(Kd, 64)
             cols = B.get(tag + ".cols", (M, ldk))
             K.im2col(x, cols, k, k, s, p)
-            ops.gemm_bf16(cols, _packed_weight(conv, B, tag, ldk), bias=bias, relu=relu, out=y.view(M, conv.cout),
+            ops.gemm_bf16(cols[:, :Kd] if ldk != Kd else cols, _packed_weight(conv, B, tag, ldk)[:, :Kd], bias=bias,
+                          relu=relu, out=y.view(M, conv.cout),
                           block_n=bn_, splits=S, cluster=cl, stats=stats)
         return Act(y, 0, stats)
     can_split = allow_slabs and _slab_enabled() and (fold or (bias is None and not relu))
@@ -409,7 +410,7 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
         ldk = _ceil(Kd, 64)
         cols = B.get(tag + ".cols", (M, ldk))
         K.im2col(x, cols, k, k, s, p)
-        ops.gemm_bf16(cols, _packed_weight(conv, B, tag, ldk), bias=ebias, relu=erelu,
+        ops.gemm_bf16(cols[:, :Kd] if ldk != Kd else cols, _packed_weight(conv, B, tag, ldk)[:, :Kd], bias=ebias, relu=erelu,
                       out=y.view(S, M, conv.cout) if S > 1 else y.view(M, conv.cout), block_n=bn_,
                       splits=S, slabs=S > 1)
     if S > 1 and fold:
@@ -489,7 +490,7 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
     if sp > 1:
         B.split_grads.append(conv.w_grad)
     with B.on_side():
-        ops.gemm_bf16(dy2, cols[:, :Kd] if Kd % 8 else cols, a_mn=True, b_mn=True, out_dtype=torch.float32,
+        ops.gemm_bf16(dy2, cols[:, :Kd] if ldk != Kd else cols, a_mn=True, b_mn=True, out_dtype=torch.float32,
                       out=conv.w_grad.view(conv.cout, Kd), splits=sp, block_n=bn_w)
     if not need_dx:
         return None

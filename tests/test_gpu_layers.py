@@ -526,3 +526,35 @@ def test_native_lenet_matches_reference_network(dev):
         opt.step()
         first = first if first is not None else l.item()
     assert l.item() < first
+
+
+def test_native_cifar_resnet20_matches_torch_module(dev):
+    from kubeml_b200 import ops
+    from kubeml_b200.models import cifar_native, cifar_resnet
+    torch.manual_seed(0)
+    net = cifar_native.resnet20(num_classes=10).to(dev)
+    net._ensure_arena()
+    with torch.no_grad():
+        for p in net.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.bfloat16().float())
+    net._arena.refresh_bf16()
+    ref = cifar_resnet.resnet20(num_classes=10).to(dev)
+    ref.load_state_dict(net.state_dict())
+    net.train(); ref.train()
+    x = torch.randn(64, 3, 32, 32, device=dev).bfloat16().float()
+    y = torch.randint(0, 10, (64,), device=dev)
+    out = net(x)
+    loss = ops.cross_entropy(out, y)
+    loss.backward()
+    out_r = ref(x)
+    loss_r = torch.nn.functional.cross_entropy(out_r, y)
+    loss_r.backward()
+    torch.cuda.synchronize()
+    assert abs(loss.item() - loss_r.item()) < 0.05
+    worst = min((torch.nn.functional.cosine_similarity(net._arena.grad(n).flatten().float(), p.grad.flatten(), dim=0).item(), n)
+                for n, p in ref.named_parameters())
+    assert worst[0] > 0.85, f"{worst[1]}: cosine {worst[0]:.4f}"
+    net.eval(); ref.eval()
+    with torch.no_grad():
+        _close(net(x), ref(x), 5e-2)

@@ -217,3 +217,32 @@ def test_lenet_program_matches_reference_network(fp32_activations):
         opt.step()
         l0 = l0 if l0 is not None else float(loss)
     assert float(loss) < l0
+
+
+def test_cifar_resnet20_program_matches_torch_module(fp32_activations):
+    """Native CIFAR ResNet (option-A shortcuts, 16/32/64 channels) against the stock-module version."""
+    from kubeml_b200.models import cifar_native, cifar_resnet
+    torch.manual_seed(0)
+    net = cifar_native.resnet20(num_classes=10)
+    net._ensure_arena()
+    with torch.no_grad():
+        for p in net.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.bfloat16().float())
+    net._arena.refresh_bf16()
+    ref = cifar_resnet.resnet20(num_classes=10)
+    assert list(net.state_dict().keys()) == list(ref.state_dict().keys())
+    ref.load_state_dict(net.state_dict())
+    net.train(); ref.train()
+    x = torch.randn(4, 3, 32, 32)
+    y = torch.randint(0, 10, (4,))
+    out = net(x)
+    ops.cross_entropy(out, y).backward()
+    out_r = ref(x)
+    torch.nn.functional.cross_entropy(out_r, y).backward()
+    torch.testing.assert_close(out, out_r, rtol=1e-4, atol=1e-4)
+    for n, p in ref.named_parameters():
+        g = net._arena.grad(n)
+        scale = p.grad.abs().max().item() + 1e-12
+        assert (g - p.grad).abs().max().item() / scale < 2e-3, n
+    assert int(net.layer3[2].bn2.num_batches_tracked) == 1
