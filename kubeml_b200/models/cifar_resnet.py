@@ -1,9 +1,9 @@
 """CIFAR ResNet-20/32/44/56/110/1202 with option-A (parameter-free, zero-padded, strided) shortcuts —
 the family the reference ships as `resnet32.py` (ml/experiments/kubeml/resnet32.py:44-239): 3x3 stem
 with 16 channels, three stages of n BasicBlocks with 16/32/64 channels, global average pool, linear.
-Stock torch modules: these networks train through the compatibility path (arena-resident weights,
-flat optimizer, fused loss, fused merge); their 16/32-channel convolutions are below the 64-channel
-granularity of the shifted-TMA implicit GEMM."""
+Stock torch modules: the compatibility path (arena-resident weights, flat optimizer, fused loss, fused
+merge, cuDNN compute) and the oracle of `models.cifar_native`, which runs the same networks on the
+hand-written kernels and is what the `resnet32` function uses by default."""
 from __future__ import annotations
 
 import torch

@@ -88,3 +88,20 @@ def test_vgg_function_native_round(kube_home, monkeypatch):
     assert h.data.train_loss[1] <= h.data.train_loss[0] + 0.2
     assert job.epoch_stats[0]["gpu_launches"] > 0
     c.shutdown()
+
+
+def test_resnet32_function_native_round(kube_home, monkeypatch):
+    """The reference's ResNet-32 / CIFAR-10 experiment function on the native CIFAR ResNet."""
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    c = Cluster(home=kube_home, max_parallelism=1)
+    rng = np.random.default_rng(0)
+    c.shard_store.create("cifar10", rng.integers(0, 255, (512, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (512,)),
+                         rng.integers(0, 255, (64, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (64,)))
+    req = TrainRequest(model_type="resnet32", batch_size=64, epochs=2, dataset="cifar10", lr=0.05,
+                       function_name="resnet32",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=4))
+    h, job = _run(c, req)
+    assert all(np.isfinite(v) for v in h.data.train_loss) and 0.5 < h.data.train_loss[0] < 10
+    assert len(h.data.accuracy) == 2 and job.epoch_stats[0]["gpu_launches"] > 0
+    c.shutdown()
