@@ -275,3 +275,14 @@ def test_gemm_two_sm_cta_pair(dev, M, N, K):
     ops.gemm_bf16(a, b, out=of, block_n=512)
     torch.cuda.synchronize()
     assert float((of - ref).abs().max()) <= 2e-3 * float(ref.abs().max())
+
+
+def test_every_kernel_family_runs(dev):
+    """bench/sanitize_target.py launches every kernel family once on small shapes (the compute-sanitizer
+    target of scripts/sanitize.sh); it must at least run clean and leave the device healthy."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench", "sanitize_target.py")], capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0 and "sanitize target ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    assert torch.zeros(4, device=dev).sum().item() == 0.0
