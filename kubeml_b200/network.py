@@ -165,7 +165,17 @@ class KubeModel(ABC):
 
     # ---- task: init ------------------------------------------------------------------------
     def __initialize(self) -> List[str]:
-        self.init()
+        # The library's hook is `init(self)` (network.py:466); the reference's README example defines
+        # `init(self, model)` (README.md:191): accept both.
+        import inspect
+        try:
+            takes_model = len(inspect.signature(self.init).parameters) >= 1
+        except (TypeError, ValueError):
+            takes_model = False
+        if takes_model:
+            self.init(self._network)
+        else:
+            self.init()
         try:
             return self._sync.publish_reference(self.args._job_id, self._network)
         except KeyError as e:
