@@ -21,6 +21,17 @@ for it in range(int(sys.argv[1]) if len(sys.argv) > 1 else 3):
     A = torch.randn(8192, 4096, device=dev).bfloat16(); Bm = torch.randn(4096, 4096, device=dev).bfloat16()
     o = torch.empty(8192, 4096, device=dev, dtype=torch.bfloat16)
     ops.gemm_bf16(A, Bm, out=o, block_n=128)
+    # the same convolution as a cluster split-K GEMM with BatchNorm statistics, then the element-wise BatchNorm
+    stc = torch.zeros(K.bn_stats_numel(128), device=dev)
+    yc = torch.empty(Nb, 4, 4, 128, device=dev, dtype=torch.bfloat16)
+    ops.conv2d_fprop(x, w, 1, out=yc, block_n=64, splits=8, cluster=True, stats=stc)
+    g1, b1 = torch.ones(128, device=dev), torch.zeros(128, device=dev)
+    mn, sd = torch.zeros(128, device=dev), torch.ones(128, device=dev)
+    K.bn_apply_train(yc, stc, None, torch.empty_like(yc), g1, b1, None, None, None, mn, sd, True)
+    # two-SM GEMM (cta_group::2) and the persistent one-CTA GEMM on the large problem
+    A2 = torch.randn(8192, 4096, device=dev).bfloat16(); B2 = torch.randn(4096, 4096, device=dev).bfloat16()
+    o2 = torch.empty(8192, 4096, device=dev, dtype=torch.bfloat16)
+    ops.gemm_bf16(A2, B2, out=o2, block_n=512)
     # BN forward on slabs, backward
     M, C = 2048, 128
     gamma, beta = torch.ones(C, device=dev), torch.zeros(C, device=dev)
