@@ -242,6 +242,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   auto tile_at = [&](int tile) { return LINEAR ? decode(tile) : T_only; };
 
   if (threadIdx.x == 0) {
+    // the descriptors are kernel parameters, not data of the previous kernel: fetch them before pdl_wait
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
     mbar_init(tmem_full_bar, 1);
     if (LINEAR) { mbar_init(tmem_full_bar + 1, 1); mbar_init(tmem_empty_bar, 4); mbar_init(tmem_empty_bar + 1, 4); }
@@ -263,8 +266,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   if (warp == 0) {
     // ===================================== TMA producer =====================================
     if (elect_one()) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
       int it = 0;                                        // chunks issued so far, across tiles
       for (int tile = tile0; tile < total_tiles; tile += tstride) {
       const Tile T = tile_at(tile);
