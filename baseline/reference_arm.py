@@ -52,6 +52,12 @@ class TensorStore:
 
 
 class _StoreHandler(socketserver.BaseRequestHandler):
+    def setup(self):
+        # Without this the accepted socket keeps Nagle on: a reply whose header segment is still
+        # un-ACKed holds the blob back for the client's delayed-ACK timer (~40 ms per tensor).
+        import socket as _socket
+        self.request.setsockopt(_socket.IPPROTO_TCP, _socket.TCP_NODELAY, 1)
+
     def handle(self):
         sys.path.insert(0, SHIMS)
         from redisai import _recv, _send
@@ -82,6 +88,7 @@ class JobServer:
         self.store, self.job_id = store, job_id
         self.cv = threading.Condition()
         self.layers = []
+        self.stats = {"merge_s": 0.0, "merges": 0, "barrier_wait_s": 0.0}
         self.reset(0)
 
     def reset(self, parallelism: int):
@@ -94,6 +101,9 @@ class JobServer:
     def _merge_locked(self):
         import numpy as np
         funcs = self.arrived
+        t0 = time.perf_counter()
+        # One thread, under the store lock: the Go job serialises Model.Update behind one mutex too
+        # (ml/pkg/model/model.go:273-274); numpy releases the GIL inside the adds.
         with self.store.lock:
             for name in self.layers:
                 acc = None
@@ -106,6 +116,8 @@ class JobServer:
                 else:
                     acc = (acc / np.float32(len(funcs))).astype(acc.dtype)
                 self.store.d[f"{self.job_id}:{name}"] = (acc.dtype.str, acc.shape, acc.tobytes())   # Model.Save
+        self.stats["merge_s"] += time.perf_counter() - t0
+        self.stats["merges"] += 1
         self.arrived = []
         self.pending = self.running
         self.generation += 1
@@ -121,8 +133,10 @@ class JobServer:
             if self.pending == 0:
                 self._merge_locked()
             else:
+                t0 = time.perf_counter()
                 while self.generation == gen:
                     self.cv.wait()
+                self.stats["barrier_wait_s"] += time.perf_counter() - t0
 
 
 def _make_job_http(job: JobServer):
@@ -137,6 +151,14 @@ def _make_job_http(job: JobServer):
             elif len(parts) == 2 and parts[0] == "reset":            # benchmark control: new epoch with N functions
                 job.reset(int(parts[1]))
                 self.send_response(200)
+            elif len(parts) == 1 and parts[0] == "stats":            # benchmark control: merge timers (and reset)
+                body = json.dumps(job.stats).encode()
+                job.stats = {"merge_s": 0.0, "merges": 0, "barrier_wait_s": 0.0}
+                self.send_response(200)
+                self.send_header("Content-Length", str(len(body)))
+                self.end_headers()
+                self.wfile.write(body)
+                return
             elif len(parts) == 1 and parts[0] == "layers":           # benchmark control: layer list from init
                 n = int(self.headers.get("Content-Length") or 0)
                 job.layers = json.loads(self.rfile.read(n).decode())
@@ -299,10 +321,31 @@ def run_reference_arm(args) -> int:
         pr.disable()
         pstats.Stats(pr, stream=sys.stderr).sort_stats("cumulative").print_stats(35)
     from bench import ClockSampler
+    import redisai as _store_shim
+    import requests as rq
     sampler = ClockSampler(local).start() if rank == 0 else None
+    for k in _store_shim.STATS:
+        _store_shim.STATS[k] = 0
+    if rank == 0:
+        rq.post(f"http://job-{job_id}.kubeml/stats")
     dt = run_epoch(args.steps, 2)
     clocks = sampler.stop() if sampler else None
     if rank == 0:
+        # where rank 0's wall time went (seconds over the whole timed region): tensor-store traffic of
+        # __load_model / __save_model as seen by the client, the job's merge, and the rest (Mongo-document
+        # unpickling, PIL transforms, H2D, forward/backward/step, loss.item(), waiting at /next)
+        job_stats = rq.post(f"http://job-{job_id}.kubeml/stats").json()
+        st = dict(_store_shim.STATS)
+        rounds = max(1, (args.steps + K_AVG - 1) // K_AVG)
+        breakdown = {
+            "rounds": rounds, "timed_region_s": round(dt, 4),
+            "load_model_s": round(st["get_s"], 4), "load_model_tensors": st["get_n"], "load_model_bytes": st["get_bytes"],
+            "save_model_s": round(st["set_s"], 4), "save_model_tensors": st["set_n"], "save_model_bytes": st["set_bytes"],
+            "job_merge_s": round(job_stats["merge_s"], 4), "job_merges": job_stats["merges"],
+            "job_barrier_wait_s_all_ranks": round(job_stats["barrier_wait_s"], 4),
+            "train_and_data_s": round(dt - st["get_s"] - st["set_s"] - job_stats["merge_s"], 4),
+            "merge_note": "single Python thread under the store lock (restates the Go job's model mutex, "
+                          "ml/pkg/model/model.go:273-274)"}
         imgs = N * args.steps * BATCH
         value = imgs / dt
         print(json.dumps({
@@ -317,6 +360,7 @@ def run_reference_arm(args) -> int:
                        "timing": "wall clock around the train fan-out incl. the final merge, max over ranks "
                                  "(the reference has no device timers); includes its per-batch loss.item()",
                        "stand_ins": "flask/redisai/pymongo shims + Python restatement of the Go job's merge"},
+            "breakdown": breakdown,
             "e2e": {"value": round(value, 1), "unit": "images/s",
                     "note": "the reference only has an end-to-end path (CPU transforms, pageable H2D, .item())"},
             "clocks": clocks}), flush=True)

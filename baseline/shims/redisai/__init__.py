@@ -3,15 +3,29 @@ store of baseline/reference_arm.py over TCP (one blob per command, like AI.TENSO
 import pickle
 import socket
 import struct
+import time
 
 import numpy as np
 
 
+STATS = {"get_s": 0.0, "get_n": 0, "get_bytes": 0, "set_s": 0.0, "set_n": 0, "set_bytes": 0}
+
+
 def _send(sock, header, blob=b""):
+    """One message = one gather-write: the 8-byte length prefix, the pickled header and the blob leave
+    in a single sendmsg (looped for partial writes), so no small segment ever waits on the peer's
+    delayed ACK.  Both ends also set TCP_NODELAY."""
     h = pickle.dumps(header, protocol=pickle.HIGHEST_PROTOCOL)
-    sock.sendall(struct.pack("<II", len(h), len(blob)) + h)
-    if blob:
-        sock.sendall(blob)
+    parts = [memoryview(struct.pack("<II", len(h), len(blob)) + h)]
+    if len(blob):
+        parts.append(memoryview(blob).cast("B"))
+    while parts:
+        sent = sock.sendmsg(parts)
+        while parts and sent >= len(parts[0]):
+            sent -= len(parts[0])
+            parts.pop(0)
+        if parts and sent:
+            parts[0] = parts[0][sent:]
 
 
 def _recv_exact(sock, n):
@@ -45,19 +59,30 @@ class Client:
         return self.sock
 
     def tensorset(self, key, tensor, shape=None, dtype=None):
-        arr = np.ascontiguousarray(tensor)       # redisai-py takes dtype/shape from the ndarray
+        t0 = time.perf_counter()
+        arr = np.asarray(tensor)                 # redisai-py takes dtype/shape from the ndarray
+        if not arr.flags.c_contiguous:
+            arr = np.ascontiguousarray(arr)
         s = self._conn()
-        _send(s, ("set", key, arr.dtype.str, arr.shape), arr.tobytes())
+        _send(s, ("set", key, arr.dtype.str, arr.shape), arr.reshape(-1).view(np.uint8).data)
         _recv(s)
+        STATS["set_s"] += time.perf_counter() - t0
+        STATS["set_n"] += 1
+        STATS["set_bytes"] += arr.nbytes
         return "OK"
 
     def tensorget(self, key, **kw):
+        t0 = time.perf_counter()
         s = self._conn()
         _send(s, ("get", key))
         (status, dt, shape), blob = _recv(s)
         if status != "ok":
             raise KeyError(key)
-        return np.frombuffer(blob, dtype=np.dtype(dt)).reshape(shape).copy()
+        out = np.frombuffer(blob, dtype=np.dtype(dt)).reshape(shape)      # the receive buffer is private: no copy
+        STATS["get_s"] += time.perf_counter() - t0
+        STATS["get_n"] += 1
+        STATS["get_bytes"] += out.nbytes
+        return out
 
     def close(self):
         if self.sock is not None:
