@@ -33,6 +33,22 @@ inline void count_launch(unsigned long long n = 1) { g_launches.fetch_add(n, std
     }                                         \
   } while (0)
 
+inline int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+
+// Function attributes (dynamic shared-memory limit, cluster size, carve-out) belong to the *current
+// device's* copy of a kernel.  One process may drive several GPUs (the in-process Cluster runs one
+// worker thread per GPU), so "configured" is one bit per device ordinal, not one flag per process.
+// Setting an attribute twice is harmless, so a lost race between two threads only repeats the call.
+struct PerDeviceOnce {
+  std::atomic<unsigned long long> done{0};
+  bool need(int dev) const { return dev < 0 || dev >= 64 || !((done.load(std::memory_order_acquire) >> dev) & 1ull); }
+  void mark(int dev) { if (dev >= 0 && dev < 64) done.fetch_or(1ull << dev, std::memory_order_release); }
+};
+
 inline int num_sms() {
   static int n = 0;
   if (n == 0) {

@@ -896,11 +896,12 @@ template <int BLOCK_N, bool A_MN, bool B_MN, bool LINEAR>
 int launch_tiles(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& a, dim3 grid, cudaStream_t s) {
   constexpr size_t smem = Stages<BLOCK_N>::value * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 /*align*/ + 640 /*barriers+taps*/;
   auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN, LINEAR>;
-  static bool configured = false;
-  if (!configured) {
+  static kml::PerDeviceOnce configured;
+  const int dev = kml::current_device();
+  if (configured.need(dev)) {
     KML_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     KML_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));   // clusters of 16
-    configured = true;
+    configured.mark(dev);
   }
   const dim3 cluster(1, 1, a.cluster_reduce ? a.splits : 1);
   KML_CUDA(kml::launch_pdl_cluster(kernel, grid, dim3(kNumThreads), smem, s, cluster, ma, mb, a));
@@ -960,10 +961,11 @@ int launch_2sm(const TensorSpec& ta, const TensorSpec& tb, const Gemm2smArgs& a,
   rc = encode_map(&mb, tb);
   if (rc) return rc;
   constexpr size_t smem = k2smStages * (kBlockM * kBlockK * 2 + (k2smN / 2) * kBlockK * 2) + 1024 + 256;
-  static bool configured = false;
-  if (!configured) {
+  static kml::PerDeviceOnce configured;
+  const int dev = kml::current_device();
+  if (configured.need(dev)) {
     KML_CUDA(cudaFuncSetAttribute(gemm2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    configured = true;
+    configured.mark(dev);
   }
   KML_CUDA(kml::launch_pdl_cluster(gemm2sm_kernel, dim3(2 * a.m_pairs, a.n_tiles, 1), dim3(kNumThreads), smem, s,
                                    dim3(2, 1, 1), ma, mb, a));

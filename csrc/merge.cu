@@ -71,7 +71,7 @@ __device__ void rank_barrier(const kml_merge_params& p, int phase, uint32_t gen)
     // generations only grow, so ">=" tolerates a fast peer that already moved on
     while (static_cast<int32_t>(ld_acquire_sys(f) - gen) < 0) {
       if (static_cast<unsigned long long>(clock64() - t0) > limit) {
-        if (p.status) atomicExch(p.status, 1 + r);
+        if (p.status) atomicOr(p.status, 1 << r);         // bit r: rank r did not arrive
         break;
       }
       __nanosleep(64);
@@ -200,6 +200,20 @@ kavg_merge_kernel(const kml_merge_params p) {
 
   if (sync_ranks) full_barrier(0);
   else if (p.fuse_sgd) full_barrier(-1);
+
+  // A peer never arrived (rank_barrier set `status` before the grid was released): the replicas are
+  // not all final, so averaging them would publish a corrupt model into every rank and throw away the
+  // optimizer state.  Touch nothing; the host sees `status`, drops the missing rank from the
+  // participant mask and relaunches (parallel/device_sync.py), as the reference's merger divides by
+  // the notifications it actually received (ml/pkg/train/job.go:383-398).
+  if (sync_ranks && p.status != nullptr && *reinterpret_cast<volatile int*>(p.status) != 0) {
+    if (!kCoop && blockIdx.x == 0 && threadIdx.x == 0) {
+      // every CTA has arrived `nbar` times; leave the local barrier state consistent for the relaunch
+      lb->count_base = s_cbase + nbar * gridDim.x;
+      lb->release_base = s_rbase + nbar;
+    }
+    return;
+  }
 
   // ---- phase 1: reduce my slice, write everyone -----------------------------------------------
   int nparts = __popc(p.participants);

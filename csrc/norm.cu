@@ -609,7 +609,7 @@ int kml_bn_apply_train(const void* x, float* stats, const void* res, void* y, co
                        float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
                        float* save_invstd, int M, int C, int relu, float eps, float momentum, void* stream) {
   KML_CHECK(x && stats && y && gamma && beta && save_mean && save_invstd, "kml_bn_apply_train: null pointer");
-  KML_CHECK(C % kVec == 0 && C <= 4 * kMaxC && M > 0, "kml_bn_apply_train: C (%d) must be a multiple of 8", C);
+  KML_CHECK(C % kVec == 0 && C <= 6144 && M > 0, "kml_bn_apply_train: C (%d) must be a multiple of 8 and <= 6144 (48 KB of shared memory)", C);
   BnApplyArgs a{static_cast<const __nv_bfloat16*>(x), stats, static_cast<const __nv_bfloat16*>(res),
                 static_cast<__nv_bfloat16*>(y), gamma, beta, running_mean, running_var, num_batches_tracked,
                 save_mean, save_invstd, M, C, relu, eps, momentum};

@@ -10,10 +10,13 @@ static thread_local char g_err[1024] = "";
 std::atomic<unsigned long long> g_launches{0};
 
 void note_kernel(const void* fn) {
+  // keyed by (kernel, device): the attribute is per device (see PerDeviceOnce in common.cuh)
   static std::mutex mu;
-  static std::unordered_set<const void*> seen;
+  static std::unordered_set<unsigned long long> seen;
+  const unsigned long long key = reinterpret_cast<unsigned long long>(fn) ^
+                                 (static_cast<unsigned long long>(current_device() + 1) << 56);
   std::lock_guard<std::mutex> lock(mu);
-  if (seen.insert(fn).second) {
+  if (seen.insert(key).second) {
     const char* e = getenv("KUBEML_UNIFORM_CARVEOUT");
     if (!(e && e[0] == '0'))
       cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);

@@ -87,7 +87,9 @@ typedef struct {
   void* w_bf16;                       /* if non-NULL: bf16 copy of the first n_sgd merged floats,
                                          refreshed by this rank after the final barrier           */
   unsigned long long timeout_cycles;  /* spin limit for the cross-rank barrier; 0 = default       */
-  int* status;                        /* device int, set non-zero if the barrier timed out        */
+  int* status;                        /* device int; on a barrier timeout bit r is set for every
+                                         rank r that did not arrive, and the kernel returns without
+                                         touching any replica or optimizer state                  */
 } kml_merge_params;
 
 /* Launches the merge on `stream` of the current device.  With generation == 0 no cross-rank

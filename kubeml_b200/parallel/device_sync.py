@@ -156,7 +156,8 @@ class RankSync:
         st = int(self.arena.status.item())
         if st != 0:
             self.arena.status.zero_()
-            raise WorkerFault(f"merge barrier timed out waiting for rank {st - 1}")
+            missing = [r for r in range(32) if (st >> r) & 1]
+            raise WorkerFault(f"merge barrier timed out waiting for rank(s) {missing}")
 
     def drain_losses(self, loss) -> float:
         return float(loss)
