@@ -247,16 +247,18 @@ class KubeModel(ABC):
 
             self._on_iteration_start()
             graphing = self._graphs_enabled()
-            begin_round = getattr(self._sync, "begin_round", None)
-            if begin_round is not None and not graphing:
-                begin_round(len(batches), self.optimizer)
+            can_fuse = getattr(self._sync, "can_fuse_last_step", None)
+            fuse_last = bool(can_fuse is not None and can_fuse(self.optimizer))
             sliced = isinstance(batches, _sliced_type())
             for idx, batch in enumerate(batches):
                 if fault and fault(a._func_id, a.epoch, round_idx, idx):
                     raise KubeMLException(f"injected fault in function {a._func_id}", 500)
                 if not sliced:
                     batch = self._batch_to_device(batch)
-                step_loss = self._graphed_step(batch, idx) if graphing else self.train(batch, idx)
+                # the round's last optimizer step is left to the merge kernel - but only for functions
+                # that were seen to call step() exactly once per batch
+                defer = fuse_last and idx == len(batches) - 1 and self._single_step is True
+                step_loss = self._graphed_step(batch, idx, defer) if graphing else self._eager_step(batch, idx, defer)
                 if stage is not None and isinstance(step_loss, torch.Tensor) and step_loss.is_cuda:
                     stage.push(step_loss)
                 elif isinstance(step_loss, torch.Tensor):
@@ -298,7 +300,24 @@ class KubeModel(ABC):
             return False
         return os.environ.get("KUBEML_CUDA_GRAPH", "1") != "0"
 
-    def _graphed_step(self, batch, idx):
+    _single_step = None      # does the user's train() call optimizer.step() exactly once per batch?
+
+    def _eager_step(self, batch, idx, defer: bool = False):
+        opt = self.optimizer
+        c0 = getattr(opt, "_step_calls", None)
+        if defer and not opt.arm_deferral():
+            defer = False
+        try:
+            out = self.train(batch, idx)
+        finally:
+            if defer:
+                opt.disarm()
+        if c0 is not None:
+            once = (opt._step_calls - c0) == 1
+            self._single_step = once if self._single_step is None else (self._single_step and once)
+        return out
+
+    def _graphed_step(self, batch, idx, defer: bool = False):
         """First two calls per (shapes, hyper-parameters) run eagerly (allocations, lazy inits), the
         third is captured, later ones replay.  The captured program only touches arena memory and
         buffers owned by the capturing KubeModel, which the cache keeps alive, so it stays valid for
@@ -312,7 +331,7 @@ class KubeModel(ABC):
                              if isinstance(v, (int, float, bool))))
         lr_now = tuple(g.get("lr") for g in getattr(opt, "param_groups", []))
         key = (self.args._job_id, type(self).__name__, tuple((tuple(t.shape), t.dtype) for t in tensors),
-               hyper, lr_now, id(getattr(self._sync, "arena", None)))
+               hyper, lr_now, id(getattr(self._sync, "arena", None)), bool(defer))
         ent = cache.get(key)
         if ent is None:
             ent = {"calls": 0, "graph": None, "failed": False}
@@ -321,12 +340,14 @@ class KubeModel(ABC):
             for s_t, t in zip(ent["static"], tensors):
                 s_t.copy_(t, non_blocking=True)
             ent["graph"].replay()
+            if ent.get("deferred"):
+                opt._deferred = True          # the captured program stops short of the optimizer launch
             self._graph_replays = getattr(self, "_graph_replays", 0) + 1
             ws["graph_launches"] = ws.get("graph_launches", 0) + ent["kernels"]
             return ent["out"]
         ent["calls"] += 1
         if ent["failed"] or ent["calls"] <= 2:
-            return self.train(batch, idx)
+            return self._eager_step(batch, idx, defer)
         try:
             static = [t.clone() for t in tensors]
             it = iter(static)
@@ -336,9 +357,16 @@ class KubeModel(ABC):
             k0 = _native_launches()
             g = torch.cuda.CUDAGraph()
             # thread_local: workers may be threads of one process, each capturing on its own GPU
-            with torch.cuda.graph(g, capture_error_mode="thread_local"):
-                out = ent["owner_train"](sbatch, idx) if "owner_train" in ent else self.train(sbatch, idx)
-            ent.update(graph=g, static=static, out=out, owner=self, kernels=_native_launches() - k0)
+            armed = bool(defer and opt.arm_deferral())
+            try:
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                    out = ent["owner_train"](sbatch, idx) if "owner_train" in ent else self.train(sbatch, idx)
+            finally:
+                if armed:
+                    opt.disarm()
+            deferred = armed and bool(getattr(opt, "_deferred", False))
+            ent.update(graph=g, static=static, out=out, owner=self, kernels=_native_launches() - k0,
+                       deferred=deferred)
             g.replay()            # the capture itself did not execute: run this batch now
             ws["graph_launches"] = ws.get("graph_launches", 0) + ent["kernels"]
             return out
@@ -346,7 +374,9 @@ class KubeModel(ABC):
             ent["failed"] = True
             self.logger.warning("CUDA graph capture of train() failed (%s); running eagerly", e)
             torch.cuda.synchronize(self.device)
-            return self.train(batch, idx)
+            if getattr(opt, "_deferred", False):
+                opt._deferred = False         # the aborted capture launched nothing
+            return self._eager_step(batch, idx, False)
 
     # ---- task: val (network.py:312-360) ----------------------------------------------------------
     def _on_validation_start(self) -> None:

@@ -35,10 +35,20 @@ def _flat_span(params: List[torch.nn.Parameter], attr: str):
 
 
 class _FlatOptimizer:
-    def __init__(self, params: Iterable[torch.nn.Parameter], defaults: dict):
-        self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
+    def __init__(self, params: Iterable, defaults: dict):
+        # torch.optim surface: an iterable of parameters, or a list of group dicts with per-group
+        # overrides (e.g. a no-decay group for BatchNorm and biases)
+        plist = list(params)
         self.defaults = defaults
-        self.param_groups = [dict(defaults, params=self.params)]
+        if plist and isinstance(plist[0], dict):
+            self.param_groups = []
+            for grp in plist:
+                grp = dict(grp)
+                grp["params"] = [p for p in grp["params"] if p.requires_grad]
+                self.param_groups.append(dict(defaults, **grp))
+        else:
+            self.param_groups = [dict(defaults, params=[p for p in plist if p.requires_grad])]
+        self.params: List[torch.nn.Parameter] = [p for g in self.param_groups for p in g["params"]]
         self.state: dict = {}
         self._arena = None
         self._flat = None
@@ -50,15 +60,18 @@ class _FlatOptimizer:
 
     def _flat_views(self):
         """(w, g) flat fp32 tensors when parameters and grads are arena slices."""
-        if self._arena is None:
+        if self._arena is None or self._flat is False:
             return None
         if self._flat is None:
             a = self._arena
             n = a.layout.n_param
-            if n == 0:
-                return None
-            first = self.params[0]
-            if first.data_ptr() != a.weights.data_ptr():
+            # The one-launch update covers the arena's whole parameter prefix with ONE set of
+            # hyper-parameters: only valid with a single group that holds every arena parameter
+            # (a frozen parameter would still get weight decay, a second group would lose its lr).
+            n_arena_params = sum(1 for e in a.layout.entries.values() if e.is_param)
+            if n == 0 or len(self.param_groups) != 1 or len(self.params) != n_arena_params \
+                    or not self.params or self.params[0].data_ptr() != a.weights.data_ptr():
+                self._flat = False
                 return None
             self._flat = (a.weights[:n], a.grads[:n])
         # grads must still be the arena slices (zero_grad(set_to_none=True) by user code breaks it)
@@ -95,6 +108,18 @@ class _FlatOptimizer:
             self._names = [(by_ptr[p.data_ptr()], p) for p in self.params if p.data_ptr() in by_ptr]
         return self._names
 
+    def _params_with_groups(self):
+        for grp in self.param_groups:
+            for p in grp["params"]:
+                yield p, grp
+
+    def _after_param_steps(self) -> None:
+        """Per-parameter updates (several groups, frozen parameters) bypass the one-launch kernel that
+        also refreshes the bf16 tensor-core copies: refresh them here."""
+        a = self._arena
+        if a is not None and getattr(a, "wbf16", None) is not None:
+            a.refresh_bf16()
+
     def reset_state(self) -> None:
         raise NotImplementedError
 
@@ -108,16 +133,37 @@ class SGD(_FlatOptimizer):
         super().__init__(params, dict(lr=lr, momentum=momentum, weight_decay=weight_decay,
                                       nesterov=nesterov))
         self._bufs: Optional[List[torch.Tensor]] = None
-        self._steps_in_round = 0
-        self._defer_at = 0
+        self._step_calls = 0          # step() invocations, counted by KubeModel around each train()
+        self._armed = False
         self._deferred = False
 
-    def defer_step_at(self, nsteps: int) -> None:
-        """The `nsteps`-th step() from now is not launched: the K-AVG merge kernel applies it in
-        the same pass that averages the replicas (only meaningful on the flat arena path)."""
-        self._steps_in_round = 0
-        self._defer_at = int(nsteps)
+    def arm_deferral(self) -> bool:
+        """The next step() is not launched: the K-AVG merge kernel applies it in the same pass that
+        averages the replicas (csrc/merge.cu phase 0).  KubeModel arms this only around the last
+        train() call of a sync round, and only for functions it has seen call step() exactly once per
+        batch; a second step() before the merge flushes the pending one first (see step())."""
+        ok = (self._arena is not None and self._flat is not False and len(self.param_groups) == 1
+              and not self.param_groups[0]["nesterov"] and bool(self.params) and self.params[0].is_cuda)
+        self._armed = bool(ok)
+        return self._armed
+
+    def disarm(self) -> None:
+        self._armed = False
+
+    def flush_deferred(self) -> None:
+        """Apply a pending deferred update with the ordinary kernel (the merge did not take it:
+        this rank sat the round out, or user code stepped again)."""
+        if not self._deferred:
+            return
         self._deferred = False
+        flat = self._flat_views()
+        if flat is None:
+            return
+        g = self.param_groups[0]
+        w, gr = flat
+        mb = self._arena.state1[: w.numel()] if g["momentum"] else None
+        ops.sgd_step_(w, gr, mb, g["lr"], g["weight_decay"], g["momentum"], g["nesterov"],
+                      w_bf16=getattr(self._arena, "wbf16", None))
 
     def reset_state(self) -> None:
         if self._arena is not None and self.defaults["momentum"]:
@@ -129,22 +175,25 @@ class SGD(_FlatOptimizer):
     def step(self) -> None:
         g = self.param_groups[0]
         lr, mom, wd, nes = g["lr"], g["momentum"], g["weight_decay"], g["nesterov"]
+        self._step_calls += 1
         flat = self._flat_views()
         if flat is not None:
             w, gr = flat
-            self._steps_in_round += 1
-            if self._defer_at and self._steps_in_round == self._defer_at and not nes and w.is_cuda:
+            if self._deferred:             # a second step() before the merge: the pending one goes first
+                self.flush_deferred()
+            if self._armed and not nes and w.is_cuda:
+                self._armed = False
                 self._deferred = True
-                self._defer_at = 0
                 return
             mb = self._arena.state1[: w.numel()] if mom else None
             ops.sgd_step_(w, gr, mb, lr, wd, mom, nes, w_bf16=getattr(self._arena, "wbf16", None))
             return
-        if mom and self._bufs is None:
+        if self._bufs is None and any(grp["momentum"] for grp in self.param_groups):
             self._bufs = [torch.zeros_like(p) for p in self.params]
-        for i, p in enumerate(self.params):
+        for i, (p, grp) in enumerate(self._params_with_groups()):
             if p.grad is None:
                 continue
+            lr, mom, wd, nes = grp["lr"], grp["momentum"], grp["weight_decay"], grp["nesterov"]
             dense = p.data.is_contiguous() and p.grad.is_contiguous()
             w, gr = (p.data.view(-1), p.grad.view(-1)) if dense else (p.data, p.grad)
             mb = (self._bufs[i].view(-1) if dense else self._bufs[i]) if mom else None
@@ -158,6 +207,7 @@ class SGD(_FlatOptimizer):
                     mb.mul_(mom).add_(d)
                     d = d.add(mb, alpha=mom) if nes else mb
                 w.add_(d, alpha=-lr)
+        self._after_param_steps()
 
 
 class Adam(_FlatOptimizer):
@@ -197,7 +247,7 @@ class Adam(_FlatOptimizer):
         if self._m is None:
             self._m = [torch.zeros_like(p) for p in self.params]
             self._v = [torch.zeros_like(p) for p in self.params]
-        for i, p in enumerate(self.params):
+        for i, (p, g) in enumerate(self._params_with_groups()):
             if p.grad is None:
                 continue
             dense = p.data.is_contiguous() and p.grad.is_contiguous()
@@ -212,3 +262,4 @@ class Adam(_FlatOptimizer):
                 v.mul_(g["betas"][1]).addcmul_(d, d, value=1 - g["betas"][1])
                 bc1, bc2 = 1 - g["betas"][0] ** self._t, 1 - g["betas"][1] ** self._t
                 w.addcdiv_(m, v.sqrt() / bc2 ** 0.5 + g["eps"], value=-g["lr"] / bc1)
+        self._after_param_steps()

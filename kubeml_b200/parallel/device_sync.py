@@ -133,21 +133,27 @@ class RankSync:
         if opt is not None and hasattr(opt, "attach_arena") and getattr(opt, "_arena", None) is not self.arena:
             opt.attach_arena(self.arena)
 
-    def begin_round(self, nsteps: int, optimizer) -> None:
-        """Arm the fused last step: our flat SGD skips its `nsteps`-th launch and the merge
-        kernel applies it in its phase 0."""
-        if hasattr(optimizer, "defer_step_at") and os.environ.get("KUBEML_FUSE_LAST_STEP", "1") != "0":
-            optimizer.defer_step_at(nsteps)
+    def can_fuse_last_step(self, optimizer) -> bool:
+        """The last local step of a round may be left to the merge kernel's phase 0:
+        our flat SGD then skips that launch (`arm_deferral`), eagerly or inside the captured step."""
+        return hasattr(optimizer, "arm_deferral") and os.environ.get("KUBEML_FUSE_LAST_STEP", "1") != "0"
 
     def publish_replica(self, job_id: str, func_id: int, network: torch.nn.Module) -> None:
         """Parameters already are the replica `{job}:{name}/{func_id}`."""
 
+    def _flush_pending_step(self) -> None:
+        opt = getattr(self._model, "optimizer", None)
+        if opt is not None and getattr(opt, "_deferred", False):
+            opt.flush_deferred()          # this rank sat the round out: no merge kernel took the step
+
     def arrive(self, job_id: str, func_id: int, round_idx: int) -> None:
         self._merge(round_idx)
+        self._flush_pending_step()
 
     def end_epoch(self, job_id: str, func_id: int, rounds_done: int) -> None:
         if rounds_done > 0:
             self._merge(rounds_done - 1)
+        self._flush_pending_step()
         stream = torch.cuda.current_stream(self.arena.device)
         stream.synchronize()
         for e0, e1 in self._events:
