@@ -188,6 +188,7 @@ def run_own(args) -> int:
     steps = int(sd["steps"])
     imgs = N * steps * BATCH
     value = imgs / sd["train_seconds"]
+    merges = int(sd.get("merges", 0)) or -(-steps // K_AVG)        # counted by the workers, not derived
     e2e = N * int(se["steps"]) * BATCH / se["train_seconds"]
     out = {
         "metric": ("images/sec VGG-16 K-AVG (K=8, batch 128/worker)" if vgg
@@ -201,10 +202,11 @@ def run_own(args) -> int:
         "config": {"model": ("vgg16" if vgg else "resnet34") + " (torchvision topology, 1000 logits) on 32x32x3",
                    "global_batch": BATCH * N,
                    "seq_len": None, "parallelism": f"kavg-dp{N}", "k": K_AVG, "model_impl": args.model_impl,
-                   "optimizer": "Adam lr 1e-4" if vgg else "SGD lr 0.1 wd 1e-4", "merges_in_timed_region": steps // K_AVG,
+                   "optimizer": "Adam lr 1e-4" if vgg else "SGD lr 0.1 wd 1e-4", "merges_in_timed_region": merges,
+                   "fused_last_sgd_steps": int(sd.get("fused_last_steps", 0)),
                    "l2": "per-step working set (fp32 weights+grads 175 MB, bf16 copies, activations) "
                          "exceeds the 126 MB L2; no explicit flush"},
-        "merge_ms_per_sync": round(1e3 * sd["merge_seconds"] / max(steps // K_AVG, 1), 4),
+        "merge_ms_per_sync": round(1e3 * sd["merge_seconds"] / max(merges, 1), 4),
         "e2e": {"value": round(e2e, 1), "unit": "images/s",
                 "h2d_bytes_per_step": int(se["h2d_bytes"] / max(int(se["steps"]), 1)),
                 "d2h_bytes_per_step": int(se["d2h_bytes"] / max(int(se["steps"]), 1)),
@@ -224,6 +226,8 @@ def main() -> int:
     ap.add_argument("--warmup", type=int, default=16)
     ap.add_argument("--impl", default="own", choices=["own", "reference", "ref-torch", "ddp"])
     ap.add_argument("--model", default="resnet34", choices=["resnet34", "vgg16"])
+    ap.add_argument("--ref-mode", default=None, choices=["fp32-eager", "bf16-eager", "bf16-graph", "fp32-graph"],
+                    help="how hard --impl ref-torch/ddp pushes the stock path (baseline/ref_torch.py)")
     ap.add_argument("--model-impl", default=os.environ.get("KUBEML_RESNET_IMPL", "auto"),
                     choices=["auto", "native", "compat"])
     args = ap.parse_args()

@@ -45,15 +45,16 @@ class Cifar10Dataset(KubeDataset):
         """x: uint8 [B,32,32,3] (HWC, as CIFAR is stored).  Native models get normalised bf16 NHWC
         from one fused kernel (flip + crop + normalise); stock modules get the float NCHW view."""
         B = x.shape[0]
+        augment = self.is_training() and os.environ.get("KUBEML_RESNET_NOAUG") != "1"   # parity runs: no randomness
         if self.native and x.is_cuda:
             aug = None
-            if self.is_training():
+            if augment:
                 r = torch.randint(0, 2 * 9 * 9, (B,), device=x.device, dtype=torch.int32)
                 aug = (r % 2) | (((r // 2) % 9) << 8) | ((r // 18) << 16)
             out = torch.empty((B, 32, 32, 3), dtype=torch.bfloat16, device=x.device)
             ops.nn.image_prep(x, out, aug, 4, _MEAN, _STD)
             return out, y.to(torch.int64)
-        if self.is_training():
+        if augment:
             # RandomHorizontalFlip + RandomCrop(32, padding=4), vectorised over the batch
             flip = torch.rand(B, device=x.device) < 0.5
             x = torch.where(flip.view(B, 1, 1, 1), x.flip(2), x)
@@ -133,6 +134,9 @@ def build_network(num_classes: int = 1000):
 
 def main():
     net = build_network(int(os.environ.get("KUBEML_RESNET_CLASSES", "1000")))
+    init = os.environ.get("KUBEML_RESNET_INIT")         # start from a saved state_dict (parity runs, warm start)
+    if init and os.path.isfile(init):
+        net.load_state_dict(torch.load(init, map_location="cpu"))
     ds = Cifar10Dataset(os.environ.get("KUBEML_RESNET_DATASET", "cifar10"))
     ds.native = bool(getattr(net, "native", False))
     return KubeResnet34(net, ds, gpu=torch.cuda.is_available()).start()

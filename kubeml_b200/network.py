@@ -120,7 +120,8 @@ class KubeModel(ABC):
             return {"loss": loss, "merge_seconds": self.merge_seconds,
                     "h2d_bytes": self.h2d_bytes, "d2h_bytes": self.d2h_bytes,
                     "train_seconds": self.train_seconds, "steps": self.steps,
-                    "gpu_launches": self.gpu_launches}, 200
+                    "gpu_launches": self.gpu_launches, "merges": int(getattr(self, "merges", 0)),
+                    "fused_last_steps": int(getattr(self, "fused_last_steps", 0))}, 200
         if self.task == "val":
             acc, loss, length = self.__validate()
             return {"loss": loss, "accuracy": acc, "length": length}, 200
@@ -287,6 +288,8 @@ class KubeModel(ABC):
         if stage is not None:
             self.d2h_bytes = stage.bytes
         self.merge_seconds = float(getattr(self._sync, "merge_seconds", 0.0))
+        self.merges = int(getattr(self._sync, "epoch_merges", 0))
+        self.fused_last_steps = int(getattr(self._sync, "epoch_fused_steps", 0))
         self._on_train_end()
         if num_iterations == 0:
             return 0.0

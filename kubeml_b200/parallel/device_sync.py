@@ -107,6 +107,8 @@ class RankSync:
             self._schedule = (round_schedule(kube_model._dataset.num_docs, a._N, a._K, a.batch_size)
                               if a._task == "train" else [])
             self.merge_seconds = 0.0
+            self.epoch_merges = 0
+            self.epoch_fused_steps = 0
             self._events = []
             # every rank of this epoch has its arena registered once the barrier opens
             self.group.epoch_barrier(self, a._N, ("train", self._epoch))
@@ -203,6 +205,7 @@ class RankSync:
             p.lr, p.weight_decay, p.momentum = g["lr"], g["weight_decay"], g["momentum"]
             opt._deferred = False
             self._fused_steps += 1
+            self.epoch_fused_steps = getattr(self, "epoch_fused_steps", 0) + 1
         uses_momentum = opt is not None and bool(getattr(opt, "defaults", {}).get("momentum", 0))
         p.momentum_buf = self.arena.ptr(L.off_state1) if uses_momentum else None
         p.w_bf16 = self.arena.ptr(L.off_bf16) if self.arena.wbf16 is not None else None
@@ -214,6 +217,7 @@ class RankSync:
         e1.record(stream)
         self._events.append((e0, e1))
         self.merges += 1
+        self.epoch_merges = getattr(self, "epoch_merges", 0) + 1
 
     def close(self) -> None:
         if self.arena is not None:
