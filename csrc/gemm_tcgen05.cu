@@ -20,9 +20,12 @@
 // For convolutions the A box is a (64ch, BW, BH, BN) window of the NHWC tensor whose origin is
 // shifted by the filter tap; out-of-bounds rows/cols are zero-filled by TMA, which *is* the padding.
 #include "common.cuh"
+#include "bn_scratch.cuh"
 #include "driver_api.h"
 #include "../include/kubeml_b200.h"
 #include <cuda.h>
+#include <mutex>
+#include <unordered_map>
 
 namespace {
 
@@ -77,6 +80,28 @@ struct GemmArgs {
   const __nv_bfloat16* bn_x;             // cluster mode: stats become {sum g, sum g * xhat}, xhat from bn_x/mean/invstd
   const float* bn_mean;
   const float* bn_invstd;
+  // ---- BatchNorm fused behind the cluster reduction (kml_bn_fuse) --------------------------------
+  // bn_mode 1 (forward): the reduced tile is the convolution output x; the kernel accumulates the batch
+  //   statistics, synchronises the whole grid, and writes y = relu?(gamma*(x-mean)*invstd + beta + res?)
+  //   plus the raw x (backward needs it) - convolution and BatchNorm in one launch.
+  // bn_mode 2 (backward): the reduced tile (+ addend) masked by mask_y is the gradient g entering a
+  //   BatchNorm; the kernel accumulates sum g and sum g*xhat, synchronises the grid and writes
+  //   dx = gamma*invstd*(g - sum_g/M - xhat*sum_gx/M), optionally g itself (residual branch), dgamma, dbeta.
+  int bn_mode;
+  kml::BnScratch* bn_sc;
+  const float* bn_gamma;
+  const float* bn_beta;
+  float* bn_rmean;
+  float* bn_rvar;
+  long long* bn_nbt;
+  float* bn_save_mean;
+  float* bn_save_invstd;
+  const __nv_bfloat16* bn_res;
+  __nv_bfloat16* bn_raw;
+  int bn_relu;
+  float bn_eps, bn_momentum;
+  float* bn_dgamma;
+  float* bn_dbeta;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -262,6 +287,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   kml::pdl_wait();       // the set-up above overlapped the previous kernel; its results are needed from here on
+  // fused BatchNorm: launch state of the software grid barrier, read early so the round trip overlaps the
+  // main loop (nobody can advance it before every CTA of this grid has passed the barrier)
+  uint2 gstate = make_uint2(0u, 0u);
+  if (args.bn_mode != 0 && warp >= 2) gstate = __ldcg(reinterpret_cast<const uint2*>(&args.bn_sc->launches));
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
@@ -511,6 +540,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     constexpr int kGroups = BLOCK_N / 4;                 // float4 groups per row
     float* part = reinterpret_cast<float*>(smem_a);
     float* st_sm = part + kBlockM * kPartStride;        // [4 warps][2][BLOCK_N] per-warp column sums
+    float* pv_sm = st_sm + 8 * BLOCK_N;                  // [BLOCK_N] pivots of the fused forward statistics
+    const int bnm = args.bn_mode;
+    if (bnm == 1 && warp >= 2) {
+      // Shifted sums: accumulate (x - pivot) and (x - pivot)^2 with pivot = running mean, so that the
+      // variance does not cancel catastrophically when |mean| >> std.  Read BEFORE the grid barrier:
+      // the running statistics are updated after it.
+      for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128) {
+        const int gc = nt * BLOCK_N + c;
+        pv_sm[c] = (args.bn_rmean != nullptr && gc < args.n_valid) ? args.bn_rmean[gc] : 0.f;
+      }
+    }
     cluster_sync_all();
     if (warp >= 2) {
       const int S = args.splits;
@@ -533,8 +573,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         for (int t = 0; t < 4; ++t)
           if (ncol + t < args.n_valid) { bm[t] = args.bn_mean[ncol + t]; bi[t] = args.bn_invstd[ncol + t]; }
       }
+      if (bnm == 1) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) bm[t] = pv_sm[c4 + t];        // forward: bm holds the pivots
+      }
       for (int r = rbeg + et / kGroups; r < rend; r += 128 / kGroups) {
-        const uint32_t laddr = smem_u32(part + r * kPartStride + c4);
+        float* own = part + r * kPartStride + c4;
+        const uint32_t laddr = smem_u32(own);
         float4 acc = ld_dsmem_f4(laddr, 0);
         for (int p = 1; p < S; ++p) {
           const float4 o = ld_dsmem_f4(laddr, static_cast<uint32_t>(p));
@@ -574,7 +619,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               if (ncol + t < args.n_valid) f[t] = __bfloat162float(my[t]) > 0.f ? f[t] : 0.f;
           }
         }
-        if (args.out_f32) {
+        if (args.out_f32 && bnm == 0) {
           float* o = static_cast<float*>(args.out) + ro;
           if (col_ok && (ro & 3) == 0) {
             *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
@@ -583,21 +628,29 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = f[t];
           }
         } else {
-          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + ro;
+          // fused BatchNorm: this is the intermediate (raw convolution output / masked gradient), stored
+          // only where a later pass needs it; the final output is written after the grid barrier
+          __nv_bfloat16* o = (bnm != 0 ? args.bn_raw : static_cast<__nv_bfloat16*>(args.out));
           __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
           __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
-          if (col_ok && (ro & 3) == 0) {
-            uint2 u;
-            u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
-            *reinterpret_cast<uint2*>(o) = u;
-          } else {
-            const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
+          if (o != nullptr) {
+            o += ro;
+            if (col_ok && (ro & 3) == 0) {
+              uint2 u;
+              u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
+              *reinterpret_cast<uint2*>(o) = u;
+            } else {
+              const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
 #pragma unroll
-            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = hv[t];
+              for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = hv[t];
+            }
           }
           // statistics of exactly the values the consumer will read back
           const float2 r0 = __bfloat1622float2(p0), r1 = __bfloat1622float2(p1);
           f[0] = r0.x; f[1] = r0.y; f[2] = r1.x; f[3] = r1.y;
+          // Stash for the pass after the grid barrier.  In place: rows [rbeg, rend) of THIS CTA's
+          // partial tile are read by this CTA only (every peer reads its own row range of it).
+          if (bnm != 0) *reinterpret_cast<float4*>(own) = make_float4(f[0], f[1], f[2], f[3]);
         }
         if (args.bn_x != nullptr) {                     // BatchNorm-backward sums: g and g * xhat
           float xh[4] = {0.f, 0.f, 0.f, 0.f};
@@ -616,12 +669,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             s1[t] += f[t];
             s2[t] = fmaf(f[t], (xh[t] - bm[t]) * bi[t], s2[t]);
           }
+        } else if (bnm == 1) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { const float d = f[t] - bm[t]; s1[t] += d; s2[t] = fmaf(d, d, s2[t]); }
         } else {
 #pragma unroll
           for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
         }
       }
-      if (args.stats != nullptr) {
+      float* gstats = args.stats;
+      if (bnm != 0) gstats = args.bn_sc->acc[gstate.x & 1u];
+      if (gstats != nullptr) {
         // No shared-memory float atomics (they compile to compare-and-swap loops): lanes that share a
         // column group fold with a shuffle, each warp writes its own row of partials, then 4-way sums.
         if (kGroups == 16) {
@@ -641,7 +699,118 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           const int c = i % BLOCK_N, which = i / BLOCK_N;
           const int gc = nt * BLOCK_N + c;
           const float tot = st_sm[i] + st_sm[2 * BLOCK_N + i] + st_sm[4 * BLOCK_N + i] + st_sm[6 * BLOCK_N + i];
-          if (gc < args.n_valid) atomicAdd(args.stats + static_cast<size_t>(which) * args.n_valid + gc, tot);
+          if (gc < args.n_valid) atomicAdd(gstats + static_cast<size_t>(which) * args.n_valid + gc, tot);
+        }
+      }
+      if (bnm != 0) {
+        // ---- whole-grid barrier: every CTA's column sums are in, then finish the BatchNorm -----------
+        kml::BnScratch* sc = args.bn_sc;
+        const unsigned ncta = gridDim.x * gridDim.y * gridDim.z;
+        const bool first_cta = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
+        if (blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1) {
+          float4* nxt = reinterpret_cast<float4*>(sc->acc[(gstate.x & 1u) ^ 1u]);    // the next launch's buffer
+          for (int i = et; i < 2 * kml::kBnMaxC / 4; i += 128) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) kml::grid_arrive_and_wait(sc, gstate.y, ncta);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (first_cta && et == 0) {                      // everyone has arrived: publish the next launch's state
+          sc->launches = gstate.x + 1u;
+          sc->bar_base = gstate.y + ncta;
+          if (bnm == 1 && args.bn_nbt != nullptr) *args.bn_nbt += 1;
+        }
+        const float* tot = sc->acc[gstate.x & 1u];
+        const float inv_m = 1.f / static_cast<float>(args.m_valid);
+        const bool writer = mt == 0 && split == 0;       // one CTA per column block records the per-channel results
+        float* co = st_sm;                               // [3][BLOCK_N] per-column coefficients
+        for (int c = et; c < BLOCK_N; c += 128) {
+          const int gc = nt * BLOCK_N + c;
+          float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+          if (gc < args.n_valid) {
+            const float t1 = __ldcg(tot + gc), t2 = __ldcg(tot + args.n_valid + gc);
+            if (bnm == 1) {
+              const float d = t1 * inv_m;
+              const float mean = pv_sm[c] + d;
+              const float var = fmaxf(t2 * inv_m - d * d, 0.f);
+              const float invstd = rsqrtf(var + args.bn_eps);
+              c0 = args.bn_gamma[gc] * invstd;
+              c1 = args.bn_beta[gc] - mean * c0;
+              if (writer) {
+                args.bn_save_mean[gc] = mean;
+                args.bn_save_invstd[gc] = invstd;
+                if (args.bn_rmean != nullptr) {
+                  const float m = static_cast<float>(args.m_valid);
+                  const float unbiased = args.m_valid > 1 ? var * m / (m - 1.f) : var;
+                  args.bn_rmean[gc] = (1.f - args.bn_momentum) * pv_sm[c] + args.bn_momentum * mean;
+                  args.bn_rvar[gc] = (1.f - args.bn_momentum) * args.bn_rvar[gc] + args.bn_momentum * unbiased;
+                }
+              }
+            } else {
+              c0 = args.bn_gamma[gc] * args.bn_invstd[gc];
+              c1 = t1 * inv_m;
+              c2 = t2 * inv_m;
+              if (writer) { args.bn_dbeta[gc] = t1; args.bn_dgamma[gc] = t2; }
+            }
+          }
+          co[c] = c0; co[BLOCK_N + c] = c1; co[2 * BLOCK_N + c] = c2;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        float k0[4], k1[4], k2[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) { k0[t] = co[c4 + t]; k1[t] = co[BLOCK_N + c4 + t]; k2[t] = co[2 * BLOCK_N + c4 + t]; }
+        for (int r = rbeg + et / kGroups; r < rend; r += 128 / kGroups) {
+          const int grow = mt * kBlockM + r;
+          if (grow >= args.m_valid) continue;
+          const float4 v = *reinterpret_cast<const float4*>(part + r * kPartStride + c4);
+          float f[4] = {v.x, v.y, v.z, v.w};
+          const long long ro = static_cast<long long>(grow) * args.ldo + ncol;
+          const bool vec = col_ok && (ro & 3) == 0;
+          if (bnm == 1) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) f[t] = fmaf(f[t], k0[t], k1[t]);
+            if (args.bn_res != nullptr) {
+              const __nv_bfloat16* rs = args.bn_res + ro;
+              if (vec) {
+                const uint2 u = __ldg(reinterpret_cast<const uint2*>(rs));
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+                const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+                f[0] += a0.x; f[1] += a0.y; f[2] += a1.x; f[3] += a1.y;
+              } else {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) f[t] += __bfloat162float(rs[t]);
+              }
+            }
+            if (args.bn_relu) {
+#pragma unroll
+              for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
+            }
+          } else {
+            float xh[4] = {0.f, 0.f, 0.f, 0.f};
+            const __nv_bfloat16* bx = args.bn_x + ro;
+            if (vec) {
+              const uint2 u = __ldg(reinterpret_cast<const uint2*>(bx));
+              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+              const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+              xh[0] = a0.x; xh[1] = a0.y; xh[2] = a1.x; xh[3] = a1.y;
+            } else {
+#pragma unroll
+              for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) xh[t] = __bfloat162float(bx[t]);
+            }
+#pragma unroll
+            for (int t = 0; t < 4; ++t) f[t] = k0[t] * (f[t] - k1[t] - (xh[t] - bm[t]) * bi[t] * k2[t]);
+          }
+          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + ro;
+          __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
+          __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
+          if (vec) {
+            uint2 u;
+            u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
+            *reinterpret_cast<uint2*>(o) = u;
+          } else {
+            const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = hv[t];
+          }
         }
       }
     }
@@ -974,6 +1143,44 @@ int launch_2sm(const TensorSpec& ta, const TensorSpec& tb, const Gemm2smArgs& a,
 }
 
 inline int ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+
+// Copies a kml_bn_fuse request into the kernel arguments (cluster mode only) and checks it.
+int apply_bn_fuse(GemmArgs& g, const kml_epilogue* epi, int block_n) {
+  const kml_bn_fuse* f = epi->bn_fuse;
+  if (f == nullptr || f->mode == 0) return 0;
+  KML_CHECK(g.cluster_reduce, "bn_fuse needs cluster mode");
+  KML_CHECK(f->mode == 1 || f->mode == 2, "bn_fuse: mode must be 1 (forward) or 2 (backward)");
+  KML_CHECK(!g.out_f32, "bn_fuse: bf16 output only");
+  KML_CHECK(g.n_valid <= kml::kBnMaxC, "bn_fuse: at most %d channels", kml::kBnMaxC);
+  KML_CHECK(f->scratch && f->gamma && f->save_mean && f->save_invstd, "bn_fuse: null pointer");
+  KML_CHECK(epi->stats == nullptr && epi->bn_x == nullptr && epi->mask_y == nullptr,
+            "bn_fuse replaces stats / mask_y / bn_x of the epilogue");
+  g.bn_mode = f->mode;
+  g.bn_sc = static_cast<kml::BnScratch*>(f->scratch);
+  g.bn_gamma = f->gamma;
+  g.bn_raw = static_cast<__nv_bfloat16*>(f->raw_out);
+  if (f->mode == 1) {
+    KML_CHECK(f->beta && f->raw_out, "bn_fuse forward: beta and raw_out are required");
+    KML_CHECK(!g.relu && g.addend == nullptr, "bn_fuse forward: ReLU / residual belong to bn_fuse, not to the GEMM epilogue");
+    g.bn_beta = f->beta; g.bn_rmean = f->running_mean; g.bn_rvar = f->running_var; g.bn_nbt = f->num_batches_tracked;
+    g.bn_save_mean = f->save_mean; g.bn_save_invstd = f->save_invstd;
+    g.bn_res = static_cast<const __nv_bfloat16*>(f->res);
+    g.bn_relu = f->relu; g.bn_eps = f->eps; g.bn_momentum = f->momentum;
+  } else {
+    KML_CHECK(f->bn_x && f->dgamma && f->dbeta, "bn_fuse backward: bn_x, dgamma and dbeta are required");
+    g.mask_y = static_cast<const __nv_bfloat16*>(f->mask_y);
+    g.bn_x = static_cast<const __nv_bfloat16*>(f->bn_x);
+    g.bn_mean = f->save_mean; g.bn_invstd = f->save_invstd;
+    g.bn_dgamma = f->dgamma; g.bn_dbeta = f->dbeta;
+  }
+  const long long ctas = static_cast<long long>(g.m_tiles) * g.n_tiles * g.z_taps * g.splits;
+  const bool bmn = g.b_kind == kMatMN || g.b_kind == kConvMN || g.b_kind == kWgtMN;
+  const bool amn = g.a_kind == kMatMN || g.a_kind == kConvMN;
+  const int cap = kml_gemm_max_coresident(block_n, amn, bmn, g.splits);
+  KML_CHECK(cap > 0 && ctas <= cap, "bn_fuse: %lld CTAs (clusters of %d) exceed the co-resident limit %d of this device",
+            ctas, g.splits, cap);
+  return 0;
+}
 inline bool pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
 
 // Pixel box of `target` pixels over a W x H x N grid: whole rows first, then rows, then images.
@@ -989,7 +1196,56 @@ bool make_geometry(int W, int H, int target, Geometry* g) {
 
 }  // namespace
 
+namespace {
+template <int BLOCK_N, bool A_MN, bool B_MN>
+int coresident_of(int cluster_size) {
+  constexpr size_t smem = Stages<BLOCK_N>::value * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 + 640;
+  auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN, false>;
+  if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) return -1;
+  cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  kml::note_kernel(reinterpret_cast<const void*>(kernel));
+  if (cluster_size <= 1) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kNumThreads, smem) != cudaSuccess) return -1;
+    return per_sm * kml::num_sms();
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1, 1, cluster_size);
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = cluster_size;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int clusters = 0;
+  if (cudaOccupancyMaxActiveClusters(&clusters, kernel, &cfg) != cudaSuccess) return -1;
+  return clusters * cluster_size;
+}
+}  // namespace
+
 extern "C" {
+
+int kml_gemm_max_coresident(int block_n, int a_mn, int b_mn, int cluster_size) {
+  // cached per (device, variant, cluster size): the occupancy queries are host-side only but not free
+  static std::mutex mu;
+  static std::unordered_map<long long, int> cache;
+  const long long key = (static_cast<long long>(kml::current_device()) << 32) | (block_n << 8) | (a_mn << 7) | (b_mn << 6) |
+                        (cluster_size & 63);
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+  }
+  int v = -1;
+  if (block_n == 64) v = !a_mn ? (b_mn ? coresident_of<64, false, true>(cluster_size) : coresident_of<64, false, false>(cluster_size))
+                               : coresident_of<64, true, true>(cluster_size);
+  else if (block_n == 128) v = !a_mn ? (b_mn ? coresident_of<128, false, true>(cluster_size) : coresident_of<128, false, false>(cluster_size))
+                                     : coresident_of<128, true, true>(cluster_size);
+  if (v <= 0) { cudaGetLastError(); kml::set_error("kml_gemm_max_coresident: occupancy query failed"); }
+  std::lock_guard<std::mutex> lock(mu);
+  cache[key] = v;
+  return v;
+}
 
 int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb, void* out,
                   long long ldo, int M, int N, int K, const kml_epilogue* epi, void* stream) {
@@ -1061,6 +1317,7 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
               "column statistics / masks need cluster mode");
     KML_CHECK(g.splits == 1 || (out_f32 && !relu), "split-K needs an fp32 output and no ReLU");
   }
+  if (int rc = apply_bn_fuse(g, epi, block_n)) return rc;
   return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
 }
 
@@ -1157,6 +1414,7 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
     g.wgt_taps = KH * KW;
     g.wgt_cin = Cout;
   }
+  if (int rc = apply_bn_fuse(g, epi, block_n)) return rc;
   return launch(ta, tb, g, block_n, static_cast<cudaStream_t>(stream));
 }
 

@@ -18,6 +18,7 @@
 // Backward: g = dy * (y > 0); dbeta = sum g; dgamma = sum g*xhat;
 //           dx = gamma*invstd*(g - dbeta/M - xhat*dgamma/M); optionally stores g for the residual branch.
 #include "common.cuh"
+#include "bn_scratch.cuh"
 #include "../include/kubeml_b200.h"
 
 namespace {
@@ -25,31 +26,16 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kVec = 8;        // channels per thread (one 16-byte bf16 vector)
 constexpr int kRows = 4;       // rows a thread keeps in registers
-constexpr int kMaxC = 2048;
+constexpr int kMaxC = kml::kBnMaxC;
 
-struct BnScratch {             // device-resident launch state, zero-initialised once
-  unsigned int launches;       // parity selects the statistics buffer of this launch
-  unsigned int bar_base;       // value of `bar` when the current launch started (read with `launches` as one uint2)
-  unsigned int bar;            // grid barrier: arrivals, monotonically increasing
-  unsigned int pad;
-  float acc[2][2 * kMaxC];
-};
+using kml::BnScratch;
 
-// Grid-wide barrier for a *regular* launch.  A cooperative launch costs ~7 us on this part (measured:
-// 9.3 us vs 1.9 us for an 8-row problem), which is more than the whole layer; the grid is sized to
-// fit the GPU at once (<= SMs x resident CTAs), the stream serialises launches, so every CTA becomes
-// resident and the spin cannot deadlock.
+// Grid-wide barrier for a *regular* launch (see csrc/bn_scratch.cuh for the co-residency argument and the
+// bounded spin).  A cooperative launch costs ~7 us on this part (measured: 9.3 us vs 1.9 us for an 8-row
+// problem), which is more than the whole layer.
 __device__ __forceinline__ void grid_barrier(BnScratch* sc, unsigned base) {
   __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(&sc->bar, 1u);
-    unsigned v;
-    do {
-      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&sc->bar) : "memory");
-    } while (v - base < gridDim.x);
-    __threadfence();
-  }
+  if (threadIdx.x == 0) kml::grid_arrive_and_wait(sc, base, gridDim.x);
   __syncthreads();
 }
 

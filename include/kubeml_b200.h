@@ -131,6 +131,44 @@ int kml_softmax_ce(const void* logits, int logits_bf16, const long long* labels,
  * through cuDNN / cuBLAS inside torch 1.7.1 (ml/environment/Dockerfile:3,20); SURVEY 2.4 lists them.
  * All operands bf16, fp32 accumulation in TMEM.
  * ---------------------------------------------------------------------------------------------- */
+/* BatchNorm fused behind a cluster-mode GEMM (kml_epilogue.bn_fuse).  The GEMM's CTAs accumulate the
+ * per-channel sums, synchronise the whole grid in software (the grid must be co-resident:
+ * kml_gemm_max_coresident), and finish the layer while the tile is still on chip - convolution +
+ * BatchNorm (+ residual + ReLU) in ONE launch forward, data gradient + BatchNorm backward in one launch
+ * backward.  The reference gets these as separate cuDNN/ATen calls.  Output must be bf16.
+ *   mode 1, forward : tile = conv output x.  Writes raw_out = x (bf16, backward needs it) and
+ *                     out = relu?(gamma*(x-mean)*invstd + beta + res?); save_mean/save_invstd, running
+ *                     statistics (momentum, unbiased variance) and num_batches_tracked like kml_bn_fwd_train.
+ *   mode 2, backward: tile (+ addend_bf16) masked by mask_y is the gradient g entering the BatchNorm whose
+ *                     forward saved bn_x / save_mean / save_invstd.  Writes raw_out = g when non-NULL (the
+ *                     residual branch needs it), out = gamma*invstd*(g - sum_g/M - xhat*sum_gxhat/M),
+ *                     dgamma, dbeta.
+ * scratch: the kml_bn_scratch_bytes() launch state shared with the kml_bn_* kernels of the same stream. */
+typedef struct {
+  int mode;
+  void* scratch;
+  const float* gamma;
+  const float* beta;               /* forward */
+  float* running_mean;             /* forward, may be NULL */
+  float* running_var;
+  long long* num_batches_tracked;  /* forward, may be NULL */
+  float* save_mean;                /* forward: written; backward: read */
+  float* save_invstd;
+  const void* res;                 /* forward: bf16 residual, may be NULL */
+  void* raw_out;
+  int relu;                        /* forward: ReLU after the residual add */
+  float eps, momentum;
+  const void* mask_y;              /* backward: bf16 output of the layer (ReLU mask), may be NULL */
+  const void* bn_x;                /* backward: bf16 BatchNorm input saved by forward */
+  float* dgamma;
+  float* dbeta;
+} kml_bn_fuse;
+
+/* Largest grid (in CTAs) of the cluster-mode GEMM variant (block_n, operand majors) with clusters of
+ * `cluster_size` that is guaranteed to be resident at once on the current device: the bound a fused
+ * BatchNorm launch must respect.  Returns <= 0 on error. */
+int kml_gemm_max_coresident(int block_n, int a_mn, int b_mn, int cluster_size);
+
 typedef struct {
   const float* bias;        /* per output column, added by K-split 0; may be NULL                   */
   const void* addend_bf16;  /* bf16 tensor shaped like the output, added before ReLU; may be NULL   */
@@ -154,6 +192,7 @@ typedef struct {
   const void* bn_x;         /* bf16, shaped like the output: the BatchNorm input saved by forward     */
   const float* bn_mean;     /* fp32 [N]                                                               */
   const float* bn_invstd;   /* fp32 [N]                                                               */
+  const kml_bn_fuse* bn_fuse; /* cluster mode only, may be NULL: finish a BatchNorm in this launch         */
 } kml_epilogue;
 
 /* out[M,N] = A * B^T.  a_mn = 0: A is [M][K] (lda = row stride); a_mn = 1: A is [K][M].  Same for B
