@@ -49,10 +49,20 @@ class MergeParams(Structure):
     ]
 
 
+class BnFuse(Structure):
+    """kml_bn_fuse (include/kubeml_b200.h): a BatchNorm finished inside a cluster-mode GEMM launch."""
+    _fields_ = [("mode", c_int), ("scratch", c_void_p), ("gamma", c_void_p), ("beta", c_void_p),
+                ("running_mean", c_void_p), ("running_var", c_void_p), ("num_batches_tracked", c_void_p),
+                ("save_mean", c_void_p), ("save_invstd", c_void_p), ("res", c_void_p), ("raw_out", c_void_p),
+                ("relu", c_int), ("eps", c_float), ("momentum", c_float), ("mask_y", c_void_p), ("bn_x", c_void_p),
+                ("dgamma", c_void_p), ("dbeta", c_void_p)]
+
+
 class Epilogue(Structure):
     _fields_ = [("bias", c_void_p), ("addend_bf16", c_void_p), ("relu", c_int), ("out_f32", c_int),
                 ("splits", c_int), ("slabs", c_int), ("block_n", c_int), ("cluster", c_int), ("stats", c_void_p),
-                ("mask_y", c_void_p), ("bn_x", c_void_p), ("bn_mean", c_void_p), ("bn_invstd", c_void_p)]
+                ("mask_y", c_void_p), ("bn_x", c_void_p), ("bn_mean", c_void_p), ("bn_invstd", c_void_p),
+                ("bn_fuse", POINTER(BnFuse))]
 
 
 def _declare(lib) -> None:
@@ -82,6 +92,7 @@ def _declare(lib) -> None:
     sig("kml_mcast_destroy", c_int, c_void_p)
     # merge / optim / loss
     sig("kml_kavg_merge", c_int, POINTER(MergeParams), c_void_p)
+    sig("kml_gemm_max_coresident", c_int, c_int, c_int, c_int, c_int)
     sig("kml_sgd_step", c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float,
         c_int, c_void_p, c_void_p)
     sig("kml_adam_step", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float,

@@ -318,10 +318,14 @@ class Act:
     produced it.  Slabs are folded by the BatchNorm kernel that consumes them (csrc/norm.cu), so a
     small, deep GEMM can be spread over the whole GPU without a reduction pass or atomics.
     `stats`: per-channel sum / sum of squares the producing GEMM accumulated (cluster split-K)."""
-    __slots__ = ("t", "slabs", "stats")
+    __slots__ = ("t", "slabs", "stats", "bn_done", "g")
 
-    def __init__(self, t: torch.Tensor, slabs: int = 0, stats: Optional[torch.Tensor] = None):
+    def __init__(self, t: torch.Tensor, slabs: int = 0, stats: Optional[torch.Tensor] = None,
+                 bn_done: bool = False, g: Optional[torch.Tensor] = None):
         self.t, self.slabs, self.stats = t, slabs, stats
+        # bn_done: the producing data-gradient GEMM already ran the consuming BatchNorm's backward
+        # (kml_bn_fuse mode 2): `t` is that layer's dx, `g` its masked incoming gradient (if asked for)
+        self.bn_done, self.g = bn_done, g
 
     @property
     def shape(self):
@@ -349,6 +353,41 @@ def _bn_bwd_fusion() -> bool:
     Off by default: measured neutral on B200 (ResNet-34 step 1.585 ms without, 1.594 ms with) - the
     heavier GEMM epilogue costs what the barrier-free BatchNorm kernel saves."""
     return os.environ.get("KUBEML_CLUSTER_BNBWD", "0") == "1"
+
+
+def _bn_fuse_enabled() -> bool:
+    """Finish BatchNorm inside the GEMM that feeds it (forward: conv + BN + residual + ReLU in one launch;
+    backward: data gradient + BN backward in one launch) - csrc/gemm_tcgen05.cu `kml_bn_fuse`.  The GEMM
+    then synchronises its whole grid in software, so it is used on the main stream only and only when the
+    grid is co-resident (`fused_plan`)."""
+    return os.environ.get("KUBEML_FUSE_BN", "1") != "0" and _cluster_enabled()
+
+
+_coresident_cache: Dict[Tuple, int] = {}
+
+
+def fused_plan(device: torch.device, m_tiles: int, n: int, chunks: int, bn0: int, b_mn: bool):
+    """(block_n, splits) for a GEMM with a fused BatchNorm epilogue, or None when no plan keeps the whole grid
+    resident at once (the fused epilogue spins on a grid-wide barrier)."""
+    if n > 2048 or n % 8:
+        return None
+    bn_, S = plan_cluster(m_tiles, n, chunks, bn0)
+    while True:
+        ctas = m_tiles * ((n + bn_ - 1) // bn_) * S
+        if device.type != "cuda":
+            return bn_, S
+        key = (device.index, bn_, b_mn, S)
+        cap = _coresident_cache.get(key)
+        if cap is None:
+            cap = ops.max_coresident(bn_, False, b_mn, S)
+            _coresident_cache[key] = cap
+        if 0 < ctas <= cap:
+            return bn_, S
+        if S == 1:
+            return None
+        S = max(1, S // 2)
+        per = -(-chunks // S)
+        S = -(-chunks // per)
 
 
 def _cluster_enabled() -> bool:
@@ -420,6 +459,47 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
     return Act(y, S if S > 1 else 0)
 
 
+def conv_bn_forward(conv: NConv2d, bn: "NBatchNorm2d", x: torch.Tensor, B: Buffers, tag: str, bntag: str,
+                    train: bool, relu: bool, res: Optional[torch.Tensor] = None, fuse: bool = True):
+    """relu?(bn(conv(x)) + res?) -> (y, x_saved) like `bn_forward`.  In training, when the GEMM's grid fits the
+    GPU at once, convolution and BatchNorm are ONE launch (the GEMM accumulates the statistics, synchronises
+    its grid and normalises the tile it still holds); otherwise GEMM (+ statistics) then `bn_forward`."""
+    if train and fuse and _bn_fuse_enabled() and conv.bias is None:
+        N, H, W, _ = x.shape
+        k, s, p = conv.k, conv.stride, conv.padding
+        Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+        M = N * Ho * Wo
+        m_tiles = (M + 127) // 128
+        direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p)
+        Kd = k * k * conv.cin
+        if direct:
+            live = sum(1 for kh in range(k) for kw in range(k)
+                       if (kh - p) <= H - 1 and (Ho - 1 + kh - p) >= 0 and (kw - p) <= W - 1 and (Wo - 1 + kw - p) >= 0)
+            chunks = live * (conv.cin // 64)
+        else:
+            chunks = (Kd + 63) // 64
+        plan = fused_plan(x.device, m_tiles, conv.cout, chunks, pick_block_n(m_tiles, conv.cout), False)
+        if plan is not None:
+            bn_, S = plan
+            raw = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
+            y = B.get(bntag + ".y", (N, Ho, Wo, conv.cout))
+            mean = B.get(bntag + ".mean", (bn.c,), torch.float32)
+            istd = B.get(bntag + ".istd", (bn.c,), torch.float32)
+            bf = ops.BnFwd(bn.weight.data, bn.bias.data, bn.running_mean, bn.running_var, bn.num_batches_tracked,
+                           mean, istd, raw, res=res, relu=relu, eps=bn.eps, momentum=bn.momentum)
+            if direct:
+                ops.conv2d_fprop(x, conv.w_bf16, p, out=y, block_n=bn_, splits=S, cluster=True, bn_fuse=bf)
+            else:
+                ldk = _ceil(Kd, 64)
+                cols = B.get(tag + ".cols", (M, ldk))
+                K.im2col(x, cols, k, k, s, p)
+                ops.gemm_bf16(cols[:, :Kd] if ldk != Kd else cols, _packed_weight(conv, B, tag, ldk)[:, :Kd],
+                              out=y.view(M, conv.cout), block_n=bn_, splits=S, cluster=True, bn_fuse=bf)
+            return y, raw
+    t = conv_forward(conv, x, B, tag, allow_slabs=True, want_stats=train)
+    return bn_forward(bn, t, B, bntag, train, relu=relu, res=res)
+
+
 def _packed_weight(conv: NConv2d, B: Buffers, tag: str, ldk: int) -> torch.Tensor:
     """[Cout, ldk] bf16 view of the filter; a padded copy only when K is not a multiple of 8."""
     Kd = conv.k * conv.k * conv.cin
@@ -464,9 +544,23 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
                    if (kh - pd) <= Ho - 1 and (H - 1 + kh - pd) >= 0 and (kw - pd) <= Wo - 1 and (W - 1 + kw - pd) >= 0)
         if allow_slabs and _cluster_enabled():
             bn_d, S = plan_cluster(m_tiles, conv.cin, live * (conv.cout // 64), bn_d)
+            if bn_next is not None and _bn_fuse_enabled():
+                # data gradient + the consuming BatchNorm's whole backward in one launch
+                plan = fused_plan(dy.device, m_tiles, conv.cin, live * (conv.cout // 64), bn_d, True)
+                if plan is not None:
+                    nbn, ntag, ny, nx = bn_next[:4]
+                    want_dres = len(bn_next) > 4 and bool(bn_next[4])
+                    bn_d, S = plan
+                    out = B.get(ntag + ".dx", (N, H, W, conv.cin))
+                    gbuf = B.get(ntag + ".dres", (N, H, W, conv.cin)) if want_dres else None
+                    bf = ops.BnBwd(nbn.weight.data, B[ntag + ".mean"], B[ntag + ".istd"], nx, nbn.g_weight, nbn.g_bias,
+                                   mask_y=ny, raw_out=gbuf)
+                    ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=out, block_n=bn_d, splits=S,
+                                     cluster=True, bn_fuse=bf)
+                    return Act(out, bn_done=True, g=gbuf)
             dx = B.get(tag + ".dx", (N, H, W, conv.cin))
             if bn_next is not None and _bn_bwd_fusion():
-                nbn, ntag, ny, nx = bn_next
+                nbn, ntag, ny, nx = bn_next[:4]
                 stats = B.get(ntag + ".bstats", (K.bn_stats_numel(conv.cin),), torch.float32, zero=True)
                 ops.conv2d_dgrad(dy, conv.w_bf16, p, H, W, addend=addend, out=dx, block_n=bn_d, splits=S,
                                  cluster=True, mask_y=ny, bn=(nx, B[ntag + ".mean"], B[ntag + ".istd"]), stats=stats)
@@ -530,6 +624,8 @@ def bn_forward(bn: NBatchNorm2d, x: Act, B: Buffers, tag: str, train: bool, relu
 
 def bn_backward(bn: NBatchNorm2d, dy: Act, y: Optional[torch.Tensor], x: torch.Tensor, B: Buffers,
                 tag: str, want_dres: bool = False):
+    if dy.bn_done:                # the data-gradient GEMM already finished this layer's backward
+        return dy.t, dy.g
     dx = B.get(tag + ".dx", tuple(x.shape))
     if dy.stats is not None:      # masked gradient + reduction sums came with the data-gradient GEMM
         K.bn_bwd_apply(dy.t, x, bn.weight.data, B[tag + ".mean"], B[tag + ".istd"], dy.stats, dx, bn.g_weight, bn.g_bias)

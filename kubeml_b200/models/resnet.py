@@ -20,7 +20,7 @@ import torch.nn as nn
 from .. import ops
 from ..ops import nn as K
 from .native import (Buffers, NativeNet, NBatchNorm2d, NConv2d, NLinear, bn_backward, bn_forward,
-                     conv_backward, conv_forward, linear_backward, linear_forward)
+                     conv_backward, conv_bn_forward, conv_forward, linear_backward, linear_forward)
 
 
 class NBasicBlock(nn.Module):
@@ -82,8 +82,7 @@ class NativeResNet(NativeNet):
         N = x.shape[0]
         B = self.buffers_for(N, train)
         S = {"x": x, "blocks": []}
-        c1 = conv_forward(self.conv1, x, B, "stem", allow_slabs=True, want_stats=train)
-        a1, c1s = bn_forward(self.bn1, c1, B, "stem.bn", train, relu=True)
+        a1, c1s = conv_bn_forward(self.conv1, self.bn1, x, B, "stem", "stem.bn", train, relu=True)
         _, H1, W1, _ = a1.shape
         Hp, Wp = (H1 + 2 - 3) // 2 + 1, (W1 + 2 - 3) // 2 + 1
         p1 = B.get("pool.y", (N, Hp, Wp, 64))
@@ -97,12 +96,10 @@ class NativeResNet(NativeNet):
                 with B.on_side():
                     td = conv_forward(blk.downsample[0], h, B, tag + ".cd", allow_slabs=True, want_stats=train)
                     idn, tds = bn_forward(blk.downsample[1], td, B, tag + ".bnd", train, relu=False)
-            t1 = conv_forward(blk.conv1, h, B, tag + ".c1", allow_slabs=True, want_stats=train)
-            a, t1s = bn_forward(blk.bn1, t1, B, tag + ".bn1", train, relu=True)
-            t2 = conv_forward(blk.conv2, a, B, tag + ".c2", allow_slabs=True, want_stats=train)
+            a, t1s = conv_bn_forward(blk.conv1, blk.bn1, h, B, tag + ".c1", tag + ".bn1", train, relu=True)
             if blk.downsample is not None:
                 B.join_side()
-            out, t2s = bn_forward(blk.bn2, t2, B, tag + ".bn2", train, relu=True, res=idn)
+            out, t2s = conv_bn_forward(blk.conv2, blk.bn2, a, B, tag + ".c2", tag + ".bn2", train, relu=True, res=idn)
             S["blocks"].append((h, t1s, a, t2s, tds, out))
             h = out
         Nn, Hh, Ww, C = h.shape
@@ -148,7 +145,7 @@ class NativeResNet(NativeNet):
                 nxt = None
                 if not first_block:              # consumer: bn2 of the block before (its output is `h`)
                     ptag, pblk = self._blocks[nblk - 2 - bi]
-                    nxt = (pblk.bn2, ptag + ".bn2", h, S["blocks"][nblk - 2 - bi][3])
+                    nxt = (pblk.bn2, ptag + ".bn2", h, S["blocks"][nblk - 2 - bi][3], True)
                 dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=g, allow_slabs=not first_block,
                                    bn_next=nxt)
             else:

@@ -303,7 +303,17 @@ class KubeModel(ABC):
             return False
         return os.environ.get("KUBEML_CUDA_GRAPH", "1") != "0"
 
-    _single_step = None      # does the user's train() call optimizer.step() exactly once per batch?
+    # Does the user's train() call optimizer.step() exactly once per batch?  Observed on eager calls and
+    # remembered in the worker's state: later invocations (epochs) only replay the captured step.
+    @property
+    def _single_step(self):
+        ws = self._inv.worker_state if self._inv is not None and self._inv.worker_state is not None else self.__dict__
+        return ws.setdefault("single_step", {}).get((self.args._job_id, type(self).__name__))
+
+    @_single_step.setter
+    def _single_step(self, v) -> None:
+        ws = self._inv.worker_state if self._inv is not None and self._inv.worker_state is not None else self.__dict__
+        ws.setdefault("single_step", {})[(self.args._job_id, type(self).__name__)] = v
 
     def _eager_step(self, batch, idx, defer: bool = False):
         opt = self.optimizer

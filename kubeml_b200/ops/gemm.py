@@ -15,9 +15,103 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
     return 0 if t is None else t.data_ptr()
 
 
+class BnFwd:
+    """A training-mode BatchNorm (+ residual + ReLU) to be finished inside the producing cluster GEMM
+    (csrc/gemm_tcgen05.cu, `kml_bn_fuse` mode 1).  `raw_out` receives the GEMM's own output (the
+    BatchNorm input, which backward needs); the GEMM's `out` becomes the layer output."""
+
+    def __init__(self, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd, raw_out,
+                 res=None, relu=False, eps=1e-5, momentum=0.1):
+        self.gamma, self.beta, self.running_mean, self.running_var, self.nbt = gamma, beta, running_mean, running_var, nbt
+        self.save_mean, self.save_invstd, self.raw_out, self.res = save_mean, save_invstd, raw_out, res
+        self.relu, self.eps, self.momentum = relu, eps, momentum
+
+    def fill(self, f, device):
+        from . import nn as K
+        f.mode = 1
+        f.scratch = K.bn_scratch(device).data_ptr()
+        f.gamma, f.beta = self.gamma.data_ptr(), self.beta.data_ptr()
+        f.running_mean, f.running_var = _ptr(self.running_mean) or None, _ptr(self.running_var) or None
+        f.num_batches_tracked = _ptr(self.nbt) or None
+        f.save_mean, f.save_invstd = self.save_mean.data_ptr(), self.save_invstd.data_ptr()
+        f.res, f.raw_out = _ptr(self.res) or None, self.raw_out.data_ptr()
+        f.relu, f.eps, f.momentum = int(self.relu), float(self.eps), float(self.momentum)
+
+    def cpu(self, y: torch.Tensor, out: torch.Tensor) -> None:
+        """fp32 restatement: y = the GEMM result (already rounded to the output dtype)."""
+        C = y.shape[-1]
+        M = y.numel() // C
+        self.raw_out.copy_(y.reshape(self.raw_out.shape))
+        xf = self.raw_out.float().reshape(M, C)
+        mean = xf.mean(0)
+        var = xf.var(0, unbiased=False)
+        invstd = torch.rsqrt(var + self.eps)
+        o = (xf - mean) * invstd * self.gamma + self.beta
+        if self.res is not None:
+            o = o + self.res.float().reshape(M, C)
+        if self.relu:
+            o = torch.relu(o)
+        out.copy_(o.reshape(out.shape))
+        self.save_mean.copy_(mean)
+        self.save_invstd.copy_(invstd)
+        if self.running_mean is not None:
+            self.running_mean.mul_(1 - self.momentum).add_(self.momentum * mean)
+            self.running_var.mul_(1 - self.momentum).add_(self.momentum * var * (M / max(M - 1, 1)))
+        if self.nbt is not None:
+            self.nbt.add_(1)
+
+
+class BnBwd:
+    """The backward of a BatchNorm finished inside the data-gradient GEMM that produces its incoming
+    gradient (`kml_bn_fuse` mode 2): g = (GEMM result + addend) * (mask_y > 0); the GEMM's `out` becomes
+    dx = gamma*invstd*(g - mean(g) - xhat*mean(g*xhat)); `raw_out` (optional) receives g."""
+
+    def __init__(self, gamma, save_mean, save_invstd, bn_x, dgamma, dbeta, mask_y=None, raw_out=None):
+        self.gamma, self.save_mean, self.save_invstd, self.bn_x = gamma, save_mean, save_invstd, bn_x
+        self.dgamma, self.dbeta, self.mask_y, self.raw_out = dgamma, dbeta, mask_y, raw_out
+
+    def fill(self, f, device):
+        from . import nn as K
+        f.mode = 2
+        f.scratch = K.bn_scratch(device).data_ptr()
+        f.gamma = self.gamma.data_ptr()
+        f.save_mean, f.save_invstd = self.save_mean.data_ptr(), self.save_invstd.data_ptr()
+        f.bn_x, f.mask_y = self.bn_x.data_ptr(), _ptr(self.mask_y) or None
+        f.raw_out = _ptr(self.raw_out) or None
+        f.dgamma, f.dbeta = self.dgamma.data_ptr(), self.dbeta.data_ptr()
+
+    def cpu(self, g: torch.Tensor, out: torch.Tensor) -> None:
+        """g: fp32 GEMM result + addend (not yet masked)."""
+        C = g.shape[-1]
+        M = g.numel() // C
+        g = g.reshape(M, C)
+        if self.mask_y is not None:
+            g = g * (self.mask_y.float().reshape(M, C) > 0)
+        g = g.to(out.dtype).float()
+        if self.raw_out is not None:
+            self.raw_out.copy_(g.reshape(self.raw_out.shape))
+        xhat = (self.bn_x.float().reshape(M, C) - self.save_mean) * self.save_invstd
+        s1, s2 = g.sum(0), (g * xhat).sum(0)
+        self.dbeta.copy_(s1)
+        self.dgamma.copy_(s2)
+        out.copy_((self.gamma * self.save_invstd * (g - s1 / M - xhat * s2 / M)).reshape(out.shape))
+
+
+def max_coresident(block_n: int, a_mn: bool, b_mn: bool, cluster: int) -> int:
+    """CTAs of the cluster-mode GEMM variant guaranteed to be resident together on the current GPU (the
+    bound a fused-BatchNorm launch, which synchronises its grid in software, must respect)."""
+    return int(_native.lib().kml_gemm_max_coresident(int(block_n), int(a_mn), int(b_mn), int(cluster)))
+
+
 def _epi(bias=None, addend=None, relu=False, out_f32=False, splits=1, block_n=0, slabs=False,
-         cluster=False, stats=None, mask_y=None, bn=None):
+         cluster=False, stats=None, mask_y=None, bn=None, bn_fuse=None, device=None):
     e = _native.Epilogue()
+    if bn_fuse is not None:
+        f = _native.BnFuse()
+        bn_fuse.fill(f, device)
+        e._bn_keep = f                        # keep the struct alive for the duration of the call
+        import ctypes as _ct
+        e.bn_fuse = _ct.pointer(f)
     e.bias = _ptr(bias) or None
     e.addend_bf16 = _ptr(addend) or None
     e.relu, e.out_f32, e.splits, e.block_n = int(relu), int(out_f32), int(splits), int(block_n)
@@ -46,8 +140,11 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
               bias: Optional[torch.Tensor] = None, relu: bool = False,
               out_dtype: torch.dtype = torch.bfloat16, out: Optional[torch.Tensor] = None,
               splits: int = 1, block_n: int = 0, addend: Optional[torch.Tensor] = None,
-              slabs: bool = False, cluster: bool = False, stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+              slabs: bool = False, cluster: bool = False, stats: Optional[torch.Tensor] = None,
+              bn_fuse=None) -> torch.Tensor:
     """out[M,N] = A · B^T (+bias, ReLU) with fp32 accumulation.
+
+    bn_fuse (`BnFwd` / `BnBwd`, cluster mode, bf16 `out` required): a BatchNorm finished inside this launch.
 
     cluster=True: the K-splits (<= 8) of a tile run as one thread-block cluster and are added through
     distributed shared memory; the output is final (any dtype, bias/addend/ReLU allowed) and `stats`
@@ -73,6 +170,9 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
             r = r + addend.float()
         if relu:
             r = torch.relu(r)
+        if bn_fuse is not None:
+            bn_fuse.cpu(r.to(out_dtype) if isinstance(bn_fuse, BnFwd) else r, out)
+            return out
         r = r.to(out_dtype)
         _cpu_stats(stats, r)
         if out is not None:
@@ -93,7 +193,8 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     if out is None:
         out = (torch.zeros if splits > 1 and not cluster else torch.empty)((M, N), dtype=out_dtype, device=a.device)
     import ctypes
-    e = _epi(bias, addend, relu, out_f32, splits, block_n, slabs and splits > 1 and not cluster, cluster, stats)
+    e = _epi(bias, addend, relu, out_f32, splits, block_n, slabs and splits > 1 and not cluster, cluster, stats,
+             bn_fuse=bn_fuse, device=a.device)
     _native.check(_native.lib().kml_gemm_bf16(
         a.data_ptr(), int(a_mn), a.stride(0), b.data_ptr(), int(b_mn), b.stride(0), out.data_ptr(),
         out.stride(-2), M, N, K, ctypes.byref(e), _native.stream_ptr()), "kml_gemm_bf16")
@@ -109,7 +210,7 @@ def conv2d_fprop_supported(H: int, W: int, Cin: int, Cout: int, KH: int, KW: int
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[torch.Tensor] = None,
                  relu: bool = False, out_dtype: torch.dtype = torch.bfloat16, splits: int = 1,
                  block_n: int = 0, out: Optional[torch.Tensor] = None, slabs: bool = False,
-                 cluster: bool = False, stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 cluster: bool = False, stats: Optional[torch.Tensor] = None, bn_fuse=None) -> torch.Tensor:
     """Stride-1 convolution, NHWC.  x: [N,H,W,Cin] bf16; w: [Cout,KH,KW,Cin] bf16 -> [N,Ho,Wo,Cout].
     The data gradient of a stride-1 convolution is this same op applied to dY with the flipped,
     channel-transposed filter and pad' = K-1-pad."""
@@ -124,6 +225,9 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
         if relu:
             y = torch.relu(y)
         y = y.permute(0, 2, 3, 1).contiguous().to(out_dtype)
+        if bn_fuse is not None:
+            bn_fuse.cpu(y, out)
+            return out
         _cpu_stats(stats, y)
         if out is not None:
             if slabs and not cluster:      # [S, N, Ho, Wo, C]: everything in slab 0, zeros elsewhere
@@ -138,7 +242,8 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
     import ctypes
     y = out if out is not None else \
         (torch.zeros if splits > 1 and not cluster else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
-    e = _epi(bias, None, relu, out_f32, splits, block_n, slabs and not cluster, cluster, stats)
+    e = _epi(bias, None, relu, out_f32, splits, block_n, slabs and not cluster, cluster, stats,
+             bn_fuse=bn_fuse, device=x.device)
     _native.check(_native.lib().kml_conv2d_fprop(
         x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_fprop")
@@ -149,7 +254,7 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
                  addend: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
                  block_n: int = 0, splits: int = 1, slabs: bool = False, cluster: bool = False,
                  mask_y: Optional[torch.Tensor] = None, bn=None,
-                 stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 stats: Optional[torch.Tensor] = None, bn_fuse=None) -> torch.Tensor:
     """Data gradient of `conv2d_fprop`: dy [N,Ho,Wo,Cout] bf16, w the *forward* filter
     [Cout,KH,KW,Cin] bf16 -> dx [N,H,W,Cin] bf16 (+ addend, the residual branch's gradient).
     Cluster mode can hand the result to a BatchNorm backward ready-made: `mask_y` (that layer's
@@ -162,6 +267,9 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
                                         dy.permute(0, 3, 1, 2).float(), padding=pad).permute(0, 2, 3, 1)
         if addend is not None:
             dx = dx + addend.float()
+        if bn_fuse is not None:
+            bn_fuse.cpu(dx, out)
+            return out
         if mask_y is not None:
             dx = dx * (mask_y.float() > 0)
         if bn is not None:
@@ -182,7 +290,7 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
     assert dy.is_contiguous() and w.is_contiguous()
     dx = out if out is not None else torch.empty((N, H, W, Cin), dtype=torch.bfloat16, device=dy.device)
     e = _epi(None, addend, False, dx.dtype == torch.float32, splits, block_n, slabs and not cluster, cluster,
-             stats, mask_y, bn)
+             stats, mask_y, bn, bn_fuse=bn_fuse, device=dy.device)
     _native.check(_native.lib().kml_conv2d_dgrad(
         dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_dgrad")

@@ -558,3 +558,117 @@ def test_native_cifar_resnet20_matches_torch_module(dev):
     net.eval(); ref.eval()
     with torch.no_grad():
         _close(net(x), ref(x), 5e-2)
+
+
+# ------------------------------------------------------------------------------------------------------
+# BatchNorm fused into the cluster GEMM (kml_bn_fuse): oracle = plain PyTorch fp32 (F.conv2d, F.batch_norm,
+# autograd), not the repository's own CPU restatement
+# ------------------------------------------------------------------------------------------------------
+def _rel(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).abs().max() / (b.abs().max() + 1e-6)).item()
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout,res,relu", [(128, 8, 64, 64, False, True), (128, 4, 128, 128, True, True),
+                                                    (128, 2, 256, 256, True, True), (128, 1, 512, 512, False, False),
+                                                    (5, 4, 64, 128, True, True), (32, 16, 64, 64, False, True)])
+def test_fused_conv_bn_forward_vs_torch(dev, N, H, Cin, Cout, res, relu):
+    import torch.nn.functional as F
+    from kubeml_b200 import ops
+    from kubeml_b200.models.native import fused_plan, pick_block_n
+    torch.manual_seed(3)
+    x = torch.randn(N, H, H, Cin, device=dev).bfloat16()
+    w = (torch.randn(Cout, 3, 3, Cin, device=dev) * (2.0 / (9 * Cin)) ** 0.5).bfloat16()
+    r = torch.randn(N, H, H, Cout, device=dev).bfloat16() if res else None
+    gamma, beta = torch.rand(Cout, device=dev) + 0.5, torch.randn(Cout, device=dev)
+    M = N * H * H
+    m_tiles = (M + 127) // 128
+    live = 9 if H > 1 else 1
+    plan = fused_plan(dev, m_tiles, Cout, live * (Cin // 64), pick_block_n(m_tiles, Cout), False)
+    assert plan is not None
+    for rep in range(3):                     # replays: the launch state (parity buffers, barrier base) must recycle
+        rm, rv = torch.full((Cout,), 0.25, device=dev), torch.ones(Cout, device=dev)
+        nbt = torch.zeros((), dtype=torch.long, device=dev)
+        mean, istd = torch.empty(Cout, device=dev), torch.empty(Cout, device=dev)
+        raw = torch.empty(N, H, H, Cout, dtype=torch.bfloat16, device=dev)
+        y = torch.empty(N, H, H, Cout, dtype=torch.bfloat16, device=dev)
+        bf = ops.BnFwd(gamma, beta, rm, rv, nbt, mean, istd, raw, res=r, relu=relu)
+        ops.conv2d_fprop(x, w, 1, out=y, block_n=plan[0], splits=plan[1], cluster=True, bn_fuse=bf)
+        torch.cuda.synchronize()
+        xc = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), padding=1)
+        rm_t, rv_t = torch.full((Cout,), 0.25, device=dev), torch.ones(Cout, device=dev)
+        yt = F.batch_norm(xc, rm_t, rv_t, gamma, beta, training=True, momentum=0.1, eps=1e-5)
+        if res:
+            yt = yt + r.float().permute(0, 3, 1, 2)
+        if relu:
+            yt = torch.relu(yt)
+        assert _rel(raw, xc.permute(0, 2, 3, 1)) < 1e-2
+        assert _rel(y, yt.permute(0, 2, 3, 1)) < 2e-2, f"rep {rep}"
+        assert _rel(mean, xc.mean((0, 2, 3))) < 1e-2
+        assert _rel(istd, torch.rsqrt(xc.var((0, 2, 3), unbiased=False) + 1e-5)) < 1e-2
+        assert _rel(rm, rm_t) < 1e-2 and _rel(rv, rv_t) < 1e-2
+        assert int(nbt.item()) == 1
+
+
+@pytest.mark.parametrize("N,H,C,Co,want_g", [(128, 8, 64, 64, True), (128, 4, 128, 128, False), (128, 2, 256, 256, True),
+                                             (128, 1, 512, 512, True), (6, 4, 128, 64, True)])
+def test_fused_dgrad_bn_backward_vs_torch_autograd(dev, N, H, C, Co, want_g):
+    """dy [N,H,H,Co] flows back through conv(C -> Co, 3x3) into a = relu(bn(xb) ); the fused launch must return
+    d loss / d xb, dgamma, dbeta (and the masked gradient g) as torch autograd computes them in fp32."""
+    import torch.nn.functional as F
+    from kubeml_b200 import ops
+    from kubeml_b200.models.native import fused_plan, pick_block_n
+    torch.manual_seed(4)
+    xb = (torch.randn(N, H, H, C, device=dev) * 1.5 + 0.3).bfloat16()
+    gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev) * 0.3
+    w = (torch.randn(Co, 3, 3, C, device=dev) * (2.0 / (9 * C)) ** 0.5).bfloat16()
+    dy = torch.randn(N, H, H, Co, device=dev).bfloat16()
+    add = torch.randn(N, H, H, C, device=dev).bfloat16()
+    # fp32 autograd oracle
+    xt = xb.float().permute(0, 3, 1, 2).clone().requires_grad_(True)
+    gt, bt = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    a = torch.relu(F.batch_norm(xt, None, None, gt, bt, training=True, eps=1e-5))
+    out = F.conv2d(a, w.float().permute(0, 3, 1, 2), padding=1)
+    ((out * dy.float().permute(0, 3, 1, 2)).sum() + (a * add.float().permute(0, 3, 1, 2)).sum()).backward()
+    mean = xb.float().mean((0, 1, 2))
+    istd = torch.rsqrt(xb.float().var((0, 1, 2), unbiased=False) + 1e-5)
+    a_bf = a.detach().permute(0, 2, 3, 1).contiguous().bfloat16()
+    M = N * H * H
+    m_tiles = (M + 127) // 128
+    live = 9 if H > 1 else 1
+    plan = fused_plan(dev, m_tiles, C, live * (Co // 64), pick_block_n(m_tiles, C), True)
+    assert plan is not None
+    for rep in range(2):
+        dx = torch.empty(N, H, H, C, dtype=torch.bfloat16, device=dev)
+        g = torch.empty(N, H, H, C, dtype=torch.bfloat16, device=dev) if want_g else None
+        dg, db = torch.empty(C, device=dev), torch.empty(C, device=dev)
+        bf = ops.BnBwd(gamma, mean, istd, xb, dg, db, mask_y=a_bf, raw_out=g)
+        ops.conv2d_dgrad(dy, w, 1, H, H, addend=add, out=dx, block_n=plan[0], splits=plan[1], cluster=True, bn_fuse=bf)
+        torch.cuda.synchronize()
+        assert _rel(dx, xt.grad.permute(0, 2, 3, 1)) < 3e-2, f"rep {rep}"
+        assert _rel(dg, gt.grad) < 2e-2 and _rel(db, bt.grad) < 2e-2
+        if want_g:
+            g_ref = (torch.nn.grad.conv2d_input(xt.shape, w.float().permute(0, 3, 1, 2), dy.float().permute(0, 3, 1, 2),
+                                                padding=1) + add.float().permute(0, 3, 1, 2)) * (a.detach() > 0)
+            assert _rel(g, g_ref.permute(0, 2, 3, 1)) < 2e-2
+
+
+def test_fused_gemm_bn_forward_ragged_vs_torch(dev):
+    """Plain GEMM (im2col'd convolutions, e.g. the 7x7 stem) with the fused epilogue; ragged M and N."""
+    import torch.nn.functional as F
+    from kubeml_b200 import ops
+    torch.manual_seed(5)
+    M, N, Kd = 1000, 72, 152
+    a = torch.randn(M, Kd, device=dev).bfloat16()
+    b = (torch.randn(N, Kd, device=dev) * 0.1).bfloat16()
+    gamma, beta = torch.rand(N, device=dev) + 0.5, torch.randn(N, device=dev)
+    rm, rv = torch.zeros(N, device=dev), torch.ones(N, device=dev)
+    mean, istd = torch.empty(N, device=dev), torch.empty(N, device=dev)
+    raw = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    y = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    bf = ops.BnFwd(gamma, beta, rm, rv, None, mean, istd, raw, relu=True)
+    ops.gemm_bf16(a, b, out=y, block_n=64, splits=2, cluster=True, bn_fuse=bf)
+    torch.cuda.synchronize()
+    xc = a.float() @ b.float().t()
+    yt = torch.relu(F.batch_norm(xc, None, None, gamma, beta, training=True))
+    assert _rel(raw, xc) < 1e-2 and _rel(y, yt) < 2e-2
