@@ -290,7 +290,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   // fused BatchNorm: launch state of the software grid barrier, read early so the round trip overlaps the
   // main loop (nobody can advance it before every CTA of this grid has passed the barrier)
   uint2 gstate = make_uint2(0u, 0u);
-  if (args.bn_mode != 0 && warp >= 2) gstate = __ldcg(reinterpret_cast<const uint2*>(&args.bn_sc->launches));
+  if (args.bn_mode != 0) gstate = __ldcg(reinterpret_cast<const uint2*>(&args.bn_sc->launches));
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
@@ -536,31 +536,47 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     // CTA `split` owns rows [rbeg, rend) of the 128-row tile: it adds the partial tiles of all
     // peers for those rows, applies the epilogue once and writes the final output.  Column sums
     // for BatchNorm fall out of the same pass (a thread keeps the same 4 columns for all its rows).
+    // All six warps take part (the producer and MMA warps are done).  The pass is latency-bound
+    // (a DSMEM round trip and up to three L2 round trips per element), so each thread works on kU rows
+    // at a time with every load of the batch issued before the first use.
     constexpr int kPartStride = BLOCK_N + 4;
     constexpr int kGroups = BLOCK_N / 4;                 // float4 groups per row
+    constexpr int kRowStep = kNumThreads / kGroups;      // rows covered by one sweep of the CTA
+    constexpr int kWarps = kNumThreads / 32;
+    constexpr int kU = 4;
     float* part = reinterpret_cast<float*>(smem_a);
-    float* st_sm = part + kBlockM * kPartStride;        // [4 warps][2][BLOCK_N] per-warp column sums
-    float* pv_sm = st_sm + 8 * BLOCK_N;                  // [BLOCK_N] pivots of the fused forward statistics
+    float* st_sm = part + kBlockM * kPartStride;        // [6 warps][2][BLOCK_N] per-warp column sums
+    float* pv_sm = st_sm + 2 * kWarps * BLOCK_N;         // [BLOCK_N] pivots of the fused forward statistics
+    float* co = pv_sm + BLOCK_N;                         // [3][BLOCK_N] per-column coefficients of the fused BatchNorm
     const int bnm = args.bn_mode;
-    if (bnm == 1 && warp >= 2) {
-      // Shifted sums: accumulate (x - pivot) and (x - pivot)^2 with pivot = running mean, so that the
-      // variance does not cancel catastrophically when |mean| >> std.  Read BEFORE the grid barrier:
-      // the running statistics are updated after it.
-      for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128) {
+    const int et = threadIdx.x;
+    if (bnm != 0) {
+      // Everything per-channel that does not depend on the batch statistics is fetched now, before the
+      // barriers.  Forward: pivot = running mean (shifted sums: (x - pivot) and (x - pivot)^2, so the
+      // variance does not cancel catastrophically when |mean| >> std; read BEFORE the grid barrier, the
+      // running statistics are updated after it), gamma, beta.  Backward: gamma * invstd.
+      for (int c = et; c < BLOCK_N; c += kNumThreads) {
         const int gc = nt * BLOCK_N + c;
-        pv_sm[c] = (args.bn_rmean != nullptr && gc < args.n_valid) ? args.bn_rmean[gc] : 0.f;
+        const bool in = gc < args.n_valid;
+        if (bnm == 1) {
+          pv_sm[c] = (args.bn_rmean != nullptr && in) ? args.bn_rmean[gc] : 0.f;
+          co[c] = in ? args.bn_gamma[gc] : 0.f;
+          co[BLOCK_N + c] = in ? args.bn_beta[gc] : 0.f;
+        } else {
+          co[c] = in ? args.bn_gamma[gc] * args.bn_invstd[gc] : 0.f;
+        }
       }
     }
     cluster_sync_all();
-    if (warp >= 2) {
+    {
       const int S = args.splits;
       const int rp = (kBlockM + S - 1) / S;
       const int rbeg = split * rp;
       const int rend = min(kBlockM, rbeg + rp);
-      const int et = threadIdx.x - 64;                   // 0..127
       const int c4 = (et % kGroups) * 4;
       const int ncol = nt * BLOCK_N + c4;
       const bool col_ok = ncol + 4 <= args.n_valid;
+      const bool fast = col_ok && (args.ldo & 3) == 0;   // 8-byte accesses: every row offset is a multiple of 4 elements
       float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
       float bv[4] = {0.f, 0.f, 0.f, 0.f};
       if (args.bias != nullptr) {
@@ -577,111 +593,132 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll
         for (int t = 0; t < 4; ++t) bm[t] = pv_sm[c4 + t];        // forward: bm holds the pivots
       }
-      for (int r = rbeg + et / kGroups; r < rend; r += 128 / kGroups) {
-        float* own = part + r * kPartStride + c4;
-        const uint32_t laddr = smem_u32(own);
-        float4 acc = ld_dsmem_f4(laddr, 0);
+      const __nv_bfloat16* ad_p = args.addend;
+      const __nv_bfloat16* my_p = args.mask_y;
+      const __nv_bfloat16* bx_p = args.bn_x;
+      auto unpack4 = [](const uint2& u, float (&v)[4]) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+        const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+        v[0] = a0.x; v[1] = a0.y; v[2] = a1.x; v[3] = a1.y;
+      };
+      auto load4 = [&](const __nv_bfloat16* p, long long ro, const uint2& pre, float (&v)[4]) {
+        if (fast) { unpack4(pre, v); return; }
+#pragma unroll
+        for (int t = 0; t < 4; ++t) v[t] = (ncol + t < args.n_valid) ? __bfloat162float(p[ro + t]) : 0.f;
+      };
+      auto store4 = [&](__nv_bfloat16* o, long long ro, const __nv_bfloat162& p0, const __nv_bfloat162& p1) {
+        if (fast) {
+          uint2 u;
+          u.x = *reinterpret_cast<const uint32_t*>(&p0); u.y = *reinterpret_cast<const uint32_t*>(&p1);
+          *reinterpret_cast<uint2*>(o + ro) = u;
+        } else {
+          const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
+#pragma unroll
+          for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[ro + t] = hv[t];
+        }
+      };
+      for (int rb = rbeg + et / kGroups; rb < rend; rb += kU * kRowStep) {
+        long long ro[kU];
+        bool ok[kU];
+        uint2 uad[kU], umy[kU], ubx[kU];
+        float4 acc[kU];
+        // (1) the L2 round trips first
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          const int r = rb + u * kRowStep;
+          const int grow = mt * kBlockM + r;
+          ok[u] = r < rend && grow < args.m_valid;
+          ro[u] = static_cast<long long>(grow) * args.ldo + ncol;
+          uad[u] = umy[u] = ubx[u] = make_uint2(0u, 0u);
+          if (ok[u] && fast) {
+            if (ad_p != nullptr) uad[u] = __ldg(reinterpret_cast<const uint2*>(ad_p + ro[u]));
+            if (my_p != nullptr) umy[u] = __ldg(reinterpret_cast<const uint2*>(my_p + ro[u]));
+            if (bx_p != nullptr) ubx[u] = __ldg(reinterpret_cast<const uint2*>(bx_p + ro[u]));
+          }
+        }
+        // (2) the partial tiles of all peers, kU loads in flight per peer
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          const int r = rb + u * kRowStep;
+          acc[u] = r < rend ? ld_dsmem_f4(smem_u32(part + r * kPartStride + c4), 0) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         for (int p = 1; p < S; ++p) {
-          const float4 o = ld_dsmem_f4(laddr, static_cast<uint32_t>(p));
-          acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
-        }
-        const int grow = mt * kBlockM + r;
-        if (grow >= args.m_valid) continue;
-        float f[4] = {acc.x + bv[0], acc.y + bv[1], acc.z + bv[2], acc.w + bv[3]};
-        const long long ro = static_cast<long long>(grow) * args.ldo + ncol;
-        if (args.addend != nullptr) {
-          const __nv_bfloat16* ad = args.addend + ro;
-          if (col_ok && (ro & 3) == 0) {
-            const uint2 u = __ldg(reinterpret_cast<const uint2*>(ad));
-            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
-            f[0] += a0.x; f[1] += a0.y; f[2] += a1.x; f[3] += a1.y;
-          } else {
+          float4 o[kU];
 #pragma unroll
-            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) f[t] += __bfloat162float(ad[t]);
+          for (int u = 0; u < kU; ++u) {
+            const int r = rb + u * kRowStep;
+            o[u] = r < rend ? ld_dsmem_f4(smem_u32(part + r * kPartStride + c4), static_cast<uint32_t>(p))
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
           }
-        }
-        if (args.relu) {
 #pragma unroll
-          for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
+          for (int u = 0; u < kU; ++u) { acc[u].x += o[u].x; acc[u].y += o[u].y; acc[u].z += o[u].z; acc[u].w += o[u].w; }
         }
-        if (args.mask_y != nullptr) {
-          const __nv_bfloat16* my = args.mask_y + ro;
-          if (col_ok && (ro & 3) == 0) {
-            const uint2 u = __ldg(reinterpret_cast<const uint2*>(my));
-            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
-            f[0] = a0.x > 0.f ? f[0] : 0.f; f[1] = a0.y > 0.f ? f[1] : 0.f;
-            f[2] = a1.x > 0.f ? f[2] : 0.f; f[3] = a1.y > 0.f ? f[3] : 0.f;
-          } else {
+        // (3) epilogue of the kU rows
 #pragma unroll
-            for (int t = 0; t < 4; ++t)
-              if (ncol + t < args.n_valid) f[t] = __bfloat162float(my[t]) > 0.f ? f[t] : 0.f;
+        for (int u = 0; u < kU; ++u) {
+          if (!ok[u]) continue;
+          float* own = part + (rb + u * kRowStep) * kPartStride + c4;
+          float f[4] = {acc[u].x + bv[0], acc[u].y + bv[1], acc[u].z + bv[2], acc[u].w + bv[3]};
+          if (ad_p != nullptr) {
+            float a[4];
+            load4(ad_p, ro[u], uad[u], a);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) f[t] += a[t];
           }
-        }
-        if (args.out_f32 && bnm == 0) {
-          float* o = static_cast<float*>(args.out) + ro;
-          if (col_ok && (ro & 3) == 0) {
-            *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
-          } else {
+          if (args.relu) {
 #pragma unroll
-            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = f[t];
+            for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
           }
-        } else {
-          // fused BatchNorm: this is the intermediate (raw convolution output / masked gradient), stored
-          // only where a later pass needs it; the final output is written after the grid barrier
-          __nv_bfloat16* o = (bnm != 0 ? args.bn_raw : static_cast<__nv_bfloat16*>(args.out));
-          __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
-          __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
-          if (o != nullptr) {
-            o += ro;
-            if (col_ok && (ro & 3) == 0) {
-              uint2 u;
-              u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
-              *reinterpret_cast<uint2*>(o) = u;
+          if (my_p != nullptr) {
+            float m[4];
+            load4(my_p, ro[u], umy[u], m);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) f[t] = m[t] > 0.f ? f[t] : 0.f;
+          }
+          if (args.out_f32 && bnm == 0) {
+            float* o = static_cast<float*>(args.out) + ro[u];
+            if (fast) {
+              *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
             } else {
-              const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
 #pragma unroll
-              for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = hv[t];
+              for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = f[t];
             }
+          } else {
+            // fused BatchNorm: this is the intermediate (raw convolution output / masked gradient), stored
+            // only where a later pass needs it; the final output is written after the grid barrier
+            __nv_bfloat16* o = (bnm != 0 ? args.bn_raw : static_cast<__nv_bfloat16*>(args.out));
+            const __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
+            const __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
+            if (o != nullptr) store4(o, ro[u], p0, p1);
+            // statistics of exactly the values the consumer will read back
+            const float2 r0 = __bfloat1622float2(p0), r1 = __bfloat1622float2(p1);
+            f[0] = r0.x; f[1] = r0.y; f[2] = r1.x; f[3] = r1.y;
+            // Stash for the pass after the grid barrier.  In place: rows [rbeg, rend) of THIS CTA's
+            // partial tile are read by this CTA only (every peer reads its own row range of it).
+            if (bnm != 0) *reinterpret_cast<float4*>(own) = make_float4(f[0], f[1], f[2], f[3]);
           }
-          // statistics of exactly the values the consumer will read back
-          const float2 r0 = __bfloat1622float2(p0), r1 = __bfloat1622float2(p1);
-          f[0] = r0.x; f[1] = r0.y; f[2] = r1.x; f[3] = r1.y;
-          // Stash for the pass after the grid barrier.  In place: rows [rbeg, rend) of THIS CTA's
-          // partial tile are read by this CTA only (every peer reads its own row range of it).
-          if (bnm != 0) *reinterpret_cast<float4*>(own) = make_float4(f[0], f[1], f[2], f[3]);
-        }
-        if (args.bn_x != nullptr) {                     // BatchNorm-backward sums: g and g * xhat
-          float xh[4] = {0.f, 0.f, 0.f, 0.f};
-          const __nv_bfloat16* bx = args.bn_x + ro;
-          if (col_ok && (ro & 3) == 0) {
-            const uint2 u = __ldg(reinterpret_cast<const uint2*>(bx));
-            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
-            xh[0] = a0.x; xh[1] = a0.y; xh[2] = a1.x; xh[3] = a1.y;
+          if (bx_p != nullptr) {                        // BatchNorm-backward sums: g and g * xhat
+            float xh[4];
+            load4(bx_p, ro[u], ubx[u], xh);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              s1[t] += f[t];
+              s2[t] = fmaf(f[t], (xh[t] - bm[t]) * bi[t], s2[t]);
+            }
+          } else if (bnm == 1) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) { const float d = f[t] - bm[t]; s1[t] += d; s2[t] = fmaf(d, d, s2[t]); }
           } else {
 #pragma unroll
-            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) xh[t] = __bfloat162float(bx[t]);
+            for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
           }
-#pragma unroll
-          for (int t = 0; t < 4; ++t) {
-            s1[t] += f[t];
-            s2[t] = fmaf(f[t], (xh[t] - bm[t]) * bi[t], s2[t]);
-          }
-        } else if (bnm == 1) {
-#pragma unroll
-          for (int t = 0; t < 4; ++t) { const float d = f[t] - bm[t]; s1[t] += d; s2[t] = fmaf(d, d, s2[t]); }
-        } else {
-#pragma unroll
-          for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
         }
       }
       float* gstats = args.stats;
       if (bnm != 0) gstats = args.bn_sc->acc[gstate.x & 1u];
       if (gstats != nullptr) {
         // No shared-memory float atomics (they compile to compare-and-swap loops): lanes that share a
-        // column group fold with a shuffle, each warp writes its own row of partials, then 4-way sums.
+        // column group fold with a shuffle, each warp writes its own row of partials, then a 6-way sum.
         if (kGroups == 16) {
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
@@ -689,16 +726,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             s2[t] += __shfl_xor_sync(0xffffffffu, s2[t], 16);
           }
         }
-        float* wsm = st_sm + (warp - 2) * 2 * BLOCK_N;    // [4 warps][2][BLOCK_N]
+        float* wsm = st_sm + warp * 2 * BLOCK_N;          // [6 warps][2][BLOCK_N]
         if (lane < kGroups) {
 #pragma unroll
           for (int t = 0; t < 4; ++t) { wsm[c4 + t] = s1[t]; wsm[BLOCK_N + c4 + t] = s2[t]; }
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-        for (int i = et; i < 2 * BLOCK_N; i += 128) {
+        __syncthreads();
+        for (int i = et; i < 2 * BLOCK_N; i += kNumThreads) {
           const int c = i % BLOCK_N, which = i / BLOCK_N;
           const int gc = nt * BLOCK_N + c;
-          const float tot = st_sm[i] + st_sm[2 * BLOCK_N + i] + st_sm[4 * BLOCK_N + i] + st_sm[6 * BLOCK_N + i];
+          float tot = 0.f;
+#pragma unroll
+          for (int w = 0; w < kWarps; ++w) tot += st_sm[w * 2 * BLOCK_N + i];
           if (gc < args.n_valid) atomicAdd(gstats + static_cast<size_t>(which) * args.n_valid + gc, tot);
         }
       }
@@ -709,11 +748,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         const bool first_cta = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
         if (blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1) {
           float4* nxt = reinterpret_cast<float4*>(sc->acc[(gstate.x & 1u) ^ 1u]);    // the next launch's buffer
-          for (int i = et; i < 2 * kml::kBnMaxC / 4; i += 128) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int i = et; i < 2 * kml::kBnMaxC / 4; i += kNumThreads) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        __syncthreads();
         if (et == 0) kml::grid_arrive_and_wait(sc, gstate.y, ncta);
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        __syncthreads();
         if (first_cta && et == 0) {                      // everyone has arrived: publish the next launch's state
           sc->launches = gstate.x + 1u;
           sc->bar_base = gstate.y + ncta;
@@ -722,8 +761,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         const float* tot = sc->acc[gstate.x & 1u];
         const float inv_m = 1.f / static_cast<float>(args.m_valid);
         const bool writer = mt == 0 && split == 0;       // one CTA per column block records the per-channel results
-        float* co = st_sm;                               // [3][BLOCK_N] per-column coefficients
-        for (int c = et; c < BLOCK_N; c += 128) {
+        for (int c = et; c < BLOCK_N; c += kNumThreads) {
           const int gc = nt * BLOCK_N + c;
           float c0 = 0.f, c1 = 0.f, c2 = 0.f;
           if (gc < args.n_valid) {
@@ -733,8 +771,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               const float mean = pv_sm[c] + d;
               const float var = fmaxf(t2 * inv_m - d * d, 0.f);
               const float invstd = rsqrtf(var + args.bn_eps);
-              c0 = args.bn_gamma[gc] * invstd;
-              c1 = args.bn_beta[gc] - mean * c0;
+              c0 = co[c] * invstd;                       // gamma * invstd
+              c1 = co[BLOCK_N + c] - mean * c0;          // beta - mean * scale
               if (writer) {
                 args.bn_save_mean[gc] = mean;
                 args.bn_save_invstd[gc] = invstd;
@@ -746,7 +784,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 }
               }
             } else {
-              c0 = args.bn_gamma[gc] * args.bn_invstd[gc];
+              c0 = co[c];                                // gamma * invstd
               c1 = t1 * inv_m;
               c2 = t2 * inv_m;
               if (writer) { args.bn_dbeta[gc] = t1; args.bn_dgamma[gc] = t2; }
@@ -754,62 +792,51 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           }
           co[c] = c0; co[BLOCK_N + c] = c1; co[2 * BLOCK_N + c] = c2;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        __syncthreads();
         float k0[4], k1[4], k2[4];
 #pragma unroll
         for (int t = 0; t < 4; ++t) { k0[t] = co[c4 + t]; k1[t] = co[BLOCK_N + c4 + t]; k2[t] = co[2 * BLOCK_N + c4 + t]; }
-        for (int r = rbeg + et / kGroups; r < rend; r += 128 / kGroups) {
-          const int grow = mt * kBlockM + r;
-          if (grow >= args.m_valid) continue;
-          const float4 v = *reinterpret_cast<const float4*>(part + r * kPartStride + c4);
-          float f[4] = {v.x, v.y, v.z, v.w};
-          const long long ro = static_cast<long long>(grow) * args.ldo + ncol;
-          const bool vec = col_ok && (ro & 3) == 0;
-          if (bnm == 1) {
+        const __nv_bfloat16* aux_p = bnm == 1 ? args.bn_res : args.bn_x;     // the one global operand of this pass
+        for (int rb = rbeg + et / kGroups; rb < rend; rb += kU * kRowStep) {
+          long long ro[kU];
+          bool ok[kU];
+          uint2 ua[kU];
+          float4 v[kU];
 #pragma unroll
-            for (int t = 0; t < 4; ++t) f[t] = fmaf(f[t], k0[t], k1[t]);
-            if (args.bn_res != nullptr) {
-              const __nv_bfloat16* rs = args.bn_res + ro;
-              if (vec) {
-                const uint2 u = __ldg(reinterpret_cast<const uint2*>(rs));
-                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-                const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
-                f[0] += a0.x; f[1] += a0.y; f[2] += a1.x; f[3] += a1.y;
-              } else {
-#pragma unroll
-                for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) f[t] += __bfloat162float(rs[t]);
-              }
-            }
-            if (args.bn_relu) {
-#pragma unroll
-              for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
-            }
-          } else {
-            float xh[4] = {0.f, 0.f, 0.f, 0.f};
-            const __nv_bfloat16* bx = args.bn_x + ro;
-            if (vec) {
-              const uint2 u = __ldg(reinterpret_cast<const uint2*>(bx));
-              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-              const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
-              xh[0] = a0.x; xh[1] = a0.y; xh[2] = a1.x; xh[3] = a1.y;
-            } else {
-#pragma unroll
-              for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) xh[t] = __bfloat162float(bx[t]);
-            }
-#pragma unroll
-            for (int t = 0; t < 4; ++t) f[t] = k0[t] * (f[t] - k1[t] - (xh[t] - bm[t]) * bi[t] * k2[t]);
+          for (int u = 0; u < kU; ++u) {
+            const int r = rb + u * kRowStep;
+            const int grow = mt * kBlockM + r;
+            ok[u] = r < rend && grow < args.m_valid;
+            ro[u] = static_cast<long long>(grow) * args.ldo + ncol;
+            ua[u] = make_uint2(0u, 0u);
+            if (ok[u] && fast && aux_p != nullptr) ua[u] = __ldg(reinterpret_cast<const uint2*>(aux_p + ro[u]));
+            if (ok[u]) v[u] = *reinterpret_cast<const float4*>(part + r * kPartStride + c4);
           }
-          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + ro;
-          __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
-          __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
-          if (vec) {
-            uint2 u;
-            u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
-            *reinterpret_cast<uint2*>(o) = u;
-          } else {
-            const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
 #pragma unroll
-            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = hv[t];
+          for (int u = 0; u < kU; ++u) {
+            if (!ok[u]) continue;
+            float f[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            if (bnm == 1) {
+#pragma unroll
+              for (int t = 0; t < 4; ++t) f[t] = fmaf(f[t], k0[t], k1[t]);
+              if (aux_p != nullptr) {
+                float a[4];
+                load4(aux_p, ro[u], ua[u], a);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) f[t] += a[t];
+              }
+              if (args.bn_relu) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
+              }
+            } else {
+              float xh[4];
+              load4(aux_p, ro[u], ua[u], xh);
+#pragma unroll
+              for (int t = 0; t < 4; ++t) f[t] = k0[t] * (f[t] - k1[t] - (xh[t] - bm[t]) * bi[t] * k2[t]);
+            }
+            store4(static_cast<__nv_bfloat16*>(args.out), ro[u], __floats2bfloat162_rn(f[0], f[1]),
+                   __floats2bfloat162_rn(f[2], f[3]));
           }
         }
       }
