@@ -101,10 +101,36 @@ def cmd_train(args) -> int:
             if err:
                 print(f"job failed: {err}", file=sys.stderr)
                 return 1
+            print(c.v1().histories().get(job_id).to_json())
         else:
-            while any(t.job.id == job_id for t in c.v1().tasks().list()):
-                time.sleep(1.0)
-        print(c.v1().histories().get(job_id).to_json())
+            # The task appears in `task list` only once the scheduler has handed it to the parameter
+            # server (its queue is polled every 10 ms), so "not listed" right after submission does not
+            # mean "finished": the history record is what marks the end.
+            seen, deadline, hist = False, time.monotonic() + 120.0, None
+            while hist is None:
+                if any(t.job.id == job_id for t in c.v1().tasks().list()):
+                    seen = True
+                else:
+                    try:
+                        hist = c.v1().histories().get(job_id)
+                        break
+                    except KubeMLException as e:
+                        if e.status_code != 404:
+                            raise
+                        if seen:
+                            time.sleep(0.2)         # the job may be between de-registration and its history write
+                            try:
+                                hist = c.v1().histories().get(job_id)
+                                break
+                            except KubeMLException:
+                                print(f"job {job_id} ended without a history record (see `kubeml logs --id {job_id}`)",
+                                      file=sys.stderr)
+                                return 1
+                        if time.monotonic() > deadline:
+                            print(f"job {job_id} never started", file=sys.stderr)
+                            return 1
+                time.sleep(0.1 if not seen else 0.5)
+            print(hist.to_json())
     return 0
 
 

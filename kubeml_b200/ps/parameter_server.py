@@ -32,6 +32,7 @@ class ParameterServer:
         self._threads: Dict[str, threading.Thread] = {}
         self._finished: Dict[str, Optional[str]] = {}    # job id -> error text (None = ok)
         self._mu = threading.Lock()
+        self._log_handlers: Dict[str, logging.Handler] = {}
 
     # ---- scheduler-facing ----------------------------------------------------------------
     def start_task(self, task: TrainTask) -> None:
@@ -40,6 +41,7 @@ class ParameterServer:
             if task.job.id in self._index:
                 raise KubeMLException(f"task {task.job.id} already exists", 400)
             self._index[task.job.id] = task
+        self._open_job_log(task.job.id)
         job = self.job_factory(task, self)
         task.job.handle = job
         self.metrics.task_started("train")
@@ -47,6 +49,35 @@ class ParameterServer:
         with self._mu:
             self._threads[task.job.id] = t
             t.start()
+
+    # ---- per-job log files: what `kubeml logs --id <job> [-f]` reads -------------------------------
+    # The reference's `logs` verb is `kubectl logs job-<id>` (ml/pkg/kubeml-cli/cmd/log.go:28-65): the
+    # job pod's stdout.  A job here is a thread, so its logger `kubeml.job.<id>` (the train job, and the
+    # workers' `kubeml.job.<id>.worker*` children) gets a file handler for the lifetime of the job.
+    def _open_job_log(self, job_id: str) -> None:
+        import os
+        from ..api import const
+        log_dir = os.path.join(const.home(), "logs")
+        try:
+            os.makedirs(log_dir, exist_ok=True)
+            h = logging.FileHandler(os.path.join(log_dir, f"job-{job_id}.log"), delay=False)
+        except OSError as e:
+            self.log.warning("cannot open the log file of job %s: %s", job_id, e)
+            return
+        h.setFormatter(logging.Formatter("%(asctime)s %(levelname)s %(name)s: %(message)s"))
+        lg = logging.getLogger(f"kubeml.job.{job_id}")
+        if lg.level == logging.NOTSET or lg.level > logging.INFO:
+            lg.setLevel(logging.INFO)
+        lg.addHandler(h)
+        with self._mu:
+            self._log_handlers[job_id] = h
+
+    def _close_job_log(self, job_id: str) -> None:
+        with self._mu:
+            h = self._log_handlers.pop(job_id, None)
+        if h is not None:
+            logging.getLogger(f"kubeml.job.{job_id}").removeHandler(h)
+            h.close()
 
     def update_task(self, task: TrainTask) -> None:
         """POST /update/{jobId} (api.go:72-119): relay the new parallelism to the job."""
@@ -76,6 +107,8 @@ class ParameterServer:
             self._finished[job_id] = None if err is None else str(err)
         if err is not None:
             self.log.error("job %s exited with error: %s", job_id, err)
+            logging.getLogger(f"kubeml.job.{job_id}").error("job exited with error: %s", err)
+        self._close_job_log(job_id)
 
     # ---- controller-facing ---------------------------------------------------------------
     def list_tasks(self) -> List[TrainTask]:

@@ -97,7 +97,14 @@ def test_controller_rest_and_cli_end_to_end(served_cluster, tmp_path, capsys, mo
     assert cli(["history", "list"]) == 0 and job_id in capsys.readouterr().out
     assert cli(["history", "get", "--network", job_id]) == 0          # the harness' drifted flag name
     assert json.loads(capsys.readouterr().out)["id"] == job_id
+    # per-job log file written by the parameter server, read by `kubeml logs` (cmd/log.go:28-65)
+    assert cli(["logs", "--id", job_id]) == 0
+    logged = capsys.readouterr().out
+    assert "Starting train job" in logged and "Training finished" in logged
+    assert cli(["logs", "--id", "deadbeef"]) == 1
+    capsys.readouterr()
     assert cli(["task", "list", "--short"]) == 0
+    assert cli(["task", "prune"]) == 0 and "Deleted 1 finished task logs" in capsys.readouterr().out
     assert cli(["function", "list"]) == 0 and "function_lenet" in capsys.readouterr().out
     assert cli(["history", "delete", "--id", job_id]) == 0
     assert http_call("GET", url + "/history") == []
