@@ -56,29 +56,29 @@ __device__ __forceinline__ void mc_st_f4(float4* p, const float4& v) {
                ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-// Cross-rank barrier executed by one thread of the grid.  slot = phase*KML_MAX_RANKS + writer.
-__device__ void rank_barrier(const kml_merge_params& p, int phase, uint32_t gen) {
-  __threadfence_system();
-#pragma unroll
-  for (int r = 0; r < KML_MAX_RANKS; ++r)
-    if ((p.participants >> r) & 1u) st_release_sys(p.flags[r] + phase * KML_MAX_RANKS + p.my_rank, gen);
-  const unsigned long long limit = p.timeout_cycles ? p.timeout_cycles : 8000000000ull;
-  const long long t0 = clock64();
-#pragma unroll
-  for (int r = 0; r < KML_MAX_RANKS; ++r) {
-    if (!((p.participants >> r) & 1u)) continue;
-    const uint32_t* f = p.flags[p.my_rank] + phase * KML_MAX_RANKS + r;
-    // generations only grow, so ">=" tolerates a fast peer that already moved on
-    while (static_cast<int32_t>(ld_acquire_sys(f) - gen) < 0) {
-      if (static_cast<unsigned long long>(clock64() - t0) > limit) {
-        if (p.status) atomicOr(p.status, 1 << r);         // bit r: rank r did not arrive
-        break;
-      }
-      __nanosleep(64);
-    }
-  }
-  __threadfence_system();
-}
+// ---------------------------------------------------------------------------------------------------
+// Signal pad of a rank (64 uint32 words inside its arena, mapped by every peer).
+//   ready[r]      generation for which rank r's replica is final       (written by r into every pad)
+//   done[r]       generation for which rank r has written its slice    (written by r into every pad)
+//   count..       local grid barrier of this GPU (monotonic counters + their values at launch)
+//   go_gen/mask   decision of this GPU's CTA 0 for a generation: the effective participant mask, or abort
+//   fin_*         CTAs of this GPU that finished writing (the last one publishes done[])
+//   dead_from[r]  != 0: rank r takes no part from that generation on (written by r itself when its
+//                 function fails - `kml_merge_tombstone` - or by a survivor that timed out on it)
+// Generations only grow within a job; all comparisons are signed differences.
+// ---------------------------------------------------------------------------------------------------
+struct MergePad {
+  uint32_t ready[KML_MAX_RANKS];
+  uint32_t done[KML_MAX_RANKS];
+  uint32_t count, release, count_base, release_base;
+  uint32_t go_gen, go_mask, fin_count, fin_base;
+  uint32_t dead_from[KML_MAX_RANKS];
+};
+static_assert(sizeof(MergePad) <= 64 * sizeof(uint32_t), "signal pad is 64 words");
+
+constexpr uint32_t kGoAbort = 0x80000000u;
+
+__device__ __forceinline__ bool reached(uint32_t flag, uint32_t gen) { return static_cast<int32_t>(flag - gen) >= 0; }
 
 // Reduce [begin, end) of NP source replicas (compact list, ascending rank) and store the average
 // to ND destinations.  U elements per thread are loaded before any is used: NP*U 16-byte loads in
@@ -115,66 +115,74 @@ __device__ __forceinline__ void reduce_range(const float4* const* src, float4* c
   }
 }
 
-// Words 16.. of a rank's signal pad: state of the intra-GPU barrier of the regular-launch variant.
-struct LocalBarrier {
-  unsigned count;         // CTA arrivals, monotonically increasing across launches
-  unsigned release;       // barriers completed, monotonically increasing
-  unsigned count_base;    // value of `count` when the current launch started
-  unsigned release_base;  // value of `release` when the current launch started
-};
-
-template <bool kMcast, bool kCoop>
+// One kernel per rank and sync round.  Structure (multi-rank case):
+//   phase 0  (optional) the round's last local SGD step on the own replica        [all CTAs]
+//            local grid barrier (only if phase 0 ran: the stream already orders everything else)
+//   signal   CTA 0 publishes ready[me] = gen in every pad, waits until every participant is ready
+//            (bounded), reads the dead table, decides the EFFECTIVE participant mask (or abort) and
+//            publishes it in the own pad; the other CTAs poll that one local word.  One decision
+//            point per GPU: either every CTA merges with the same mask or none touches anything.
+//   phase 1  the rank owns 1/P' of the buffer: loads that slice from every effective participant
+//            (peer loads, or one multimem.ld_reduce), averages, stores it into every replica
+//   done     the last CTA to finish publishes done[me] = gen in every pad (no grid barrier)
+//   phase 3  bf16 copy of the merged parameters, slice by slice as the owners' done flags arrive -
+//            the wait for the slowest peer overlaps the conversion of the slices already there
+// A survivor never blocks on a failed rank: a function that fails marks itself dead first
+// (kml_merge_tombstone), a rank that just disappears costs one bounded wait, after which the kernel
+// returns WITHOUT touching any replica and reports the missing ranks in `status`.
+template <bool kCoop>
 __global__ void __launch_bounds__(kThreads)
 kavg_merge_kernel(const kml_merge_params p) {
   __shared__ const float4* s_src[KML_MAX_RANKS];
   __shared__ float4* s_dst[KML_MAX_RANKS];
-  __shared__ unsigned s_cbase, s_rbase;
-  // Two ways to synchronise the grid with itself and with the other ranks:
-  //  kCoop  cooperative launch: grid.sync / flag exchange by one thread / grid.sync (used when the
-  //         caller provides no signal pad, i.e. the single-GPU emulation in the tests);
-  //  !kCoop regular launch (a cooperative launch costs several microseconds on this part): CTAs
-  //         arrive on a counter in the rank's own signal pad, the last one to arrive performs the
-  //         cross-rank flag exchange on behalf of the GPU and then releases the others.  The grid
-  //         is sized to be co-resident, so the spin cannot deadlock.
-  LocalBarrier* lb = kCoop ? nullptr : reinterpret_cast<LocalBarrier*>(p.flags[p.my_rank] + 2 * KML_MAX_RANKS);
-  if (!kCoop && threadIdx.x == 0) {
-    s_cbase = *reinterpret_cast<volatile unsigned*>(&lb->count_base);
-    s_rbase = *reinterpret_cast<volatile unsigned*>(&lb->release_base);
+  __shared__ unsigned s_cbase, s_rbase, s_fbase, s_go;
+  const bool sync_ranks = p.generation != 0;
+  const uint32_t gen = p.generation;
+  MergePad* pad = (kCoop && !sync_ranks) ? nullptr : reinterpret_cast<MergePad*>(p.flags[p.my_rank]);
+  const unsigned long long limit = p.timeout_cycles ? p.timeout_cycles : 8000000000ull;
+  // A merge of this epoch already failed: later ones queued behind it return at once (the host deals
+  // with the failure at its next synchronisation point).
+  if (sync_ranks && p.status != nullptr && *reinterpret_cast<volatile int*>(p.status) != 0) return;
+  if (threadIdx.x == 0 && pad != nullptr) {
+    s_cbase = *reinterpret_cast<volatile unsigned*>(&pad->count_base);
+    s_rbase = *reinterpret_cast<volatile unsigned*>(&pad->release_base);
+    s_fbase = *reinterpret_cast<volatile unsigned*>(&pad->fin_base);
   }
   unsigned nbar = 0;
-  auto full_barrier = [&](int rank_phase /* -1: this GPU only */) {
+  auto local_barrier = [&]() {      // every CTA of this GPU
     ++nbar;
     if constexpr (kCoop) {
-      cg::grid_group grid = cg::this_grid();
-      grid.sync();
-      if (rank_phase >= 0) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) rank_barrier(p, rank_phase, p.generation);
-        grid.sync();
-      }
+      cg::this_grid().sync();
     } else {
       __syncthreads();
       if (threadIdx.x == 0) {
-        __threadfence_system();
-        const unsigned arrived = atomicAdd(&lb->count, 1u) + 1u - s_cbase;
+        __threadfence();
+        const unsigned arrived = atomicAdd(&pad->count, 1u) + 1u - s_cbase;
         if (arrived == nbar * gridDim.x) {
-          if (rank_phase >= 0) rank_barrier(p, rank_phase, p.generation);
-          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&lb->release), "r"(s_rbase + nbar) : "memory");
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&pad->release), "r"(s_rbase + nbar) : "memory");
         } else {
           unsigned v;
+          const long long t0 = clock64();
           do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&lb->release) : "memory");
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&pad->release) : "memory");
+            if (static_cast<unsigned long long>(clock64() - t0) > limit) { asm volatile("trap;"); }
           } while (v - s_rbase < nbar);
         }
-        __threadfence_system();
+        __threadfence();
       }
       __syncthreads();
+    }
+  };
+  auto finish_bases = [&]() {       // leave the monotonic counters consistent for the next launch
+    if (!kCoop && nbar && blockIdx.x == 0 && threadIdx.x == 0) {
+      pad->count_base = s_cbase + nbar * gridDim.x;
+      pad->release_base = s_rbase + nbar;
     }
   };
   const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
   const size_t n4 = p.n_f32 / 4;
   const size_t nsgd4 = p.n_sgd / 4;
-  const bool sync_ranks = p.generation != 0;
 
   // ---- phase 0: fused last local step on the own replica --------------------------------------
   if (p.fuse_sgd) {
@@ -196,28 +204,68 @@ kavg_merge_kernel(const kml_merge_params p) {
       wv.z = fmaf(-p.lr, d.z, wv.z); wv.w = fmaf(-p.lr, d.w, wv.w);
       w[i] = wv;
     }
+    local_barrier();                // the whole replica is final before anyone is told so
   }
 
-  if (sync_ranks) full_barrier(0);
-  else if (p.fuse_sgd) full_barrier(-1);
-
-  // A peer never arrived (rank_barrier set `status` before the grid was released): the replicas are
-  // not all final, so averaging them would publish a corrupt model into every rank and throw away the
-  // optimizer state.  Touch nothing; the host sees `status`, drops the missing rank from the
-  // participant mask and relaunches (parallel/device_sync.py), as the reference's merger divides by
-  // the notifications it actually received (ml/pkg/train/job.go:383-398).
-  if (sync_ranks && p.status != nullptr && *reinterpret_cast<volatile int*>(p.status) != 0) {
-    if (!kCoop && blockIdx.x == 0 && threadIdx.x == 0) {
-      // every CTA has arrived `nbar` times; leave the local barrier state consistent for the relaunch
-      lb->count_base = s_cbase + nbar * gridDim.x;
-      lb->release_base = s_rbase + nbar;
+  // ---- signal / decide ---------------------------------------------------------------------------
+  uint32_t eff = p.participants;
+  if (sync_ranks) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      __threadfence_system();
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r)
+        if ((p.participants >> r) & 1u)
+          st_release_sys(&reinterpret_cast<MergePad*>(p.flags[r])->ready[p.my_rank], gen);
+      uint32_t missing = 0;
+      const long long t0 = clock64();
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r) {
+        if (!((p.participants >> r) & 1u)) continue;
+        while (!reached(ld_acquire_sys(&pad->ready[r]), gen)) {
+          if (static_cast<unsigned long long>(clock64() - t0) > limit) { missing |= 1u << r; break; }
+          __nanosleep(32);
+        }
+      }
+      uint32_t dead = 0;
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r) {
+        const uint32_t d = ld_acquire_sys(&pad->dead_from[r]);
+        if (d != 0 && reached(gen, d)) dead |= 1u << r;
+      }
+      uint32_t decision = p.participants & ~dead;
+      if ((dead >> p.my_rank) & 1u) {                   // the others gave up on this rank: it must not write
+        if (p.status) atomicOr(p.status, KML_MERGE_EVICTED);
+        decision = kGoAbort;
+      } else if (missing & ~dead) {
+        if (p.status) atomicOr(p.status, static_cast<int>(missing & ~dead));
+        decision = kGoAbort;
+      }
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(&pad->go_mask) = decision;
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&pad->go_gen), "r"(gen) : "memory");
     }
-    return;
+    if (threadIdx.x == 0) {
+      unsigned v;
+      const long long t0 = clock64();
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&pad->go_gen) : "memory");
+        if (static_cast<unsigned long long>(clock64() - t0) > 2 * limit + 4000000000ull) { asm volatile("trap;"); }
+      } while (v != gen);
+      s_go = *reinterpret_cast<volatile uint32_t*>(&pad->go_mask);
+      __threadfence_system();
+    }
+    __syncthreads();
+    eff = s_go;
+    if (eff & kGoAbort) {           // nothing was touched (apart from this rank's own last local step)
+      finish_bases();
+      return;
+    }
   }
 
   // ---- phase 1: reduce my slice, write everyone -----------------------------------------------
-  int nparts = __popc(p.participants);
-  int pos = __popc(p.participants & ((1u << p.my_rank) - 1u));
+  const int nparts = __popc(eff);
+  const int pos = __popc(eff & ((1u << p.my_rank) - 1u));
+  const uint32_t wmask = sync_ranks ? ((p.write_mask | eff) & ~(p.participants & ~eff)) : p.write_mask;
   size_t begin = 0, end = n4;
   if (sync_ranks) {
     begin = n4 * pos / nparts;
@@ -225,7 +273,7 @@ kavg_merge_kernel(const kml_merge_params p) {
   }
   const float inv = 1.0f / static_cast<float>(nparts);
 
-  if constexpr (kMcast) {
+  if (p.mcast != nullptr && sync_ranks && eff == p.participants) {
     float4* mc = reinterpret_cast<float4*>(p.mcast);
     constexpr int U = 4;                       // loads in flight per thread: NVLink round trips are ~2 us
     size_t i = begin + tid;
@@ -246,15 +294,14 @@ kavg_merge_kernel(const kml_merge_params p) {
     }
   } else {
     const float fn = static_cast<float>(nparts);
-    int nd = 0;
     if (threadIdx.x == 0) {
       int ns = 0, ndl = 0;
       for (int r = 0; r < KML_MAX_RANKS; ++r) {
-        if ((p.participants >> r) & 1u) s_src[ns++] = reinterpret_cast<const float4*>(p.replica[r]);
-        if ((p.write_mask >> r) & 1u) s_dst[ndl++] = reinterpret_cast<float4*>(p.replica[r]);
+        if ((eff >> r) & 1u) s_src[ns++] = reinterpret_cast<const float4*>(p.replica[r]);
+        if ((wmask >> r) & 1u) s_dst[ndl++] = reinterpret_cast<float4*>(p.replica[r]);
       }
     }
-    nd = __popc(p.write_mask);
+    const int nd = __popc(wmask);
     __syncthreads();
     switch (nparts) {
       case 1: reduce_range<1, 8>(s_src, s_dst, nd, begin, end, tid, nthreads, fn); break;
@@ -274,11 +321,11 @@ kavg_merge_kernel(const kml_merge_params p) {
       long long s = 0;
 #pragma unroll
       for (int r = 0; r < KML_MAX_RANKS; ++r)
-        if ((p.participants >> r) & 1u) s += p.ireplica[r][i];
+        if ((eff >> r) & 1u) s += p.ireplica[r][i];
       s = s / static_cast<long long>(nparts);  // C++ '/' truncates toward zero like Go
 #pragma unroll
       for (int r = 0; r < KML_MAX_RANKS; ++r)
-        if ((p.write_mask >> r) & 1u) p.ireplica[r][i] = s;
+        if ((wmask >> r) & 1u) p.ireplica[r][i] = s;
     }
   }
 
@@ -289,15 +336,12 @@ kavg_merge_kernel(const kml_merge_params p) {
     for (size_t i = tid; i < nsgd4; i += nthreads) __stcs(m + i, z);
   }
 
-  if (sync_ranks) full_barrier(1);
-  else if (p.w_bf16) full_barrier(-1);
-
-  // ---- phase 3: refresh the local bf16 tensor-core copy of the merged parameters ---------------
-  if (p.w_bf16) {
-    const float4* w = reinterpret_cast<const float4*>(p.replica[p.my_rank]);
-    uint2* wb = reinterpret_cast<uint2*>(p.w_bf16);
-    for (size_t i = tid; i < nsgd4; i += nthreads) {
-      const float4 v = ld_cg_f4(w + i);
+  uint2* wb = reinterpret_cast<uint2*>(p.w_bf16);
+  const float4* wme = reinterpret_cast<const float4*>(p.replica[p.my_rank]);
+  auto to_bf16 = [&](size_t lo, size_t hi) {   // this CTA's share of [lo, hi) of the merged parameters
+    if (hi > nsgd4) hi = nsgd4;
+    for (size_t i = lo + tid; i < hi; i += nthreads) {
+      const float4 v = ld_cg_f4(wme + i);
       __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y);
       __nv_bfloat162 b = __floats2bfloat162_rn(v.z, v.w);
       uint2 r;
@@ -305,15 +349,91 @@ kavg_merge_kernel(const kml_merge_params p) {
       r.y = *reinterpret_cast<uint32_t*>(&b);
       wb[i] = r;
     }
+  };
+
+  if (!sync_ranks) {
+    if (wb != nullptr) { local_barrier(); to_bf16(0, nsgd4); }
+    finish_bases();
+    return;
   }
-  if (!kCoop && nbar && blockIdx.x == 0 && threadIdx.x == 0) {
-    // every CTA read the bases before its first arrival and everyone has arrived nbar times
-    lb->count_base = s_cbase + nbar * gridDim.x;
-    lb->release_base = s_rbase + nbar;
+
+  // ---- done: the last CTA of this GPU to get here tells every rank that slice `pos` has landed --------
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned fin = atomicAdd(&pad->fin_count, 1u) + 1u - s_fbase;
+    if (fin == gridDim.x) {
+      __threadfence_system();
+#pragma unroll
+      for (int r = 0; r < KML_MAX_RANKS; ++r)
+        if ((eff >> r) & 1u) st_release_sys(&reinterpret_cast<MergePad*>(p.flags[r])->done[p.my_rank], gen);
+      pad->fin_base = s_fbase + gridDim.x;              // every CTA of this launch has read it
+    }
+  }
+
+  // ---- phase 3: bf16 copy, slice by slice as their owners finish (own slice first) -----------------
+  // Also the exit condition: when this kernel ends every slice has landed in this replica, and every peer
+  // has finished reading this replica (it published done[] after its reads), so the next local step may
+  // write it.
+  {
+    int idx = 0;
+    for (int k = 0; k < nparts; ++k) {
+      const int j = (pos + k) % nparts;                 // position of the owner within eff
+      int owner = 0;
+      for (int r = 0, c = 0; r < KML_MAX_RANKS; ++r)
+        if ((eff >> r) & 1u) { if (c == j) owner = r; ++c; }
+      if (threadIdx.x == 0) {
+        const long long t0 = clock64();
+        while (!reached(ld_acquire_sys(&pad->done[owner]), gen)) {
+          if (static_cast<unsigned long long>(clock64() - t0) > limit) {
+            if (p.status) atomicOr(p.status, KML_MERGE_LATE | (1 << owner));     // a peer died mid-merge
+            break;
+          }
+          __nanosleep(32);
+        }
+      }
+      __syncthreads();
+      if (wb != nullptr) to_bf16(n4 * j / nparts, n4 * (j + 1) / nparts);
+      ++idx;
+    }
+    (void)idx;
+  }
+  finish_bases();
+}
+
+// A rank that fails in the middle of an epoch marks itself dead for the rest of it: dead_from[me] =
+// `from_gen` in every pad FIRST, then ready/done = `tombstone` (a generation past every round of the
+// epoch), so no survivor ever waits for it and every survivor that gets past its flag sees it dead.
+__global__ void merge_tombstone_kernel(const kml_merge_params p, uint32_t from_gen, uint32_t tombstone) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  __threadfence_system();
+  for (int r = 0; r < KML_MAX_RANKS; ++r) {
+    if (p.flags[r] == nullptr) continue;
+    MergePad* q = reinterpret_cast<MergePad*>(p.flags[r]);
+    st_release_sys(&q->dead_from[p.my_rank], from_gen);
+    __threadfence_system();
+    if (tombstone != 0) {
+      st_release_sys(&q->ready[p.my_rank], tombstone);
+      st_release_sys(&q->done[p.my_rank], tombstone);
+    }
   }
 }
 
 }  // namespace
+
+// Marks rank `who` dead from generation `from_gen` on in the pads listed in p->flags (all of them when the
+// failing rank calls it for itself, only the caller's own when a survivor records a rank that timed out)
+// and raises that rank's flags to `tombstone`; from_gen == 0 clears the mark (a rank re-joining).
+extern "C" int kml_merge_mark_dead(const kml_merge_params* pp, int who, uint32_t from_gen, uint32_t tombstone,
+                                   void* stream) {
+  KML_CHECK(pp != nullptr && who >= 0 && who < KML_MAX_RANKS, "kml_merge_mark_dead: bad arguments");
+  kml_merge_params p = *pp;
+  p.my_rank = who;
+  merge_tombstone_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(p, from_gen, tombstone);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
 
 extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
   KML_CHECK(pp != nullptr, "kml_kavg_merge: null params");
@@ -333,22 +453,15 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
   }
   if (p.fuse_sgd) KML_CHECK(p.grad != nullptr, "fuse_sgd set without grad");
   KML_CHECK(p.n_sgd % 4 == 0 && p.n_sgd <= p.n_f32, "n_sgd (%zu) must be a multiple of 4 and <= n_f32", p.n_sgd);
-  const bool use_mc = p.mcast != nullptr && p.generation != 0;
+  if (p.generation == 0) p.mcast = nullptr;
 
-  int dev = 0;
-  KML_CUDA(cudaGetDevice(&dev));
-  static int force_coop = -1;
-  if (force_coop < 0) {
-    // measured on 2xB200: with ~300 CTAs the counter/spin barrier is slower than grid.sync
-    // (LeNet-size merge 34 us vs 23 us), so the cooperative variant stays the default
-    const char* e = getenv("KUBEML_MERGE_COOP");
-    force_coop = (e && e[0] == '0') ? 0 : 1;
-  }
-  const bool coop = force_coop || p.flags[p.my_rank] == nullptr;
-  auto kernel = coop ? (use_mc ? kavg_merge_kernel<true, true> : kavg_merge_kernel<false, true>)
-                     : (use_mc ? kavg_merge_kernel<true, false> : kavg_merge_kernel<false, false>);
+  // Cooperative launch only for the single-GPU emulation without a signal pad (tests); every real merge is
+  // a regular launch whose grid is sized to be co-resident (its CTAs wait for one another on counters).
+  const bool coop = p.flags[p.my_rank] == nullptr;
+  KML_CHECK(!(coop && p.generation != 0), "kml_kavg_merge: a multi-rank merge needs the signal pads");
+  auto kernel = coop ? kavg_merge_kernel<true> : kavg_merge_kernel<false>;
   // launch shape: tunable for experiments (KUBEML_MERGE_THREADS in {128,256,512},
-  // KUBEML_MERGE_CTAS_PER_SM); the grid must stay co-resident (cooperative launch checks it)
+  // KUBEML_MERGE_CTAS_PER_SM); the grid must stay co-resident
   static int threads = 0, ctas_per_sm = 0;
   if (threads == 0) {
     const char* e = getenv("KUBEML_MERGE_THREADS");
@@ -358,8 +471,8 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
     ctas_per_sm = c ? atoi(c) : 2;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
-  static int occ[4] = {0, 0, 0, 0};
-  const int vi = (use_mc ? 1 : 0) + (coop ? 2 : 0);
+  static int occ[2] = {0, 0};
+  const int vi = coop ? 1 : 0;
   if (occ[vi] == 0) {
     int o = 0;
     KML_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, threads, 0));

@@ -36,4 +36,5 @@ const char* kml_last_error(void) { return kml::g_err; }
 int kml_version(void) { return 100; }
 unsigned long long kml_launch_count(void) { return kml::g_launches.load(); }
 void kml_reset_launch_count(void) { kml::g_launches.store(0); }
+int kml_num_sms(void) { return kml::num_sms(); }
 }

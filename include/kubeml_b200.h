@@ -25,6 +25,9 @@ int kml_version(void);
 /* Number of kernels this library has launched in the calling process (bench "gpu_launches"). */
 unsigned long long kml_launch_count(void);
 void kml_reset_launch_count(void);
+/* Streaming multiprocessors of the current device (148 on B200): the number every split / tile plan of the
+ * Python side is sized against. */
+int kml_num_sms(void);
 
 /* ------------------------------------------------------------------------------------------------
  * Weight arena: device memory allocated through the CUDA VMM API so that it can be exported to the
@@ -91,6 +94,15 @@ typedef struct {
                                          rank r that did not arrive, and the kernel returns without
                                          touching any replica or optimizer state                  */
 } kml_merge_params;
+
+/* Bits of *status beyond the per-rank "did not arrive" bits 0..7. */
+#define KML_MERGE_EVICTED 0x40000000   /* the other ranks declared THIS rank dead: it did not merge   */
+#define KML_MERGE_LATE    0x20000000   /* a peer vanished after the merge had started (bits 0..7: who) */
+/* Failure handling of the device merge (the reference divides by the notifications it received and lets
+ * an epoch stand if one function answered, ml/pkg/train/job.go:383-398, train/util.go:144-166):
+ * marks rank `who` dead from generation `from_gen` on in every pad listed in p->flags and raises its
+ * flags to `tombstone` so that nobody waits for it; from_gen = 0 clears the mark (the rank re-joins). */
+int kml_merge_mark_dead(const kml_merge_params* p, int who, uint32_t from_gen, uint32_t tombstone, void* stream);
 
 /* Launches the merge on `stream` of the current device.  With generation == 0 no cross-rank
  * barrier is executed and the calling rank reduces the whole buffer (single-GPU emulation). */

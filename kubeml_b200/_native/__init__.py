@@ -49,6 +49,10 @@ class MergeParams(Structure):
     ]
 
 
+MERGE_EVICTED = 0x40000000      # KML_MERGE_EVICTED / KML_MERGE_LATE of include/kubeml_b200.h
+MERGE_LATE = 0x20000000
+
+
 class BnFuse(Structure):
     """kml_bn_fuse (include/kubeml_b200.h): a BatchNorm finished inside a cluster-mode GEMM launch."""
     _fields_ = [("mode", c_int), ("scratch", c_void_p), ("gamma", c_void_p), ("beta", c_void_p),
@@ -75,6 +79,7 @@ def _declare(lib) -> None:
     sig("kml_version", c_int)
     sig("kml_launch_count", c_ulonglong)
     sig("kml_reset_launch_count", None)
+    sig("kml_num_sms", c_int)
     # arena
     sig("kml_arena_create", c_int, c_int, c_size_t, c_int, POINTER(c_void_p))
     sig("kml_arena_destroy", c_int, c_void_p)
@@ -93,6 +98,7 @@ def _declare(lib) -> None:
     # merge / optim / loss
     sig("kml_kavg_merge", c_int, POINTER(MergeParams), c_void_p)
     sig("kml_gemm_max_coresident", c_int, c_int, c_int, c_int, c_int)
+    sig("kml_merge_mark_dead", c_int, c_void_p, c_int, c_uint32, c_uint32, c_void_p)
     sig("kml_sgd_step", c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float,
         c_int, c_void_p, c_void_p)
     sig("kml_adam_step", c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float,

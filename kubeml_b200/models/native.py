@@ -272,13 +272,31 @@ class NativeNet(nn.Module):
 # ---------------------------------------------------------------------------------------------
 # layer programs shared by the models
 # ---------------------------------------------------------------------------------------------
-_SMS = 148
+_sms_cached: Optional[int] = None
 
 
-def auto_splits(tiles: int, chunks: int, min_chunks: int = 2, budget: int = _SMS) -> int:
+def sm_count() -> int:
+    """SMs of the GPU the plans are sized for: asked from the native library (`kml_num_sms`) when a device is
+    present, 148 (B200) for the CPU restatement."""
+    global _sms_cached
+    if _sms_cached is None:
+        n = 148
+        if torch.cuda.is_available():
+            try:
+                from .. import _native
+                n = int(_native.lib().kml_num_sms()) or 148
+            except Exception:  # noqa: BLE001 - planning must not fail because the count is unknown
+                n = 148
+        _sms_cached = n
+    return _sms_cached
+
+
+def auto_splits(tiles: int, chunks: int, min_chunks: int = 2, budget: Optional[int] = None) -> int:
     """K-splits for a GEMM with `tiles` output tiles and `chunks` 64-deep reduction chunks: enough
     CTAs to cover the GPU (`budget` CTAs), never fewer than `min_chunks` chunks per CTA, and only
     split counts that leave no CTA without work."""
+    if budget is None:
+        budget = sm_count()
     if tiles >= budget or chunks < 2 * min_chunks:
         return 1
     s = max(1, min(budget // max(tiles, 1), chunks // min_chunks))
@@ -290,7 +308,7 @@ def pick_block_n(m_tiles: int, n: int) -> int:
     """128-wide tiles only when there are enough of them to occupy the GPU."""
     if n <= 64:
         return 64
-    return 128 if m_tiles * ((n + 127) // 128) >= _SMS // 2 else 64
+    return 128 if m_tiles * ((n + 127) // 128) >= sm_count() // 2 else 64
 
 
 def plan_cluster(m_tiles: int, n: int, chunks: int, bn0: int):
@@ -298,15 +316,16 @@ def plan_cluster(m_tiles: int, n: int, chunks: int, bn0: int):
     chunks times a TMA round trip, whatever the tile width (measured: 0.42 us per chunk for 128x64 and
     128x128 alike), so when the default choice leaves long K loops a wider tile - half the tiles, twice
     the splits - halves the time (VGG 512->512 on 4x4: 72 -> 36 chunks per CTA)."""
-    def plan(bn, budget=_SMS):
+    def plan(bn, budget=None):
+        budget = budget or sm_count()
         tiles = m_tiles * ((n + bn - 1) // bn)
         S = min(auto_splits(tiles, chunks, min_chunks=_CL_MIN_CHUNKS, budget=budget), _CLUSTER_MAX)
         return -(-chunks // S), S, bn
     best = plan(bn0)
     if best[0] > 12:                       # long K loops: consider wider tiles and two CTAs per SM
-        cands = [plan(bn0, 2 * _SMS)]
+        cands = [plan(bn0, 2 * sm_count())]
         if bn0 == 64 and n >= 128:
-            cands += [plan(128), plan(128, 2 * _SMS)]
+            cands += [plan(128), plan(128, 2 * sm_count())]
         for c in cands:
             if c[0] < best[0]:
                 best = c
@@ -649,7 +668,7 @@ def linear_forward(fc: NLinear, x: torch.Tensor, B: Buffers, tag: str, relu: boo
     bn_ = pick_block_n(m_tiles, fc.cout)
     tiles = m_tiles * ((fc.cout + bn_ - 1) // bn_)
     # a long reduction (VGG fc1: 392 chunks) may take two CTAs per SM
-    S = auto_splits(tiles, (fc.cin + 63) // 64, min_chunks=8, budget=2 * _SMS) if (_slab_enabled() and fc.cout % 8 == 0) else 1
+    S = auto_splits(tiles, (fc.cin + 63) // 64, min_chunks=8, budget=2 * sm_count()) if (_slab_enabled() and fc.cout % 8 == 0) else 1
     if S > 1:
         slabs = B.get(tag + ".slabs", (S, M, fc.cout), torch.float32)
         ops.gemm_bf16(x, fc.w_bf16, out=slabs, block_n=bn_, splits=S, slabs=True)

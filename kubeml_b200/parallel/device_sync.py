@@ -39,6 +39,10 @@ from .arena import ArenaLayout, WeightArena
 log = logging.getLogger("kubeml.device_sync")
 
 
+def _bits(mask: int) -> List[int]:
+    return [r for r in range(32) if (mask >> r) & 1]
+
+
 class PeerTable:
     """Addresses, valid on *this* rank's GPU, of every known rank's arena regions."""
 
@@ -78,6 +82,11 @@ class RankSync:
         self._model = None
         self._write_mask = 0
         self._fused_steps = 0
+        self._seq = 0                 # job-wide number of this fan-out: generations never repeat
+        self._dead = 0                # ranks this rank has given up on for the current epoch
+        self._status_host: Optional[torch.Tensor] = None
+        self._round_launched = -1
+        self.recovered = 0            # merges re-run without a missing rank
 
     # ---- init task -----------------------------------------------------------------------
     def publish_reference(self, job_id: str, network: torch.nn.Module) -> List[str]:
@@ -104,6 +113,12 @@ class RankSync:
         join_for = (kube_model._inv.query or {}).get("joinFor") if a._task == "join" else None
         if a._task == "train" or join_for == "train":
             self._epoch = int(a.epoch)
+            q = kube_model._inv.query or {}
+            self._seq = int(q.get("syncSeq", self._epoch))
+            self._dead = 0
+            self._round_launched = -1
+            self.arena.status.zero_()
+            self._clear_dead_mark()
             self._schedule = (round_schedule(kube_model._dataset.num_docs, a._N, a._K, a.batch_size)
                               if a._task == "train" else [])
             self.merge_seconds = 0.0
@@ -143,6 +158,54 @@ class RankSync:
     def publish_replica(self, job_id: str, func_id: int, network: torch.nn.Module) -> None:
         """Parameters already are the replica `{job}:{name}/{func_id}`."""
 
+    # ---- generations -------------------------------------------------------------------------------
+    # One number per (fan-out, round, attempt), strictly increasing over the life of a job (modulo 2^32;
+    # the kernel compares signed differences): the flags in the signal pads only ever grow, so a repeated
+    # number would let a barrier pass without waiting.  The fan-out number comes from the train job
+    # (`syncSeq`), so every rank - also one that joins later - derives the same value.
+    def _gen(self, round_idx: int, attempt: int = 0) -> int:
+        return (((self._seq & 0x3FF) << 22) | (((round_idx + 1) & 0x3FFFF) << 4) | (attempt & 0xF)) & 0xFFFFFFFF
+
+    def _tombstone(self) -> int:
+        return (((self._seq & 0x3FF) << 22) | 0x3FFFFF) & 0xFFFFFFFF
+
+    def _pads(self, only_self: bool = False):
+        p = _native.MergeParams()
+        for r, addr in self.peers.flags.items():
+            if not only_self or r == self.rank:
+                p.flags[r] = addr
+        p.my_rank = self.rank
+        return p
+
+    def _clear_dead_mark(self) -> None:
+        """A rank that (re-)joins an epoch is alive again: clear its mark in every pad it can reach.
+        Runs before the epoch's membership barrier, so every peer sees it before the first merge."""
+        if len(self.peers.flags) <= 1:
+            return
+        stream = torch.cuda.current_stream(self.arena.device)
+        _native.check(_native.lib().kml_merge_mark_dead(ctypes.byref(self._pads()), self.rank, 0, 0,
+                                                        int(stream.cuda_stream)), "kml_merge_mark_dead")
+        stream.synchronize()
+
+    def abandon(self, round_idx: int) -> None:
+        """This worker's function failed in round `round_idx` of the epoch (before its merge): tell every
+        peer not to wait for it and not to count it - the divisor of the reference's merger is the number
+        of notifications it received (ml/pkg/train/job.go:383-398) and a failed function does not block
+        the others (function.go:180-190)."""
+        if self.arena is None or len(self.peers.flags) <= 1:
+            return
+        try:
+            stream = torch.cuda.current_stream(self.arena.device)
+            stream.synchronize()                    # merges already launched have run (or timed out)
+            first = max(round_idx, self._round_launched + 1)
+            _native.check(_native.lib().kml_merge_mark_dead(ctypes.byref(self._pads()), self.rank,
+                                                            self._gen(first), self._tombstone(),
+                                                            int(stream.cuda_stream)), "kml_merge_mark_dead")
+            stream.synchronize()
+            log.warning("rank %d left epoch %d at round %d", self.rank, self._epoch, first)
+        except Exception as e:  # noqa: BLE001 - already on an error path
+            log.error("rank %d could not announce its failure: %s", self.rank, e)
+
     def _flush_pending_step(self) -> None:
         opt = getattr(self._model, "optimizer", None)
         if opt is not None and getattr(opt, "_deferred", False):
@@ -158,26 +221,57 @@ class RankSync:
         self._flush_pending_step()
         stream = torch.cuda.current_stream(self.arena.device)
         stream.synchronize()
+        if rounds_done > 0:
+            self.check_round(rounds_done - 1)
+            stream.synchronize()
         for e0, e1 in self._events:
             self.merge_seconds += e0.elapsed_time(e1) / 1e3
         self._events = []
-        st = int(self.arena.status.item())
-        if st != 0:
+
+    def check_round(self, round_idx: int) -> None:
+        """Called after the host has synchronised with the stream that ran round `round_idx`'s merge.
+        A merge that timed out on some ranks touched nothing: record those ranks as dead for the rest of
+        the epoch and run the merge again without them (up to 3 times); being declared dead by the
+        others, or losing a peer half-way through a merge, fails this worker."""
+        if self._status_host is None or round_idx != self._round_launched:
+            return
+        st = int(self._status_host[0])
+        attempt = 0
+        while st != 0:
             self.arena.status.zero_()
-            missing = [r for r in range(32) if (st >> r) & 1]
-            raise WorkerFault(f"merge barrier timed out waiting for rank(s) {missing}")
+            if st & _native.MERGE_EVICTED:
+                raise WorkerFault(f"rank {self.rank} was dropped from the merge by its peers (it arrived too late)")
+            if st & _native.MERGE_LATE:
+                raise WorkerFault(f"a peer vanished in the middle of a merge (ranks {_bits(st & 0xFF)})")
+            missing = st & 0xFF
+            attempt += 1
+            if attempt > 3 or missing == 0:
+                raise WorkerFault(f"merge barrier timed out waiting for rank(s) {_bits(missing)}")
+            log.warning("rank %d: rank(s) %s missed round %d of epoch %d; merging without them", self.rank,
+                        _bits(missing), round_idx, self._epoch)
+            self._dead |= missing
+            stream = torch.cuda.current_stream(self.arena.device)
+            for r in _bits(missing):          # in the own pad only: the peers reach the same verdict themselves
+                _native.check(_native.lib().kml_merge_mark_dead(ctypes.byref(self._pads(only_self=True)), r,
+                                                                self._gen(round_idx), self._tombstone(),
+                                                                int(stream.cuda_stream)), "kml_merge_mark_dead")
+            self._merge(round_idx, attempt=attempt, allow_fuse=False)
+            stream.synchronize()
+            self.recovered += 1
+            st = int(self._status_host[0])
 
     def drain_losses(self, loss) -> float:
         return float(loss)
 
     # ---- the merge -----------------------------------------------------------------------
-    def _merge(self, round_idx: int) -> None:
+    def _merge(self, round_idx: int, attempt: int = 0, allow_fuse: bool = True) -> None:
         parts = self._schedule[round_idx] if round_idx < len(self._schedule) else [self.rank]
         if self.rank not in parts:
             return
         pmask = 0
         for r in parts:
             pmask |= 1 << r
+        pmask &= ~self._dead
         opt = getattr(self._model, "optimizer", None)
         p = _native.MergeParams()
         L = self.layout
@@ -190,15 +284,17 @@ class RankSync:
         p.n_sgd = L.n_param
         p.my_rank = self.rank
         p.participants = pmask
-        p.write_mask = self._write_mask | pmask
-        single = len(parts) == 1 and p.write_mask == pmask
-        p.generation = 0 if single else ((self._epoch & 0x7FFF) << 16) + round_idx + 1
-        use_mc = (self.peers.mcast and frozenset(parts) == self.peers.mcast_ranks
+        p.write_mask = (self._write_mask | pmask) & ~self._dead
+        single = len(parts) == 1 and (self._write_mask | pmask) == pmask
+        p.generation = 0 if single else self._gen(round_idx, attempt)
+        use_mc = (self.peers.mcast and frozenset(parts) == self.peers.mcast_ranks and not self._dead
                   and p.write_mask == pmask and os.environ.get("KUBEML_MERGE_NVLS", "1") != "0")
         p.mcast = self.peers.mcast if use_mc else None
         p.status = self.arena.ptr(L.off_status)
-        p.timeout_cycles = int(float(os.environ.get("KUBEML_MERGE_TIMEOUT_S", "20")) * 1.9e9)
-        if opt is not None and getattr(opt, "_deferred", False):
+        tmo = os.environ.get("KUBEML_MERGE_TIMEOUT_MS")
+        tmo_s = float(tmo) / 1e3 if tmo else float(os.environ.get("KUBEML_MERGE_TIMEOUT_S", "20"))
+        p.timeout_cycles = int(tmo_s * 1.9e9)
+        if opt is not None and getattr(opt, "_deferred", False) and allow_fuse:
             g = opt.param_groups[0]
             p.fuse_sgd = 1
             p.grad = self.arena.ptr(L.off_grad)
@@ -215,6 +311,11 @@ class RankSync:
         _native.check(_native.lib().kml_kavg_merge(ctypes.byref(p), int(stream.cuda_stream)),
                       "kml_kavg_merge")
         e1.record(stream)
+        if not single:
+            if self._status_host is None:
+                self._status_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._status_host.copy_(self.arena.status, non_blocking=True)     # read after the round's host sync
+        self._round_launched = round_idx
         self._events.append((e0, e1))
         self.merges += 1
         self.epoch_merges = getattr(self, "epoch_merges", 0) + 1

@@ -53,13 +53,26 @@ def test_noalloc_matches_scratch_variant_twice(dtype):
     torch.cuda.synchronize()
 
     is_bf16 = int(dtype == torch.bfloat16)
-    for rows, classes, x, y, ref, new in bufs:
+    free_before = allocs_before = None
+    for i, (rows, classes, x, y, ref, new) in enumerate(bufs):
         _native.check(lib.kml_softmax_ce(x.data_ptr(), is_bf16, y.data_ptr(), rows, classes,
                                          ref["loss"].data_ptr(), ref["dl"].data_ptr(), ref["corr"].data_ptr(),
                                          ref["scratch"].data_ptr(), stream), "kml_softmax_ce")
+        if i == 1:
+            # The promise itself: the call takes no device memory.  Checked on the second call, after the
+            # first one did the once-per-device set-up (which allocates nothing either, but this way the
+            # driver's lazy module loading cannot blur the reading): free device memory as the driver
+            # reports it (cudaMemGetInfo) and torch's allocation counter must both stand still.
+            torch.cuda.synchronize()
+            free_before = torch.cuda.mem_get_info(dev)[0]
+            allocs_before = torch.cuda.memory_stats(dev).get("allocation.all.allocated", 0)
         _native.check(lib.kml_softmax_ce_noalloc(x.data_ptr(), is_bf16, y.data_ptr(), rows, classes,
                                                  new["loss"].data_ptr(), new["dl"].data_ptr(),
                                                  new["corr"].data_ptr(), stream), "kml_softmax_ce_noalloc")
+        if i == 1:
+            torch.cuda.synchronize()
+            assert torch.cuda.mem_get_info(dev)[0] == free_before, "kml_softmax_ce_noalloc changed the free device memory"
+            assert torch.cuda.memory_stats(dev).get("allocation.all.allocated", 0) == allocs_before
     torch.cuda.synchronize()
 
     tol = 1e-5 if dtype == torch.float32 else 2e-2      # the tolerances of tests/test_gpu_native.py
