@@ -19,7 +19,7 @@
 //      they finish and free their slots, so they can delay a spinning grid but not starve it.
 //   What is NOT covered: two grids that both spin (two training streams on ONE GPU).  Each can be
 //   partly resident and wait for slots the other holds.  The spin is therefore bounded: after
-//   kSpinLimit cycles the kernel prints a diagnostic and traps, which fails the launch instead of
+//   kSpinLimit cycles the kernel traps, which fails the launch ("unspecified launch failure") instead of
 //   hanging the GPU.  One training stream per GPU is the supported configuration.
 #pragma once
 #include <cuda_runtime.h>
@@ -41,22 +41,18 @@ struct BnScratch {
 // One thread of the CTA calls this after the CTA's own threads have synchronised; returns when
 // `ncta` CTAs have arrived since `base`.
 __device__ __forceinline__ void grid_arrive_and_wait(BnScratch* sc, unsigned base, unsigned ncta) {
-  __threadfence();
-  atomicAdd(&sc->bar, 1u);
+  // release-arrive / acquire-poll: the release is cumulative over what this thread observed through the
+  // CTA barrier before it, so no separate fences are needed on either side
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(&sc->bar), "r"(1u) : "memory");
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&sc->bar) : "memory");
   if (v - base < ncta) {
     const long long t0 = clock64();
     do {
       asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&sc->bar) : "memory");
-      if (clock64() - t0 > kSpinLimit) {
-        printf("kubeml_b200: grid barrier timed out (%u of %u CTAs arrived) - two spinning grids on one GPU?\n",
-               v - base, ncta);
-        asm volatile("trap;");
-      }
+      if (clock64() - t0 > kSpinLimit) asm volatile("trap;");   // fails the launch instead of hanging the GPU
     } while (v - base < ncta);
   }
-  __threadfence();
 }
 
 }  // namespace kml

@@ -206,7 +206,7 @@ __device__ __forceinline__ void box_origin(const Geometry& g, int idx, int& w0, 
 // LINEAR: tiles are addressed by a linear, band-rasterised index (1-D grid, optionally persistent) -
 // the variant for problems of many tiles.  !LINEAR: one tile per CTA straight from the 3-D block index
 // (no index arithmetic at all) - the variant for the small, latency-bound launches and cluster mode.
-template <int BLOCK_N, bool A_MN, bool B_MN, bool LINEAR>
+template <int BLOCK_N, bool A_MN, bool B_MN, bool LINEAR, int BN_MODE = 0>
 __global__ void __launch_bounds__(kNumThreads, 2)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const GemmArgs args) {
@@ -290,7 +290,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   // fused BatchNorm: launch state of the software grid barrier, read early so the round trip overlaps the
   // main loop (nobody can advance it before every CTA of this grid has passed the barrier)
   uint2 gstate = make_uint2(0u, 0u);
-  if (args.bn_mode != 0) gstate = __ldcg(reinterpret_cast<const uint2*>(&args.bn_sc->launches));
+  if constexpr (BN_MODE != 0) gstate = __ldcg(reinterpret_cast<const uint2*>(&args.bn_sc->launches));
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
@@ -529,7 +529,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   }
 
   __syncthreads();
-  if (args.cluster_reduce) {
+  if constexpr (BN_MODE != 0) {
+  // ===== cluster reduction + fused BatchNorm (kml_bn_fuse); instantiated only for the variants that use it =====
+  {
     const Tile T0 = tile_at(tile0);                      // cluster mode is never persistent: one tile
     const int mt = T0.mt, nt = T0.nt, split = T0.split;
     // ---- split-K reduction across the cluster through distributed shared memory ----------------
@@ -548,7 +550,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     float* st_sm = part + kBlockM * kPartStride;        // [6 warps][2][BLOCK_N] per-warp column sums
     float* pv_sm = st_sm + 2 * kWarps * BLOCK_N;         // [BLOCK_N] pivots of the fused forward statistics
     float* co = pv_sm + BLOCK_N;                         // [3][BLOCK_N] per-column coefficients of the fused BatchNorm
-    const int bnm = args.bn_mode;
+    constexpr int bnm = BN_MODE;
     const int et = threadIdx.x;
     if (bnm != 0) {
       // Everything per-channel that does not depend on the batch statistics is fetched now, before the
@@ -843,6 +845,153 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     }
     cluster_sync_all();                                  // peers may still be reading this CTA's partial tile
   }
+  } else if (args.cluster_reduce) {
+    const Tile T0 = tile_at(tile0);                      // cluster mode is never persistent: one tile
+    const int mt = T0.mt, nt = T0.nt, split = T0.split;
+    // ---- split-K reduction across the cluster through distributed shared memory ----------------
+    // CTA `split` owns rows [rbeg, rend) of the 128-row tile: it adds the partial tiles of all
+    // peers for those rows, applies the epilogue once and writes the final output.  Column sums
+    // for BatchNorm fall out of the same pass (a thread keeps the same 4 columns for all its rows).
+    constexpr int kPartStride = BLOCK_N + 4;
+    constexpr int kGroups = BLOCK_N / 4;                 // float4 groups per row
+    float* part = reinterpret_cast<float*>(smem_a);
+    float* st_sm = part + kBlockM * kPartStride;        // [4 warps][2][BLOCK_N] per-warp column sums
+    cluster_sync_all();
+    if (warp >= 2) {
+      const int S = args.splits;
+      const int rp = (kBlockM + S - 1) / S;
+      const int rbeg = split * rp;
+      const int rend = min(kBlockM, rbeg + rp);
+      const int et = threadIdx.x - 64;                   // 0..127
+      const int c4 = (et % kGroups) * 4;
+      const int ncol = nt * BLOCK_N + c4;
+      const bool col_ok = ncol + 4 <= args.n_valid;
+      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+      float bv[4] = {0.f, 0.f, 0.f, 0.f};
+      if (args.bias != nullptr) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) bv[t] = __ldg(args.bias + ncol + t);
+      }
+      float bm[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {0.f, 0.f, 0.f, 0.f};
+      if (args.bn_x != nullptr) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          if (ncol + t < args.n_valid) { bm[t] = args.bn_mean[ncol + t]; bi[t] = args.bn_invstd[ncol + t]; }
+      }
+      for (int r = rbeg + et / kGroups; r < rend; r += 128 / kGroups) {
+        const uint32_t laddr = smem_u32(part + r * kPartStride + c4);
+        float4 acc = ld_dsmem_f4(laddr, 0);
+        for (int p = 1; p < S; ++p) {
+          const float4 o = ld_dsmem_f4(laddr, static_cast<uint32_t>(p));
+          acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
+        }
+        const int grow = mt * kBlockM + r;
+        if (grow >= args.m_valid) continue;
+        float f[4] = {acc.x + bv[0], acc.y + bv[1], acc.z + bv[2], acc.w + bv[3]};
+        const long long ro = static_cast<long long>(grow) * args.ldo + ncol;
+        if (args.addend != nullptr) {
+          const __nv_bfloat16* ad = args.addend + ro;
+          if (col_ok && (ro & 3) == 0) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(ad));
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+            f[0] += a0.x; f[1] += a0.y; f[2] += a1.x; f[3] += a1.y;
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) f[t] += __bfloat162float(ad[t]);
+          }
+        }
+        if (args.relu) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
+        }
+        if (args.mask_y != nullptr) {
+          const __nv_bfloat16* my = args.mask_y + ro;
+          if (col_ok && (ro & 3) == 0) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(my));
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+            f[0] = a0.x > 0.f ? f[0] : 0.f; f[1] = a0.y > 0.f ? f[1] : 0.f;
+            f[2] = a1.x > 0.f ? f[2] : 0.f; f[3] = a1.y > 0.f ? f[3] : 0.f;
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+              if (ncol + t < args.n_valid) f[t] = __bfloat162float(my[t]) > 0.f ? f[t] : 0.f;
+          }
+        }
+        if (args.out_f32) {
+          float* o = static_cast<float*>(args.out) + ro;
+          if (col_ok && (ro & 3) == 0) {
+            *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = f[t];
+          }
+        } else {
+          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + ro;
+          __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
+          __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
+          if (col_ok && (ro & 3) == 0) {
+            uint2 u;
+            u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
+            *reinterpret_cast<uint2*>(o) = u;
+          } else {
+            const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = hv[t];
+          }
+          // statistics of exactly the values the consumer will read back
+          const float2 r0 = __bfloat1622float2(p0), r1 = __bfloat1622float2(p1);
+          f[0] = r0.x; f[1] = r0.y; f[2] = r1.x; f[3] = r1.y;
+        }
+        if (args.bn_x != nullptr) {                     // BatchNorm-backward sums: g and g * xhat
+          float xh[4] = {0.f, 0.f, 0.f, 0.f};
+          const __nv_bfloat16* bx = args.bn_x + ro;
+          if (col_ok && (ro & 3) == 0) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2*>(bx));
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+            const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+            xh[0] = a0.x; xh[1] = a0.y; xh[2] = a1.x; xh[3] = a1.y;
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) xh[t] = __bfloat162float(bx[t]);
+          }
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            s1[t] += f[t];
+            s2[t] = fmaf(f[t], (xh[t] - bm[t]) * bi[t], s2[t]);
+          }
+        } else {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
+        }
+      }
+      if (args.stats != nullptr) {
+        // No shared-memory float atomics (they compile to compare-and-swap loops): lanes that share a
+        // column group fold with a shuffle, each warp writes its own row of partials, then 4-way sums.
+        if (kGroups == 16) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            s1[t] += __shfl_xor_sync(0xffffffffu, s1[t], 16);
+            s2[t] += __shfl_xor_sync(0xffffffffu, s2[t], 16);
+          }
+        }
+        float* wsm = st_sm + (warp - 2) * 2 * BLOCK_N;    // [4 warps][2][BLOCK_N]
+        if (lane < kGroups) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { wsm[c4 + t] = s1[t]; wsm[BLOCK_N + c4 + t] = s2[t]; }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+        for (int i = et; i < 2 * BLOCK_N; i += 128) {
+          const int c = i % BLOCK_N, which = i / BLOCK_N;
+          const int gc = nt * BLOCK_N + c;
+          const float tot = st_sm[i] + st_sm[2 * BLOCK_N + i] + st_sm[4 * BLOCK_N + i] + st_sm[6 * BLOCK_N + i];
+          if (gc < args.n_valid) atomicAdd(args.stats + static_cast<size_t>(which) * args.n_valid + gc, tot);
+        }
+      }
+    }
+    cluster_sync_all();                                  // peers may still be reading this CTA's partial tile
+  }
   if (warp == 1) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
@@ -1088,10 +1237,10 @@ int encode_map(CUtensorMap* map, const TensorSpec& t) {
   return 0;
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN, bool LINEAR>
+template <int BLOCK_N, bool A_MN, bool B_MN, bool LINEAR, int BN_MODE = 0>
 int launch_tiles(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& a, dim3 grid, cudaStream_t s) {
   constexpr size_t smem = Stages<BLOCK_N>::value * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 /*align*/ + 640 /*barriers+taps*/;
-  auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN, LINEAR>;
+  auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN, LINEAR, BN_MODE>;
   static kml::PerDeviceOnce configured;
   const int dev = kml::current_device();
   if (configured.need(dev)) {
@@ -1140,6 +1289,20 @@ int launch(const TensorSpec& ta, const TensorSpec& tb, const GemmArgs& a, int bl
     return launch_variant<256, true, true>(ma, mb, a, s);
   }
   KML_CHECK(!(amn && !bmn), "A MN-major with B K-major is not instantiated");
+  if (a.bn_mode != 0) {
+    // The fused-BatchNorm epilogue lives in its own instantiations (forward: both operands K-major;
+    // backward: the data-gradient form, B MN-major), so that every other launch keeps the lean kernel:
+    // measured, one kernel carrying all epilogues cost every GEMM of the step ~1 us (168 vs 128
+    // registers and a third more code to fetch on a cold instruction cache).
+    const dim3 grid(a.m_tiles, a.n_tiles, a.z_taps * a.splits);
+    KML_CHECK(!amn && a.cluster_reduce && ((a.bn_mode == 1 && !bmn) || (a.bn_mode == 2 && bmn)),
+              "bn_fuse: forward takes K-major operands, backward the data-gradient form (B MN-major)");
+    if (a.bn_mode == 1)
+      return block_n == 64 ? launch_tiles<64, false, false, false, 1>(ma, mb, a, grid, s)
+                           : launch_tiles<128, false, false, false, 1>(ma, mb, a, grid, s);
+    return block_n == 64 ? launch_tiles<64, false, true, false, 2>(ma, mb, a, grid, s)
+                         : launch_tiles<128, false, true, false, 2>(ma, mb, a, grid, s);
+  }
   if (block_n == 64) {
     if (!amn && !bmn) return launch_variant<64, false, false>(ma, mb, a, s);
     if (!amn && bmn) return launch_variant<64, false, true>(ma, mb, a, s);
@@ -1224,10 +1387,10 @@ bool make_geometry(int W, int H, int target, Geometry* g) {
 }  // namespace
 
 namespace {
-template <int BLOCK_N, bool A_MN, bool B_MN>
+template <int BLOCK_N, bool B_MN, int BN_MODE>
 int coresident_of(int cluster_size) {
   constexpr size_t smem = Stages<BLOCK_N>::value * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) + 1024 + 640;
-  auto kernel = gemm_tcgen05_kernel<BLOCK_N, A_MN, B_MN, false>;
+  auto kernel = gemm_tcgen05_kernel<BLOCK_N, false, B_MN, false, BN_MODE>;
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) return -1;
   cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   kml::note_kernel(reinterpret_cast<const void*>(kernel));
@@ -1264,10 +1427,10 @@ int kml_gemm_max_coresident(int block_n, int a_mn, int b_mn, int cluster_size) {
     if (it != cache.end()) return it->second;
   }
   int v = -1;
-  if (block_n == 64) v = !a_mn ? (b_mn ? coresident_of<64, false, true>(cluster_size) : coresident_of<64, false, false>(cluster_size))
-                               : coresident_of<64, true, true>(cluster_size);
-  else if (block_n == 128) v = !a_mn ? (b_mn ? coresident_of<128, false, true>(cluster_size) : coresident_of<128, false, false>(cluster_size))
-                                     : coresident_of<128, true, true>(cluster_size);
+  if (!a_mn) {     // the fused-BatchNorm instantiations: forward (B K-major) and backward (B MN-major)
+    if (block_n == 64) v = b_mn ? coresident_of<64, true, 2>(cluster_size) : coresident_of<64, false, 1>(cluster_size);
+    else if (block_n == 128) v = b_mn ? coresident_of<128, true, 2>(cluster_size) : coresident_of<128, false, 1>(cluster_size);
+  }
   if (v <= 0) { cudaGetLastError(); kml::set_error("kml_gemm_max_coresident: occupancy query failed"); }
   std::lock_guard<std::mutex> lock(mu);
   cache[key] = v;

@@ -184,6 +184,12 @@ kavg_merge_kernel(const kml_merge_params p) {
   const size_t n4 = p.n_f32 / 4;
   const size_t nsgd4 = p.n_sgd / 4;
 
+  // One participant that is also the only destination (N = 1, or a rank alone in a late round): the average
+  // of one replica is that replica (x / 1.0f == x), so nothing moves.  What is left is the fused last step -
+  // which then also writes the bf16 copy itself - and the optimizer reset.
+  const bool solo = !sync_ranks && __popc(p.participants) == 1 && p.write_mask == p.participants;
+  uint2* wb0 = (solo && p.w_bf16 != nullptr) ? reinterpret_cast<uint2*>(p.w_bf16) : nullptr;
+
   // ---- phase 0: fused last local step on the own replica --------------------------------------
   if (p.fuse_sgd) {
     float4* w = reinterpret_cast<float4*>(p.replica[p.my_rank]);
@@ -203,8 +209,24 @@ kavg_merge_kernel(const kml_merge_params p) {
       wv.x = fmaf(-p.lr, d.x, wv.x); wv.y = fmaf(-p.lr, d.y, wv.y);
       wv.z = fmaf(-p.lr, d.z, wv.z); wv.w = fmaf(-p.lr, d.w, wv.w);
       w[i] = wv;
+      if (wb0 != nullptr) {
+        __nv_bfloat162 a = __floats2bfloat162_rn(wv.x, wv.y);
+        __nv_bfloat162 b = __floats2bfloat162_rn(wv.z, wv.w);
+        uint2 r;
+        r.x = *reinterpret_cast<uint32_t*>(&a);
+        r.y = *reinterpret_cast<uint32_t*>(&b);
+        wb0[i] = r;
+      }
     }
-    local_barrier();                // the whole replica is final before anyone is told so
+    if (!solo) local_barrier();     // the whole replica is final before anyone is told so
+  }
+  if (solo) {
+    if (p.momentum_buf) {           // optimizer reset (network.py:121-128)
+      float4* m = reinterpret_cast<float4*>(p.momentum_buf);
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (size_t i = tid; i < nsgd4; i += nthreads) __stcs(m + i, z);
+    }
+    return;
   }
 
   // ---- signal / decide ---------------------------------------------------------------------------

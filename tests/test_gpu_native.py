@@ -114,6 +114,8 @@ def _merge_single_gpu(dev, replicas_f, replicas_i, parts, write, fuse=None):
         p.n_sgd = fuse["n"]
         p.lr, p.weight_decay, p.momentum = fuse["lr"], fuse["wd"], fuse["mom"]
         p.momentum_buf = fuse["mbuf"].data_ptr() if fuse.get("mbuf") is not None else None
+        if fuse.get("wbf16") is not None:
+            p.w_bf16 = fuse["wbf16"].data_ptr()
     _native.check(lib.kml_kavg_merge(ctypes.byref(p), _native.stream_ptr()), "kml_kavg_merge")
     torch.cuda.synchronize()
     assert int(status.item()) == 0
@@ -156,6 +158,28 @@ def test_merge_fused_last_sgd_step_and_reset(dev):
     torch.testing.assert_close(w[0], want, rtol=1e-6, atol=1e-6)
     torch.testing.assert_close(w[1], want, rtol=1e-6, atol=1e-6)
     assert float(mb.abs().max()) == 0.0       # optimizer state reset in the same pass
+
+
+def test_merge_single_participant_is_the_fused_step_only(dev):
+    """One participant, one destination: the average is the identity, so the kernel is exactly the round's
+    last SGD step (+ bf16 copy + optimizer reset) - what a 1-GPU job pays per sync."""
+    torch.manual_seed(6)
+    n, npar = 4 * 5000, 4 * 4000
+    w = torch.randn(n, device=dev)
+    g = torch.randn(npar, device=dev)
+    mb = torch.randn(npar, device=dev)
+    wb = torch.zeros(npar, dtype=torch.bfloat16, device=dev)
+    lr, wd, mom = 0.05, 1e-3, 0.9
+    want = w.clone()
+    want[:npar] -= lr * (mom * mb + g + wd * w[:npar])
+    _merge_single_gpu(dev, [w], None, [0], [0], fuse=dict(grad=g, n=npar, lr=lr, wd=wd, mom=mom, mbuf=mb, wbf16=wb))
+    torch.testing.assert_close(w, want, rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(wb.float(), want[:npar].bfloat16().float(), rtol=0, atol=0)
+    assert float(mb.abs().max()) == 0.0
+    # without a pending step nothing changes
+    before = w.clone()
+    _merge_single_gpu(dev, [w], None, [0], [0])
+    torch.testing.assert_close(w, before, rtol=0, atol=0)
 
 
 # ------------------------------------------------------------------------------------- tcgen05 GEMM
