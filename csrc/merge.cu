@@ -259,6 +259,16 @@ kavg_merge_kernel(const kml_merge_params p) {
         if (p.status) atomicOr(p.status, KML_MERGE_EVICTED);
         decision = kGoAbort;
       } else if (missing & ~dead) {
+        // Record the verdict where the late rank will look before it does anything: in every pad, its
+        // own included.  (A rank that arrives in the microsecond between this decision and the marks
+        // landing can still slip through; the timeout is seconds, the window an NVLink round trip.)
+#pragma unroll
+        for (int m = 0; m < KML_MAX_RANKS; ++m) {
+          if (!(((missing & ~dead) >> m) & 1u)) continue;
+#pragma unroll
+          for (int r = 0; r < KML_MAX_RANKS; ++r)
+            if (p.flags[r] != nullptr) st_release_sys(&reinterpret_cast<MergePad*>(p.flags[r])->dead_from[m], gen);
+        }
         if (p.status) atomicOr(p.status, static_cast<int>(missing & ~dead));
         decision = kGoAbort;
       }

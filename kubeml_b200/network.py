@@ -116,7 +116,15 @@ class KubeModel(ABC):
         if self.task == "init":
             return self.__initialize(), 200
         if self.task == "train":
-            loss = self.__train()
+            try:
+                loss = self.__train()
+            except BaseException:
+                # a failed function must not hold up the others: tell the peers this rank is out for the
+                # rest of the epoch (the reference's deferred finish path, ml/pkg/train/function.go:180-190)
+                abandon = getattr(self._sync, "abandon", None)
+                if abandon is not None:
+                    abandon(getattr(self, "_round_idx", 0))
+                raise
             return {"loss": loss, "merge_seconds": self.merge_seconds,
                     "h2d_bytes": self.h2d_bytes, "d2h_bytes": self.d2h_bytes,
                     "train_seconds": self.train_seconds, "steps": self.steps,
@@ -220,7 +228,7 @@ class KubeModel(ABC):
         intervals = range(assigned.start, assigned.stop, per_iter) if per_iter > 0 else range(0)
 
         opts = self._inv.services.options or {}
-        fault = opts.get("inject_fault")
+        fault = _fault_hook(opts.get("inject_fault") or os.environ.get("KUBEML_INJECT_FAULT"))
         on_cuda = self.device.type == "cuda"
         loss_host = 0.0
         loss_dev: Number = 0.0
@@ -241,7 +249,9 @@ class KubeModel(ABC):
             t_ev0.record()
         import time as _time
         t_wall = _time.perf_counter()
+        self._round_idx = 0
         for round_idx, i in enumerate(intervals):
+            self._round_idx = round_idx
             self._dataset._load_train_data(start=i, end=min(assigned.stop, i + per_iter))
             batches = self._dataset._batches(self.batch_size, self.device)
             num_iterations += len(batches)
@@ -274,6 +284,9 @@ class KubeModel(ABC):
                 self._sync.arrive(a._job_id, a._func_id, round_idx)
             if stage is not None:
                 loss_host += stage.drain()
+                check = getattr(self._sync, "check_round", None)
+                if check is not None:            # the host is in step with the stream here: did the merge go through?
+                    check(round_idx)
 
         self._sync.end_epoch(a._job_id, a._func_id, len(intervals))
         if on_cuda:
@@ -496,6 +509,35 @@ class _LossStage:
         self.drain_into = 0.0
         self.n = 0
         return v
+
+
+def _fault_hook(spec):
+    """`inject_fault` option: a callable (func_id, epoch, round, batch) -> bool, or the picklable text form
+    "func@epoch[:round[:batch]][/stall=seconds]" (e.g. "1@2:1" = function 1 fails in epoch 2 at the start of
+    round 1; with /stall=3 it sleeps 3 s there instead of failing) that
+    process-per-GPU workers and the `--inject-fault` CLI flag use."""
+    if spec is None or callable(spec):
+        return spec
+    try:
+        text, _, stall = str(spec).partition("/stall=")
+        who, _, when = text.partition("@")
+        parts = [int(v) for v in when.split(":")] if when else []
+        func, epoch = int(who), (parts[0] if parts else 1)
+        rnd = parts[1] if len(parts) > 1 else 0
+        bat = parts[2] if len(parts) > 2 else 0
+        stall_s = float(stall) if stall else 0.0
+    except ValueError:
+        raise KubeMLException(f"bad inject_fault spec {spec!r} (want func@epoch[:round[:batch]][/stall=seconds])", 400)
+
+    def hook(f, e, r, b):
+        if not (f == func and int(e) == epoch and r == rnd and b == bat):
+            return False
+        if stall_s > 0:          # a straggler, not a failure: the worker goes quiet for a while
+            import time
+            time.sleep(stall_s)
+            return False
+        return True
+    return hook
 
 
 def _native_launches() -> int:

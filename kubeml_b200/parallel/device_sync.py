@@ -251,8 +251,9 @@ class RankSync:
                         _bits(missing), round_idx, self._epoch)
             self._dead |= missing
             stream = torch.cuda.current_stream(self.arena.device)
-            for r in _bits(missing):          # in the own pad only: the peers reach the same verdict themselves
-                _native.check(_native.lib().kml_merge_mark_dead(ctypes.byref(self._pads(only_self=True)), r,
+            for r in _bits(missing):          # (the kernel that timed out already wrote the marks; this adds the
+                #                                tombstone flags so that no later round waits for the rank)
+                _native.check(_native.lib().kml_merge_mark_dead(ctypes.byref(self._pads()), r,
                                                                 self._gen(round_idx), self._tombstone(),
                                                                 int(stream.cuda_stream)), "kml_merge_mark_dead")
             self._merge(round_idx, attempt=attempt, allow_fuse=False)

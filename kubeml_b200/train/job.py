@@ -31,6 +31,19 @@ from .history import HistoryStore
 from .invoker import Invoker, Result
 
 
+# Fan-outs of a job id, counted for the life of the control-plane process: the device merge derives its
+# barrier generations from it (kubeml_b200.parallel.device_sync.RankSync._gen), and those must never
+# repeat while the workers keep the job's arena - also when a new TrainJob object reuses a job id.
+_SYNC_SEQ: Dict[str, int] = {}
+_SYNC_SEQ_LOCK = threading.Lock()
+
+
+def _next_sync_seq(job_id: str) -> int:
+    with _SYNC_SEQ_LOCK:
+        _SYNC_SEQ[job_id] = _SYNC_SEQ.get(job_id, 0) + 1
+        return _SYNC_SEQ[job_id]
+
+
 class TrainJob:
     def __init__(self, task: TrainTask, invoker: Invoker, tensor_store: TensorStore,
                  history_store: Optional[HistoryStore] = None,
@@ -175,7 +188,8 @@ class TrainJob:
                 self._barrier = barrier
 
         start = time.time()
-        queries = [self._query("train", i, n) for i in range(n)]
+        seq = _next_sync_seq(self.job_id)
+        queries = [dict(self._query("train", i, n), syncSeq=seq) for i in range(n)]
         on_done = (lambda fid, ok: barrier.finished(fid, ok)) if barrier is not None else None
         results = self.invoker.invoke_many(self.task.request.function_name, queries, on_done)
         ok = self._check_function_errors(results)

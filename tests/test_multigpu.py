@@ -16,7 +16,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _torchrun(n, script, *args, port=29541, timeout=600, env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), script, *args]
-    e = dict(os.environ, KUBEML_MERGE_TIMEOUT_S="5", **(env or {}))
+    e = dict(os.environ)
+    e["KUBEML_MERGE_TIMEOUT_S"] = "5"
+    e.update(env or {})
     return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=e, cwd=ROOT)
 
 
@@ -75,3 +77,41 @@ def test_elastic_parallelism_grows_between_epochs(tmp_path):
     assert h["parallelism"][0] == 1.0 and h["parallelism"][1] == 2.0
     assert len(h["train_loss"]) == 3 and all(np.isfinite(h["train_loss"]))
     assert len(h["accuracy"]) == 3
+
+
+def _ngpus():
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_failed_worker_does_not_stall_or_count_in_the_device_merge(tmp_path, n):
+    """Function 1 raises at the start of round 1 of epoch 1.  The reference lets the epoch stand when one
+    function answered and divides by the replicas it received (ml/pkg/train/job.go:383-398,
+    train/util.go:144-166); on the device path the failing rank marks itself dead in every signal pad, so the
+    survivors neither wait for it (no timeout is involved) nor count it, and it is back in epoch 2."""
+    if _ngpus() < n:
+        pytest.skip(f"needs {n} GPUs")
+    import time
+    t0 = time.time()
+    res = _result(_torchrun(n, os.path.join(ROOT, "tests", "mp_scripts", "spmd_fault.py"), str(tmp_path), "1@1:1",
+                            port=29551, env={"KUBEML_MERGE_TIMEOUT_S": "30"}))
+    assert res["error"] is None
+    h = res["history"]
+    assert len(h["train_loss"]) == 2 and all(np.isfinite(h["train_loss"]))
+    assert h["parallelism"] == [float(n), float(n)]
+    assert res["recovered"] == 0                      # nobody had to time out
+    assert time.time() - t0 < 120                     # far below n_rounds x 30 s of barrier timeouts
+
+
+def test_stalled_worker_is_dropped_after_the_round_timeout_and_evicted(tmp_path):
+    """Function 1 goes quiet for 4 s in round 1 (no failure announced).  The survivors' merge times out after
+    0.5 s without touching anything, they record the rank as dead, merge again without it and finish the
+    epoch; the straggler finds itself evicted when it arrives and fails instead of corrupting the model."""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    res = _result(_torchrun(2, os.path.join(ROOT, "tests", "mp_scripts", "spmd_fault.py"), str(tmp_path),
+                            "1@1:1/stall=4", port=29553, env={"KUBEML_MERGE_TIMEOUT_MS": "500"}))
+    assert res["error"] is None
+    h = res["history"]
+    assert len(h["train_loss"]) == 2 and all(np.isfinite(h["train_loss"]))
+    assert res["recovered"] >= 1
