@@ -207,6 +207,9 @@ def run_own(args) -> int:
                    "l2": "per-step working set (fp32 weights+grads 175 MB, bf16 copies, activations) "
                          "exceeds the 126 MB L2; no explicit flush"},
         "merge_ms_per_sync": round(1e3 * sd["merge_seconds"] / max(merges, 1), 4),
+        # of which the kernel spent waiting for the slowest rank to finish its K local steps (clocked in the
+        # kernel); the rest is the merge's own work
+        "merge_wait_ms_per_sync": round(1e3 * float(sd.get("merge_wait_seconds", 0.0)) / max(merges, 1), 4),
         "e2e": {"value": round(e2e, 1), "unit": "images/s",
                 "h2d_bytes_per_step": int(se["h2d_bytes"] / max(int(se["steps"]), 1)),
                 "d2h_bytes_per_step": int(se["d2h_bytes"] / max(int(se["steps"]), 1)),

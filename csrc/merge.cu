@@ -73,6 +73,9 @@ struct MergePad {
   uint32_t count, release, count_base, release_base;
   uint32_t go_gen, go_mask, fin_count, fin_base;
   uint32_t dead_from[KML_MAX_RANKS];
+  uint32_t pad0[16];
+  unsigned long long wait_ns;      // words 48-49: time this GPU's merges spent waiting for peers to become ready
+  unsigned long long waits;        // words 50-51: number of merges counted in wait_ns          (host resets both)
 };
 static_assert(sizeof(MergePad) <= 64 * sizeof(uint32_t), "signal pad is 64 words");
 
@@ -238,6 +241,8 @@ kavg_merge_kernel(const kml_merge_params p) {
       for (int r = 0; r < KML_MAX_RANKS; ++r)
         if ((p.participants >> r) & 1u)
           st_release_sys(&reinterpret_cast<MergePad*>(p.flags[r])->ready[p.my_rank], gen);
+      unsigned long long ts0;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ts0));
       uint32_t missing = 0;
       const long long t0 = clock64();
 #pragma unroll
@@ -248,6 +253,10 @@ kavg_merge_kernel(const kml_merge_params p) {
           __nanosleep(32);
         }
       }
+      unsigned long long ts1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ts1));
+      pad->wait_ns += ts1 - ts0;                         // how long the slowest peer kept this GPU waiting
+      pad->waits += 1;
       uint32_t dead = 0;
 #pragma unroll
       for (int r = 0; r < KML_MAX_RANKS; ++r) {

@@ -129,6 +129,7 @@ class KubeModel(ABC):
                     "h2d_bytes": self.h2d_bytes, "d2h_bytes": self.d2h_bytes,
                     "train_seconds": self.train_seconds, "steps": self.steps,
                     "gpu_launches": self.gpu_launches, "merges": int(getattr(self, "merges", 0)),
+                    "merge_wait_seconds": float(getattr(self._sync, "merge_wait_seconds", 0.0)),
                     "fused_last_steps": int(getattr(self, "fused_last_steps", 0))}, 200
         if self.task == "val":
             acc, loss, length = self.__validate()

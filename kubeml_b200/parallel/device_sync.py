@@ -122,6 +122,8 @@ class RankSync:
             self._schedule = (round_schedule(kube_model._dataset.num_docs, a._N, a._K, a.batch_size)
                               if a._task == "train" else [])
             self.merge_seconds = 0.0
+            self.merge_wait_seconds = 0.0
+            self.arena.flags[48:52].zero_()
             self.epoch_merges = 0
             self.epoch_fused_steps = 0
             self._events = []
@@ -227,6 +229,10 @@ class RankSync:
         for e0, e1 in self._events:
             self.merge_seconds += e0.elapsed_time(e1) / 1e3
         self._events = []
+        # of which: waiting for the slowest peer to finish its local steps (clocked inside the kernel)
+        w = self.arena.flags[48:52].cpu().view(torch.int64)
+        self.merge_wait_seconds = float(w[0]) / 1e9
+        self.arena.flags[48:52].zero_()
 
     def check_round(self, round_idx: int) -> None:
         """Called after the host has synchronised with the stream that ran round `round_idx`'s merge.

@@ -220,6 +220,7 @@ class TrainJob:
             "d2h_bytes": sum(int(p.get("d2h_bytes", 0)) for _, p, _ in ok),
             "gpu_launches": sum(int(p.get("gpu_launches", 0)) for _, p, _ in ok),
             "merges": max(int(p.get("merges", 0)) for _, p, _ in ok),
+            "merge_wait_seconds": max(float(p.get("merge_wait_seconds", 0.0)) for _, p, _ in ok),
             "fused_last_steps": max(int(p.get("fused_last_steps", 0)) for _, p, _ in ok)})
         samples = self._epoch_samples()
         self.history.images_per_second.append(samples / elapsed if elapsed > 0 and samples else 0.0)
