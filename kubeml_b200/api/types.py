@@ -67,6 +67,9 @@ class TrainOptions(_Wire):
     validate_every: int = field(default=0, metadata=_j("validate_every"))
     k: int = field(default=-1, metadata=_j("k"))
     goal_accuracy: float = field(default=100.0, metadata=_j("goal_accuracy"))
+    # Extension (the reference keeps no model past the end of a job): start from the checkpoint
+    # of an earlier task instead of the function's fresh initialisation.
+    resume_from: str = field(default="", metadata=_j("resume_from"))
 
 
 @dataclass

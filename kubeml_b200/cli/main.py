@@ -91,7 +91,8 @@ def cmd_train(args) -> int:
                        options=TrainOptions(default_parallelism=args.parallelism,
                                             static_parallelism=args.static,
                                             validate_every=args.validate_every, k=K,
-                                            goal_accuracy=args.goal_accuracy))
+                                            goal_accuracy=args.goal_accuracy,
+                                            resume_from=getattr(args, "resume", "") or ""))
     job_id = c.v1().networks().train(req)
     print(job_id)
     if getattr(args, "local", False) or args.wait:
@@ -267,6 +268,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--K", "-K", dest="K", type=int, default=-1)
     p.add_argument("--sparse-avg", action="store_true")
     p.add_argument("--goal-accuracy", type=float, default=100.0)
+    p.add_argument("--resume", default="", metavar="TASK_ID",
+                   help="start from the checkpoint of an earlier task ($KUBEML_HOME/checkpoints/<id>)")
     p.add_argument("--wait", action="store_true", help="block until the task finishes, print its history")
     p.set_defaults(fn=cmd_train)
 

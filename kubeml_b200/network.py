@@ -186,6 +186,16 @@ class KubeModel(ABC):
             self.init(self._network)
         else:
             self.init()
+        q = self._inv.query or {}
+        if q.get("resumeFrom"):
+            # warm start: the checkpoint of an earlier task replaces the function's initialisation before the
+            # reference model is published (to the tensor store or, on GPUs, into rank 0's arena)
+            from .utils.checkpoint import load_checkpoint
+            state, _ = load_checkpoint(q["ckptDir"], q["resumeFrom"])
+            missing = set(self._network.state_dict()) ^ set(state)
+            if missing:
+                raise StorageError(KeyError(f"checkpoint {q['resumeFrom']} does not match the network: {sorted(missing)[:4]}"))
+            self._network.load_state_dict(state)
         try:
             return self._sync.publish_reference(self.args._job_id, self._network)
         except KeyError as e:

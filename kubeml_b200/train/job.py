@@ -164,8 +164,17 @@ class TrainJob:
                 "batchSize": r.batch_size, "lr": r.lr, "epoch": self.epoch}
 
     def _init(self) -> None:
-        payload, status = self.invoker.invoke_one(0, self.task.request.function_name,
-                                                  self._query("init", 0, 1))
+        q = self._query("init", 0, 1)
+        resume = getattr(self.task.request.options, "resume_from", "")
+        if resume:
+            if not self.checkpoint_dir:
+                raise KubeMLException("resume_from needs a checkpoint directory", 400)
+            import os
+            if not os.path.isfile(os.path.join(self.checkpoint_dir, resume, "model.pt")):
+                raise KubeMLException(f"no checkpoint of task {resume}", 404)
+            q.update(resumeFrom=resume, ckptDir=self.checkpoint_dir)
+            self.log.info("resuming from the checkpoint of task %s", resume)
+        payload, status = self.invoker.invoke_one(0, self.task.request.function_name, q)
         if status != 200:
             raise KubeMLException(f"error invoking init function: {payload}", status)
         layers = list(payload or [])

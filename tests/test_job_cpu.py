@@ -173,3 +173,24 @@ def test_missing_dataset_and_function_errors(cluster):
     req.function_name = "does_not_exist"
     _, err, _ = _run(cluster, req)
     assert err is not None and "does not exist" in err
+
+
+def test_resume_from_checkpoint_continues_where_the_first_task_stopped(cluster):
+    """W24: a task started with `resume_from` trains on from the checkpointed model: one epoch + one resumed
+    epoch give the same model as two epochs in one task (same data order, optimizer state is reset at every
+    sync anyway)."""
+    torch.set_num_threads(1)
+    _mnist(cluster.shard_store)
+    mk = lambda epochs, resume="": TrainRequest(
+        model_type="lenet", batch_size=64, epochs=epochs, dataset="mnist", lr=0.01, function_name="lenet",
+        options=TrainOptions(default_parallelism=2, static_parallelism=True, validate_every=0, k=16, resume_from=resume))
+    j1, err, _ = _run(cluster, mk(1))
+    assert err is None
+    j2, err, job2 = _run(cluster, mk(1, resume=j1))
+    assert err is None
+    want_sd, _ = _oracle_kavg(cluster.shard_store, 2, 16, 64, 0.01, 2)
+    for k, v in want_sd.items():
+        got = cluster.tensor_store.tensorget(f"{j2}:{k}")
+        np.testing.assert_allclose(got, v.numpy(), rtol=1e-4, atol=1e-6)
+    _, err, _ = _run(cluster, mk(1, resume="nosuchjob"))
+    assert err is not None and "no checkpoint" in str(err)
