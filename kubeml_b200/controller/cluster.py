@@ -96,6 +96,7 @@ class Cluster:
         job = TrainJob(task, invoker, self.tensor_store, history_store=self.histories,
                        scheduler=self.scheduler, ps=ps, device_mode=device_mode,
                        checkpoint_dir=self.checkpoint_dir)
+        job.trace_dir = os.path.join(self.home, "traces")     # host timeline always; device spans with options["trace"]
         self.jobs[task.job.id] = job
         return job
 

@@ -135,6 +135,7 @@ class SlicedBatches(BatchSource):
         self.n = len(ds.data)
         self.h2d_bytes = 0
         self._resident = False
+        self.trace = [] if getattr(ds, "_trace", False) else None     # (batch, start event, end event) of each H2D copy
         if device.type == "cuda" and getattr(ds, "_device_resident", False):
             # kernel-only measurements: the round's data is staged on the device up front
             src_x = ds._pinned_data if ds._pinned_data is not None else torch.from_numpy(np.array(ds.data))
@@ -159,10 +160,16 @@ class SlicedBatches(BatchSource):
         if self.device.type != "cuda" or self._resident:
             return xb, yb, None
         with torch.cuda.stream(self._copy_stream):
+            t0 = None
+            if self.trace is not None:         # timed events only when a trace was asked for
+                t0 = torch.cuda.Event(enable_timing=True)
+                t0.record(self._copy_stream)
             xd = xb.to(self.device, non_blocking=True)
             yd = yb.to(self.device, non_blocking=True)
-            ev = torch.cuda.Event()
+            ev = torch.cuda.Event(enable_timing=t0 is not None)
             ev.record(self._copy_stream)
+            if t0 is not None:
+                self.trace.append((i, t0, ev))
         self.h2d_bytes += xb.numel() * xb.element_size() + yb.numel() * yb.element_size()
         return xd, yd, ev
 

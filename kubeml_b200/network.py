@@ -130,7 +130,8 @@ class KubeModel(ABC):
                     "train_seconds": self.train_seconds, "steps": self.steps,
                     "gpu_launches": self.gpu_launches, "merges": int(getattr(self, "merges", 0)),
                     "merge_wait_seconds": float(getattr(self._sync, "merge_wait_seconds", 0.0)),
-                    "fused_last_steps": int(getattr(self, "fused_last_steps", 0))}, 200
+                    "fused_last_steps": int(getattr(self, "fused_last_steps", 0)),
+                    **({"trace": self.trace} if getattr(self, "trace", None) else {})}, 200
         if self.task == "val":
             acc, loss, length = self.__validate()
             return {"loss": loss, "accuracy": acc, "length": length}, 200
@@ -248,6 +249,9 @@ class KubeModel(ABC):
         self.h2d_bytes = self.d2h_bytes = 0
         self._dataset._want_pinned = on_cuda and self._dataset._has_batch_transform()
         self._dataset._device_resident = bool(opts.get("device_resident_data"))
+        tracing = on_cuda and bool(opts.get("trace") or os.environ.get("KUBEML_TRACE") == "1")
+        self._dataset._trace = tracing
+        trace_steps, trace_h2d = [], []
         # per-step results are copied device->host asynchronously into page-locked memory and read
         # after the round's merge was queued: one sync per round, not one `.item()` per batch
         stage = _LossStage(self.device) if on_cuda else None
@@ -280,7 +284,14 @@ class KubeModel(ABC):
                 # the round's last optimizer step is left to the merge kernel - but only for functions
                 # that were seen to call step() exactly once per batch
                 defer = fuse_last and idx == len(batches) - 1 and self._single_step is True
+                if tracing:
+                    s0 = torch.cuda.Event(enable_timing=True)
+                    s0.record()
                 step_loss = self._graphed_step(batch, idx, defer) if graphing else self._eager_step(batch, idx, defer)
+                if tracing:
+                    s1 = torch.cuda.Event(enable_timing=True)
+                    s1.record()
+                    trace_steps.append((round_idx, idx, s0, s1))
                 if stage is not None and isinstance(step_loss, torch.Tensor) and step_loss.is_cuda:
                     stage.push(step_loss)
                 elif isinstance(step_loss, torch.Tensor):
@@ -289,6 +300,8 @@ class KubeModel(ABC):
                     loss_host += float(step_loss)
             self._on_iteration_end()
             self.h2d_bytes += getattr(batches, "h2d_bytes", 0)
+            if tracing and getattr(batches, "trace", None):
+                trace_h2d += [(round_idx, b, e0, e1) for b, e0, e1 in batches.trace]
 
             # every round but the last blocks on the merge barrier (network.py:305-306)
             if i != intervals[-1]:
@@ -299,11 +312,20 @@ class KubeModel(ABC):
                 if check is not None:            # the host is in step with the stream here: did the merge go through?
                     check(round_idx)
 
+        merge_events = list(getattr(self._sync, "_events", [])) if tracing else []
         self._sync.end_epoch(a._job_id, a._func_id, len(intervals))
         if on_cuda:
             t_ev1.record()
             torch.cuda.synchronize(self.device)
             self.train_seconds = t_ev0.elapsed_time(t_ev1) / 1e3
+            if tracing:
+                # device timeline of this worker's epoch, milliseconds from the epoch's first event: compute
+                # steps, host->device copies (copy stream) and merges - what shows the copy of batch i+1 under
+                # the compute of batch i
+                rel = lambda e0, e1: (round(t_ev0.elapsed_time(e0), 4), round(e0.elapsed_time(e1), 4))
+                self.trace = {"step": [(r, b) + rel(e0, e1) for r, b, e0, e1 in trace_steps],
+                              "h2d": [(r, b) + rel(e0, e1) for r, b, e0, e1 in trace_h2d],
+                              "merge": [(i, 0) + rel(e0, e1) for i, (e0, e1) in enumerate(merge_events)]}
         else:
             self.train_seconds = _time.perf_counter() - t_wall
         self.steps = num_iterations

@@ -85,6 +85,12 @@ class TrainJob:
         self._sched_cv = threading.Condition()
         self._barrier: Optional[MergeBarrier] = None
         self._barrier_lock = threading.Lock()
+        # Timeline of the job: host spans of every phase, and - when the workers were asked to trace
+        # (`options["trace"]` / KUBEML_TRACE=1) - their device spans (steps, H2D copies, merges) on one row per
+        # worker and stream; written to <trace_dir>/<job>.trace.json for chrome://tracing / Perfetto.
+        from ..utils.tracing import ChromeTrace
+        self.trace = ChromeTrace()
+        self.trace_dir: Optional[str] = None
         self.merge_log: List[Dict[str, Any]] = []   # (epoch, participants, seconds) per merge
         self.epoch_stats: List[Dict[str, Any]] = []  # per epoch: device-timed seconds, steps, bytes
 
@@ -122,12 +128,14 @@ class TrainJob:
         return self.history
 
     def _run(self) -> None:
-        self._init()
+        with self.trace.span("init", job=self.job_id):
+            self._init()
         self.start_time = time.time()
         req = self.task.request
         self.epoch = 1
         while self.epoch <= req.epochs:
-            self._train_epoch()
+            with self.trace.span(f"epoch {self.epoch}", parallelism=self.parallelism):
+                self._train_epoch()
 
             if not self.static and self.epoch < req.epochs and self.scheduler is not None:
                 self._ask_scheduler()
@@ -135,7 +143,8 @@ class TrainJob:
             if (self.validate_every != 0 and self.epoch % self.validate_every == 0
                     and self.epoch != req.epochs):
                 try:
-                    self._validate()
+                    with self.trace.span(f"validate {self.epoch}"):
+                        self._validate()
                 except KubeMLException as e:
                     self.log.error("error performing validation: %s", e)
 
@@ -155,6 +164,13 @@ class TrainJob:
                 self.log.error("error performing validation: %s", e)
         self._save_history()
         self.log.info("Training finished after %d epochs", min(self.epoch, req.epochs))
+        if self.trace_dir:
+            try:
+                import os
+                os.makedirs(self.trace_dir, exist_ok=True)
+                self.trace.save(os.path.join(self.trace_dir, f"{self.job_id}.trace.json"))
+            except OSError as e:
+                self.log.error("could not write the trace: %s", e)
 
     # ------------------------------------------------------------------ phases
     def _query(self, task: str, func_id: int, n: int) -> Dict[str, Any]:
@@ -231,6 +247,16 @@ class TrainJob:
             "merges": max(int(p.get("merges", 0)) for _, p, _ in ok),
             "merge_wait_seconds": max(float(p.get("merge_wait_seconds", 0.0)) for _, p, _ in ok),
             "fused_last_steps": max(int(p.get("fused_last_steps", 0)) for _, p, _ in ok)})
+        epoch_t0_us = (start - (time.time() - time.perf_counter()) - self.trace._t0) * 1e6
+        for fid, p, _ in ok:
+            tr = p.get("trace") if isinstance(p, dict) else None
+            if not tr:
+                continue
+            for lane, key in enumerate(("step", "h2d", "merge")):
+                for r, b, t_ms, d_ms in tr.get(key, []):
+                    self.trace.device_span(f"{key} r{r} b{b}" if key != "merge" else f"merge {r}",
+                                           epoch_t0_us + 1e3 * t_ms, 1e3 * d_ms, tid=fid * 4 + lane,
+                                           epoch=self.epoch, worker=fid, stream=key)
         samples = self._epoch_samples()
         self.history.images_per_second.append(samples / elapsed if elapsed > 0 and samples else 0.0)
         self._push_metrics()

@@ -105,3 +105,57 @@ def test_resnet32_function_native_round(kube_home, monkeypatch):
     assert all(np.isfinite(v) for v in h.data.train_loss) and 0.5 < h.data.train_loss[0] < 10
     assert len(h.data.accuracy) == 2 and job.epoch_stats[0]["gpu_launches"] > 0
     c.shutdown()
+
+
+def test_trace_shows_the_next_batch_copied_under_the_current_step(kube_home, monkeypatch):
+    """minibatches come from pinned host shards with cudaMemcpyAsync on a copy stream, double
+    buffered against compute.  With tracing on, the job's Chrome trace carries every step, copy and merge as
+    device-timed spans: the copy of batch b+1 must start before step b has finished."""
+    import json, os
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    monkeypatch.setenv("KUBEML_RESNET_CLASSES", "10")
+    c = Cluster(home=kube_home, max_parallelism=1, options={"trace": True})
+    rng = np.random.default_rng(0)
+    c.shard_store.create("cifar10", rng.integers(0, 255, (2048, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (2048,)),
+                         rng.integers(0, 255, (64, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (64,)))
+    req = TrainRequest(model_type="resnet34", batch_size=128, epochs=2, dataset="cifar10", lr=0.05,
+                       function_name="resnet34",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=0, k=8))
+    h, job = _run(c, req)
+    path = os.path.join(kube_home, "traces", f"{job.job_id}.trace.json")
+    ev = json.load(open(path))["traceEvents"]
+    names = {e["name"] for e in ev}
+    assert {"init", "epoch 1", "epoch 2"} <= names
+    dev = [e for e in ev if e.get("cat") == "device" and e["args"]["epoch"] == 2]
+    steps = {(e["name"]): e for e in dev if e["args"]["stream"] == "step"}
+    copies = {(e["name"]): e for e in dev if e["args"]["stream"] == "h2d"}
+    assert len(steps) == 16 and len(copies) == 16 and any(e["args"]["stream"] == "merge" for e in dev)
+    overlapped = 0
+    for b in range(7):
+        s, cnext = steps[f"step r0 b{b}"], copies[f"h2d r0 b{b + 1}"]
+        if cnext["ts"] < s["ts"] + s["dur"]:
+            overlapped += 1
+    assert overlapped >= 5, f"only {overlapped} of 7 copies ran under the previous step"
+    c.shutdown()
+
+
+def test_resume_on_the_device_path(kube_home, monkeypatch):
+    """A resumed task starts from the checkpoint written from rank 0's arena (W24)."""
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    from kubeml_b200.utils.checkpoint import load_checkpoint
+    c = Cluster(home=kube_home, max_parallelism=1)
+    rng = np.random.default_rng(0)
+    c.shard_store.create("mnist", rng.integers(0, 255, (512, 28, 28), dtype=np.uint8), rng.integers(0, 10, (512,)),
+                         rng.integers(0, 255, (64, 28, 28), dtype=np.uint8), rng.integers(0, 10, (64,)))
+    mk = lambda lr, resume="": TrainRequest(
+        model_type="lenet", batch_size=64, epochs=1, dataset="mnist", lr=lr, function_name="lenet",
+        options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=0, k=2, resume_from=resume))
+    h1, job1 = _run(c, mk(0.01))
+    sd1, _ = load_checkpoint(c.checkpoint_dir, job1.job_id)
+    h2, job2 = _run(c, mk(1e-12, resume=job1.job_id))          # a step size of nothing: the model must come back unchanged
+    sd2, _ = load_checkpoint(c.checkpoint_dir, job2.job_id)
+    for k in sd1:
+        torch.testing.assert_close(sd2[k].float(), sd1[k].float(), rtol=1e-5, atol=1e-6)
+    c.shutdown()
