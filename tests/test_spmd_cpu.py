@@ -48,3 +48,30 @@ print("ok", rank)
     for r, p in enumerate(procs):
         out, err = p.communicate(timeout=120)
         assert p.returncode == 0 and f"ok {r}" in out, err[-2000:]
+
+
+def test_dead_worker_is_detected_by_heartbeat_not_by_a_collective_timeout(tmp_path):
+    """worker liveness.  Rank 1 dies without a word while rank 0 waits for its result; the fan-out
+    must come back with an error for that function after the heartbeat timeout (2 s here), not after the
+    10-minute process-group timeout, and the next fan-out must not wait for the dead rank at all."""
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    script = os.path.join(ROOT, "tests", "mp_scripts", "spmd_liveness.py")
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES="", RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r),
+                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), KUBEML_HEARTBEAT_TIMEOUT_S="2",
+                   KUBEML_HOME=str(tmp_path), OMP_NUM_THREADS="1")
+        procs.append(subprocess.Popen([sys.executable, script], stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                                      text=True, env=env, cwd=ROOT))
+    out0, err0 = procs[0].communicate(timeout=180)
+    procs[1].wait(timeout=60)
+    assert procs[1].returncode == 17
+    assert procs[0].returncode == 0, err0[-3000:]
+    res = next(json.loads(l[7:]) for l in out0.splitlines() if l.startswith("RESULT "))
+    assert [p[0]["rank"] for p in res["first"]] == [0, 1]
+    dead = res["after_death"][1]
+    assert dead[1] == 503 and "not responding" in dead[0]["error"]
+    assert res["after_death"][0][1] == 200                 # rank 0's own share still ran
+    assert 1.0 < res["detect_s"] < 20.0
+    assert res["later"][1][1] == 503 and res["later_s"] < 1.0
