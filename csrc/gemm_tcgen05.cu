@@ -58,6 +58,8 @@ struct GemmArgs {
   int k_chunks;                          // chunks of 64 along the reduction dim (all taps included)
   // convolution description
   int kw, pad_w, pad_h, cblocks;         // filter width, padding, channel blocks per tap
+  int conv_stride;                       // convolution stride (>= 1): activation boxes walk the input with this
+                                         // element stride (the tensor map carries it), origins scale with it
   unsigned long long tap_mask;           // kConvK: taps that touch at least one real pixel
   Geometry tile_geo;                     // kConvK: output-tile pixel box
   Geometry chunk_geo;                    // kConvMN: reduction pixel box
@@ -319,8 +321,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         } else if (args.a_kind == kConvK) {
           const int tap = tap_list[kc / args.cblocks];
           const int cb = kc % args.cblocks;
-          tma_load_4d(&map_a, full_bar + s, sa, cb * kBlockK, tw0 + tap % args.kw - args.pad_w,
-                      th0 + tap / args.kw - args.pad_h, tn0);
+          tma_load_4d(&map_a, full_bar + s, sa, cb * kBlockK, tw0 * args.conv_stride + tap % args.kw - args.pad_w,
+                      th0 * args.conv_stride + tap / args.kw - args.pad_h, tn0);
         } else if (args.a_kind == kMatMN) {
 #pragma unroll
           for (int hb = 0; hb < kBlockM / 64; ++hb)
@@ -354,7 +356,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         } else {
 #pragma unroll
           for (int hb = 0; hb < BLOCK_N / 64; ++hb)
-            tma_load_4d(&map_b, full_bar + s, sb + hb * kHalfBytes, nt * BLOCK_N + hb * 64, cw + z_dw, ch + z_dh, cn);
+            tma_load_4d(&map_b, full_bar + s, sb + hb * kHalfBytes, nt * BLOCK_N + hb * 64, cw * args.conv_stride + z_dw,
+                        ch * args.conv_stride + z_dh, cn);
         }
       }
       }   // tiles
@@ -1209,7 +1212,9 @@ struct TensorSpec {          // rank-4 view, dim 0 innermost (contiguous)
   const void* ptr;
   uint64_t dim[4];
   uint64_t stride_bytes[3];  // strides of dims 1..3
-  uint32_t box[4];
+  uint32_t box[4];           // extent walked in each dimension (elements of the tensor)
+  uint32_t estride[4];       // traversal stride per dimension; 0 = 1.  A box of extent e with stride s delivers
+                             // ceil(e / s) elements: how a strided convolution reads every s-th pixel
 };
 
 int encode_map(CUtensorMap* map, const TensorSpec& t) {
@@ -1222,7 +1227,8 @@ int encode_map(CUtensorMap* map, const TensorSpec& t) {
   cuuint64_t dims[4] = {t.dim[0], t.dim[1], t.dim[2], t.dim[3]};
   cuuint64_t strides[3] = {t.stride_bytes[0], t.stride_bytes[1], t.stride_bytes[2]};
   cuuint32_t box[4] = {t.box[0], t.box[1], t.box[2], t.box[3]};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
+  cuuint32_t estr[4] = {t.estride[0] ? t.estride[0] : 1, t.estride[1] ? t.estride[1] : 1,
+                        t.estride[2] ? t.estride[2] : 1, t.estride[3] ? t.estride[3] : 1};
   KML_CHECK((reinterpret_cast<uintptr_t>(t.ptr) & 15u) == 0, "tensor map base must be 16-byte aligned");
   for (int i = 0; i < 3; ++i) KML_CHECK(strides[i] % 16 == 0, "tensor map stride %d (%llu) not a multiple of 16 bytes", i, (unsigned long long)strides[i]);
   CUresult r = d->cuTensorMapEncodeTiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(t.ptr), dims,
@@ -1489,7 +1495,7 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
   g.n_tiles = ceil_div(N, block_n);
   g.k_chunks = ceil_div(K, kBlockK);
   g.splits = splits > g.k_chunks ? g.k_chunks : splits;
-  g.z_taps = 1; g.kw = 1; g.cblocks = 1;
+  g.z_taps = 1; g.kw = 1; g.cblocks = 1; g.conv_stride = 1;
   g.out = out; g.ldo = ldo; g.m_valid = M; g.n_valid = N;
   g.bias = bias; g.relu = relu; g.out_f32 = out_f32;
   g.addend = static_cast<const __nv_bfloat16*>(epi->addend_bf16);
@@ -1512,11 +1518,20 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
 }
 
 static int conv_like(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
-                     int pad, const kml_epilogue* epi, bool dgrad, void* stream);
+                     int pad, int stride, const kml_epilogue* epi, bool dgrad, void* stream);
 
 int kml_conv2d_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                      int pad, const kml_epilogue* epi, void* stream) {
-  return conv_like(x, w, y, N, H, W, Cin, Cout, KH, KW, pad, epi, false, stream);
+  return conv_like(x, w, y, N, H, W, Cin, Cout, KH, KW, pad, 1, epi, false, stream);
+}
+
+// Strided convolution as the same implicit GEMM: the activation tensor map walks the input with element
+// stride `stride` in W and H (cuTensorMapEncodeTiled elementStrides), the box origin is stride * (output
+// pixel) + tap - pad, out-of-range pixels are zero-filled by TMA.  No im2col buffer exists.
+int kml_conv2d_fprop_strided(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH,
+                             int KW, int pad, int stride, const kml_epilogue* epi, void* stream) {
+  KML_CHECK(stride >= 1 && stride <= 8, "kml_conv2d_fprop_strided: stride must be in 1..8");
+  return conv_like(x, w, y, N, H, W, Cin, Cout, KH, KW, pad, stride, epi, false, stream);
 }
 
 // Data gradient of the stride-1 convolution y = conv(x, w, pad): dx[N,H,W,Cin] from dy[N,Ho,Wo,Cout]
@@ -1527,11 +1542,11 @@ int kml_conv2d_dgrad(const void* dy, const void* w, void* dx, int N, int H, int 
   const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
   // as a forward conv: input dy [N,Ho,Wo,Cout], output dx [N,H,W,Cin], padding K-1-pad
   KML_CHECK(KH == KW, "kml_conv2d_dgrad: square filters only");
-  return conv_like(dy, w, dx, N, Ho, Wo, Cout, Cin, KH, KW, KH - 1 - pad, epi, true, stream);
+  return conv_like(dy, w, dx, N, Ho, Wo, Cout, Cin, KH, KW, KH - 1 - pad, 1, epi, true, stream);
 }
 
 static int conv_like(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
-                     int pad, const kml_epilogue* epi, bool dgrad, void* stream) {
+                     int pad, int stride, const kml_epilogue* epi, bool dgrad, void* stream) {
   const kml_epilogue dflt = {};
   if (!epi) epi = &dflt;
   const float* bias = epi->bias;
@@ -1540,7 +1555,7 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
   KML_CHECK(x && w && y, "kml_conv2d_fprop: null pointer");
   KML_CHECK(Cin % 64 == 0, "kml_conv2d_fprop: Cin (%d) must be a multiple of 64 (use the im2col path otherwise)", Cin);
   KML_CHECK(Cout % 8 == 0, "kml_conv2d_fprop: Cout (%d) must be a multiple of 8", Cout);
-  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   KML_CHECK(Ho > 0 && Wo > 0 && KH * KW <= 64, "kml_conv2d_fprop: bad geometry");
   GemmArgs g{};
   KML_CHECK(make_geometry(Wo, Ho, kBlockM, &g.tile_geo),
@@ -1552,7 +1567,9 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
   ta.dim[0] = Cin; ta.dim[1] = W; ta.dim[2] = H; ta.dim[3] = N;
   ta.stride_bytes[0] = static_cast<uint64_t>(Cin) * 2; ta.stride_bytes[1] = ta.stride_bytes[0] * W;
   ta.stride_bytes[2] = ta.stride_bytes[1] * H;
-  ta.box[0] = 64; ta.box[1] = g.tile_geo.bw; ta.box[2] = g.tile_geo.bh; ta.box[3] = g.tile_geo.bn;
+  ta.box[0] = 64; ta.box[1] = g.tile_geo.bw * stride; ta.box[2] = g.tile_geo.bh * stride; ta.box[3] = g.tile_geo.bn;
+  ta.estride[1] = ta.estride[2] = stride;
+  KML_CHECK(ta.box[1] <= 256 && ta.box[2] <= 256, "kml_conv2d_fprop: output tile x stride exceeds the TMA box limit");
   const long long Kt = static_cast<long long>(KH) * KW * Cin;
   tb.ptr = w;
   tb.dim[0] = Kt; tb.dim[1] = Cout; tb.dim[2] = tb.dim[3] = 1;
@@ -1564,12 +1581,17 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
   int ntaps = 0;
   for (int kh = 0; kh < KH; ++kh)
     for (int kw = 0; kw < KW; ++kw) {
-      const bool h_hit = (kh - pad) <= (H - 1) && (Ho - 1 + kh - pad) >= 0;
-      const bool w_hit = (kw - pad) <= (W - 1) && (Wo - 1 + kw - pad) >= 0;
+      // some output row / column reads a real pixel through this tap: s*o + k - pad in [0, H) for an o in [0, Ho)
+      auto hits = [&](int k, int extent, int outs) {
+        for (int o = 0; o < outs; ++o) { const int i = stride * o + k - pad; if (i >= 0 && i < extent) return true; }
+        return false;
+      };
+      const bool h_hit = hits(kh, H, Ho);
+      const bool w_hit = hits(kw, W, Wo);
       if (h_hit && w_hit) { mask |= 1ull << (kh * KW + kw); ++ntaps; }
     }
   g.a_kind = kConvK; g.b_kind = kMatK;
-  g.tap_mask = mask; g.kw = KW; g.pad_w = pad; g.pad_h = pad; g.cblocks = Cin / 64;
+  g.tap_mask = mask; g.kw = KW; g.pad_w = pad; g.pad_h = pad; g.cblocks = Cin / 64; g.conv_stride = stride;
   const long long Mtot = static_cast<long long>(N) * Ho * Wo;
   const int imgs_per_tile = g.tile_geo.bn;
   g.m_tiles = g.tile_geo.tiles_h * ceil_div(N, imgs_per_tile);
@@ -1610,9 +1632,15 @@ static int conv_like(const void* x, const void* w, void* y, int N, int H, int W,
 
 int kml_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                      int pad, int splits, int block_n, void* stream) {
+  return kml_conv2d_wgrad_strided(x, dy, dw, N, H, W, Cin, Cout, KH, KW, pad, 1, splits, block_n, stream);
+}
+
+int kml_conv2d_wgrad_strided(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int KH,
+                             int KW, int pad, int stride, int splits, int block_n, void* stream) {
   KML_CHECK(x && dy && dw, "kml_conv2d_wgrad: null pointer");
+  KML_CHECK(stride >= 1 && stride <= 8, "kml_conv2d_wgrad: stride must be in 1..8");
   KML_CHECK(Cin % 8 == 0 && Cout % 8 == 0, "kml_conv2d_wgrad: channel counts must be multiples of 8");
-  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   KML_CHECK(Ho > 0 && Wo > 0, "kml_conv2d_wgrad: bad geometry");
   GemmArgs g{};
   KML_CHECK(make_geometry(Wo, Ho, kBlockK, &g.chunk_geo),
@@ -1628,9 +1656,11 @@ int kml_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int
   tb.dim[0] = Cin; tb.dim[1] = W; tb.dim[2] = H; tb.dim[3] = N;
   tb.stride_bytes[0] = static_cast<uint64_t>(Cin) * 2; tb.stride_bytes[1] = tb.stride_bytes[0] * W;
   tb.stride_bytes[2] = tb.stride_bytes[1] * H;
-  tb.box[0] = 64; tb.box[1] = g.chunk_geo.bw; tb.box[2] = g.chunk_geo.bh; tb.box[3] = g.chunk_geo.bn;
+  tb.box[0] = 64; tb.box[1] = g.chunk_geo.bw * stride; tb.box[2] = g.chunk_geo.bh * stride; tb.box[3] = g.chunk_geo.bn;
+  tb.estride[1] = tb.estride[2] = stride;     // the input is read at stride * (output pixel) + tap - pad
+  KML_CHECK(tb.box[1] <= 256 && tb.box[2] <= 256, "kml_conv2d_wgrad: pixel box x stride exceeds the TMA box limit");
   g.a_kind = kConvMN; g.b_kind = kConvMN;
-  g.kw = KW; g.pad_w = pad; g.pad_h = pad; g.cblocks = 1;
+  g.kw = KW; g.pad_w = pad; g.pad_h = pad; g.cblocks = 1; g.conv_stride = stride;
   g.m_tiles = ceil_div(Cout, kBlockM);
   g.n_tiles = ceil_div(Cin, block_n);
   g.k_chunks = g.chunk_geo.tiles_h * ceil_div(N, g.chunk_geo.bn);

@@ -215,6 +215,12 @@ int kml_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_m
  * Needs Cin % 64 == 0, Cout % 8 == 0 and a power-of-two output grid (else use im2col + gemm). */
 int kml_conv2d_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout,
                      int KH, int KW, int pad, const kml_epilogue* epi, void* stream);
+/* The same with a stride (ResNet's 3x3/2 and 1x1/2 convolutions): still no im2col buffer, the tensor map
+ * walks the input with an element stride.  Output grid (H+2p-K)/s+1 must be a power of two. */
+int kml_conv2d_fprop_strided(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout,
+                             int KH, int KW, int pad, int stride, const kml_epilogue* epi, void* stream);
+int kml_conv2d_wgrad_strided(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout,
+                             int KH, int KW, int pad, int stride, int splits, int block_n, void* stream);
 /* Data gradient of the same convolution from the forward filter (no transposed weight copy). */
 int kml_conv2d_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
                      int KH, int KW, int pad, const kml_epilogue* epi, void* stream);

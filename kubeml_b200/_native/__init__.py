@@ -115,6 +115,10 @@ def _declare(lib) -> None:
         c_longlong, c_int, c_int, c_int, POINTER(Epilogue), c_void_p)
     sig("kml_conv2d_fprop", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
         c_int, c_int, c_int, POINTER(Epilogue), c_void_p)
+    sig("kml_conv2d_fprop_strided", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_int, c_int, c_int, POINTER(Epilogue), c_void_p)
+    sig("kml_conv2d_wgrad_strided", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+        c_int, c_int, c_int, c_int, c_int, c_int, c_void_p)
     sig("kml_conv2d_dgrad", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
         c_int, c_int, c_int, POINTER(Epilogue), c_void_p)
     sig("kml_conv2d_wgrad", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,

@@ -44,6 +44,14 @@ def _ceil(a: int, b: int) -> int:
     return (a + b - 1) // b * b
 
 
+def live_taps(H: int, W: int, Ho: int, Wo: int, k: int, p: int, s: int = 1) -> int:
+    """Filter taps that read at least one real pixel (the others lie entirely in the zero padding and are
+    skipped by the implicit GEMM): 1 of 9 on a 1x1 map, 4 of 9 for a 3x3/2 convolution from 2x2 to 1x1."""
+    def hit(kk, extent, outs):
+        return any(0 <= s * o + kk - p < extent for o in range(outs))
+    return sum(1 for kh in range(k) for kw in range(k) if hit(kh, H, Ho) and hit(kw, W, Wo))
+
+
 class NConv2d(nn.Module):
     """Parameter holder with torch's `Conv2d` naming: `weight` [Cout,Cin,KH,KW] (+ `bias`)."""
 
@@ -62,8 +70,10 @@ class NConv2d(nn.Module):
 
     @property
     def direct(self) -> bool:
-        """Can the shifted-TMA implicit GEMM take this layer (else im2col + GEMM)?"""
-        return self.stride == 1 and self.cin % 64 == 0 and self.cout % 8 == 0
+        """Can the shifted-TMA implicit GEMM take this layer (else im2col + GEMM)?  Any stride: the tensor
+        map walks the input with an element stride.  (Only the data gradient of a strided layer still goes
+        through a column buffer.)"""
+        return self.cin % 64 == 0 and self.cout % 8 == 0
 
 
 class NBatchNorm2d(nn.Module):
@@ -427,12 +437,10 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
     m_tiles = (M + 127) // 128
     bn_ = pick_block_n(m_tiles, conv.cout)
     tiles = m_tiles * ((conv.cout + bn_ - 1) // bn_)
-    direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p)
+    direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p, s)
     Kd = k * k * conv.cin
     if direct:
-        live = sum(1 for kh in range(k) for kw in range(k)
-                   if (kh - p) <= H - 1 and (Ho - 1 + kh - p) >= 0 and (kw - p) <= W - 1 and (Wo - 1 + kw - p) >= 0)
-        chunks = live * (conv.cin // 64)
+        chunks = live_taps(H, W, Ho, Wo, k, p, s) * (conv.cin // 64)
     else:
         chunks = (Kd + 63) // 64
     if allow_slabs and _cluster_enabled() and (want_stats or fold):
@@ -445,7 +453,7 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
         cl = S > 1 or stats is not None
         if direct:
             ops.conv2d_fprop(x, conv.w_bf16, p, bias=bias, relu=relu, out=y, block_n=bn_, splits=S, cluster=cl,
-                             stats=stats)
+                             stats=stats, stride=s)
         else:
             ldk = _ceil(Kd, 64)
             cols = B.get(tag + ".cols", (M, ldk))
@@ -463,7 +471,7 @@ def conv_forward(conv: NConv2d, x: torch.Tensor, B: Buffers, tag: str, bias=None
         y = B.get(tag + ".y", (N, Ho, Wo, conv.cout))
         ebias, erelu = bias, relu
     if direct:
-        ops.conv2d_fprop(x, conv.w_bf16, p, bias=ebias, relu=erelu, out=y, block_n=bn_, splits=S, slabs=S > 1)
+        ops.conv2d_fprop(x, conv.w_bf16, p, bias=ebias, relu=erelu, out=y, block_n=bn_, splits=S, slabs=S > 1, stride=s)
     else:
         ldk = _ceil(Kd, 64)
         cols = B.get(tag + ".cols", (M, ldk))
@@ -489,12 +497,10 @@ def conv_bn_forward(conv: NConv2d, bn: "NBatchNorm2d", x: torch.Tensor, B: Buffe
         Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
         M = N * Ho * Wo
         m_tiles = (M + 127) // 128
-        direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p)
+        direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p, s)
         Kd = k * k * conv.cin
         if direct:
-            live = sum(1 for kh in range(k) for kw in range(k)
-                       if (kh - p) <= H - 1 and (Ho - 1 + kh - p) >= 0 and (kw - p) <= W - 1 and (Wo - 1 + kw - p) >= 0)
-            chunks = live * (conv.cin // 64)
+            chunks = live_taps(H, W, Ho, Wo, k, p, s) * (conv.cin // 64)
         else:
             chunks = (Kd + 63) // 64
         plan = fused_plan(x.device, m_tiles, conv.cout, chunks, pick_block_n(m_tiles, conv.cout), False)
@@ -507,7 +513,7 @@ def conv_bn_forward(conv: NConv2d, bn: "NBatchNorm2d", x: torch.Tensor, B: Buffe
             bf = ops.BnFwd(bn.weight.data, bn.bias.data, bn.running_mean, bn.running_var, bn.num_batches_tracked,
                            mean, istd, raw, res=res, relu=relu, eps=bn.eps, momentum=bn.momentum)
             if direct:
-                ops.conv2d_fprop(x, conv.w_bf16, p, out=y, block_n=bn_, splits=S, cluster=True, bn_fuse=bf)
+                ops.conv2d_fprop(x, conv.w_bf16, p, out=y, block_n=bn_, splits=S, cluster=True, bn_fuse=bf, stride=s)
             else:
                 ldk = _ceil(Kd, 64)
                 cols = B.get(tag + ".cols", (M, ldk))
@@ -542,7 +548,7 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
     Ho, Wo = dy.shape[1], dy.shape[2]
     M = N * Ho * Wo
     dy2 = dy.view(M, conv.cout)
-    direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p)
+    direct = conv.direct and ops.conv2d_fprop_supported(H, W, conv.cin, conv.cout, k, k, p, s)
     chunks = (M + 63) // 64
     if direct:
         bn_w = 128 if conv.cin > 64 else 64
@@ -552,15 +558,24 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
         if sp > 1:
             B.split_grads.append(conv.w_grad)
         with B.on_side():
-            ops.conv2d_wgrad(x, dy, k, k, p, out=conv.w_grad, splits=sp, block_n=bn_w)
+            ops.conv2d_wgrad(x, dy, k, k, p, out=conv.w_grad, splits=sp, block_n=bn_w, stride=s)
         if not need_dx:
             return None
+        if s != 1:
+            # A strided layer's data gradient scatters: dY . W into a column buffer, then col2im gathers it
+            # (+ addend) into dX.  Forward and weight gradient above needed no such buffer.
+            Kd = k * k * conv.cin
+            dcols = B.get(tag + ".dcols", (M, Kd))
+            ops.gemm_bf16(dy2, conv.w_bf16.view(conv.cout, Kd), b_mn=True, out=dcols,
+                          block_n=pick_block_n((M + 127) // 128, Kd))
+            dx = B.get(tag + ".dx", (N, H, W, conv.cin))
+            K.col2im(dcols, addend, dx, k, k, s, p)
+            return Act(dx)
         m_tiles = (N * H * W + 127) // 128
         bn_d = pick_block_n(m_tiles, conv.cin)
         dtiles = m_tiles * ((conv.cin + bn_d - 1) // bn_d)
         pd = k - 1 - p
-        live = sum(1 for kh in range(k) for kw in range(k)
-                   if (kh - pd) <= Ho - 1 and (H - 1 + kh - pd) >= 0 and (kw - pd) <= Wo - 1 and (W - 1 + kw - pd) >= 0)
+        live = live_taps(Ho, Wo, H, W, k, pd)
         if allow_slabs and _cluster_enabled():
             bn_d, S = plan_cluster(m_tiles, conv.cin, live * (conv.cout // 64), bn_d)
             if bn_next is not None and _bn_fuse_enabled():

@@ -201,27 +201,31 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: boo
     return out
 
 
-def conv2d_fprop_supported(H: int, W: int, Cin: int, Cout: int, KH: int, KW: int, pad: int) -> bool:
-    Ho, Wo = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+def conv2d_fprop_supported(H: int, W: int, Cin: int, Cout: int, KH: int, KW: int, pad: int, stride: int = 1) -> bool:
+    """Can the implicit GEMM (shifted, strided TMA boxes; no im2col buffer) take this convolution forward and
+    for its weight gradient?  (The data gradient is implicit for stride 1 only.)"""
+    Ho, Wo = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
     pow2 = lambda v: v > 0 and (v & (v - 1)) == 0
-    return Cin % 64 == 0 and Cout % 8 == 0 and pow2(Ho) and pow2(Wo) and Wo <= 128 and KH * KW <= 64
+    return (Cin % 64 == 0 and Cout % 8 == 0 and pow2(Ho) and pow2(Wo) and Wo * stride <= 128 and KH * KW <= 64
+            and 1 <= stride <= 8)
 
 
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[torch.Tensor] = None,
                  relu: bool = False, out_dtype: torch.dtype = torch.bfloat16, splits: int = 1,
                  block_n: int = 0, out: Optional[torch.Tensor] = None, slabs: bool = False,
-                 cluster: bool = False, stats: Optional[torch.Tensor] = None, bn_fuse=None) -> torch.Tensor:
-    """Stride-1 convolution, NHWC.  x: [N,H,W,Cin] bf16; w: [Cout,KH,KW,Cin] bf16 -> [N,Ho,Wo,Cout].
+                 cluster: bool = False, stats: Optional[torch.Tensor] = None, bn_fuse=None,
+                 stride: int = 1) -> torch.Tensor:
+    """Convolution (any stride the TMA box allows), NHWC.  x: [N,H,W,Cin] bf16; w: [Cout,KH,KW,Cin] bf16 -> [N,Ho,Wo,Cout].
     The data gradient of a stride-1 convolution is this same op applied to dY with the flipped,
     channel-transposed filter and pad' = K-1-pad."""
     N, H, W, Cin = x.shape
     Cout, KH, KW, _ = w.shape
-    Ho, Wo = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+    Ho, Wo = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
     if out is not None:
         out_dtype = out.dtype
     if not x.is_cuda:
         y = F.conv2d(x.permute(0, 3, 1, 2).float(), w.permute(0, 3, 1, 2).float(),
-                     None if bias is None else bias.float(), padding=pad)
+                     None if bias is None else bias.float(), padding=pad, stride=stride)
         if relu:
             y = torch.relu(y)
         y = y.permute(0, 2, 3, 1).contiguous().to(out_dtype)
@@ -244,8 +248,8 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, pad: int, *, bias: Optional[t
         (torch.zeros if splits > 1 and not cluster else torch.empty)((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
     e = _epi(bias, None, relu, out_f32, splits, block_n, slabs and not cluster, cluster, stats,
              bn_fuse=bn_fuse, device=x.device)
-    _native.check(_native.lib().kml_conv2d_fprop(
-        x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, ctypes.byref(e),
+    _native.check(_native.lib().kml_conv2d_fprop_strided(
+        x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, int(stride), ctypes.byref(e),
         _native.stream_ptr()), "kml_conv2d_fprop")
     return y
 
@@ -298,14 +302,15 @@ def conv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, pad: int, H: int, W: int, *,
 
 
 def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, KH: int, KW: int, pad: int, *,
-                 out: Optional[torch.Tensor] = None, splits: int = 1, block_n: int = 0) -> torch.Tensor:
-    """Weight gradient of the stride-1 NHWC convolution: dW[Cout,KH,KW,Cin] fp32.  A caller-provided
+                 out: Optional[torch.Tensor] = None, splits: int = 1, block_n: int = 0,
+                 stride: int = 1) -> torch.Tensor:
+    """Weight gradient of the NHWC convolution: dW[Cout,KH,KW,Cin] fp32.  A caller-provided
     `out` must hold zeros (K-splits are combined with red.add; a single split stores)."""
     N, H, W, Cin = x.shape
     Cout = dy.shape[3]
     if not x.is_cuda:
         g = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2).float(), (Cout, Cin, KH, KW),
-                                        dy.permute(0, 3, 1, 2).float(), padding=pad)
+                                        dy.permute(0, 3, 1, 2).float(), padding=pad, stride=stride)
         g = g.permute(0, 2, 3, 1).contiguous()
         if out is not None:
             out.add_(g)
@@ -314,7 +319,7 @@ def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, KH: int, KW: int, pad: int, 
     assert x.is_contiguous() and dy.is_contiguous()
     if out is None:
         out = torch.zeros((Cout, KH, KW, Cin), dtype=torch.float32, device=x.device)
-    _native.check(_native.lib().kml_conv2d_wgrad(
-        x.data_ptr(), dy.data_ptr(), out.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, int(splits),
+    _native.check(_native.lib().kml_conv2d_wgrad_strided(
+        x.data_ptr(), dy.data_ptr(), out.data_ptr(), N, H, W, Cin, Cout, KH, KW, pad, int(stride), int(splits),
         int(block_n), _native.stream_ptr()), "kml_conv2d_wgrad")
     return out
