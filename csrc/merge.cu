@@ -35,6 +35,15 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
   float4 v;
   asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];"
@@ -236,11 +245,13 @@ kavg_merge_kernel(const kml_merge_params p) {
   uint32_t eff = p.participants;
   if (sync_ranks) {
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-      __threadfence_system();
+      // one system-scope fence, then plain flag stores to all peers at once (a release store per peer
+      // would serialise a fence round trip per peer: 8 x ~2 us on the latency-bound small merges)
+      fence_acq_rel_sys();
 #pragma unroll
       for (int r = 0; r < KML_MAX_RANKS; ++r)
         if ((p.participants >> r) & 1u)
-          st_release_sys(&reinterpret_cast<MergePad*>(p.flags[r])->ready[p.my_rank], gen);
+          st_relaxed_sys(&reinterpret_cast<MergePad*>(p.flags[r])->ready[p.my_rank], gen);
       unsigned long long ts0;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ts0));
       uint32_t missing = 0;
@@ -248,11 +259,11 @@ kavg_merge_kernel(const kml_merge_params p) {
 #pragma unroll
       for (int r = 0; r < KML_MAX_RANKS; ++r) {
         if (!((p.participants >> r) & 1u)) continue;
-        while (!reached(ld_acquire_sys(&pad->ready[r]), gen)) {
+        while (!reached(ld_relaxed_sys(&pad->ready[r]), gen)) {
           if (static_cast<unsigned long long>(clock64() - t0) > limit) { missing |= 1u << r; break; }
-          __nanosleep(32);
         }
       }
+      fence_acq_rel_sys();                               // acquire once for all the flags just seen
       unsigned long long ts1;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ts1));
       pad->wait_ns += ts1 - ts0;                         // how long the slowest peer kept this GPU waiting
@@ -260,7 +271,7 @@ kavg_merge_kernel(const kml_merge_params p) {
       uint32_t dead = 0;
 #pragma unroll
       for (int r = 0; r < KML_MAX_RANKS; ++r) {
-        const uint32_t d = ld_acquire_sys(&pad->dead_from[r]);
+        const uint32_t d = ld_relaxed_sys(&pad->dead_from[r]);
         if (d != 0 && reached(gen, d)) dead |= 1u << r;
       }
       uint32_t decision = p.participants & ~dead;
@@ -404,10 +415,10 @@ kavg_merge_kernel(const kml_merge_params p) {
     __threadfence_system();
     const unsigned fin = atomicAdd(&pad->fin_count, 1u) + 1u - s_fbase;
     if (fin == gridDim.x) {
-      __threadfence_system();
+      fence_acq_rel_sys();
 #pragma unroll
       for (int r = 0; r < KML_MAX_RANKS; ++r)
-        if ((eff >> r) & 1u) st_release_sys(&reinterpret_cast<MergePad*>(p.flags[r])->done[p.my_rank], gen);
+        if ((eff >> r) & 1u) st_relaxed_sys(&reinterpret_cast<MergePad*>(p.flags[r])->done[p.my_rank], gen);
       pad->fin_base = s_fbase + gridDim.x;              // every CTA of this launch has read it
     }
   }
@@ -425,13 +436,13 @@ kavg_merge_kernel(const kml_merge_params p) {
         if ((eff >> r) & 1u) { if (c == j) owner = r; ++c; }
       if (threadIdx.x == 0) {
         const long long t0 = clock64();
-        while (!reached(ld_acquire_sys(&pad->done[owner]), gen)) {
+        while (!reached(ld_relaxed_sys(&pad->done[owner]), gen)) {
           if (static_cast<unsigned long long>(clock64() - t0) > limit) {
             if (p.status) atomicOr(p.status, KML_MERGE_LATE | (1 << owner));     // a peer died mid-merge
             break;
           }
-          __nanosleep(32);
         }
+        fence_acq_rel_sys();
       }
       __syncthreads();
       if (wb != nullptr) to_bf16(n4 * j / nparts, n4 * (j + 1) / nparts);
