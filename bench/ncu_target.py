@@ -17,6 +17,27 @@ for it in range(int(sys.argv[1]) if len(sys.argv) > 1 else 3):
     ops.conv2d_dgrad(x, w, 1, 4, 4, out=y, block_n=64)
     dw = torch.zeros(128, 3, 3, 128, device=dev)
     ops.conv2d_wgrad(x, x, 3, 3, 1, out=dw, splits=16, block_n=128)
+    # round 2: convolution + BatchNorm (+ReLU) in one launch, and data gradient + BatchNorm backward in one
+    # launch (kml_bn_fuse), at the layer2 shape the models use; a stride-2 convolution without im2col
+    from kubeml_b200.models.native import fused_plan, pick_block_n
+    C = 128
+    gam, bet = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    sm_, si_ = torch.empty(C, device=dev), torch.empty(C, device=dev)
+    raw = torch.empty(Nb, 4, 4, C, device=dev, dtype=torch.bfloat16)
+    yf = torch.empty_like(raw)
+    bn_, S_ = fused_plan(dev, 16, C, 18, pick_block_n(16, C), False)
+    ops.conv2d_fprop(x, w, 1, out=yf, block_n=bn_, splits=S_, cluster=True,
+                     bn_fuse=ops.BnFwd(gam, bet, rm, rv, None, sm_, si_, raw, relu=True))
+    dgm, dbt = torch.empty(C, device=dev), torch.empty(C, device=dev)
+    dxf, gf_ = torch.empty_like(raw), torch.empty_like(raw)
+    bn_, S_ = fused_plan(dev, 16, C, 18, pick_block_n(16, C), True)
+    ops.conv2d_dgrad(x, w, 1, 4, 4, addend=raw, out=dxf, block_n=bn_, splits=S_, cluster=True,
+                     bn_fuse=ops.BnBwd(gam, sm_, si_, raw, dgm, dbt, mask_y=yf, raw_out=gf_))
+    x8 = torch.randn(Nb, 8, 8, 64, device=dev).bfloat16()
+    w2 = torch.randn(128, 3, 3, 64, device=dev).bfloat16()
+    ops.conv2d_fprop(x8, w2, 1, stride=2, splits=4, cluster=True, out=torch.empty(Nb, 4, 4, 128, device=dev, dtype=torch.bfloat16))
+    ops.conv2d_wgrad(x8, raw, 3, 3, 1, stride=2, splits=8, out=torch.zeros(128, 3, 3, 64, device=dev))
     # a large plain GEMM so the tensor pipe is visible: 8192 x 4096 x 4096
     A = torch.randn(8192, 4096, device=dev).bfloat16(); Bm = torch.randn(4096, 4096, device=dev).bfloat16()
     o = torch.empty(8192, 4096, device=dev, dtype=torch.bfloat16)
