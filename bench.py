@@ -178,13 +178,23 @@ def run_own(args) -> int:
     run_job(f"{ds_prefix}_w{args.warmup}", resident=False)
     run_job(f"{ds_prefix}_w{args.warmup}", resident=True)
 
+    # Each timed run is one epoch of exactly `--steps` steps per worker.  The run is repeated (3 times by
+    # default) and the MEDIAN run is reported: a single 30-200 ms region is at the mercy of one host hiccup
+    # (round 1's N=4 end-to-end outlier); every sample is listed under "samples_ms_per_step".
     sampler = ClockSampler(0).start()
-    job_e2e = run_job(f"{ds_prefix}_t{args.steps}", resident=False)
-    job_dev = run_job(f"{ds_prefix}_t{args.steps}", resident=True)
+    reps = max(1, int(os.environ.get("KUBEML_BENCH_REPEATS", "3")))
+    e2e_jobs = [run_job(f"{ds_prefix}_t{args.steps}", resident=False) for _ in range(reps)]
+    dev_jobs = [run_job(f"{ds_prefix}_t{args.steps}", resident=True) for _ in range(reps)]
     clocks = sampler.stop()
     rt.stop()
 
+    def median_job(jobs):
+        ranked = sorted(jobs, key=lambda j: j.epoch_stats[-1]["train_seconds"])
+        return ranked[len(ranked) // 2]
+    job_dev, job_e2e = median_job(dev_jobs), median_job(e2e_jobs)
     sd, se = job_dev.epoch_stats[-1], job_e2e.epoch_stats[-1]
+    samples = {"device": [round(1e3 * j.epoch_stats[-1]["train_seconds"] / max(int(j.epoch_stats[-1]["steps"]), 1), 4) for j in dev_jobs],
+               "e2e": [round(1e3 * j.epoch_stats[-1]["train_seconds"] / max(int(j.epoch_stats[-1]["steps"]), 1), 4) for j in e2e_jobs]}
     steps = int(sd["steps"])
     imgs = N * steps * BATCH
     value = imgs / sd["train_seconds"]
@@ -203,6 +213,7 @@ def run_own(args) -> int:
                    "global_batch": BATCH * N,
                    "seq_len": None, "parallelism": f"kavg-dp{N}", "k": K_AVG, "model_impl": args.model_impl,
                    "optimizer": "Adam lr 1e-4" if vgg else "SGD lr 0.1 wd 1e-4", "merges_in_timed_region": merges,
+                   "timed_runs": reps, "reported": "median run",
                    "fused_last_sgd_steps": int(sd.get("fused_last_steps", 0)),
                    "l2": "per-step working set (fp32 weights+grads 175 MB, bf16 copies, activations) "
                          "exceeds the 126 MB L2; no explicit flush"},
@@ -215,6 +226,7 @@ def run_own(args) -> int:
                 "d2h_bytes_per_step": int(se["d2h_bytes"] / max(int(se["steps"]), 1)),
                 "ms_per_step": round(1e3 * se["train_seconds"] / max(int(se["steps"]), 1), 4)},
         "gpu_launches": int(sd["gpu_launches"]),
+        "samples_ms_per_step": samples,
         "clocks": clocks,
     }
     print(json.dumps(out), flush=True)

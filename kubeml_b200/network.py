@@ -149,8 +149,46 @@ class KubeModel(ABC):
             # into the peers and takes part in the epoch's membership barrier
             self._set_device()
             self._sync.attach(self)
+            if (self._inv.query or {}).get("joinFor") == "train":
+                self._prewarm_join()
             return {}, 200
         raise KubeMLException(f"Task {self.task} not recognized", 400)
+
+    def _prewarm_join(self) -> None:
+        """An idle worker of a growing job gets ready while the active ones train: the first time it is told to
+        `join` a training epoch it runs the user's train() on one batch - the eager warm-up calls and the CUDA
+        graph captures (with and without the deferred optimizer step) that its first real epoch would otherwise
+        pay while its peers wait for it in the merge.  Its replica is scratch until then: the sync engine copies
+        the merged model again when the worker becomes active (`RankSync._stale`)."""
+        ws = self._inv.worker_state if self._inv.worker_state is not None else {}
+        done = ws.setdefault("prewarmed", set())
+        job = self.args._job_id
+        if (job in done or self.device is None or self.device.type != "cuda" or not self._graphs_enabled()
+                or os.environ.get("KUBEML_PREWARM_JOIN", "1") == "0" or self._dataset.num_docs <= 0):
+            return
+        done.add(job)
+        try:
+            self._network.train()
+            self._config_optimizer()
+            self._sync.load_reference(job, self._network)
+            ds = self._dataset
+            ds._want_pinned, ds._device_resident, ds._trace = False, False, False
+            ds._load_train_data(start=0, end=min(self._dataset.num_docs, -(-self.batch_size // 64)))
+            batches = ds._batches(self.batch_size, self.device)
+            batch = next(iter(batches))
+            can_fuse = getattr(self._sync, "can_fuse_last_step", None)
+            variants = [False] + ([True] if can_fuse is not None and can_fuse(self.optimizer) else [])
+            for defer in variants:
+                for _ in range(4):            # two eager calls, the capture, one replay
+                    self._graphed_step(batch, 0, defer and self._single_step is True)
+                    if getattr(self.optimizer, "_deferred", False):
+                        self.optimizer._deferred = False
+            torch.cuda.synchronize(self.device)
+            self._sync._stale = True
+            self.logger.info("function %d pre-warmed for job %s", self.args._func_id, job)
+        except Exception as e:  # noqa: BLE001 - a failed warm-up only costs time later
+            self.logger.warning("pre-warm of function %d failed: %s", self.args._func_id, e)
+            self._sync._stale = True
 
     # ---- optimizer (network.py:99-138) ---------------------------------------------------------
     def _config_optimizer(self) -> None:

@@ -107,8 +107,11 @@ class RankSync:
         net = kube_model._network
         joined = self.arena is None
         self._ensure_arena(net, kube_model.device, copy_in=False)
-        if joined:
+        if joined or (a._task == "train" and getattr(self, "_stale", False)):
+            # a worker that joins the job, or one that used its replica as scratch while idle (pre-warm),
+            # starts from the merged model
             self.group.copy_reference_into(self)
+            self._stale = False
         self.arena.bind(net, copy_in=False)      # also refreshes the bf16 operand copy
         join_for = (kube_model._inv.query or {}).get("joinFor") if a._task == "join" else None
         if a._task == "train" or join_for == "train":
