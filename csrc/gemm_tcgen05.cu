@@ -441,7 +441,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         __syncwarp();
         if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
       }
-      if (args.cluster_reduce) {
+      if (BN_MODE != 0 || args.cluster_reduce) {
         // partial tile -> own shared memory (the pipeline ring is idle now); the reduction across the
         // cluster and the real epilogue follow after the role branches
         float* part = reinterpret_cast<float*>(smem_a) + (q * 32 + lane) * (BLOCK_N + 4) + c0;
@@ -451,6 +451,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                                                              __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
         continue;
       }
+      if constexpr (BN_MODE == 0) {      // (the fused-BatchNorm instantiations never store from here)
       if (!row_ok) continue;
       const int ncol0 = nt * BLOCK_N + c0;                // column within the (per-tap) N range
       const long long off = static_cast<long long>(row) * args.ldo + col_base + c0 +
@@ -526,6 +527,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             if (ncol0 + j < args.n_valid) o[j] = __float2bfloat16_rn(f[j]);
         }
       }
+      }   // BN_MODE == 0
     }
     }   // tiles
     tcgen05_fence_before();
@@ -534,315 +536,265 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   __syncthreads();
   if constexpr (BN_MODE != 0) {
   // ===== cluster reduction + fused BatchNorm (kml_bn_fuse); instantiated only for the variants that use it =====
+  // Everything here runs once per CTA on a cold instruction cache (ncu: ~12 % of this kernel's stall samples
+  // were instruction fetches), so the code is kept small: one mode per instantiation, 8-byte vector accesses
+  // only (the host checks N % 4 == 0 and ldo % 4 == 0, so a float4 column group is either whole or absent).
   {
+    constexpr bool kFwd = BN_MODE == 1;
     const Tile T0 = tile_at(tile0);                      // cluster mode is never persistent: one tile
     const int mt = T0.mt, nt = T0.nt, split = T0.split;
-    // ---- split-K reduction across the cluster through distributed shared memory ----------------
-    // CTA `split` owns rows [rbeg, rend) of the 128-row tile: it adds the partial tiles of all
-    // peers for those rows, applies the epilogue once and writes the final output.  Column sums
-    // for BatchNorm fall out of the same pass (a thread keeps the same 4 columns for all its rows).
-    // All six warps take part (the producer and MMA warps are done).  The pass is latency-bound
-    // (a DSMEM round trip and up to three L2 round trips per element), so each thread works on kU rows
-    // at a time with every load of the batch issued before the first use.
     constexpr int kPartStride = BLOCK_N + 4;
     constexpr int kGroups = BLOCK_N / 4;                 // float4 groups per row
-    constexpr int kRowStep = kNumThreads / kGroups;      // rows covered by one sweep of the CTA
+    constexpr int kRowStep = kNumThreads / kGroups;      // rows covered by one sweep of the CTA (all six warps)
     constexpr int kWarps = kNumThreads / 32;
-    constexpr int kU = 4;
+    constexpr int kU = 4;                                // rows a thread has in flight (latency-bound pass)
     float* part = reinterpret_cast<float*>(smem_a);
     float* st_sm = part + kBlockM * kPartStride;        // [6 warps][2][BLOCK_N] per-warp column sums
-    float* pv_sm = st_sm + 2 * kWarps * BLOCK_N;         // [BLOCK_N] pivots of the fused forward statistics
-    float* co = pv_sm + BLOCK_N;                         // [3][BLOCK_N] per-column coefficients of the fused BatchNorm
-    constexpr int bnm = BN_MODE;
+    float* pv_sm = st_sm + 2 * kWarps * BLOCK_N;         // [BLOCK_N] pivots of the forward statistics
+    float* co = pv_sm + BLOCK_N;                         // [3][BLOCK_N] per-column coefficients
     const int et = threadIdx.x;
-    if (bnm != 0) {
-      // Everything per-channel that does not depend on the batch statistics is fetched now, before the
-      // barriers.  Forward: pivot = running mean (shifted sums: (x - pivot) and (x - pivot)^2, so the
-      // variance does not cancel catastrophically when |mean| >> std; read BEFORE the grid barrier, the
-      // running statistics are updated after it), gamma, beta.  Backward: gamma * invstd.
-      for (int c = et; c < BLOCK_N; c += kNumThreads) {
-        const int gc = nt * BLOCK_N + c;
-        const bool in = gc < args.n_valid;
-        if (bnm == 1) {
-          pv_sm[c] = (args.bn_rmean != nullptr && in) ? args.bn_rmean[gc] : 0.f;
-          co[c] = in ? args.bn_gamma[gc] : 0.f;
-          co[BLOCK_N + c] = in ? args.bn_beta[gc] : 0.f;
-        } else {
-          co[c] = in ? args.bn_gamma[gc] * args.bn_invstd[gc] : 0.f;
-        }
+    // Per-channel inputs that do not depend on the batch statistics, fetched before the barriers.  Forward:
+    // pivot = running mean (shifted sums (x - pivot), (x - pivot)^2: no catastrophic cancellation when
+    // |mean| >> std; read BEFORE the grid barrier, the running statistics change after it), gamma, beta.
+    // Backward: gamma * invstd.
+    for (int c = et; c < BLOCK_N; c += kNumThreads) {
+      const int gc = nt * BLOCK_N + c;
+      const bool in = gc < args.n_valid;
+      if constexpr (kFwd) {
+        pv_sm[c] = (args.bn_rmean != nullptr && in) ? args.bn_rmean[gc] : 0.f;
+        co[c] = in ? args.bn_gamma[gc] : 0.f;
+        co[BLOCK_N + c] = in ? args.bn_beta[gc] : 0.f;
+      } else {
+        co[c] = in ? args.bn_gamma[gc] * args.bn_invstd[gc] : 0.f;
       }
     }
     cluster_sync_all();
-    {
-      const int S = args.splits;
-      const int rp = (kBlockM + S - 1) / S;
-      const int rbeg = split * rp;
-      const int rend = min(kBlockM, rbeg + rp);
-      const int c4 = (et % kGroups) * 4;
-      const int ncol = nt * BLOCK_N + c4;
-      const bool col_ok = ncol + 4 <= args.n_valid;
-      const bool fast = col_ok && (args.ldo & 3) == 0;   // 8-byte accesses: every row offset is a multiple of 4 elements
-      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
-      float bv[4] = {0.f, 0.f, 0.f, 0.f};
-      if (args.bias != nullptr) {
+    const int S = args.splits;
+    const int rp = (kBlockM + S - 1) / S;
+    const int rbeg = split * rp;
+    const int rend = min(kBlockM, rbeg + rp);
+    const int c4 = (et % kGroups) * 4;
+    const int ncol = nt * BLOCK_N + c4;
+    const bool col_ok = ncol + 4 <= args.n_valid;
+    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    float bm[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {0.f, 0.f, 0.f, 0.f};
+    if constexpr (kFwd) {
 #pragma unroll
-        for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) bv[t] = __ldg(args.bias + ncol + t);
-      }
-      float bm[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {0.f, 0.f, 0.f, 0.f};
-      if (args.bn_x != nullptr) {
+      for (int t = 0; t < 4; ++t) bm[t] = pv_sm[c4 + t];          // forward: bm holds the pivots
+    } else if (col_ok) {
 #pragma unroll
-        for (int t = 0; t < 4; ++t)
-          if (ncol + t < args.n_valid) { bm[t] = args.bn_mean[ncol + t]; bi[t] = args.bn_invstd[ncol + t]; }
-      }
-      if (bnm == 1) {
+      for (int t = 0; t < 4; ++t) { bm[t] = args.bn_mean[ncol + t]; bi[t] = args.bn_invstd[ncol + t]; }
+    }
+    const __nv_bfloat16* ad_p = args.addend;
+    const __nv_bfloat16* my_p = args.mask_y;
+    const __nv_bfloat16* bx_p = args.bn_x;
+    auto unpack4 = [](const uint2& u, float (&v)[4]) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+      const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
+      v[0] = a0.x; v[1] = a0.y; v[2] = a1.x; v[3] = a1.y;
+    };
+    auto pack4 = [](const float (&f)[4]) {
+      const __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]), p1 = __floats2bfloat162_rn(f[2], f[3]);
+      uint2 u;
+      u.x = *reinterpret_cast<const uint32_t*>(&p0); u.y = *reinterpret_cast<const uint32_t*>(&p1);
+      return u;
+    };
+    // ---- pass 1: reduce the partial tiles, (backward: + addend, mask), round, stash, column sums -------
+#pragma unroll 1
+    for (int rb = rbeg + et / kGroups; rb < rend; rb += kU * kRowStep) {
+      long long ro[kU];
+      bool ok[kU];
+      uint2 uad[kU], umy[kU], ubx[kU];
+      float4 acc[kU];
 #pragma unroll
-        for (int t = 0; t < 4; ++t) bm[t] = pv_sm[c4 + t];        // forward: bm holds the pivots
-      }
-      const __nv_bfloat16* ad_p = args.addend;
-      const __nv_bfloat16* my_p = args.mask_y;
-      const __nv_bfloat16* bx_p = args.bn_x;
-      auto unpack4 = [](const uint2& u, float (&v)[4]) {
-        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-        const float2 a0 = __bfloat1622float2(h[0]), a1 = __bfloat1622float2(h[1]);
-        v[0] = a0.x; v[1] = a0.y; v[2] = a1.x; v[3] = a1.y;
-      };
-      auto load4 = [&](const __nv_bfloat16* p, long long ro, const uint2& pre, float (&v)[4]) {
-        if (fast) { unpack4(pre, v); return; }
-#pragma unroll
-        for (int t = 0; t < 4; ++t) v[t] = (ncol + t < args.n_valid) ? __bfloat162float(p[ro + t]) : 0.f;
-      };
-      auto store4 = [&](__nv_bfloat16* o, long long ro, const __nv_bfloat162& p0, const __nv_bfloat162& p1) {
-        if (fast) {
-          uint2 u;
-          u.x = *reinterpret_cast<const uint32_t*>(&p0); u.y = *reinterpret_cast<const uint32_t*>(&p1);
-          *reinterpret_cast<uint2*>(o + ro) = u;
-        } else {
-          const __nv_bfloat16 hv[4] = {p0.x, p0.y, p1.x, p1.y};
-#pragma unroll
-          for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[ro + t] = hv[t];
+      for (int u = 0; u < kU; ++u) {                       // the L2 round trips first
+        const int r = rb + u * kRowStep;
+        const int grow = mt * kBlockM + r;
+        ok[u] = col_ok && r < rend && grow < args.m_valid;
+        ro[u] = static_cast<long long>(grow) * args.ldo + ncol;
+        uad[u] = umy[u] = ubx[u] = make_uint2(0u, 0u);
+        if constexpr (!kFwd) {
+          if (ok[u]) {
+            if (ad_p != nullptr) uad[u] = __ldg(reinterpret_cast<const uint2*>(ad_p + ro[u]));
+            if (my_p != nullptr) umy[u] = __ldg(reinterpret_cast<const uint2*>(my_p + ro[u]));
+            ubx[u] = __ldg(reinterpret_cast<const uint2*>(bx_p + ro[u]));
+          }
         }
-      };
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {                       // the partial tiles, kU loads in flight per peer
+        const int r = rb + u * kRowStep;
+        acc[u] = r < rend ? ld_dsmem_f4(smem_u32(part + r * kPartStride + c4), 0) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll 1
+      for (int p = 1; p < S; ++p) {
+        float4 o[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          const int r = rb + u * kRowStep;
+          o[u] = r < rend ? ld_dsmem_f4(smem_u32(part + r * kPartStride + c4), static_cast<uint32_t>(p))
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) { acc[u].x += o[u].x; acc[u].y += o[u].y; acc[u].z += o[u].z; acc[u].w += o[u].w; }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        if (!ok[u]) continue;
+        float f[4] = {acc[u].x, acc[u].y, acc[u].z, acc[u].w};
+        if constexpr (!kFwd) {
+          if (ad_p != nullptr) {
+            float a[4];
+            unpack4(uad[u], a);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) f[t] += a[t];
+          }
+          if (my_p != nullptr) {
+            float m[4];
+            unpack4(umy[u], m);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) f[t] = m[t] > 0.f ? f[t] : 0.f;
+          }
+        }
+        // the intermediate (raw convolution output / masked gradient) is stored where a later pass needs it;
+        // statistics and the stash use exactly the rounded values the consumer will read back
+        const uint2 pk = pack4(f);
+        if (args.bn_raw != nullptr) *reinterpret_cast<uint2*>(args.bn_raw + ro[u]) = pk;
+        unpack4(pk, f);
+        // Stash for the pass after the grid barrier.  In place: rows [rbeg, rend) of THIS CTA's partial tile
+        // are read by this CTA only (every peer reads its own row range of it).
+        *reinterpret_cast<float4*>(part + (rb + u * kRowStep) * kPartStride + c4) = make_float4(f[0], f[1], f[2], f[3]);
+        if constexpr (kFwd) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { const float d = f[t] - bm[t]; s1[t] += d; s2[t] = fmaf(d, d, s2[t]); }
+        } else {
+          float xh[4];
+          unpack4(ubx[u], xh);
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], (xh[t] - bm[t]) * bi[t], s2[t]); }
+        }
+      }
+    }
+    // ---- column sums: shuffle fold, one row per warp, 6-way sum, one atomic per column per CTA ---------
+    kml::BnScratch* sc = args.bn_sc;
+    float* gstats = sc->acc[gstate.x & 1u];
+    if (kGroups == 16) {
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        s1[t] += __shfl_xor_sync(0xffffffffu, s1[t], 16);
+        s2[t] += __shfl_xor_sync(0xffffffffu, s2[t], 16);
+      }
+    }
+    {
+      float* wsm = st_sm + warp * 2 * BLOCK_N;
+      if (lane < kGroups) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) { wsm[c4 + t] = s1[t]; wsm[BLOCK_N + c4 + t] = s2[t]; }
+      }
+    }
+    __syncthreads();
+    for (int i = et; i < 2 * BLOCK_N; i += kNumThreads) {
+      const int c = i % BLOCK_N, which = i / BLOCK_N;
+      const int gc = nt * BLOCK_N + c;
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) tot += st_sm[w * 2 * BLOCK_N + i];
+      if (gc < args.n_valid) atomicAdd(gstats + static_cast<size_t>(which) * args.n_valid + gc, tot);
+    }
+    // ---- whole-grid barrier: every CTA's column sums are in, then finish the BatchNorm --------------
+    const unsigned ncta = gridDim.x * gridDim.y * gridDim.z;
+    if (blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1) {
+      float4* nxt = reinterpret_cast<float4*>(sc->acc[(gstate.x & 1u) ^ 1u]);    // the next launch's buffer
+      for (int i = et; i < 2 * kml::kBnMaxC / 4; i += kNumThreads) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();
+    if (et == 0) kml::grid_arrive_and_wait(sc, gstate.y, ncta);
+    __syncthreads();
+    if ((blockIdx.x | blockIdx.y | blockIdx.z) == 0 && et == 0) {   // everyone has arrived: publish the next launch's state
+      sc->launches = gstate.x + 1u;
+      sc->bar_base = gstate.y + ncta;
+      if (kFwd && args.bn_nbt != nullptr) *args.bn_nbt += 1;
+    }
+    {
+      const float inv_m = 1.f / static_cast<float>(args.m_valid);
+      const bool writer = mt == 0 && split == 0;         // one CTA per column block records the per-channel results
+      for (int c = et; c < BLOCK_N; c += kNumThreads) {
+        const int gc = nt * BLOCK_N + c;
+        float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+        if (gc < args.n_valid) {
+          const float t1 = __ldcg(gstats + gc), t2 = __ldcg(gstats + args.n_valid + gc);
+          if constexpr (kFwd) {
+            const float d = t1 * inv_m;
+            const float mean = pv_sm[c] + d;
+            const float var = fmaxf(t2 * inv_m - d * d, 0.f);
+            const float invstd = rsqrtf(var + args.bn_eps);
+            c0 = co[c] * invstd;                         // gamma * invstd
+            c1 = co[BLOCK_N + c] - mean * c0;            // beta - mean * scale
+            if (writer) {
+              args.bn_save_mean[gc] = mean;
+              args.bn_save_invstd[gc] = invstd;
+              if (args.bn_rmean != nullptr) {
+                const float m = static_cast<float>(args.m_valid);
+                const float unbiased = args.m_valid > 1 ? var * m / (m - 1.f) : var;
+                args.bn_rmean[gc] = (1.f - args.bn_momentum) * pv_sm[c] + args.bn_momentum * mean;
+                args.bn_rvar[gc] = (1.f - args.bn_momentum) * args.bn_rvar[gc] + args.bn_momentum * unbiased;
+              }
+            }
+          } else {
+            c0 = co[c];                                  // gamma * invstd
+            c1 = t1 * inv_m;
+            c2 = t2 * inv_m;
+            if (writer) { args.bn_dbeta[gc] = t1; args.bn_dgamma[gc] = t2; }
+          }
+        }
+        co[c] = c0; co[BLOCK_N + c] = c1; co[2 * BLOCK_N + c] = c2;
+      }
+    }
+    __syncthreads();
+    // ---- pass 2: normalise (forward: + residual, ReLU) / input gradient (backward), write the output ----
+    {
+      float k0[4], k1[4], k2[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { k0[t] = co[c4 + t]; k1[t] = co[BLOCK_N + c4 + t]; k2[t] = co[2 * BLOCK_N + c4 + t]; }
+      const __nv_bfloat16* aux_p = kFwd ? args.bn_res : args.bn_x;     // the one global operand of this pass
+      __nv_bfloat16* outp = static_cast<__nv_bfloat16*>(args.out);
+#pragma unroll 1
       for (int rb = rbeg + et / kGroups; rb < rend; rb += kU * kRowStep) {
         long long ro[kU];
         bool ok[kU];
-        uint2 uad[kU], umy[kU], ubx[kU];
-        float4 acc[kU];
-        // (1) the L2 round trips first
+        uint2 ua[kU];
+        float4 v[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
           const int r = rb + u * kRowStep;
           const int grow = mt * kBlockM + r;
-          ok[u] = r < rend && grow < args.m_valid;
+          ok[u] = col_ok && r < rend && grow < args.m_valid;
           ro[u] = static_cast<long long>(grow) * args.ldo + ncol;
-          uad[u] = umy[u] = ubx[u] = make_uint2(0u, 0u);
-          if (ok[u] && fast) {
-            if (ad_p != nullptr) uad[u] = __ldg(reinterpret_cast<const uint2*>(ad_p + ro[u]));
-            if (my_p != nullptr) umy[u] = __ldg(reinterpret_cast<const uint2*>(my_p + ro[u]));
-            if (bx_p != nullptr) ubx[u] = __ldg(reinterpret_cast<const uint2*>(bx_p + ro[u]));
+          ua[u] = make_uint2(0u, 0u);
+          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ok[u]) {
+            if (aux_p != nullptr) ua[u] = __ldg(reinterpret_cast<const uint2*>(aux_p + ro[u]));
+            v[u] = *reinterpret_cast<const float4*>(part + r * kPartStride + c4);
           }
         }
-        // (2) the partial tiles of all peers, kU loads in flight per peer
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-          const int r = rb + u * kRowStep;
-          acc[u] = r < rend ? ld_dsmem_f4(smem_u32(part + r * kPartStride + c4), 0) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        for (int p = 1; p < S; ++p) {
-          float4 o[kU];
-#pragma unroll
-          for (int u = 0; u < kU; ++u) {
-            const int r = rb + u * kRowStep;
-            o[u] = r < rend ? ld_dsmem_f4(smem_u32(part + r * kPartStride + c4), static_cast<uint32_t>(p))
-                            : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-#pragma unroll
-          for (int u = 0; u < kU; ++u) { acc[u].x += o[u].x; acc[u].y += o[u].y; acc[u].z += o[u].z; acc[u].w += o[u].w; }
-        }
-        // (3) epilogue of the kU rows
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
           if (!ok[u]) continue;
-          float* own = part + (rb + u * kRowStep) * kPartStride + c4;
-          float f[4] = {acc[u].x + bv[0], acc[u].y + bv[1], acc[u].z + bv[2], acc[u].w + bv[3]};
-          if (ad_p != nullptr) {
-            float a[4];
-            load4(ad_p, ro[u], uad[u], a);
+          float f[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          float a[4];
+          unpack4(ua[u], a);
+          if constexpr (kFwd) {
 #pragma unroll
-            for (int t = 0; t < 4; ++t) f[t] += a[t];
-          }
-          if (args.relu) {
+            for (int t = 0; t < 4; ++t) f[t] = fmaf(f[t], k0[t], k1[t]) + a[t];       // a = residual or zeros
+            if (args.bn_relu) {
 #pragma unroll
-            for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
-          }
-          if (my_p != nullptr) {
-            float m[4];
-            load4(my_p, ro[u], umy[u], m);
-#pragma unroll
-            for (int t = 0; t < 4; ++t) f[t] = m[t] > 0.f ? f[t] : 0.f;
-          }
-          if (args.out_f32 && bnm == 0) {
-            float* o = static_cast<float*>(args.out) + ro[u];
-            if (fast) {
-              *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
-            } else {
-#pragma unroll
-              for (int t = 0; t < 4; ++t) if (ncol + t < args.n_valid) o[t] = f[t];
+              for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
             }
           } else {
-            // fused BatchNorm: this is the intermediate (raw convolution output / masked gradient), stored
-            // only where a later pass needs it; the final output is written after the grid barrier
-            __nv_bfloat16* o = (bnm != 0 ? args.bn_raw : static_cast<__nv_bfloat16*>(args.out));
-            const __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]);
-            const __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2], f[3]);
-            if (o != nullptr) store4(o, ro[u], p0, p1);
-            // statistics of exactly the values the consumer will read back
-            const float2 r0 = __bfloat1622float2(p0), r1 = __bfloat1622float2(p1);
-            f[0] = r0.x; f[1] = r0.y; f[2] = r1.x; f[3] = r1.y;
-            // Stash for the pass after the grid barrier.  In place: rows [rbeg, rend) of THIS CTA's
-            // partial tile are read by this CTA only (every peer reads its own row range of it).
-            if (bnm != 0) *reinterpret_cast<float4*>(own) = make_float4(f[0], f[1], f[2], f[3]);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) f[t] = k0[t] * (f[t] - k1[t] - (a[t] - bm[t]) * bi[t] * k2[t]);
           }
-          if (bx_p != nullptr) {                        // BatchNorm-backward sums: g and g * xhat
-            float xh[4];
-            load4(bx_p, ro[u], ubx[u], xh);
-#pragma unroll
-            for (int t = 0; t < 4; ++t) {
-              s1[t] += f[t];
-              s2[t] = fmaf(f[t], (xh[t] - bm[t]) * bi[t], s2[t]);
-            }
-          } else if (bnm == 1) {
-#pragma unroll
-            for (int t = 0; t < 4; ++t) { const float d = f[t] - bm[t]; s1[t] += d; s2[t] = fmaf(d, d, s2[t]); }
-          } else {
-#pragma unroll
-            for (int t = 0; t < 4; ++t) { s1[t] += f[t]; s2[t] = fmaf(f[t], f[t], s2[t]); }
-          }
-        }
-      }
-      float* gstats = args.stats;
-      if (bnm != 0) gstats = args.bn_sc->acc[gstate.x & 1u];
-      if (gstats != nullptr) {
-        // No shared-memory float atomics (they compile to compare-and-swap loops): lanes that share a
-        // column group fold with a shuffle, each warp writes its own row of partials, then a 6-way sum.
-        if (kGroups == 16) {
-#pragma unroll
-          for (int t = 0; t < 4; ++t) {
-            s1[t] += __shfl_xor_sync(0xffffffffu, s1[t], 16);
-            s2[t] += __shfl_xor_sync(0xffffffffu, s2[t], 16);
-          }
-        }
-        float* wsm = st_sm + warp * 2 * BLOCK_N;          // [6 warps][2][BLOCK_N]
-        if (lane < kGroups) {
-#pragma unroll
-          for (int t = 0; t < 4; ++t) { wsm[c4 + t] = s1[t]; wsm[BLOCK_N + c4 + t] = s2[t]; }
-        }
-        __syncthreads();
-        for (int i = et; i < 2 * BLOCK_N; i += kNumThreads) {
-          const int c = i % BLOCK_N, which = i / BLOCK_N;
-          const int gc = nt * BLOCK_N + c;
-          float tot = 0.f;
-#pragma unroll
-          for (int w = 0; w < kWarps; ++w) tot += st_sm[w * 2 * BLOCK_N + i];
-          if (gc < args.n_valid) atomicAdd(gstats + static_cast<size_t>(which) * args.n_valid + gc, tot);
-        }
-      }
-      if (bnm != 0) {
-        // ---- whole-grid barrier: every CTA's column sums are in, then finish the BatchNorm -----------
-        kml::BnScratch* sc = args.bn_sc;
-        const unsigned ncta = gridDim.x * gridDim.y * gridDim.z;
-        const bool first_cta = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
-        if (blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1) {
-          float4* nxt = reinterpret_cast<float4*>(sc->acc[(gstate.x & 1u) ^ 1u]);    // the next launch's buffer
-          for (int i = et; i < 2 * kml::kBnMaxC / 4; i += kNumThreads) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        __syncthreads();
-        if (et == 0) kml::grid_arrive_and_wait(sc, gstate.y, ncta);
-        __syncthreads();
-        if (first_cta && et == 0) {                      // everyone has arrived: publish the next launch's state
-          sc->launches = gstate.x + 1u;
-          sc->bar_base = gstate.y + ncta;
-          if (bnm == 1 && args.bn_nbt != nullptr) *args.bn_nbt += 1;
-        }
-        const float* tot = sc->acc[gstate.x & 1u];
-        const float inv_m = 1.f / static_cast<float>(args.m_valid);
-        const bool writer = mt == 0 && split == 0;       // one CTA per column block records the per-channel results
-        for (int c = et; c < BLOCK_N; c += kNumThreads) {
-          const int gc = nt * BLOCK_N + c;
-          float c0 = 0.f, c1 = 0.f, c2 = 0.f;
-          if (gc < args.n_valid) {
-            const float t1 = __ldcg(tot + gc), t2 = __ldcg(tot + args.n_valid + gc);
-            if (bnm == 1) {
-              const float d = t1 * inv_m;
-              const float mean = pv_sm[c] + d;
-              const float var = fmaxf(t2 * inv_m - d * d, 0.f);
-              const float invstd = rsqrtf(var + args.bn_eps);
-              c0 = co[c] * invstd;                       // gamma * invstd
-              c1 = co[BLOCK_N + c] - mean * c0;          // beta - mean * scale
-              if (writer) {
-                args.bn_save_mean[gc] = mean;
-                args.bn_save_invstd[gc] = invstd;
-                if (args.bn_rmean != nullptr) {
-                  const float m = static_cast<float>(args.m_valid);
-                  const float unbiased = args.m_valid > 1 ? var * m / (m - 1.f) : var;
-                  args.bn_rmean[gc] = (1.f - args.bn_momentum) * pv_sm[c] + args.bn_momentum * mean;
-                  args.bn_rvar[gc] = (1.f - args.bn_momentum) * args.bn_rvar[gc] + args.bn_momentum * unbiased;
-                }
-              }
-            } else {
-              c0 = co[c];                                // gamma * invstd
-              c1 = t1 * inv_m;
-              c2 = t2 * inv_m;
-              if (writer) { args.bn_dbeta[gc] = t1; args.bn_dgamma[gc] = t2; }
-            }
-          }
-          co[c] = c0; co[BLOCK_N + c] = c1; co[2 * BLOCK_N + c] = c2;
-        }
-        __syncthreads();
-        float k0[4], k1[4], k2[4];
-#pragma unroll
-        for (int t = 0; t < 4; ++t) { k0[t] = co[c4 + t]; k1[t] = co[BLOCK_N + c4 + t]; k2[t] = co[2 * BLOCK_N + c4 + t]; }
-        const __nv_bfloat16* aux_p = bnm == 1 ? args.bn_res : args.bn_x;     // the one global operand of this pass
-        for (int rb = rbeg + et / kGroups; rb < rend; rb += kU * kRowStep) {
-          long long ro[kU];
-          bool ok[kU];
-          uint2 ua[kU];
-          float4 v[kU];
-#pragma unroll
-          for (int u = 0; u < kU; ++u) {
-            const int r = rb + u * kRowStep;
-            const int grow = mt * kBlockM + r;
-            ok[u] = r < rend && grow < args.m_valid;
-            ro[u] = static_cast<long long>(grow) * args.ldo + ncol;
-            ua[u] = make_uint2(0u, 0u);
-            if (ok[u] && fast && aux_p != nullptr) ua[u] = __ldg(reinterpret_cast<const uint2*>(aux_p + ro[u]));
-            if (ok[u]) v[u] = *reinterpret_cast<const float4*>(part + r * kPartStride + c4);
-          }
-#pragma unroll
-          for (int u = 0; u < kU; ++u) {
-            if (!ok[u]) continue;
-            float f[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-            if (bnm == 1) {
-#pragma unroll
-              for (int t = 0; t < 4; ++t) f[t] = fmaf(f[t], k0[t], k1[t]);
-              if (aux_p != nullptr) {
-                float a[4];
-                load4(aux_p, ro[u], ua[u], a);
-#pragma unroll
-                for (int t = 0; t < 4; ++t) f[t] += a[t];
-              }
-              if (args.bn_relu) {
-#pragma unroll
-                for (int t = 0; t < 4; ++t) f[t] = fmaxf(f[t], 0.f);
-              }
-            } else {
-              float xh[4];
-              load4(aux_p, ro[u], ua[u], xh);
-#pragma unroll
-              for (int t = 0; t < 4; ++t) f[t] = k0[t] * (f[t] - k1[t] - (xh[t] - bm[t]) * bi[t] * k2[t]);
-            }
-            store4(static_cast<__nv_bfloat16*>(args.out), ro[u], __floats2bfloat162_rn(f[0], f[1]),
-                   __floats2bfloat162_rn(f[2], f[3]));
-          }
+          *reinterpret_cast<uint2*>(outp + ro[u]) = pack4(f);
         }
       }
     }
@@ -1348,6 +1300,8 @@ int apply_bn_fuse(GemmArgs& g, const kml_epilogue* epi, int block_n) {
   KML_CHECK(f->mode == 1 || f->mode == 2, "bn_fuse: mode must be 1 (forward) or 2 (backward)");
   KML_CHECK(!g.out_f32, "bn_fuse: bf16 output only");
   KML_CHECK(g.n_valid <= kml::kBnMaxC, "bn_fuse: at most %d channels", kml::kBnMaxC);
+  KML_CHECK(g.n_valid % 4 == 0 && g.ldo % 4 == 0 && g.bias == nullptr,
+            "bn_fuse: channels and the output row stride must be multiples of 4, no bias (BatchNorm absorbs it)");
   KML_CHECK(f->scratch && f->gamma && f->save_mean && f->save_invstd, "bn_fuse: null pointer");
   KML_CHECK(epi->stats == nullptr && epi->bn_x == nullptr && epi->mask_y == nullptr,
             "bn_fuse replaces stats / mask_y / bn_x of the epilogue");

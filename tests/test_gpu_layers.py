@@ -702,3 +702,45 @@ def test_strided_conv_implicit_gemm_vs_torch(dev, N, H, Cin, Cout, k, p):
         dw = ops.conv2d_wgrad(x, dy, k, k, p, stride=s, splits=sp)
         torch.cuda.synchronize()
         assert _rel(dw, gw.permute(0, 2, 3, 1)) < 1e-2, f"splits {sp}"
+
+
+def test_grid_barrier_kernels_finish_while_another_stream_occupies_the_gpu(dev):
+    """The kernels that synchronise their whole grid in software (csrc/bn_scratch.cuh: BatchNorm forward /
+    backward, the fused conv+BatchNorm GEMMs) rely on co-residency.  Kernels of OTHER streams that never wait on
+    anything (here: a long two-CTA-per-SM GEMM, relaunched to keep every SM busy) may delay them but must not
+    starve them: they finish, the spinning grid gets its slots, and the results are right."""
+    import torch.nn.functional as F
+    from kubeml_b200 import ops
+    from kubeml_b200.ops import nn as K
+    from kubeml_b200.models.native import fused_plan, pick_block_n
+    torch.manual_seed(9)
+    side = torch.cuda.Stream(device=dev)
+    A = torch.randn(8192, 4096, device=dev).bfloat16()
+    Bm = torch.randn(4096, 4096, device=dev).bfloat16()
+    big = torch.empty(8192, 4096, device=dev, dtype=torch.bfloat16)
+    N, H, C = 128, 8, 64
+    x = torch.randn(N, H, H, C, device=dev).bfloat16()
+    w = (torch.randn(C, 3, 3, C, device=dev) * 0.06).bfloat16()
+    gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
+    xc = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), padding=1)
+    want = torch.relu(F.batch_norm(xc, None, None, gamma, beta, training=True)).permute(0, 2, 3, 1)
+    plan = fused_plan(dev, N * H * H // 128, C, 9, pick_block_n(N * H * H // 128, C), False)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        for _ in range(12):                                   # ~3 ms of a persistent GEMM on every SM
+            ops.gemm_bf16(A, Bm, out=big, block_n=128)
+    for rep in range(20):
+        rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+        mean, istd = torch.empty(C, device=dev), torch.empty(C, device=dev)
+        raw = torch.empty(N, H, H, C, dtype=torch.bfloat16, device=dev)
+        y = torch.empty_like(raw)
+        ops.conv2d_fprop(x, w, 1, out=y, block_n=plan[0], splits=plan[1], cluster=True,
+                         bn_fuse=ops.BnFwd(gamma, beta, rm, rv, None, mean, istd, raw, relu=True))
+        y2 = torch.empty_like(raw)
+        K.bn_fwd_train(raw.view(-1, C), None, y2.view(-1, C), gamma, beta, None, None, None, mean, istd, True)
+        dx = torch.empty_like(raw)
+        dg, db = torch.empty(C, device=dev), torch.empty(C, device=dev)
+        K.bn_bwd(y.view(-1, C), y2.view(-1, C), raw.view(-1, C), gamma, mean, istd, dx.view(-1, C), None, dg, db)
+    torch.cuda.synchronize()
+    assert _rel(y, want) < 2e-2 and _rel(y2, want) < 2e-2
+    assert torch.isfinite(dx.float()).all()
