@@ -114,6 +114,24 @@ class NativeResNet(NativeNet):
             self._saved = S
         return logits
 
+    def _mark_tail_ready(self, B: Buffers) -> None:
+        """Called in the backward pass once every gradient of layer4 and fc has been issued: publishes
+        (flat offset of layer4's first parameter, event on the main stream, event on the weight-gradient stream)
+        for the flat optimizer, which then updates that tail of the arena while the rest of the backward pass
+        still runs (`kubeml_b200.optim.SGD.step`)."""
+        a = self._arena
+        if a is None or a.weights.device.type != "cuda":
+            return
+        lo = a.layout.entries["layer4.0.conv1.weight"].offset
+        if lo % 64:
+            return
+        dev = a.weights.device
+        ev_main, ev_side = torch.cuda.Event(), torch.cuda.Event()
+        ev_main.record(torch.cuda.current_stream(dev))
+        side = getattr(B, "_side", None)
+        ev_side.record(side if (side is not None and getattr(B, "_side_used", False)) else torch.cuda.current_stream(dev))
+        a.early_ready = (lo, ev_main, ev_side)
+
     # ---------------------------------------------------------------------------------- backward
     def _backward_impl(self, dlogits: torch.Tensor) -> None:
         from .native import Act, act_dtype
@@ -134,6 +152,8 @@ class NativeResNet(NativeNet):
         nblk = len(self._blocks)
         for bi, ((tag, blk), (h, t1, a, t2, td, out)) in enumerate(zip(reversed(self._blocks),
                                                                          reversed(S["blocks"]))):
+            if tag == "layer3." + str(len(self.layer3) - 1):
+                self._mark_tail_ready(B)          # layer4 and fc are done: their optimizer update may start
             first_block = bi == nblk - 1          # its input gradient feeds the max-pool backward (dense)
             # out = relu(bn2(t2) + idn)
             dt2, g = bn_backward(blk.bn2, dh, out, t2, B, tag + ".bn2", want_dres=True)
