@@ -18,7 +18,7 @@ import torch.nn as nn
 
 from ..ops import nn as K
 from .native import (Act, Buffers, NativeNet, NBatchNorm2d, NConv2d, NLinear, act_dtype, bn_backward, bn_forward,
-                     conv_backward, conv_forward, linear_backward, linear_forward)
+                     conv_backward, conv_bn_forward, conv_forward, linear_backward, linear_forward)
 
 
 class NCifarBlock(nn.Module):
@@ -68,8 +68,7 @@ class NativeCifarResNet(NativeNet):
         x = self._to_nhwc(x)
         N = x.shape[0]
         B = self.buffers_for(N, train)
-        c1 = conv_forward(self.conv1, x, B, "stem", allow_slabs=True, want_stats=train)
-        h, c1s = bn_forward(self.bn1, c1, B, "stem.bn", train, relu=True)
+        h, c1s = conv_bn_forward(self.conv1, self.bn1, x, B, "stem", "stem.bn", train, relu=True)
         saved = []
         for tag, blk in self._blocks:
             idn = h
@@ -77,10 +76,9 @@ class NativeCifarResNet(NativeNet):
                 n_, H, W, C = h.shape
                 idn = B.get(tag + ".sc", (n_, H // 2, W // 2, C + 2 * blk.pad), zero=True)
                 idn[..., blk.pad:blk.pad + C].copy_(h[:, ::2, ::2, :])
-            t1 = conv_forward(blk.conv1, h, B, tag + ".c1", allow_slabs=True, want_stats=train)
-            a, t1s = bn_forward(blk.bn1, t1, B, tag + ".bn1", train, relu=True)
-            t2 = conv_forward(blk.conv2, a, B, tag + ".c2", allow_slabs=True, want_stats=train)
-            out, t2s = bn_forward(blk.bn2, t2, B, tag + ".bn2", train, relu=True, res=idn)
+            # convolution + BatchNorm (+ shortcut + ReLU) in one launch where the GEMM's grid fits the GPU at once
+            a, t1s = conv_bn_forward(blk.conv1, blk.bn1, h, B, tag + ".c1", tag + ".bn1", train, relu=True)
+            out, t2s = conv_bn_forward(blk.conv2, blk.bn2, a, B, tag + ".c2", tag + ".bn2", train, relu=True, res=idn)
             saved.append((h, t1s, a, t2s, out))
             h = out
         n_, H, W, C = h.shape
