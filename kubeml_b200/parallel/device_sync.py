@@ -454,104 +454,125 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
         self.rank, self.world = rank, world
         self.fdx = FdExchange(rank, world, sock_dir)
         self._jobs: Dict[str, RankSync] = {}
+        self._members: Dict[str, List[int]] = {}
         self.rs = RankSync(self, rank)          # engine of the most recent job (benchmarks use one job at a time)
         self.rs._imported, self.rs._mcast = [], None
         self._tag = 1000 * (job_tag + 1)
         self._holder = 0
 
+    # A job runs on a set of ranks ("members", physical rank numbers in function-id order): all ranks by
+    # default, a GPU subset when several jobs share the box.  Inside a job everything is indexed by the
+    # LOGICAL rank = function id = position in `members` (slots of the signal pads, replica tables).
+    def set_members(self, job_id: Optional[str], members: List[int]) -> None:
+        if job_id:
+            self._members[job_id] = list(members)
+
+    def _members_of(self, rs: RankSync) -> List[int]:
+        return getattr(rs, "members", None) or list(range(self.world))
+
     def for_func(self, func_id: int) -> RankSync:
-        if func_id != self.rank:
-            raise MergeError(RuntimeError(f"function {func_id} scheduled on rank {self.rank}"))
         return self.rs
 
     def engine_for(self, job_id: str, func_id: int) -> RankSync:
         """One engine (arena, peer mappings, multicast object) per job: a control plane may run
         several jobs with different models over the same worker processes."""
-        if func_id != self.rank:
-            raise MergeError(RuntimeError(f"function {func_id} scheduled on rank {self.rank}"))
+        members = self._members.get(job_id) or list(range(self.world))
+        if self.rank not in members or members.index(self.rank) != func_id:
+            raise MergeError(RuntimeError(f"function {func_id} of job {job_id} scheduled on rank {self.rank} "
+                                          f"(members {members})"))
         rs = self._jobs.get(job_id)
         if rs is None:
-            rs = RankSync(self, self.rank)
+            rs = RankSync(self, func_id)
             rs._imported, rs._mcast = [], None
+            rs.members = members
+            import zlib
+            rs._tag = (zlib.crc32(job_id.encode()) & 0x3FFF) * 4096     # per-job tag space of the fd exchange
             self._jobs[job_id] = rs
             self.rs = rs
         return rs
 
     def release(self, job_id: str) -> None:
         rs = self._jobs.pop(job_id, None)
+        self._members.pop(job_id, None)
         if rs is not None:
             self._close_rank(rs)
 
-    def _next_tag(self) -> int:
+    def _next_tag(self, rs: Optional[RankSync] = None) -> int:
+        if rs is not None and hasattr(rs, "_tag"):
+            rs._tag += 1
+            return rs._tag
         self._tag += 1
         return self._tag
 
     def register(self, rs: RankSync) -> None:
         lib = _native.lib()
         dev = rs.arena.device.index or 0
+        members = self._members_of(rs)
         rs.peers.add(rs.rank, rs.arena.base, rs.layout)
-        if self.world == 1:
+        if len(members) == 1:
             return
         fd = ctypes.c_int(-1)
         _native.check(lib.kml_arena_export_fd(rs.arena.handle, ctypes.byref(fd)), "kml_arena_export_fd")
-        got = self.fdx.all_gather_fds([fd.value], self._next_tag())
+        got = self.fdx.all_gather_fds([fd.value], self._next_tag(rs), members=members)
         os.close(fd.value)
-        for peer in range(self.world):
+        for logical, peer in enumerate(members):
             if peer == self.rank:
                 continue
             h = ctypes.c_void_p()
-            _native.check(lib.kml_arena_import_fd(dev, got[peer][0], rs.arena.nbytes, ctypes.byref(h)),
+            _native.check(lib.kml_arena_import_fd(dev, got[logical][0], rs.arena.nbytes, ctypes.byref(h)),
                           f"kml_arena_import_fd(rank {peer})")
-            os.close(got[peer][0])
+            os.close(got[logical][0])
             rs._imported.append(h)
-            rs.peers.add(peer, int(lib.kml_arena_ptr(h)), rs.layout)
+            rs.peers.add(logical, int(lib.kml_arena_ptr(h)), rs.layout)
         self._setup_multicast(rs, dev)
 
     def _setup_multicast(self, rs: RankSync, dev: int) -> None:
+        members = self._members_of(rs)
+        root = members[0]
         if os.environ.get("KUBEML_MERGE_NVLS", "1") == "0":
-            self.fdx.barrier(self._next_tag())
+            self.fdx.barrier(self._next_tag(rs), members=members)
             return
         lib = _native.lib()
         sup = ctypes.c_int(0)
         ok = lib.kml_mcast_supported(dev, ctypes.byref(sup)) == 0 and sup.value != 0
         m = ctypes.c_void_p()
         fds: List[int] = []
-        if self.rank == 0 and ok:
-            if lib.kml_mcast_create(self.world, rs.arena.nbytes, ctypes.byref(m)) == 0:
+        if self.rank == root and ok:
+            if lib.kml_mcast_create(len(members), rs.arena.nbytes, ctypes.byref(m)) == 0:
                 fd = ctypes.c_int(-1)
                 if lib.kml_mcast_export_fd(m, ctypes.byref(fd)) == 0:
                     fds = [fd.value]
             else:
                 log.warning("multicast create failed: %s", lib.kml_last_error().decode())
-        got = self.fdx.broadcast_fds(fds, 0, self._next_tag())
+        got = self.fdx.broadcast_fds(fds, root, self._next_tag(rs), members=members)
         for f in fds:
             os.close(f)
         have = bool(got) and ok
-        if have and self.rank != 0:
-            if lib.kml_mcast_import_fd(got[0], self.world, rs.arena.nbytes, ctypes.byref(m)) != 0:
+        if have and self.rank != root:
+            if lib.kml_mcast_import_fd(got[0], len(members), rs.arena.nbytes, ctypes.byref(m)) != 0:
                 have = False
             os.close(got[0])
         if have and lib.kml_mcast_add_device(m, dev) != 0:
             log.warning("multicast add_device failed: %s", lib.kml_last_error().decode())
             have = False
         # everyone must have added its device before anyone binds
-        self.fdx.barrier(self._next_tag())
+        self.fdx.barrier(self._next_tag(rs), members=members)
         mc_ptr = ctypes.c_void_p()
         if have and lib.kml_mcast_bind(m, dev, rs.arena.handle, ctypes.byref(mc_ptr)) != 0:
             log.warning("multicast bind failed: %s", lib.kml_last_error().decode())
             have = False
-        have = self.fdx.all_agree(have, self._next_tag())
+        have = self.fdx.all_agree(have, self._next_tag(rs), members=members)
         if have:
             rs._mcast = m
             rs.peers.mcast = int(mc_ptr.value) + rs.layout.off_f32
-            rs.peers.mcast_ranks = frozenset(range(self.world))
-            log.info("rank %d: NVLS multicast mapping ready", self.rank)
+            rs.peers.mcast_ranks = frozenset(range(len(members)))
+            log.info("rank %d: NVLS multicast mapping ready (%d GPUs)", self.rank, len(members))
 
     def set_reference_holder(self, rank: int) -> None:
         self._holder = rank
 
     def copy_reference_into(self, rs: RankSync) -> None:
-        if self.world == 1 or rs.rank == self._holder:
+        if len(self._members_of(rs)) == 1 or rs.rank == self._holder:
             return
         src = rs.peers.weights.get(self._holder)
         if src is None:
@@ -567,8 +588,9 @@ class SpmdDeviceSyncGroup(DeviceSyncGroup):
         torch.cuda.current_stream(rs.arena.device).synchronize()
 
     def epoch_barrier(self, rs: RankSync, n: int, key) -> None:
-        if self.world > 1:
-            self.fdx.barrier(self._next_tag())
+        members = self._members_of(rs)
+        if len(members) > 1:
+            self.fdx.barrier(self._next_tag(rs), members=members)
 
     def _close_rank(self, rs: RankSync) -> None:
         lib = _native.lib()

@@ -52,10 +52,14 @@ class FdExchange:
                     raise TimeoutError(f"rank {self.rank}: peer {peer} never opened {path}")
                 time.sleep(0.01)
 
-    def all_gather_fds(self, fds: List[int], tag: int, timeout: float = 120.0) -> List[List[int]]:
-        """Every rank contributes `fds`; returns, per rank, the fds it contributed (received copies
-        are new descriptors owned by the caller; the own entry is the list passed in)."""
-        for peer in range(self.world):
+    def all_gather_fds(self, fds: List[int], tag: int, timeout: float = 120.0,
+                       members: Optional[List[int]] = None) -> List[List[int]]:
+        """Every rank of `members` (default: the whole world) contributes `fds`; returns, per member in the
+        order of `members`, the fds it contributed (received copies are new descriptors owned by the caller;
+        the own entry is the list passed in).  Exchanges of disjoint member sets (two jobs on different GPU
+        subsets) do not interfere: messages are matched by (sender, tag) and tags are scoped per job."""
+        members = list(range(self.world)) if members is None else list(members)
+        for peer in members:
             if peer == self.rank:
                 continue
             s = self._connect(peer, timeout)
@@ -64,12 +68,13 @@ class FdExchange:
                 socket.send_fds(s, [struct.pack("<iii", self.rank, tag, len(fds))], fds)
             finally:
                 s.close()
-        out: List[Optional[List[int]]] = [None] * self.world
+        out: Dict[int, Optional[List[int]]] = {m: None for m in members}
         out[self.rank] = list(fds)
         for key in [k for k in self._pending if k[1] == tag]:
-            out[key[0]] = self._pending.pop(key)
+            if key[0] in out:
+                out[key[0]] = self._pending.pop(key)
         self.server.settimeout(timeout)
-        while any(o is None for o in out):
+        while any(o is None for o in out.values()):
             conn, _ = self.server.accept()
             try:
                 msg, got, _, _ = socket.recv_fds(conn, 12, 64)
@@ -77,29 +82,32 @@ class FdExchange:
             finally:
                 conn.close()
             got = list(got)[:n] if n else []
-            if t == tag:
+            if t == tag and src in out:
                 out[src] = got
             else:
                 self._pending[(src, t)] = got
-        return out  # type: ignore[return-value]
+        return [out[m] for m in members]  # type: ignore[misc]
 
-    def broadcast_fds(self, fds: List[int], root: int, tag: int, timeout: float = 120.0) -> List[int]:
-        got = self.all_gather_fds(fds if self.rank == root else [], tag, timeout)
-        return got[root]
+    def broadcast_fds(self, fds: List[int], root: int, tag: int, timeout: float = 120.0,
+                      members: Optional[List[int]] = None) -> List[int]:
+        members = list(range(self.world)) if members is None else list(members)
+        got = self.all_gather_fds(fds if self.rank == root else [], tag, timeout, members)
+        return got[members.index(root)]
 
-    def all_agree(self, ok: bool, tag: int, timeout: float = 120.0) -> bool:
-        """True iff every rank passed ok=True (a yes vote travels as one descriptor)."""
+    def all_agree(self, ok: bool, tag: int, timeout: float = 120.0, members: Optional[List[int]] = None) -> bool:
+        """True iff every member passed ok=True (a yes vote travels as one descriptor)."""
+        members = list(range(self.world)) if members is None else list(members)
         fd = os.open(os.devnull, os.O_RDONLY) if ok else -1
-        got = self.all_gather_fds([fd] if ok else [], tag, timeout)
+        got = self.all_gather_fds([fd] if ok else [], tag, timeout, members)
         yes = all(len(g) > 0 for g in got)
-        for r, g in enumerate(got):
+        for m, g in zip(members, got):
             for f in g:
-                if r != self.rank or f == fd:
+                if m != self.rank or f == fd:
                     os.close(f)
         return yes
 
-    def barrier(self, tag: int, timeout: float = 120.0) -> None:
-        self.all_gather_fds([], tag, timeout)
+    def barrier(self, tag: int, timeout: float = 120.0, members: Optional[List[int]] = None) -> None:
+        self.all_gather_fds([], tag, timeout, members)
 
     def close(self) -> None:
         try:

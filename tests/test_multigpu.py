@@ -115,3 +115,19 @@ def test_stalled_worker_is_dropped_after_the_round_timeout_and_evicted(tmp_path)
     h = res["history"]
     assert len(h["train_loss"]) == 2 and all(np.isfinite(h["train_loss"]))
     assert res["recovered"] >= 1
+
+
+def test_two_jobs_train_side_by_side_on_disjoint_gpu_pairs(tmp_path):
+    """The reference runs one pod per job, several at once (ml/pkg/ps/api.go:139-222).  Here two jobs take two GPUs
+    each out of the same worker pool and train concurrently: separate arenas, peer mappings, multicast objects
+    and signal pads per job, fan-outs through per-rank mailboxes."""
+    if _ngpus() < 4:
+        pytest.skip("needs 4 GPUs")
+    res = _result(_torchrun(4, os.path.join(ROOT, "tests", "mp_scripts", "spmd_two_jobs.py"), str(tmp_path), port=29555))
+    a, b = res["jobA"], res["jobB"]
+    assert a["error"] is None and b["error"] is None
+    assert sorted(a["ranks"] + b["ranks"]) == [0, 1, 2, 3] and not set(a["ranks"]) & set(b["ranks"])
+    assert len(a["train_loss"]) == 3 and len(b["train_loss"]) == 3
+    assert all(np.isfinite(a["train_loss"])) and all(np.isfinite(b["train_loss"]))
+    assert a["train_loss"] != b["train_loss"]            # different learning rates: really two models
+    assert res["overlap_s"] > 0.2                         # they ran at the same time, not one after the other

@@ -75,3 +75,27 @@ def test_dead_worker_is_detected_by_heartbeat_not_by_a_collective_timeout(tmp_pa
     assert res["after_death"][0][1] == 200                 # rank 0's own share still ran
     assert 1.0 < res["detect_s"] < 20.0
     assert res["later"][1][1] == 503 and res["later_s"] < 1.0
+
+
+def test_fan_outs_to_disjoint_ranks_overlap(tmp_path):
+    """Per-rank mailboxes: two fan-outs (two jobs on disjoint GPU subsets) do not serialise behind one lock, and
+    the rank allocator hands out disjoint subsets."""
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    script = os.path.join(ROOT, "tests", "mp_scripts", "spmd_mailbox.py")
+    procs = []
+    for r in range(3):
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES="", RANK=str(r), WORLD_SIZE="3", LOCAL_RANK=str(r),
+                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), KUBEML_HOME=str(tmp_path), OMP_NUM_THREADS="1")
+        procs.append(subprocess.Popen([sys.executable, script], stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                                      text=True, env=env, cwd=ROOT))
+    out0, err0 = procs[0].communicate(timeout=180)
+    for p in procs[1:]:
+        p.wait(timeout=60)
+    assert procs[0].returncode == 0, err0[-3000:]
+    res = next(json.loads(l[7:]) for l in out0.splitlines() if l.startswith("RESULT "))
+    assert res["both_s"] < 1.8                                    # 2 x 1 s of work in ~1 s
+    assert res["res"]["1"][0][0]["rank"] == 1 and res["res"]["2"][0][0]["rank"] == 2
+    assert res["res"]["1"][0][0]["members"] == [1]
+    assert res["held"] == [0, 1] and res["refused_when_short"] is True
+    assert [p[0]["rank"] for p in res["everyone"]] == [0, 1, 2]
