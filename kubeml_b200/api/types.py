@@ -30,6 +30,8 @@ class _Wire:
         for f in dataclasses.fields(self):
             if f.metadata.get("skip"):
                 continue
+            if f.metadata.get("omitempty") and not getattr(self, f.name):
+                continue            # extensions of the reference's schema stay off the wire unless used
             out[f.metadata.get("json", f.name)] = _plain(getattr(self, f.name))
         return out
 
@@ -69,7 +71,7 @@ class TrainOptions(_Wire):
     goal_accuracy: float = field(default=100.0, metadata=_j("goal_accuracy"))
     # Extension (the reference keeps no model past the end of a job): start from the checkpoint
     # of an earlier task instead of the function's fresh initialisation.
-    resume_from: str = field(default="", metadata=_j("resume_from"))
+    resume_from: str = field(default="", metadata=dict(_j("resume_from"), omitempty=True))
 
 
 @dataclass
