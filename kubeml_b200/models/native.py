@@ -321,13 +321,13 @@ def pick_block_n(m_tiles: int, n: int) -> int:
     return 128 if m_tiles * ((n + 127) // 128) >= sm_count() // 2 else 64
 
 
-def plan_cluster(m_tiles: int, n: int, chunks: int, bn0: int):
+def plan_cluster(m_tiles: int, n: int, chunks: int, bn0: int, base_budget: Optional[int] = None):
     """(block_n, splits) for a cluster split-K GEMM.  In this regime a CTA's time is its number of K
     chunks times a TMA round trip, whatever the tile width (measured: 0.42 us per chunk for 128x64 and
     128x128 alike), so when the default choice leaves long K loops a wider tile - half the tiles, twice
     the splits - halves the time (VGG 512->512 on 4x4: 72 -> 36 chunks per CTA)."""
     def plan(bn, budget=None):
-        budget = budget or sm_count()
+        budget = budget or base_budget or sm_count()
         tiles = m_tiles * ((n + bn - 1) // bn)
         S = min(auto_splits(tiles, chunks, min_chunks=_CL_MIN_CHUNKS, budget=budget), _CLUSTER_MAX)
         return -(-chunks // S), S, bn
@@ -400,7 +400,8 @@ def fused_plan(device: torch.device, m_tiles: int, n: int, chunks: int, bn0: int
     resident at once (the fused epilogue spins on a grid-wide barrier)."""
     if n > 2048 or n % 8:
         return None
-    bn_, S = plan_cluster(m_tiles, n, chunks, bn0)
+    budget = int(os.environ.get("KUBEML_FUSED_BUDGET", "0")) or None
+    bn_, S = plan_cluster(m_tiles, n, chunks, bn0, base_budget=budget)
     while True:
         ctas = m_tiles * ((n + bn_ - 1) // bn_) * S
         if device.type != "cuda":
