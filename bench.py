@@ -182,6 +182,7 @@ def run_own(args) -> int:
     # default) and the MEDIAN run is reported: a single 30-200 ms region is at the mercy of one host hiccup
     # (round 1's N=4 end-to-end outlier); every sample is listed under "samples_ms_per_step".
     sampler = ClockSampler(0).start()
+    time.sleep(0.5)      # nvidia-smi's start-up (driver queries) must not land inside the first timed run
     reps = max(1, int(os.environ.get("KUBEML_BENCH_REPEATS", "3")))
     e2e_jobs = [run_job(f"{ds_prefix}_t{args.steps}", resident=False) for _ in range(reps)]
     dev_jobs = [run_job(f"{ds_prefix}_t{args.steps}", resident=True) for _ in range(reps)]
