@@ -158,6 +158,13 @@ __device__ __forceinline__ float4 ld_dsmem_f4(uint32_t laddr, uint32_t rank) {
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(raddr) : "memory");
   return v;
 }
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t laddr, uint32_t rank) {
+  uint32_t raddr;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(laddr), "r"(rank));
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(raddr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -675,9 +682,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
       }
     }
-    // ---- column sums: shuffle fold, one row per warp, 6-way sum, one atomic per column per CTA ---------
+    // ---- column sums: shuffle fold, one row per warp, 6-way sum per CTA --------------------------------
     kml::BnScratch* sc = args.bn_sc;
     float* gstats = sc->acc[gstate.x & 1u];
+    float* cs = co + 3 * BLOCK_N;                        // [2][BLOCK_N] this CTA's column sums (cluster-local mode)
+    // One 128-row tile holds every row of the layer (M <= 128: the 1x1 maps of ResNet's last stage): the cluster
+    // that computes a column block already has the complete statistics of its columns.  The CTAs then exchange
+    // their sums through distributed shared memory - no global atomics, no grid-wide barrier.
+    const bool local_stats = args.m_tiles == 1;
     if (kGroups == 16) {
 #pragma unroll
       for (int t = 0; t < 4; ++t) {
@@ -699,21 +711,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       float tot = 0.f;
 #pragma unroll
       for (int w = 0; w < kWarps; ++w) tot += st_sm[w * 2 * BLOCK_N + i];
-      if (gc < args.n_valid) atomicAdd(gstats + static_cast<size_t>(which) * args.n_valid + gc, tot);
+      if (local_stats) cs[i] = tot;
+      else if (gc < args.n_valid) atomicAdd(gstats + static_cast<size_t>(which) * args.n_valid + gc, tot);
     }
-    // ---- whole-grid barrier: every CTA's column sums are in, then finish the BatchNorm --------------
-    const unsigned ncta = gridDim.x * gridDim.y * gridDim.z;
-    if (blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1) {
-      float4* nxt = reinterpret_cast<float4*>(sc->acc[(gstate.x & 1u) ^ 1u]);    // the next launch's buffer
-      for (int i = et; i < 2 * kml::kBnMaxC / 4; i += kNumThreads) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    __syncthreads();
-    if (et == 0) kml::grid_arrive_and_wait(sc, gstate.y, ncta);
-    __syncthreads();
-    if ((blockIdx.x | blockIdx.y | blockIdx.z) == 0 && et == 0) {   // everyone has arrived: publish the next launch's state
-      sc->launches = gstate.x + 1u;
-      sc->bar_base = gstate.y + ncta;
-      if (kFwd && args.bn_nbt != nullptr) *args.bn_nbt += 1;
+    if (local_stats) {
+      cluster_sync_all();                                // every CTA's sums are in its shared memory
+      if ((blockIdx.x | blockIdx.y | blockIdx.z) == 0 && et == 0 && kFwd && args.bn_nbt != nullptr) *args.bn_nbt += 1;
+    } else {
+      // ---- whole-grid barrier: every CTA's column sums are in, then finish the BatchNorm ------------
+      const unsigned ncta = gridDim.x * gridDim.y * gridDim.z;
+      if (blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1) {
+        float4* nxt = reinterpret_cast<float4*>(sc->acc[(gstate.x & 1u) ^ 1u]);    // the next launch's buffer
+        for (int i = et; i < 2 * kml::kBnMaxC / 4; i += kNumThreads) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      __syncthreads();
+      if (et == 0) kml::grid_arrive_and_wait(sc, gstate.y, ncta);
+      __syncthreads();
+      if ((blockIdx.x | blockIdx.y | blockIdx.z) == 0 && et == 0) {   // everyone has arrived: publish the next launch's state
+        sc->launches = gstate.x + 1u;
+        sc->bar_base = gstate.y + ncta;
+        if (kFwd && args.bn_nbt != nullptr) *args.bn_nbt += 1;
+      }
     }
     {
       const float inv_m = 1.f / static_cast<float>(args.m_valid);
@@ -722,7 +740,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         const int gc = nt * BLOCK_N + c;
         float c0 = 0.f, c1 = 0.f, c2 = 0.f;
         if (gc < args.n_valid) {
-          const float t1 = __ldcg(gstats + gc), t2 = __ldcg(gstats + args.n_valid + gc);
+          float t1 = 0.f, t2 = 0.f;
+          if (local_stats) {
+            for (int p = 0; p < S; ++p) {
+              t1 += ld_dsmem_f32(smem_u32(cs + c), static_cast<uint32_t>(p));
+              t2 += ld_dsmem_f32(smem_u32(cs + BLOCK_N + c), static_cast<uint32_t>(p));
+            }
+          } else {
+            t1 = __ldcg(gstats + gc); t2 = __ldcg(gstats + args.n_valid + gc);
+          }
           if constexpr (kFwd) {
             const float d = t1 * inv_m;
             const float mean = pv_sm[c] + d;
