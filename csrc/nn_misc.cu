@@ -846,6 +846,20 @@ int kml_bias_act(const float* x_slabs, int nslabs, size_t slab_stride, const flo
   return 0;
 }
 
+// Writes the device's global nanosecond timer into slot[idx]: a timeline of a captured training step without a
+// profiler (bench/step_timeline.py).  A regular launch: it orders behind everything before it on the stream.
+__global__ void stamp_kernel(unsigned long long* slots, int idx) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  slots[idx] = t;
+}
+int kml_stamp(unsigned long long* slots, int idx, void* stream) {
+  KML_CHECK(slots != nullptr && idx >= 0, "kml_stamp: bad arguments");
+  stamp_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(slots, idx);
+  KML_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int kml_pack_rows_bf16(const float* src, void* dst, int rows, int cols, int ld, void* stream) {
   KML_CHECK(src && dst && ld >= cols, "kml_pack_rows_bf16: bad arguments");
   KML_CUDA(kml::launch_pdl(pack_rows_kernel, dim3(grid_for(static_cast<size_t>(rows) * ld)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), src, static_cast<__nv_bfloat16*>(dst), rows, cols, ld));

@@ -279,6 +279,9 @@ int kml_im2col(const void* x, void* cols, int N, int H, int W, int C, int KH, in
 int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, int W, int C, int KH, int KW,
                int stride, int pad, int ldk, void* stream);
 int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld, void* stream);
+/* slots[idx] = %globaltimer (ns), stream-ordered: per-phase timeline of a captured step (no reference
+ * counterpart; the reference logs one wall-clock line around its merge, ml/pkg/train/job.go:397,412). */
+int kml_stamp(unsigned long long* slots, int idx, void* stream);
 int kml_pack_rows_bf16(const float* src, void* dst_bf16, int rows, int cols, int ld, void* stream);
 /* VGG-style layers (ReLU fused in the producing GEMM, Dropout p=0.5 in the classifier, the
  * AdaptiveAvgPool2d((7,7)) of torchvision vgg on a 1x1 map; ml/experiments/kubeml/function_vgg11.py). */

@@ -148,6 +148,7 @@ def _declare(lib) -> None:
     sig("kml_col2im", c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
         c_int, c_int, c_void_p)
     sig("kml_colsum_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_longlong, c_void_p)
+    sig("kml_stamp", c_int, c_void_p, c_int, c_void_p)
     sig("kml_pack_rows_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
     sig("kml_relu_bwd", c_int, c_void_p, c_void_p, c_void_p, c_float, c_size_t, c_void_p)
     sig("kml_relu_bwd_cols", c_int, c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_float, c_void_p,

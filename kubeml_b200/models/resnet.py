@@ -54,6 +54,9 @@ class NativeResNet(NativeNet):
         self._blocks = [(f"layer{i}.{j}", blk) for i in range(1, 5)
                         for j, blk in enumerate(getattr(self, f"layer{i}"))]
         self._saved: Optional[dict] = None
+        import os
+        self._stamps_on = os.environ.get("KUBEML_STAMPS") == "1"
+        self.stamps: Optional[torch.Tensor] = None
 
     # wgrad reduces over N*Ho*Wo pixels: shallow-and-wide early layers need K-splits to fill the GPU
     @staticmethod
@@ -77,10 +80,23 @@ class NativeResNet(NativeNet):
             return x.permute(0, 2, 3, 1).contiguous().to(act_dtype())
         raise ValueError(f"unexpected input shape {tuple(x.shape)}")
 
+    # Optional phase timeline (KUBEML_STAMPS=1, bench/step_timeline.py): the GPU timer is written into
+    # `self.stamps[i]` at stage boundaries of the forward and backward programs.
+    STAMP_NAMES = ["start", "stem", "layer1", "layer2", "layer3", "layer4", "head_fwd", "bwd_head", "bwd_layer4",
+                   "bwd_layer3", "bwd_layer2", "bwd_layer1", "bwd_stem_end"]
+
+    def _stamp(self, name: str) -> None:
+        if not self._stamps_on:
+            return
+        if self.stamps is None or self.stamps.device != self._arena.weights.device:
+            self.stamps = torch.zeros(32, dtype=torch.int64, device=self._arena.weights.device)
+        K.stamp(self.stamps, self.STAMP_NAMES.index(name))
+
     def _forward_impl(self, x: torch.Tensor, train: bool) -> torch.Tensor:
         x = self._to_nhwc_bf16(x)
         N = x.shape[0]
         B = self.buffers_for(N, train)
+        self._stamp("start")
         S = {"x": x, "blocks": []}
         a1, c1s = conv_bn_forward(self.conv1, self.bn1, x, B, "stem", "stem.bn", train, relu=True)
         _, H1, W1, _ = a1.shape
@@ -90,7 +106,10 @@ class NativeResNet(NativeNet):
         K.maxpool_fwd(a1, p1, idx, 3, 2, 1)
         S.update(c1=c1s, a1=a1, p1=p1)
         h = p1
+        self._stamp("stem")
         for tag, blk in self._blocks:
+            if tag.endswith(".0") and not tag.startswith("layer1"):
+                self._stamp("layer" + str(int(tag[5]) - 1))
             idn, tds = h, None
             if blk.downsample is not None:       # the projection shortcut runs next to the main branch
                 with B.on_side():
@@ -102,6 +121,7 @@ class NativeResNet(NativeNet):
             out, t2s = conv_bn_forward(blk.conv2, blk.bn2, a, B, tag + ".c2", tag + ".bn2", train, relu=True, res=idn)
             S["blocks"].append((h, t1s, a, t2s, tds, out))
             h = out
+        self._stamp("layer4")
         Nn, Hh, Ww, C = h.shape
         if Hh * Ww == 1:
             pooled = h.view(Nn, C)
@@ -109,6 +129,7 @@ class NativeResNet(NativeNet):
             pooled = B.get("avg.y", (Nn, C))
             K.avgpool_fwd(h, pooled)
         logits = linear_forward(self.fc, pooled, B, "fc")
+        self._stamp("head_fwd")
         S.update(last=h, pooled=pooled, B=B)
         if train:
             self._saved = S
@@ -150,8 +171,11 @@ class NativeResNet(NativeNet):
             K.avgpool_bwd(dpooled, t)
             dh = Act(t)
         nblk = len(self._blocks)
+        self._stamp("bwd_head")
         for bi, ((tag, blk), (h, t1, a, t2, td, out)) in enumerate(zip(reversed(self._blocks),
                                                                          reversed(S["blocks"]))):
+            if bi > 0 and tag.endswith("." + str(len(getattr(self, tag[:6])) - 1)):
+                self._stamp("bwd_layer" + str(int(tag[5]) + 1))
             if tag == "layer3." + str(len(self.layer3) - 1):
                 self._mark_tail_ready(B)          # layer4 and fc are done: their optimizer update may start
             first_block = bi == nblk - 1          # its input gradient feeds the max-pool backward (dense)
@@ -173,11 +197,13 @@ class NativeResNet(NativeNet):
                 did = conv_backward(blk.downsample[0], h, dtd, B, tag + ".cd")
                 dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=did.t)
         # stem
+        self._stamp("bwd_layer1")
         da1 = B.get("pool.dx", tuple(S["a1"].shape))
         K.maxpool_bwd(dh.dense(B, "pool.dy"), B["pool.idx"], da1, 3, 2, 1)
         dc1, _ = bn_backward(self.bn1, Act(da1), S["a1"], S["c1"], B, "stem.bn")
         conv_backward(self.conv1, S["x"], dc1, B, "stem", need_dx=False)
         self._end_backward(B)
+        self._stamp("bwd_stem_end")
 
 
 def resnet34(num_classes: int = 1000) -> NativeResNet:

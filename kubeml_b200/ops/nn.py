@@ -269,6 +269,12 @@ def colsum(x, out) -> None:
     out.copy_(x.float().sum(0))
 
 
+def stamp(slots, idx: int) -> None:
+    """slots[idx] (int64 on the device) = the GPU's nanosecond timer when the stream gets here."""
+    if slots.is_cuda:
+        _native.check(_native.lib().kml_stamp(slots.data_ptr(), int(idx), _native.stream_ptr()), "kml_stamp")
+
+
 def pack_rows(src, dst) -> None:
     """dst bf16 [rows, ld] <- src fp32 [rows, cols], zero padded."""
     rows, cols = src.shape
