@@ -24,6 +24,7 @@
 #include "driver_api.h"
 #include "../include/kubeml_b200.h"
 #include <cuda.h>
+#include <algorithm>
 #include <mutex>
 #include <unordered_map>
 
@@ -1380,11 +1381,26 @@ int coresident_of(int cluster_size) {
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) return -1;
   cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   kml::note_kernel(reinterpret_cast<const void*>(kernel));
-  if (cluster_size <= 1) {
-    int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kNumThreads, smem) != cudaSuccess) return -1;
-    return per_sm * kml::num_sms();
-  }
+  int api_per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&api_per_sm, kernel, kNumThreads, smem) != cudaSuccess) return -1;
+  if (api_per_sm < 1) api_per_sm = 1;
+  // The runtime's occupancy calculator answers 1 CTA per SM for these kernels; ncu's launch__occupancy_limit_*
+  // (registers 2, shared memory 2) and the hardware say 2: a 256-CTA grid of the fused kernel passes its
+  // grid-wide barrier on 148 SMs (profiles/r2).  Count what the resources allow - registers in 8-register
+  // units per thread, dynamic + 1 KB reserved shared memory against the 228 KB of an SM - and scale the API's
+  // answer by it (KUBEML_FUSED_CAP_SCALE=1 keeps the raw API number).  Every spin is bounded: a grid that does
+  // not fit fails the launch instead of hanging.
+  cudaFuncAttributes fa;
+  if (cudaFuncGetAttributes(&fa, kernel) != cudaSuccess) return -1;
+  int dev = kml::current_device(), smem_sm = 0, regs_sm = 0;
+  cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+  cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
+  const int regs_cta = ((fa.numRegs + 7) / 8 * 8) * kNumThreads;
+  int by_res = std::min(smem_sm / static_cast<int>(smem + 1024), regs_cta > 0 ? regs_sm / regs_cta : 1);
+  by_res = std::max(1, std::min(by_res, 2));
+  static const int want_scale = [] { const char* e = getenv("KUBEML_FUSED_CAP_SCALE"); return e ? atoi(e) : 2; }();
+  const int scale = std::max(1, std::min(want_scale, by_res / api_per_sm));
+  if (cluster_size <= 1) return api_per_sm * scale * kml::num_sms();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(1, 1, cluster_size);
   cfg.blockDim = dim3(kNumThreads);
@@ -1395,11 +1411,29 @@ int coresident_of(int cluster_size) {
   cfg.attrs = attr; cfg.numAttrs = 1;
   int clusters = 0;
   if (cudaOccupancyMaxActiveClusters(&clusters, kernel, &cfg) != cudaSuccess) return -1;
-  return clusters * cluster_size;
+  return clusters * cluster_size * scale;
 }
 }  // namespace
 
 extern "C" {
+
+// Resident CTAs per SM of one instantiation as the occupancy calculator sees it (diagnostics).
+int kml_gemm_blocks_per_sm(int block_n, int b_mn, int bn_mode) {
+  constexpr size_t smem64 = Stages<64>::value * (kBlockM * kBlockK * 2 + 64 * kBlockK * 2) + 1024 + 640;
+  int per_sm = -1;
+  if (block_n != 64) return -1;
+  const void* k = bn_mode == 0 ? (b_mn ? (const void*)gemm_tcgen05_kernel<64, false, true, false, 0> : (const void*)gemm_tcgen05_kernel<64, false, false, false, 0>)
+                 : bn_mode == 1 ? (const void*)gemm_tcgen05_kernel<64, false, false, false, 1>
+                                : (const void*)gemm_tcgen05_kernel<64, false, true, false, 2>;
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem64));
+  kml::note_kernel(k);
+  cudaFuncAttributes fa;
+  cudaFuncGetAttributes(&fa, k);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kNumThreads, smem64);
+  kml::set_error("regs %d static smem %zu max dyn %d carveout %d blocks/SM %d (dyn smem %zu)", fa.numRegs, fa.sharedSizeBytes,
+                 fa.maxDynamicSharedSizeBytes, fa.preferredShmemCarveout, per_sm, smem64);
+  return per_sm;
+}
 
 int kml_gemm_max_coresident(int block_n, int a_mn, int b_mn, int cluster_size) {
   // cached per (device, variant, cluster size): the occupancy queries are host-side only but not free

@@ -180,6 +180,9 @@ typedef struct {
  * `cluster_size` that is guaranteed to be resident at once on the current device: the bound a fused
  * BatchNorm launch must respect.  Returns <= 0 on error. */
 int kml_gemm_max_coresident(int block_n, int a_mn, int b_mn, int cluster_size);
+/* Diagnostics: resident CTAs per SM of the 64-wide instantiation (bn_mode 0/1/2) per the occupancy calculator;
+ * kml_last_error() then holds the function attributes it was computed from. */
+int kml_gemm_blocks_per_sm(int block_n, int b_mn, int bn_mode);
 
 typedef struct {
   const float* bias;        /* per output column, added by K-split 0; may be NULL                   */
