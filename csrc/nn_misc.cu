@@ -571,6 +571,46 @@ image_prep_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict
 }
 
 
+// The same with the flip / crop offsets drawn inside the kernel: sample n of call number `ctr` gets a hash of
+// (seed, ctr, n).  state = {calls so far, finished-block ticket} lives on the device and is advanced by the last
+// block to finish, so the kernel can sit in a replayed CUDA graph and no host-side random tensors (and the
+// handful of tiny kernels that build them) are needed per step.
+__global__ void __launch_bounds__(kThreads)
+image_prep_rand_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict__ y, unsigned long long* state,
+                       unsigned seed, int N, int H, int W, int C, int pad, float m0, float m1, float m2, float s0, float s1,
+                       float s2) {
+  kml::pdl_launch_dependents();
+  kml::pdl_wait();
+  const unsigned ctr = static_cast<unsigned>(*reinterpret_cast<volatile unsigned long long*>(state));
+  const unsigned span = 2u * pad + 1u;
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    size_t p = i / C;
+    int w = static_cast<int>(p % W); p /= W;
+    int h = static_cast<int>(p % H);
+    const int n = static_cast<int>(p / H);
+    unsigned r = (static_cast<unsigned>(n) * 0x9E3779B1u) ^ (ctr * 0x85EBCA77u) ^ seed;
+    r ^= r >> 16; r *= 0x7feb352du; r ^= r >> 15; r *= 0x846ca68bu; r ^= r >> 16;
+    h += static_cast<int>((r >> 8) % span) - pad;
+    w += static_cast<int>((r >> 20) % span) - pad;
+    const bool inside = h >= 0 && h < H && w >= 0 && w < W;
+    if (r & 1u) w = W - 1 - w;
+    const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2);
+    const float istd = c == 0 ? s0 : (c == 1 ? s1 : s2);
+    float v = 0.f;
+    if (inside) v = static_cast<float>(x[((static_cast<size_t>(n) * H + h) * W + w) * C + c]) * (1.f / 255.f);
+    y[i] = __float2bfloat16_rn((v - mean) * istd);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    // every block read `ctr` at its start; the last one to finish moves the call counter on
+    const unsigned ticket = atomicInc(reinterpret_cast<unsigned*>(state + 1), gridDim.x - 1);
+    if (ticket == gridDim.x - 1) *state = static_cast<unsigned long long>(ctr) + 1ull;
+  }
+}
+
 // ---------------------------------------------------------------------------------- VGG-style layers
 // g = scale * dy * (y > 0): gradient through a ReLU that was fused into the producing GEMM's epilogue;
 // with y the *dropped* output and scale = 1/(1-p) it is also the gradient through ReLU -> Dropout
@@ -874,6 +914,17 @@ int kml_image_prep(const void* x_u8, void* y_bf16, const int* aug, int N, int H,
   const size_t total = static_cast<size_t>(N) * H * W * C;
   KML_CUDA(kml::launch_pdl(image_prep_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const unsigned char*>(x_u8), static_cast<__nv_bfloat16*>(y_bf16), aug, N, H, W, C, pad, mean3[0], mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2]));
   KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
+int kml_image_prep_rand(const void* x_u8, void* y_bf16, unsigned long long* state, unsigned seed, int N, int H, int W,
+                        int C, int pad, const float* mean3, const float* std3, void* stream) {
+  KML_CHECK(x_u8 && y_bf16 && state && mean3 && std3 && C <= 3 && pad >= 0, "kml_image_prep_rand: bad arguments");
+  const size_t total = static_cast<size_t>(N) * H * W * C;
+  KML_CUDA(kml::launch_pdl(image_prep_rand_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream),
+                           static_cast<const unsigned char*>(x_u8), static_cast<__nv_bfloat16*>(y_bf16), state, seed, N, H, W, C,
+                           pad, mean3[0], mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2]));
   kml::count_launch();
   return 0;
 }

@@ -282,6 +282,11 @@ int kml_im2col(const void* x, void* cols, int N, int H, int W, int C, int KH, in
 int kml_col2im(const void* dcols, const void* addend, void* dx, int N, int H, int W, int C, int KH, int KW,
                int stride, int pad, int ldk, void* stream);
 int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld, void* stream);
+/* kml_image_prep with the flip / crop offsets drawn in the kernel from a hash of (seed, call number, sample);
+ * state = uint64[2] on the device, zero at start, advanced by the kernel (CUDA-graph replay safe).  Replaces the
+ * per-sample PIL transforms of ml/experiments/kubeml/function_resnet34.py:17-30. */
+int kml_image_prep_rand(const void* x_u8, void* y_bf16, unsigned long long* state, unsigned seed, int N, int H, int W,
+                        int C, int pad, const float* mean3, const float* std3, void* stream);
 /* slots[idx] = %globaltimer (ns), stream-ordered: per-phase timeline of a captured step (no reference
  * counterpart; the reference logs one wall-clock line around its merge, ml/pkg/train/job.go:397,412). */
 int kml_stamp(unsigned long long* slots, int idx, void* stream);

@@ -47,13 +47,14 @@ class Cifar10Dataset(KubeDataset):
         B = x.shape[0]
         augment = self.is_training() and os.environ.get("KUBEML_RESNET_NOAUG") != "1"   # parity runs: no randomness
         if self.native and x.is_cuda:
-            aug = None
-            if augment:
-                r = torch.randint(0, 2 * 9 * 9, (B,), device=x.device, dtype=torch.int32)
-                aug = (r % 2) | (((r // 2) % 9) << 8) | ((r // 18) << 16)
             out = torch.empty((B, 32, 32, 3), dtype=torch.bfloat16, device=x.device)
-            ops.nn.image_prep(x, out, aug, 4, _MEAN, _STD)
-            return out, y.to(torch.int64)
+            state = None
+            if augment:        # flip + crop(32, padding 4) drawn inside the kernel: one launch, no host-side random tensors
+                state = self._consts.get(("aug", x.device))
+                if state is None:
+                    state = self._consts[("aug", x.device)] = torch.zeros(2, dtype=torch.int64, device=x.device)
+            ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED)
+            return out, (y if y.dtype == torch.int64 else y.to(torch.int64))
         if augment:
             # RandomHorizontalFlip + RandomCrop(32, padding=4), vectorised over the batch
             flip = torch.rand(B, device=x.device) < 0.5

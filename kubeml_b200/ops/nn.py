@@ -286,9 +286,18 @@ def pack_rows(src, dst) -> None:
     dst[:, :cols].copy_(src)
 
 
-def image_prep(x_u8, y, aug, pad: int, mean: Tuple[float, float, float], std: Tuple[float, float, float]) -> None:
-    """uint8 NHWC -> normalised bf16 NHWC with optional per-sample flip/crop codes (see header)."""
+def image_prep(x_u8, y, aug, pad: int, mean: Tuple[float, float, float], std: Tuple[float, float, float],
+               rand_state=None, seed: int = 0) -> None:
+    """uint8 NHWC -> normalised bf16 NHWC with optional per-sample flip/crop codes (see header).  With
+    `rand_state` (int64[2] on the device, zeros) the codes are drawn inside the kernel instead of being passed."""
     N, H, W, C = x_u8.shape
+    if x_u8.is_cuda and rand_state is not None:
+        m = (ctypes.c_float * 3)(*mean)
+        s = (ctypes.c_float * 3)(*std)
+        _native.check(_native.lib().kml_image_prep_rand(x_u8.data_ptr(), y.data_ptr(), rand_state.data_ptr(),
+                                                        int(seed) & 0xFFFFFFFF, N, H, W, C, pad, m, s,
+                                                        _native.stream_ptr()), "kml_image_prep_rand")
+        return
     if x_u8.is_cuda:
         m = (ctypes.c_float * 3)(*mean)
         s = (ctypes.c_float * 3)(*std)

@@ -744,3 +744,40 @@ def test_grid_barrier_kernels_finish_while_another_stream_occupies_the_gpu(dev):
     torch.cuda.synchronize()
     assert _rel(y, want) < 2e-2 and _rel(y2, want) < 2e-2
     assert torch.isfinite(dx.float()).all()
+
+
+def test_image_prep_with_in_kernel_augmentation(dev):
+    """Flip / crop offsets drawn inside the kernel: every sample must equal the explicit-code transform for one of the
+    2 x 9 x 9 codes, the codes must differ between samples and between calls, and the device-side call counter moves."""
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(0)
+    N, pad = 16, 4
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    x = torch.randint(0, 256, (N, 32, 32, 3), dtype=torch.uint8, device=dev)
+    state = torch.zeros(2, dtype=torch.int64, device=dev)
+    outs = []
+    for call in range(2):
+        y = torch.empty(N, 32, 32, 3, dtype=torch.bfloat16, device=dev)
+        K.image_prep(x, y, None, pad, mean, std, rand_state=state, seed=123)
+        outs.append(y)
+    torch.cuda.synchronize()
+    assert int(state[0].item()) == 2
+    cand = {}
+    for flip in (0, 1):
+        for dy in range(9):
+            for dx in range(9):
+                code = flip | (dy << 8) | (dx << 16)
+                yy = torch.empty(N, 32, 32, 3, dtype=torch.bfloat16, device=dev)
+                K.image_prep(x, yy, torch.full((N,), code, dtype=torch.int32, device=dev), pad, mean, std)
+                cand[code] = yy
+    torch.cuda.synchronize()
+    codes = []
+    for y in outs:
+        row = []
+        for n in range(N):
+            hit = [c for c, yy in cand.items() if torch.equal(yy[n], y[n])]
+            assert hit, f"sample {n} matches no flip/crop code"
+            row.append(hit[0])
+        codes.append(row)
+    assert len(set(codes[0])) > N // 2              # not one code for the whole batch
+    assert codes[0] != codes[1]                     # and not the same codes on the next call
