@@ -203,7 +203,38 @@ kavg_merge_kernel(const kml_merge_params p) {
   uint2* wb0 = (solo && p.w_bf16 != nullptr) ? reinterpret_cast<uint2*>(p.w_bf16) : nullptr;
 
   // ---- phase 0: fused last local step on the own replica --------------------------------------
-  if (p.fuse_sgd) {
+  if (p.fuse_sgd == 2) {
+    // Adam (torch.optim.Adam semantics, csrc/optim.cu): bias corrections from the device-side step count
+    float4* w = reinterpret_cast<float4*>(p.replica[p.my_rank]);
+    const float4* g = reinterpret_cast<const float4*>(p.grad);
+    float4* m1 = reinterpret_cast<float4*>(p.momentum_buf);
+    float4* m2 = reinterpret_cast<float4*>(p.state2);
+    const int t = (p.step_dev ? *reinterpret_cast<volatile int*>(p.step_dev) : 0) + 1;
+    const float bc1 = 1.f - powf(p.beta1, static_cast<float>(t));
+    const float bc2_sqrt = sqrtf(1.f - powf(p.beta2, static_cast<float>(t)));
+    const float step_size = p.lr / bc1;
+    for (size_t i = tid; i < nsgd4; i += nthreads) {
+      float4 wv = w[i], gv = __ldcs(g + i), a = m1[i], b = m2[i];
+      float* wp = &wv.x; float* gp = &gv.x; float* ap = &a.x; float* bp = &b.x;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float gr = fmaf(p.weight_decay, wp[k], gp[k]);
+        ap[k] = fmaf(p.beta1, ap[k], (1.f - p.beta1) * gr);
+        bp[k] = fmaf(p.beta2, bp[k], (1.f - p.beta2) * gr * gr);
+        wp[k] -= step_size * (ap[k] / (sqrtf(bp[k]) / bc2_sqrt + p.eps));
+      }
+      w[i] = wv;                 // the moments are dead after the merge (optimizer reset): not written back
+      if (wb0 != nullptr) {
+        __nv_bfloat162 x0 = __floats2bfloat162_rn(wv.x, wv.y);
+        __nv_bfloat162 x1 = __floats2bfloat162_rn(wv.z, wv.w);
+        uint2 r;
+        r.x = *reinterpret_cast<uint32_t*>(&x0);
+        r.y = *reinterpret_cast<uint32_t*>(&x1);
+        wb0[i] = r;
+      }
+    }
+    if (!solo) local_barrier();
+  } else if (p.fuse_sgd) {
     float4* w = reinterpret_cast<float4*>(p.replica[p.my_rank]);
     const float4* g = reinterpret_cast<const float4*>(p.grad);
     const float4* m = reinterpret_cast<const float4*>(p.momentum_buf);
@@ -232,12 +263,29 @@ kavg_merge_kernel(const kml_merge_params p) {
     }
     if (!solo) local_barrier();     // the whole replica is final before anyone is told so
   }
-  if (solo) {
-    if (p.momentum_buf) {           // optimizer reset (network.py:121-128)
+  auto reset_optimizer = [&]() {    // the reference discards optimizer state at every sync (network.py:121-128)
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.momentum_buf) {
       float4* m = reinterpret_cast<float4*>(p.momentum_buf);
-      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
       for (size_t i = tid; i < nsgd4; i += nthreads) __stcs(m + i, z);
     }
+    if (p.state2) {
+      float4* m = reinterpret_cast<float4*>(p.state2);
+      for (size_t i = tid; i < nsgd4; i += nthreads) __stcs(m + i, z);
+    }
+  };
+  if (solo) {
+    // the step count is read by every CTA in phase 0: only the grid's last CTA may clear it
+    __shared__ unsigned s_last;
+    if (p.step_dev != nullptr && p.fuse_sgd == 2) {
+      __syncthreads();
+      if (threadIdx.x == 0) s_last = atomicInc(reinterpret_cast<unsigned*>(p.step_dev + 1), gridDim.x - 1) == gridDim.x - 1;
+      __syncthreads();
+      if (s_last && threadIdx.x == 0) p.step_dev[0] = 0;
+    } else if (p.step_dev != nullptr && tid == 0 && p.state2 != nullptr) {
+      p.step_dev[0] = 0;
+    }
+    reset_optimizer();
     return;
   }
 
@@ -382,11 +430,8 @@ kavg_merge_kernel(const kml_merge_params p) {
   }
 
   // ---- phase 2: optimizer reset -----------------------------------------------------------------
-  if (p.momentum_buf) {
-    float4* m = reinterpret_cast<float4*>(p.momentum_buf);
-    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (size_t i = tid; i < nsgd4; i += nthreads) __stcs(m + i, z);
-  }
+  reset_optimizer();
+  if (p.step_dev != nullptr && p.state2 != nullptr && tid == 0) p.step_dev[0] = 0;   // every CTA read it before the local barrier
 
   uint2* wb = reinterpret_cast<uint2*>(p.w_bf16);
   const float4* wme = reinterpret_cast<const float4*>(p.replica[p.my_rank]);
@@ -504,6 +549,7 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
       KML_CHECK(p.flags[r] != nullptr, "flags[%d] is null", r);
   }
   if (p.fuse_sgd) KML_CHECK(p.grad != nullptr, "fuse_sgd set without grad");
+  if (p.fuse_sgd == 2) KML_CHECK(p.momentum_buf != nullptr && p.state2 != nullptr, "fused Adam step needs both moment buffers");
   KML_CHECK(p.n_sgd % 4 == 0 && p.n_sgd <= p.n_f32, "n_sgd (%zu) must be a multiple of 4 and <= n_f32", p.n_sgd);
   if (p.generation == 0) p.mcast = nullptr;
 

@@ -93,6 +93,12 @@ typedef struct {
   int* status;                        /* device int; on a barrier timeout bit r is set for every
                                          rank r that did not arrive, and the kernel returns without
                                          touching any replica or optimizer state                  */
+  /* fuse_sgd == 2: the fused last local step is Adam (function_vgg11.py's optimizer) instead of SGD:
+   * momentum_buf = exp_avg, state2 = exp_avg_sq (both zeroed after the merge: the optimizer reset), step count
+   * on the device (step_dev[0], reset to 0 after the merge), lr / weight_decay as above. */
+  float* state2;
+  float beta1, beta2, eps;
+  int* step_dev;
 } kml_merge_params;
 
 /* Bits of *status beyond the per-rank "did not arrive" bits 0..7. */

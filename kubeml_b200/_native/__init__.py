@@ -46,6 +46,11 @@ class MergeParams(Structure):
         ("w_bf16", c_void_p),
         ("timeout_cycles", c_ulonglong),
         ("status", c_void_p),
+        ("state2", c_void_p),
+        ("beta1", c_float),
+        ("beta2", c_float),
+        ("eps", c_float),
+        ("step_dev", c_void_p),
     ]
 
 

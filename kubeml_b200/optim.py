@@ -53,6 +53,10 @@ class _FlatOptimizer:
         self.state: dict = {}
         self._arena = None
         self._flat = None
+        self._step_calls = 0          # step() invocations, counted by KubeModel around each train()
+        self._armed = False
+        self._deferred = False
+        self._state_clean = False     # the merge kernel zeroed the optimizer state: reset_state() has nothing to do
 
     # -- arena attachment (done by DeviceSync.attach / models) --------------------------------
     def attach_arena(self, arena) -> None:
@@ -109,6 +113,43 @@ class _FlatOptimizer:
             self._names = [(by_ptr[p.data_ptr()], p) for p in self.params if p.data_ptr() in by_ptr]
         return self._names
 
+    # ---- the round's last step, left to the K-AVG merge kernel (csrc/merge.cu phase 0) -------------------
+    def arm_deferral(self) -> bool:
+        """The next step() is not launched: the K-AVG merge kernel applies it in the same pass that
+        averages the replicas.  KubeModel arms this only around the last train() call of a sync round, and
+        only for functions it has seen call step() exactly once per batch; a second step() before the merge
+        flushes the pending one first (see step())."""
+        ok = (self._arena is not None and self._flat is not False and len(self.param_groups) == 1
+              and not self.param_groups[0].get("nesterov", False) and bool(self.params) and self.params[0].is_cuda)
+        self._armed = bool(ok)
+        return self._armed
+
+    def disarm(self) -> None:
+        self._armed = False
+
+    def flush_deferred(self) -> None:
+        """Apply a pending deferred update with the ordinary kernel (the merge did not take it:
+        this rank sat the round out, or user code stepped again)."""
+        if not self._deferred:
+            return
+        self._deferred = False
+        flat = self._flat_views()
+        if flat is not None:
+            self._flat_step(*flat)
+
+    def _take_deferral(self) -> bool:
+        """Inside step() on the flat path: True when this call is the one the merge kernel will apply."""
+        if self._deferred:                 # a second step() before the merge: the pending one goes first
+            self.flush_deferred()
+        if self._armed:
+            self._armed = False
+            self._deferred = True
+            return True
+        return False
+
+    def _flat_step(self, w, gr) -> None:
+        raise NotImplementedError
+
     def _params_with_groups(self):
         for grp in self.param_groups:
             for p in grp["params"]:
@@ -134,82 +175,53 @@ class SGD(_FlatOptimizer):
         super().__init__(params, dict(lr=lr, momentum=momentum, weight_decay=weight_decay,
                                       nesterov=nesterov))
         self._bufs: Optional[List[torch.Tensor]] = None
-        self._step_calls = 0          # step() invocations, counted by KubeModel around each train()
-        self._armed = False
-        self._deferred = False
-
-    def arm_deferral(self) -> bool:
-        """The next step() is not launched: the K-AVG merge kernel applies it in the same pass that
-        averages the replicas (csrc/merge.cu phase 0).  KubeModel arms this only around the last
-        train() call of a sync round, and only for functions it has seen call step() exactly once per
-        batch; a second step() before the merge flushes the pending one first (see step())."""
-        ok = (self._arena is not None and self._flat is not False and len(self.param_groups) == 1
-              and not self.param_groups[0]["nesterov"] and bool(self.params) and self.params[0].is_cuda)
-        self._armed = bool(ok)
-        return self._armed
-
-    def disarm(self) -> None:
-        self._armed = False
-
-    def flush_deferred(self) -> None:
-        """Apply a pending deferred update with the ordinary kernel (the merge did not take it:
-        this rank sat the round out, or user code stepped again)."""
-        if not self._deferred:
-            return
-        self._deferred = False
-        flat = self._flat_views()
-        if flat is None:
-            return
-        g = self.param_groups[0]
-        w, gr = flat
-        mb = self._arena.state1[: w.numel()] if g["momentum"] else None
-        ops.sgd_step_(w, gr, mb, g["lr"], g["weight_decay"], g["momentum"], g["nesterov"],
-                      w_bf16=getattr(self._arena, "wbf16", None))
 
     def reset_state(self) -> None:
-        if self._arena is not None and self.defaults["momentum"]:
+        if self._arena is not None and self.defaults["momentum"] and not self._state_clean:
             ops.fill_(self._arena.state1[: max(self._arena.layout.n_param, 4)], 0.0)
         self._bufs = None
         self.state = {}
+
+    def _flat_step(self, w, gr) -> None:
+        g = self.param_groups[0]
+        lr, mom, wd, nes = g["lr"], g["momentum"], g["weight_decay"], g["nesterov"]
+        mb = self._arena.state1[: w.numel()] if mom else None
+        wb = getattr(self._arena, "wbf16", None)
+        early = getattr(self._arena, "early_ready", None)
+        if early is not None and w.is_cuda and os.environ.get("KUBEML_SGD_OVERLAP", "1") != "0":
+            # The network told us that the gradients of the parameter tail [lo, n) were final early in its
+            # backward pass (ResNet: layer4 + fc, 62 % of the bytes).  Their update runs on its own stream
+            # behind exactly those two events: under graph capture it becomes a node that depends only on
+            # them, so it overlaps the rest of the backward pass instead of trailing it.
+            lo, ev_main, ev_side = early
+            self._arena.early_ready = None
+            cur = torch.cuda.current_stream(w.device)
+            st = getattr(self._arena, "_opt_stream", None)
+            if st is None:
+                st = self._arena._opt_stream = torch.cuda.Stream(device=w.device)
+            st.wait_event(ev_main)
+            st.wait_event(ev_side)
+            with torch.cuda.stream(st):
+                ops.sgd_step_(w[lo:], gr[lo:], mb[lo:] if mb is not None else None, lr, wd, mom, nes,
+                              w_bf16=wb[lo:] if wb is not None else None)
+            ops.sgd_step_(w[:lo], gr[:lo], mb[:lo] if mb is not None else None, lr, wd, mom, nes,
+                          w_bf16=wb[:lo] if wb is not None else None)
+            cur.wait_stream(st)
+            return
+        ops.sgd_step_(w, gr, mb, lr, wd, mom, nes, w_bf16=wb)
 
     @torch.no_grad()
     def step(self) -> None:
         g = self.param_groups[0]
         lr, mom, wd, nes = g["lr"], g["momentum"], g["weight_decay"], g["nesterov"]
         self._step_calls += 1
+        self._state_clean = False
         flat = self._flat_views()
         if flat is not None:
             w, gr = flat
-            if self._deferred:             # a second step() before the merge: the pending one goes first
-                self.flush_deferred()
-            if self._armed and not nes and w.is_cuda:
-                self._armed = False
-                self._deferred = True
+            if w.is_cuda and not nes and self._take_deferral():
                 return
-            mb = self._arena.state1[: w.numel()] if mom else None
-            wb = getattr(self._arena, "wbf16", None)
-            early = getattr(self._arena, "early_ready", None)
-            if early is not None and w.is_cuda and os.environ.get("KUBEML_SGD_OVERLAP", "1") != "0":
-                # The network told us that the gradients of the parameter tail [lo, n) were final early in its
-                # backward pass (ResNet: layer4 + fc, 62 % of the bytes).  Their update runs on its own stream
-                # behind exactly those two events: under graph capture it becomes a node that depends only on
-                # them, so it overlaps the rest of the backward pass instead of trailing it.
-                lo, ev_main, ev_side = early
-                self._arena.early_ready = None
-                cur = torch.cuda.current_stream(w.device)
-                st = getattr(self._arena, "_opt_stream", None)
-                if st is None:
-                    st = self._arena._opt_stream = torch.cuda.Stream(device=w.device)
-                st.wait_event(ev_main)
-                st.wait_event(ev_side)
-                with torch.cuda.stream(st):
-                    ops.sgd_step_(w[lo:], gr[lo:], mb[lo:] if mb is not None else None, lr, wd, mom, nes,
-                                  w_bf16=wb[lo:] if wb is not None else None)
-                ops.sgd_step_(w[:lo], gr[:lo], mb[:lo] if mb is not None else None, lr, wd, mom, nes,
-                              w_bf16=wb[:lo] if wb is not None else None)
-                cur.wait_stream(st)
-                return
-            ops.sgd_step_(w, gr, mb, lr, wd, mom, nes, w_bf16=wb)
+            self._flat_step(w, gr)
             return
         if self._bufs is None and any(grp["momentum"] for grp in self.param_groups):
             self._bufs = [torch.zeros_like(p) for p in self.params]
@@ -247,7 +259,7 @@ class Adam(_FlatOptimizer):
 
     def reset_state(self) -> None:
         self._t = 0
-        if self._arena is not None:
+        if self._arena is not None and not self._state_clean:
             n = max(self._arena.layout.n_param, 4)
             ops.fill_(self._arena.state1[:n], 0.0)
             ops.fill_(self._arena.state2[:n], 0.0)
@@ -255,17 +267,25 @@ class Adam(_FlatOptimizer):
         self._m = self._v = None
         self.state = {}
 
+    def _flat_step(self, w, gr) -> None:
+        g = self.param_groups[0]
+        n = w.numel()
+        ops.adam_step_(w, gr, self._arena.state1[:n], self._arena.state2[:n], self._t, g["lr"],
+                       g["betas"], g["eps"], g["weight_decay"], w_bf16=getattr(self._arena, "wbf16", None),
+                       step_dev=self._arena.opt_step if w.is_cuda else None)
+
     @torch.no_grad()
     def step(self) -> None:
         g = self.param_groups[0]
         self._t += 1
+        self._step_calls += 1
+        self._state_clean = False
         flat = self._flat_views()
         if flat is not None:
             w, gr = flat
-            n = w.numel()
-            ops.adam_step_(w, gr, self._arena.state1[:n], self._arena.state2[:n], self._t, g["lr"],
-                           g["betas"], g["eps"], g["weight_decay"], w_bf16=getattr(self._arena, "wbf16", None),
-                           step_dev=self._arena.opt_step if w.is_cuda else None)
+            if w.is_cuda and self._take_deferral():
+                return
+            self._flat_step(w, gr)
             return
         if self._m is None:
             self._m = [torch.zeros_like(p) for p in self.params]

@@ -304,16 +304,26 @@ class RankSync:
         tmo = os.environ.get("KUBEML_MERGE_TIMEOUT_MS")
         tmo_s = float(tmo) / 1e3 if tmo else float(os.environ.get("KUBEML_MERGE_TIMEOUT_S", "20"))
         p.timeout_cycles = int(tmo_s * 1.9e9)
+        is_adam = opt is not None and "betas" in getattr(opt, "defaults", {})
         if opt is not None and getattr(opt, "_deferred", False) and allow_fuse:
             g = opt.param_groups[0]
-            p.fuse_sgd = 1
+            p.fuse_sgd = 2 if is_adam else 1
             p.grad = self.arena.ptr(L.off_grad)
-            p.lr, p.weight_decay, p.momentum = g["lr"], g["weight_decay"], g["momentum"]
+            p.lr, p.weight_decay = g["lr"], g["weight_decay"]
+            if is_adam:
+                p.beta1, p.beta2, p.eps = g["betas"][0], g["betas"][1], g["eps"]
+            else:
+                p.momentum = g["momentum"]
             opt._deferred = False
             self._fused_steps += 1
             self.epoch_fused_steps = getattr(self, "epoch_fused_steps", 0) + 1
         uses_momentum = opt is not None and bool(getattr(opt, "defaults", {}).get("momentum", 0))
-        p.momentum_buf = self.arena.ptr(L.off_state1) if uses_momentum else None
+        p.momentum_buf = self.arena.ptr(L.off_state1) if (uses_momentum or is_adam) else None
+        if is_adam:                          # both moments and the step count are reset by the merge
+            p.state2 = self.arena.ptr(L.off_state2)
+            p.step_dev = self.arena.opt_step.data_ptr()
+        if opt is not None and hasattr(opt, "_state_clean"):
+            opt._state_clean = True           # reset_state() at the start of the next round has nothing left to do
         p.w_bf16 = self.arena.ptr(L.off_bf16) if self.arena.wbf16 is not None else None
         stream = torch.cuda.current_stream(self.arena.device)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

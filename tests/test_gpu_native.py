@@ -116,6 +116,11 @@ def _merge_single_gpu(dev, replicas_f, replicas_i, parts, write, fuse=None):
         p.momentum_buf = fuse["mbuf"].data_ptr() if fuse.get("mbuf") is not None else None
         if fuse.get("wbf16") is not None:
             p.w_bf16 = fuse["wbf16"].data_ptr()
+        if fuse.get("adam") is not None:          # (exp_avg_sq, beta1, beta2, eps, step_dev)
+            p.fuse_sgd = 2
+            p.state2 = fuse["adam"][0].data_ptr()
+            p.beta1, p.beta2, p.eps = fuse["adam"][1], fuse["adam"][2], fuse["adam"][3]
+            p.step_dev = fuse["adam"][4].data_ptr()
     _native.check(lib.kml_kavg_merge(ctypes.byref(p), _native.stream_ptr()), "kml_kavg_merge")
     torch.cuda.synchronize()
     assert int(status.item()) == 0
@@ -180,6 +185,35 @@ def test_merge_single_participant_is_the_fused_step_only(dev):
     before = w.clone()
     _merge_single_gpu(dev, [w], None, [0], [0])
     torch.testing.assert_close(w, before, rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("nrep", [1, 2])
+def test_merge_fused_last_adam_step_and_reset(dev, nrep):
+    """The Adam form of the fused last step (function_vgg11.py's optimizer): replica 0 takes its third Adam step
+    inside the merge kernel, then the replicas are averaged and both moments and the step count are reset."""
+    torch.manual_seed(8)
+    n = 4 * 2048
+    p0 = torch.randn(n, device=dev, requires_grad=True)
+    opt = torch.optim.Adam([p0], lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=1e-3)
+    grads = [torch.randn(n, device=dev) for _ in range(3)]
+    for g in grads[:2]:                      # two ordinary steps build up the moments
+        p0.grad = g.clone(); opt.step()
+    st = opt.state[p0]
+    w = [p0.detach().clone()] + [torch.randn(n, device=dev) for _ in range(nrep - 1)]
+    m1, m2 = st["exp_avg"].clone(), st["exp_avg_sq"].clone()
+    step_dev = torch.tensor([2, 0], dtype=torch.int32, device=dev)
+    p0.grad = grads[2].clone(); opt.step()   # the oracle's third step
+    want = p0.detach().clone()
+    for other in w[1:]:
+        want = want + other
+    want = want / nrep
+    parts = list(range(nrep))
+    _merge_single_gpu(dev, w, None, parts, parts,
+                      fuse=dict(grad=grads[2], n=n, lr=1e-2, wd=1e-3, mom=0.0, mbuf=m1, adam=(m2, 0.9, 0.99, 1e-8, step_dev)))
+    for r in parts:
+        torch.testing.assert_close(w[r], want, rtol=2e-5, atol=2e-6)
+    assert float(m1.abs().max()) == 0.0 and float(m2.abs().max()) == 0.0
+    assert int(step_dev[0].item()) == 0
 
 
 # ------------------------------------------------------------------------------------- tcgen05 GEMM
