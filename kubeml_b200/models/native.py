@@ -538,7 +538,7 @@ def _packed_weight(conv: NConv2d, B: Buffers, tag: str, ldk: int) -> torch.Tenso
 
 def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, tag: str,
                   need_dx: bool = True, addend: Optional[torch.Tensor] = None,
-                  allow_slabs: bool = False, bn_next=None) -> Optional[Act]:
+                  allow_slabs: bool = False, bn_next=None, wgrad_budget: Optional[int] = None) -> Optional[Act]:
     """Weight gradient into the arena; data gradient (+ addend) returned (bf16, or fp32 slabs when
     `allow_slabs`: the consumer must then be a BatchNorm backward).
     `bn_next` = (bn module, tag, y, x_saved) of the BatchNorm whose backward consumes this gradient:
@@ -555,10 +555,11 @@ def conv_backward(conv: NConv2d, x: torch.Tensor, dy: torch.Tensor, B: Buffers, 
         bn_w = 128 if conv.cin > 64 else 64
         tiles = ((conv.cout + 127) // 128) * ((conv.cin + bn_w - 1) // bn_w) * k * k
         # gradients accumulate with red.add across splits; _begin_backward cleared them
-        # weight gradients run next to the data-gradient chain on the side stream and have slack: aiming them at
-        # half of the SMs leaves the chain more room (measured: 148 -> 74 CTAs, 1.219 -> 1.209 ms per ResNet-34
-        # step; 37 is slower again).  KUBEML_WGRAD_BUDGET overrides.
-        sp = auto_splits(tiles, chunks, budget=int(os.environ.get("KUBEML_WGRAD_BUDGET", "0")) or sm_count() // 2)
+        # weight gradients run next to the data-gradient chain on the side stream; where they have slack (the
+        # latency-bound ResNet steps) the model aims them at half of the SMs, which leaves the chain more room
+        # (measured: 148 -> 74 CTAs, 1.219 -> 1.209 ms per ResNet-34 step; 37 is slower again; VGG, whose
+        # weight gradients are large GEMMs, keeps the whole GPU).  KUBEML_WGRAD_BUDGET overrides.
+        sp = auto_splits(tiles, chunks, budget=int(os.environ.get("KUBEML_WGRAD_BUDGET", "0")) or wgrad_budget)
         if sp > 1:
             B.split_grads.append(conv.w_grad)
         with B.on_side():

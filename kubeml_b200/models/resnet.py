@@ -171,6 +171,8 @@ class NativeResNet(NativeNet):
             K.avgpool_bwd(dpooled, t)
             dh = Act(t)
         nblk = len(self._blocks)
+        from .native import sm_count
+        wb = sm_count() // 2                 # weight gradients have slack here: leave half of the SMs to the chain
         self._stamp("bwd_head")
         for bi, ((tag, blk), (h, t1, a, t2, td, out)) in enumerate(zip(reversed(self._blocks),
                                                                          reversed(S["blocks"]))):
@@ -183,7 +185,7 @@ class NativeResNet(NativeNet):
             dt2, g = bn_backward(blk.bn2, dh, out, t2, B, tag + ".bn2", want_dres=True)
             # the data-gradient GEMMs mask and pre-reduce for the BatchNorm backward that follows them
             da = conv_backward(blk.conv2, a, dt2, B, tag + ".c2", allow_slabs=True,
-                               bn_next=(blk.bn1, tag + ".bn1", a, t1))
+                               bn_next=(blk.bn1, tag + ".bn1", a, t1), wgrad_budget=wb)
             dt1, _ = bn_backward(blk.bn1, da, a, t1, B, tag + ".bn1")
             if blk.downsample is None:
                 nxt = None
@@ -191,11 +193,11 @@ class NativeResNet(NativeNet):
                     ptag, pblk = self._blocks[nblk - 2 - bi]
                     nxt = (pblk.bn2, ptag + ".bn2", h, S["blocks"][nblk - 2 - bi][3], True)
                 dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=g, allow_slabs=not first_block,
-                                   bn_next=nxt)
+                                   bn_next=nxt, wgrad_budget=wb)
             else:
                 dtd, _ = bn_backward(blk.downsample[1], Act(g), None, td, B, tag + ".bnd")
-                did = conv_backward(blk.downsample[0], h, dtd, B, tag + ".cd")
-                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=did.t)
+                did = conv_backward(blk.downsample[0], h, dtd, B, tag + ".cd", wgrad_budget=wb)
+                dh = conv_backward(blk.conv1, h, dt1, B, tag + ".c1", addend=did.t, wgrad_budget=wb)
         # stem
         self._stamp("bwd_layer1")
         da1 = B.get("pool.dx", tuple(S["a1"].shape))
