@@ -186,8 +186,15 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
 
   float v[kRows][kVec];
   float s[kVec], q[kVec];
+  // Shifted sums: (x - pivot) and (x - pivot)^2 with pivot = running mean, so that E[x^2] - E[x]^2 does not
+  // cancel catastrophically when |mean| >> std and M is large (the sums are combined with fp32 atomics in
+  // arbitrary order).  Read here, before the grid barrier; the running statistics are updated after it.
+  float pv[kVec];
 #pragma unroll
-  for (int i = 0; i < kVec; ++i) s[i] = q[i] = 0.f;
+  for (int i = 0; i < kVec; ++i) {
+    s[i] = q[i] = 0.f;
+    pv[i] = (a.running_mean != nullptr && active) ? a.running_mean[c0 + i] : 0.f;
+  }
   if (active) {
 #pragma unroll
     for (int r = 0; r < kRows; ++r) {
@@ -204,7 +211,7 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
           cvt8(u, v[r]);                           // statistics of exactly what backward will read
         }
 #pragma unroll
-        for (int i = 0; i < kVec; ++i) { s[i] += v[r][i]; q[i] = fmaf(v[r][i], v[r][i], q[i]); }
+        for (int i = 0; i < kVec; ++i) { const float d = v[r][i] - pv[i]; s[i] += d; q[i] = fmaf(d, d, q[i]); }
       }
     }
     for (int row = row0 + kRows * row_stride; row < a.M; row += row_stride) {   // rare: very large M
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
       load_row(a.x, a.xs, a.nslabs, ss, static_cast<size_t>(row) * a.C + c0, f);
       if (a.x_out) { const uint4 u = pack8(f); *reinterpret_cast<uint4*>(a.x_out + static_cast<size_t>(row) * a.C + c0) = u; cvt8(u, f); }
 #pragma unroll
-      for (int i = 0; i < kVec; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+      for (int i = 0; i < kVec; ++i) { const float d = f[i] - pv[i]; s[i] += d; q[i] = fmaf(d, d, q[i]); }
     }
   }
   combine_stats(a.scratch, bn_state, a.C, c0, active, s, q, sm, a.wide_smem != 0);
@@ -222,8 +229,9 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
 #pragma unroll
   for (int i = 0; i < kVec; ++i) {
     const int c = c0 + i;
-    const float mean = sm[c] * inv_m;
-    const float var = fmaxf(sm[a.C + c] * inv_m - mean * mean, 0.f);
+    const float dm = sm[c] * inv_m;                      // mean - pivot
+    const float mean = pv[i] + dm;
+    const float var = fmaxf(sm[a.C + c] * inv_m - dm * dm, 0.f);
     const float invstd = rsqrtf(var + a.eps);
     sc[i] = a.gamma[c] * invstd;
     sh[i] = a.beta[c] - mean * sc[i];
@@ -232,7 +240,7 @@ __global__ void __launch_bounds__(kThreads) bn_fwd_train_kernel(const BnFwdArgs 
       a.save_invstd[c] = invstd;
       if (a.running_mean) {
         const float unbiased = a.M > 1 ? var * static_cast<float>(a.M) / static_cast<float>(a.M - 1) : var;
-        a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
+        a.running_mean[c] = (1.f - a.momentum) * pv[i] + a.momentum * mean;
         a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * unbiased;
       }
     }

@@ -186,8 +186,11 @@ def test_native_resnet18_matches_torchvision(dev):
         r = p.grad.flatten()
         table.append((torch.nn.functional.cosine_similarity(g, r, dim=0).item(), n))
     print("\n".join(f"{c:.4f} {n}" for c, n in table))
-    worst = min(table)
-    assert worst[0] > 0.85, f"{worst[1]}: cosine {worst[0]:.4f}"
+    # bf16 operands against fp32: every layer's gradient must point the same way.  0.98 for everything but the
+    # input stem (3-channel 7x7 convolution fed by 18 layers of rounding) and the first BatchNorm behind it.
+    for c, n in table:
+        floor = 0.93 if n in ("conv1.weight", "bn1.weight", "bn1.bias") else 0.98
+        assert c > floor, f"{n}: cosine {c:.4f} (floor {floor})"
     # eval mode uses running statistics and no autograd
     net.eval(); ref.eval()
     with torch.no_grad():
@@ -781,3 +784,134 @@ def test_image_prep_with_in_kernel_augmentation(dev):
         codes.append(row)
     assert len(set(codes[0])) > N // 2              # not one code for the whole batch
     assert codes[0] != codes[1]                     # and not the same codes on the next call
+
+
+# ------------------------------------------------------------------------------------------------------
+# standalone layer kernels against plain PyTorch (fp32 functional ops / autograd), not the repository's own CPU
+# restatement; errors are relative to each column's own scale so a small-magnitude channel cannot hide
+# ------------------------------------------------------------------------------------------------------
+def _col_rel(a, b):
+    a, b = a.float().cpu().reshape(-1, a.shape[-1]), b.float().cpu().reshape(-1, b.shape[-1])
+    return ((a - b).abs().amax(0) / (b.abs().amax(0) + 1e-3)).max().item()
+
+
+@pytest.mark.parametrize("M,C,relu,res", [(8192, 64, True, False), (2048, 128, True, True), (100, 72, False, True),
+                                          (32768, 64, True, False)])
+def test_batchnorm_kernels_vs_torch(dev, M, C, relu, res):
+    import torch.nn.functional as F
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(12)
+    x = (torch.randn(M, C, device=dev) * 2 + 0.5).bfloat16()
+    r = torch.randn(M, C, device=dev).bfloat16() if res else None
+    gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
+    dy = torch.randn(M, C, device=dev).bfloat16()
+    y = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
+    rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    nbt = torch.zeros((), dtype=torch.long, device=dev)
+    mean, istd = torch.empty(C, device=dev), torch.empty(C, device=dev)
+    K.bn_fwd_train(x, r, y, gamma, beta, rm, rv, nbt, mean, istd, relu)
+    dx = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
+    dres = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
+    dg, db = torch.empty(C, device=dev), torch.empty(C, device=dev)
+    K.bn_bwd(dy, y if relu else None, x, gamma, mean, istd, dx, dres, dg, db)
+    torch.cuda.synchronize()
+    xt = x.float().clone().requires_grad_(True)
+    gt, bt = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rmt, rvt = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    out = F.batch_norm(xt, rmt, rvt, gt, bt, training=True, momentum=0.1, eps=1e-5)
+    if res:
+        out = out + r.float()
+    if relu:
+        out = torch.relu(out)
+    (out * dy.float()).sum().backward()
+    assert _col_rel(y, out.detach()) < 2e-2
+    assert _col_rel(rm.view(1, -1), rmt.view(1, -1)) < 1e-2 and _col_rel(rv.view(1, -1), rvt.view(1, -1)) < 1e-2
+    assert _col_rel(dx, xt.grad) < 4e-2
+    assert _col_rel(dg.view(1, -1), gt.grad.view(1, -1)) < 2e-2 and _col_rel(db.view(1, -1), bt.grad.view(1, -1)) < 2e-2
+    mask = (out.detach() > 0) if relu else torch.ones_like(out, dtype=torch.bool)
+    assert _col_rel(dres, dy.float() * mask) < 1e-2
+
+
+@pytest.mark.parametrize("N,H,C,k,s,p", [(4, 16, 64, 3, 2, 1), (2, 8, 128, 2, 2, 0)])
+def test_pooling_kernels_vs_torch(dev, N, H, C, k, s, p):
+    import torch.nn.functional as F
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(13)
+    x = torch.randn(N, H, H, C, device=dev).bfloat16()
+    Ho = (H + 2 * p - k) // s + 1
+    y = torch.empty(N, Ho, Ho, C, dtype=torch.bfloat16, device=dev)
+    idx = torch.empty(N, Ho, Ho, C, dtype=torch.uint8, device=dev)
+    K.maxpool_fwd(x, y, idx, k, s, p)
+    dy = torch.randn(N, Ho, Ho, C, device=dev).bfloat16()
+    dx = torch.empty_like(x)
+    K.maxpool_bwd(dy, idx, dx, k, s, p)
+    xt = x.float().permute(0, 3, 1, 2).clone().requires_grad_(True)
+    yt = F.max_pool2d(xt, k, s, p)
+    (yt * dy.float().permute(0, 3, 1, 2)).sum().backward()
+    torch.cuda.synchronize()
+    assert torch.equal(y.float(), yt.detach().permute(0, 2, 3, 1))
+    assert _col_rel(dx, xt.grad.permute(0, 2, 3, 1)) < 1e-2
+    # global average pool
+    pooled = torch.empty(N, C, dtype=torch.bfloat16, device=dev)
+    K.avgpool_fwd(x, pooled)
+    torch.cuda.synchronize()
+    assert _col_rel(pooled, x.float().mean((1, 2))) < 1e-2
+
+
+def test_native_resnet34_trains_like_torchvision_fp32_for_20_steps(dev):
+    """BASELINE's "final-loss parity", small: the bf16 native ResNet-34 and the fp32 torchvision ResNet-34 start from
+    the same weights and see the same 20 batches (SGD lr 0.05, wd 1e-4, the reference's recipe shape,
+    ml/experiments/kubeml/function_resnet34.py:62-80); their loss curves must stay together."""
+    import torchvision
+    from kubeml_b200 import ops
+    from kubeml_b200.models import resnet34
+    from kubeml_b200.optim import SGD
+    torch.manual_seed(21)
+    net = resnet34(num_classes=10).to(dev)
+    net._ensure_arena()
+    ref = torchvision.models.resnet34(num_classes=10).to(dev)
+    ref.load_state_dict(net.state_dict())
+    opt = SGD(net.parameters(), lr=0.05, weight_decay=1e-4)
+    opt.attach_arena(net._arena)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.05, weight_decay=1e-4)
+    torch.backends.cudnn.allow_tf32 = False
+    net.train(); ref.train()
+    teacher = torch.randn(3 * 8 * 8, 10, device=dev)
+    ln, lr_ = [], []
+    for step in range(20):
+        x = torch.randn(128, 3, 32, 32, device=dev)
+        y = (torch.nn.functional.avg_pool2d(x, 4).flatten(1) @ teacher).argmax(1)
+        opt.zero_grad()
+        loss = ops.cross_entropy(net(x.bfloat16().float()), y)
+        loss.backward(); opt.step()
+        ropt.zero_grad()
+        loss_r = torch.nn.functional.cross_entropy(ref(x), y)
+        loss_r.backward(); ropt.step()
+        ln.append(loss.item()); lr_.append(loss_r.item())
+    torch.cuda.synchronize()
+    print("native", [round(v, 3) for v in ln]); print("fp32  ", [round(v, 3) for v in lr_])
+    assert abs(ln[0] - lr_[0]) < 0.05
+    assert max(abs(a - b) for a, b in zip(ln, lr_)) < 0.35                   # the curves stay together...
+    assert abs(sum(ln[-5:]) - sum(lr_[-5:])) / 5 < 0.15                      # ...and end at the same level
+    assert sum(ln[-5:]) < sum(ln[:5])                                        # while actually learning
+
+
+def test_batchnorm_variance_with_large_mean_and_many_rows(dev):
+    """|mean| >> std at M = 131072: E[x^2] - E[x]^2 in fp32 loses the variance; the kernels accumulate shifted sums
+    around the running mean instead (csrc/norm.cu, csrc/gemm_tcgen05.cu).  With the running mean near the batch mean
+    (any step after the first few) the batch variance must come out to 1 %."""
+    from kubeml_b200.ops import nn as K
+    torch.manual_seed(14)
+    M, C = 131072, 64
+    x = (8.0 + 0.05 * torch.randn(M, C, device=dev)).bfloat16()
+    xd = x.double()
+    var_ref = xd.var(0, unbiased=False)
+    gamma, beta = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    y = torch.empty(M, C, dtype=torch.bfloat16, device=dev)
+    rm, rv = torch.full((C,), 7.9, device=dev), torch.ones(C, device=dev)
+    mean, istd = torch.empty(C, device=dev), torch.empty(C, device=dev)
+    K.bn_fwd_train(x, None, y, gamma, beta, rm, rv, None, mean, istd, False)
+    torch.cuda.synchronize()
+    var_got = 1.0 / istd.double() ** 2 - 1e-5
+    assert ((var_got - var_ref).abs() / var_ref).max().item() < 1e-2
+    assert (mean.double() - xd.mean(0)).abs().max().item() < 1e-3
