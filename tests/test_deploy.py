@@ -1,0 +1,103 @@
+"""deploy/ is what replaces the reference's Helm chart (ml/charts/kubeml: Deployments + Services, a Prometheus
+ServiceMonitor scraped every 10 s, the Grafana dashboard).  These tests start what the unit files start, with the
+environment file's values, and check that Prometheus' scrape target and every dashboard query are really served."""
+import json
+import os
+import re
+import shlex
+import socket
+import subprocess
+import sys
+import time
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DEPLOY = os.path.join(ROOT, "deploy")
+
+
+def _env_file():
+    env = {}
+    for line in open(os.path.join(DEPLOY, "kubeml.env")):
+        line = line.strip()
+        if line and not line.startswith("#"):
+            k, _, v = line.partition("=")
+            env[k] = v
+    return env
+
+
+def _exec_start(unit):
+    text = open(os.path.join(DEPLOY, "systemd", unit)).read()
+    assert "[Unit]" in text and "[Service]" in text and "[Install]" in text
+    assert "EnvironmentFile=/etc/kubeml_b200/kubeml.env" in text
+    return re.search(r"^ExecStart=(.*)$", text, re.M).group(1)
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _wait_http(url, timeout=90):
+    from kubeml_b200.httpd import http_call
+    deadline = time.time() + timeout
+    while time.time() < deadline:
+        try:
+            return http_call("GET", url)
+        except Exception:  # noqa: BLE001
+            time.sleep(0.3)
+    raise AssertionError(f"{url} never answered")
+
+
+def _start(cmd, env, tmp_path):
+    e = dict(os.environ)
+    e.update(env)
+    e.update(KUBEML_HOME=str(tmp_path), CUDA_VISIBLE_DEVICES="", PYTHONPATH=ROOT)
+    argv = shlex.split(cmd)
+    assert argv[:2] == ["/usr/bin/env", "python"]
+    return subprocess.Popen([sys.executable] + argv[2:], env=e, cwd=str(tmp_path), stdout=subprocess.PIPE,
+                            stderr=subprocess.STDOUT, text=True)
+
+
+@pytest.mark.parametrize("unit", ["kubeml.service", "kubeml-workers.service"])
+def test_unit_file_command_brings_up_the_control_plane(unit, tmp_path):
+    from kubeml_b200.httpd import http_call
+    env = _env_file()
+    port = _free_port()
+    env["KUBEML_CONTROLLER_PORT"] = str(port)
+    cmd = _exec_start(unit).replace("${KUBEML_CONTROLLER_PORT}", str(port))
+    if "torch.distributed.run" in cmd:          # one worker on this GPU-less box instead of eight
+        cmd = cmd.replace("--nproc-per-node 8", "--nproc-per-node 1").replace("--master-port 29400",
+                                                                             f"--master-port {_free_port()}")
+    proc = _start(cmd, env, tmp_path)
+    try:
+        url = f"http://127.0.0.1:{port}"
+        assert _wait_http(url + "/health") is None
+        # what deploy/prometheus.yml scrapes: the target and the path must be served by this process
+        prom = open(os.path.join(DEPLOY, "prometheus.yml")).read()
+        assert f'targets: ["127.0.0.1:{_env_file()["KUBEML_CONTROLLER_PORT"]}"]' in prom
+        path = re.search(r"metrics_path:\s*(\S+)", prom).group(1)
+        metrics = http_call("GET", url + path).decode()
+        assert "kubeml_job_running_total" in metrics
+        assert http_call("GET", url + "/tasks") == [] and http_call("GET", url + "/dataset") == []
+    finally:
+        proc.terminate()
+        try:
+            proc.wait(timeout=20)
+        except subprocess.TimeoutExpired:
+            proc.kill()
+
+
+def test_every_dashboard_query_names_a_metric_the_parameter_server_exports():
+    from kubeml_b200.ps.metrics import MetricsRegistry
+    from kubeml_b200.api.types import MetricUpdate
+    dash = json.load(open(os.path.join(DEPLOY, "grafana", "KubeML.json")))
+    exprs = re.findall(r'"expr":\s*"([a-zA-Z_:][a-zA-Z0-9_:]*)', json.dumps(dash))
+    assert len(exprs) >= 6
+    reg = MetricsRegistry()
+    reg.task_started("train")
+    reg.update("abcd1234", MetricUpdate(validation_loss=1.0, accuracy=50.0, train_loss=2.0, parallelism=2,
+                                        epoch_duration=3.0))
+    text = reg.render()
+    for name in set(exprs):
+        assert re.search(rf"^{name}\{{", text, re.M), f"dashboard queries {name}, /metrics does not export it"
