@@ -10,7 +10,7 @@ Data: CIFAR-shaped images with teacher labels (bench/loss_parity.make_data) so t
 is batch {128} x K {8, -1 (one merge per epoch)} x N {1, 2, 4, ... <= GPUs}.  Prints one JSON line with, per grid
 point, total time, final accuracy and time-to-accuracy for two definitions the reference's notebooks use
 (`tta`: first epoch at or above the goal; `tta_crossbow`: median of the last 5 epochs at or above it)."""
-import json, os, sys, tempfile
+import importlib.util, json, os, sys, tempfile
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
@@ -23,7 +23,11 @@ def main():
     os.environ["KUBEML_HOME"] = home
     os.environ["KUBEML_RESNET_DATASET"] = "teacher"
     os.environ["KUBEML_RESNET_NOAUG"] = "1"
-    from bench.loss_parity import make_data
+    # bench.py at the repository root shadows the bench/ directory as a module name: load the file itself
+    spec = importlib.util.spec_from_file_location(
+        "kubeml_bench_loss_parity", os.path.join(os.path.dirname(os.path.abspath(__file__)), "loss_parity.py"))
+    lp = importlib.util.module_from_spec(spec); spec.loader.exec_module(lp)
+    make_data = lp.make_data
     from kubeml_b200.controller.client import make_kubeml_client
     from kubeml_b200.controller.cluster import Cluster
     from kubeml_b200.experiments import analysis, harness
@@ -32,7 +36,8 @@ def main():
     rt = SpmdRuntime(shard_store=default_store())
     if rank != 0:
         rt.serve(); rt.close(); return
-    cluster = Cluster(home=home, max_parallelism=world, invoker_factory=lambda c, task: _invoker(rt))
+    cluster = Cluster(home=home, max_parallelism=world, invoker_factory=lambda c, task: _invoker(rt),
+                      tensor_store=rt.tensor_store)
     rt.services.shard_store = cluster.shard_store
     if not cluster.shard_store.exists("teacher"):
         xtr, ytr, xte, yte = make_data(64 * 128, 2048)

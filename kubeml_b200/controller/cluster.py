@@ -31,11 +31,12 @@ from .controller import Controller
 class Cluster:
     def __init__(self, home: Optional[str] = None, max_parallelism: Optional[int] = None,
                  invoker_factory: Optional[Callable[["Cluster", TrainTask], Invoker]] = None,
-                 options: Optional[dict] = None, start: bool = True):
+                 options: Optional[dict] = None, start: bool = True, tensor_store: Optional[TensorStore] = None):
         self.home = home or const.home()
         os.makedirs(self.home, exist_ok=True)
         self.shard_store = ShardStore(os.path.join(self.home, "datasets"))
-        self.tensor_store = TensorStore()
+        # the store the workers publish into: with process-per-GPU workers it is the runtime's (runtime/spmd.py)
+        self.tensor_store = tensor_store if tensor_store is not None else TensorStore()
         self.histories = HistoryStore(os.path.join(self.home, "history"))
         self.functions = FunctionRegistry(os.path.join(self.home, "functions"))
         self.checkpoint_dir = os.path.join(self.home, "checkpoints")
@@ -92,7 +93,10 @@ class Cluster:
 
     def _make_job(self, task: TrainTask, ps: ParameterServer) -> TrainJob:
         invoker = self.invoker_factory(self, task)
-        device_mode = getattr(getattr(invoker, "services", None), "device_sync", None) is not None
+        sv = getattr(invoker, "services", None)
+        # the workers merge among themselves (device kernel, or a collective on a GPU-less box): no host-side merge
+        device_mode = (getattr(sv, "device_sync", None) is not None
+                       or "sync_factory" in (getattr(sv, "options", None) or {}))
         job = TrainJob(task, invoker, self.tensor_store, history_store=self.histories,
                        scheduler=self.scheduler, ps=ps, device_mode=device_mode,
                        checkpoint_dir=self.checkpoint_dir)

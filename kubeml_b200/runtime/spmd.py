@@ -186,6 +186,10 @@ class SpmdRuntime:
             self.group = SpmdDeviceSyncGroup(self.rank, self.world)
         self.services = Services(shard_store=self.shard_store, tensor_store=self.tensor_store,
                                  barrier=None, device_sync=self.group, options=dict(options or {}))
+        if self.group is None:
+            # no GPUs: the merge is an all-reduce over the control group (static parallelism == world size only)
+            from ..train.sync import CollectiveSync
+            self.services.options.setdefault("sync_factory", lambda: CollectiveSync(self.tensor_store))
         self.worker = Worker(self.services, self.registry,
                              gpu_id=self.local_rank if cuda else None, name=f"rank{self.rank}")
         self._lock = threading.Lock()       # rank 0's own share of a fan-out

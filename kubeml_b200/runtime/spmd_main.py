@@ -29,7 +29,8 @@ def main() -> int:
         rt.serve()
         rt.close()
         return 0
-    cluster = Cluster(max_parallelism=rt.world, invoker_factory=lambda c, task: rt.invoker())
+    cluster = Cluster(max_parallelism=rt.world, invoker_factory=lambda c, task: rt.invoker(),
+                      tensor_store=rt.tensor_store)
     rt.services.shard_store = cluster.shard_store
     cluster.serve(host=args.host, controller_port=args.port)
     print(f"kubeml control plane on http://{args.host}:{cluster.controller_port} with {rt.world} GPU workers", flush=True)

@@ -80,6 +80,33 @@ def test_unit_file_command_brings_up_the_control_plane(unit, tmp_path):
         metrics = http_call("GET", url + path).decode()
         assert "kubeml_job_running_total" in metrics
         assert http_call("GET", url + "/tasks") == [] and http_call("GET", url + "/dataset") == []
+        if "torch.distributed.run" in cmd:
+            # the process-per-GPU deployment must also *train*: dataset upload, a LeNet job through the scheduler
+            # and the worker rank, history back over HTTP (on this GPU-less box the merge is the collective path)
+            import numpy as np
+            from kubeml_b200.api.types import TrainOptions, TrainRequest
+            from kubeml_b200.controller.client import make_kubeml_client
+            rng = np.random.default_rng(0)
+            files = {}
+            for name, arr in (("xtr", rng.integers(0, 255, (256, 28, 28), dtype=np.uint8)),
+                              ("ytr", rng.integers(0, 10, (256,))),
+                              ("xte", rng.integers(0, 255, (64, 28, 28), dtype=np.uint8)),
+                              ("yte", rng.integers(0, 10, (64,)))):
+                files[name] = str(tmp_path / f"{name}.npy")
+                np.save(files[name], arr)
+            v1 = make_kubeml_client(url=url).v1()
+            v1.datasets().create("mnist", files["xtr"], files["ytr"], files["xte"], files["yte"])
+            job_id = v1.networks().train(TrainRequest(
+                model_type="lenet", batch_size=64, epochs=2, dataset="mnist", lr=0.01, function_name="lenet",
+                options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=2)))
+            deadline, hist = time.time() + 240, None
+            while time.time() < deadline and hist is None:
+                try:
+                    hist = v1.histories().get(job_id)
+                except Exception:  # noqa: BLE001
+                    time.sleep(0.5)
+            assert hist is not None, "the job never produced a history"
+            assert len(hist.data.train_loss) == 2 and len(hist.data.accuracy) == 2
     finally:
         proc.terminate()
         try:

@@ -178,19 +178,30 @@ def test_native_resnet18_matches_torchvision(dev):
     loss_r.backward()
     torch.cuda.synchronize()
     assert abs(loss.item() - loss_r.item()) < 0.05
-    # bf16 activations and gradients through 18 layers: direction must be preserved everywhere
-    # (exact agreement of the *program* is checked in fp32 on the CPU, tests/test_native_models.py)
+    # The oracle is fp32; this network keeps bf16 activations and gradients.  How far bf16 alone moves each layer's
+    # gradient is measured, not guessed: the same torchvision network under torch.autocast(bfloat16) against the same
+    # fp32 run.  (At 32x32 input layer4 is 1x1, so its BatchNorm sees 64 samples per channel and amplifies rounding;
+    # the early layers receive 18 layers of accumulated rounding.)  Each layer here must be within 0.03 of what
+    # stock bf16 achieves and never below 0.85; exact agreement of the *program* is checked in fp32 on the CPU
+    # (tests/test_native_models_cpu.py).
+    ref16 = torchvision.models.resnet18(num_classes=10).to(dev).to(memory_format=torch.channels_last)
+    ref16.load_state_dict(net.state_dict())
+    ref16.train()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        loss16 = torch.nn.functional.cross_entropy(ref16(x.contiguous(memory_format=torch.channels_last)).float(), y)
+    loss16.backward()
+    g16 = {n: p.grad.flatten().float() for n, p in ref16.named_parameters()}
     table = []
     for n, p in ref.named_parameters():
         g = net._arena.grad(n).flatten().float()
         r = p.grad.flatten()
-        table.append((torch.nn.functional.cosine_similarity(g, r, dim=0).item(), n))
-    print("\n".join(f"{c:.4f} {n}" for c, n in table))
-    # bf16 operands against fp32: every layer's gradient must point the same way.  0.98 for everything but the
-    # input stem (3-channel 7x7 convolution fed by 18 layers of rounding) and the first BatchNorm behind it.
-    for c, n in table:
-        floor = 0.93 if n in ("conv1.weight", "bn1.weight", "bn1.bias") else 0.98
-        assert c > floor, f"{n}: cosine {c:.4f} (floor {floor})"
+        cos = torch.nn.functional.cosine_similarity
+        table.append((cos(g, r, dim=0).item(), cos(g16[n], r, dim=0).item(), n))
+    print("native-vs-fp32  autocast-vs-fp32  parameter")
+    print("\n".join(f"{c:.4f} {c16:.4f} {n}" for c, c16, n in table))
+    for c, c16, n in table:
+        floor = max(0.85, min(0.98, c16 - 0.03))
+        assert c > floor, f"{n}: cosine {c:.4f}, stock bf16 autocast reaches {c16:.4f} (floor {floor:.3f})"
     # eval mode uses running statistics and no autograd
     net.eval(); ref.eval()
     with torch.no_grad():
