@@ -146,6 +146,7 @@ def run_own(args) -> int:
     # region then copies each step's batch host->device from pinned memory
     for name in (f"{ds_prefix}_w{args.warmup}", f"{ds_prefix}_t{args.steps}"):
         store.pinned(name, "train")
+        store.resident(name, "train", torch.device("cuda", torch.cuda.current_device()))   # for the device-timed runs
 
     if rank != 0:
         rt.serve()
@@ -154,7 +155,7 @@ def run_own(args) -> int:
 
     histories = HistoryStore(os.path.join(home, "history"))
 
-    def run_job(dataset: str, resident: bool):
+    def run_job(dataset: str, resident: bool, trace: bool = False):
         req = TrainRequest(model_type=args.model, batch_size=BATCH, epochs=1, dataset=dataset,
                            lr=1e-4 if vgg else 0.1, function_name=args.model,
                            options=TrainOptions(default_parallelism=N, static_parallelism=True,
@@ -164,7 +165,7 @@ def run_own(args) -> int:
         task = TrainTask(request=req, job=JobInfo(id="bench", state=JobState(parallelism=N)))
         inv = rt.invoker()
         inv.env = {ds_env: dataset, "KUBEML_RESNET_IMPL": args.model_impl}
-        inv.options = {"device_resident_data": resident}
+        inv.options = {"device_resident_data": resident, "trace": trace}
         job = TrainJob(task, inv, rt.tensor_store, history_store=histories, device_mode=True,
                        skip_final_validation=True)
         job.release_on_finish = False
@@ -187,6 +188,12 @@ def run_own(args) -> int:
     e2e_jobs = [run_job(f"{ds_prefix}_t{args.steps}", resident=False) for _ in range(reps)]
     dev_jobs = [run_job(f"{ds_prefix}_t{args.steps}", resident=True) for _ in range(reps)]
     clocks = sampler.stop()
+    timeline = None
+    if os.environ.get("KUBEML_BENCH_GAPS") == "1":
+        # one more epoch, outside every timed region, with device spans recorded around each step and merge:
+        # where the time between the captured steps goes (KUBEML_BENCH_GAPS=1 python bench.py ...)
+        timeline = {"device_resident": round_timeline(run_job(f"{ds_prefix}_t{args.steps}", resident=True, trace=True)),
+                    "e2e": round_timeline(run_job(f"{ds_prefix}_t{args.steps}", resident=False, trace=True))}
     rt.stop()
 
     def median_job(jobs):
@@ -230,9 +237,34 @@ def run_own(args) -> int:
         "samples_ms_per_step": samples,
         "clocks": clocks,
     }
+    if timeline is not None:
+        out["round_timeline_us"] = timeline
     print(json.dumps(out), flush=True)
     rt.close()
     return 0
+
+
+def round_timeline(job) -> dict:
+    """Mean device-time spans of worker 0's traced epoch, microseconds: a step (event before the batch is handed
+    to the step until after its last launch), the gap between consecutive steps of a round, the gap from a round's
+    last step to its merge, the merge, and the gap from the merge to the next round's first step."""
+    tr = job.worker_traces.get(0) or next(iter(job.worker_traces.values()), None)
+    if not tr:
+        return {}
+    steps = sorted((r, b, t, d) for r, b, t, d in tr["step"])
+    merges = {int(r): (t, d) for r, _, t, d in tr["merge"]}
+    mean = lambda v: round(1e3 * sum(v) / len(v), 1) if v else None
+    in_round, to_merge, to_next = [], [], []
+    for a, b in zip(steps, steps[1:]):
+        if a[0] == b[0]:
+            in_round.append(b[2] - (a[2] + a[3]))
+        elif a[0] in merges:
+            m = merges[a[0]]
+            to_merge.append(m[0] - (a[2] + a[3]))
+            to_next.append(b[2] - (m[0] + m[1]))
+    return {"step": mean([d for *_, d in steps]), "gap_between_steps": mean(in_round),
+            "gap_last_step_to_merge": mean(to_merge), "merge": mean([d for _, d in merges.values()]),
+            "gap_merge_to_next_round": mean(to_next), "rounds": len(merges)}
 
 
 def main() -> int:

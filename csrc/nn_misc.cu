@@ -578,9 +578,13 @@ image_prep_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict
 __global__ void __launch_bounds__(kThreads)
 image_prep_rand_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict__ y, unsigned long long* state,
                        unsigned seed, int N, int H, int W, int C, int pad, float m0, float m1, float m2, float s0, float s1,
-                       float s2) {
+                       float s2, const long long* __restrict__ lab_in, long long* __restrict__ lab_out) {
   kml::pdl_launch_dependents();
   kml::pdl_wait();
+  // the batch's labels ride along into their fixed buffer (the captured step reads both from fixed addresses):
+  // no separate device-to-device copy between two training steps
+  if (lab_out != nullptr && blockIdx.x == 0)
+    for (int i = threadIdx.x; i < N; i += blockDim.x) lab_out[i] = lab_in[i];
   const unsigned ctr = static_cast<unsigned>(*reinterpret_cast<volatile unsigned long long*>(state));
   const unsigned span = 2u * pad + 1u;
   const size_t total = static_cast<size_t>(N) * H * W * C;
@@ -900,6 +904,23 @@ int kml_stamp(unsigned long long* slots, int idx, void* stream) {
   return 0;
 }
 
+// A step's scalar result (its loss) goes to page-locked host memory with a plain store from a one-thread kernel
+// instead of a copy-engine transfer: a 4-byte cudaMemcpyAsync in the middle of a compute stream costs two engine
+// hand-overs (compute -> copy -> compute, several microseconds each) between consecutive training steps.
+__global__ void post_f32_kernel(const float* __restrict__ src, float* dst_host, int n) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dst_host[i] = src[i];
+  __threadfence_system();
+}
+int kml_post_f32(const float* src, float* dst_host, int n, void* stream) {
+  KML_CHECK(src != nullptr && dst_host != nullptr && n > 0, "kml_post_f32: bad arguments");
+  void* dev_view = nullptr;          // identical to dst_host under unified addressing; asked for, not assumed
+  KML_CUDA(cudaHostGetDevicePointer(&dev_view, dst_host, 0));
+  post_f32_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(src, static_cast<float*>(dev_view), n);
+  KML_CUDA(cudaGetLastError());
+  kml::count_launch();
+  return 0;
+}
+
 int kml_pack_rows_bf16(const float* src, void* dst, int rows, int cols, int ld, void* stream) {
   KML_CHECK(src && dst && ld >= cols, "kml_pack_rows_bf16: bad arguments");
   KML_CUDA(kml::launch_pdl(pack_rows_kernel, dim3(grid_for(static_cast<size_t>(rows) * ld)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream), src, static_cast<__nv_bfloat16*>(dst), rows, cols, ld));
@@ -919,12 +940,15 @@ int kml_image_prep(const void* x_u8, void* y_bf16, const int* aug, int N, int H,
 }
 
 int kml_image_prep_rand(const void* x_u8, void* y_bf16, unsigned long long* state, unsigned seed, int N, int H, int W,
-                        int C, int pad, const float* mean3, const float* std3, void* stream) {
+                        int C, int pad, const float* mean3, const float* std3, const long long* labels_in,
+                        long long* labels_out, void* stream) {
   KML_CHECK(x_u8 && y_bf16 && state && mean3 && std3 && C <= 3 && pad >= 0, "kml_image_prep_rand: bad arguments");
+  KML_CHECK((labels_in == nullptr) == (labels_out == nullptr), "kml_image_prep_rand: labels_in and labels_out go together");
   const size_t total = static_cast<size_t>(N) * H * W * C;
   KML_CUDA(kml::launch_pdl(image_prep_rand_kernel, dim3(grid_for(total)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream),
                            static_cast<const unsigned char*>(x_u8), static_cast<__nv_bfloat16*>(y_bf16), state, seed, N, H, W, C,
-                           pad, mean3[0], mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2]));
+                           pad, mean3[0], mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2], labels_in,
+                           labels_out));
   kml::count_launch();
   return 0;
 }

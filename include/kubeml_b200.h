@@ -292,10 +292,15 @@ int kml_colsum_bf16(const void* x, float* out, int rows, int cols, long long ld,
  * state = uint64[2] on the device, zero at start, advanced by the kernel (CUDA-graph replay safe).  Replaces the
  * per-sample PIL transforms of ml/experiments/kubeml/function_resnet34.py:17-30. */
 int kml_image_prep_rand(const void* x_u8, void* y_bf16, unsigned long long* state, unsigned seed, int N, int H, int W,
-                        int C, int pad, const float* mean3, const float* std3, void* stream);
+                        int C, int pad, const float* mean3, const float* std3, const long long* labels_in,
+                        long long* labels_out /* both or neither: labels_out[0..N) = labels_in[0..N) */, void* stream);
 /* slots[idx] = %globaltimer (ns), stream-ordered: per-phase timeline of a captured step (no reference
  * counterpart; the reference logs one wall-clock line around its merge, ml/pkg/train/job.go:397,412). */
 int kml_stamp(unsigned long long* slots, int idx, void* stream);
+/* dst_host[0..n) = src[0..n): device scalars stored straight into page-locked (device-visible) host memory by a
+ * kernel, stream-ordered; the host reads them after synchronising with the stream.  Stands where the reference
+ * calls loss.item() on every batch (python/kubeml/kubeml/network.py:288-300). */
+int kml_post_f32(const float* src, float* dst_host, int n, void* stream);
 int kml_pack_rows_bf16(const float* src, void* dst_bf16, int rows, int cols, int ld, void* stream);
 /* VGG-style layers (ReLU fused in the producing GEMM, Dropout p=0.5 in the classifier, the
  * AdaptiveAvgPool2d((7,7)) of torchvision vgg on a 1x1 map; ml/experiments/kubeml/function_vgg11.py). */

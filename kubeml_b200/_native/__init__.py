@@ -154,8 +154,9 @@ def _declare(lib) -> None:
         c_int, c_int, c_void_p)
     sig("kml_colsum_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_longlong, c_void_p)
     sig("kml_stamp", c_int, c_void_p, c_int, c_void_p)
+    sig("kml_post_f32", c_int, c_void_p, c_void_p, c_int, c_void_p)
     sig("kml_image_prep_rand", c_int, c_void_p, c_void_p, c_void_p, c_uint32, c_int, c_int, c_int, c_int, c_int,
-        POINTER(c_float), POINTER(c_float), c_void_p)
+        POINTER(c_float), POINTER(c_float), c_void_p, c_void_p, c_void_p)
     sig("kml_pack_rows_bf16", c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p)
     sig("kml_relu_bwd", c_int, c_void_p, c_void_p, c_void_p, c_float, c_size_t, c_void_p)
     sig("kml_relu_bwd_cols", c_int, c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_float, c_void_p,

@@ -88,6 +88,7 @@ class KubeDataset(data.Dataset, ABC):
                 self._pinned_data, self._pinned_labels = px[lo:hi], py[lo:hi].reshape(-1)
             else:
                 self._pinned_data = self._pinned_labels = None
+            self._split, self._rows = split, (minibatches.start, minibatches.stop)
         except OSError as e:
             raise StorageError(e)
         return x, np.asarray(y).reshape(-1)
@@ -137,10 +138,12 @@ class SlicedBatches(BatchSource):
         self._resident = False
         self.trace = [] if getattr(ds, "_trace", False) else None     # (batch, start event, end event) of each H2D copy
         if device.type == "cuda" and getattr(ds, "_device_resident", False):
-            # kernel-only measurements: the round's data is staged on the device up front
-            src_x = ds._pinned_data if ds._pinned_data is not None else torch.from_numpy(np.array(ds.data))
-            src_y = ds._pinned_labels if ds._pinned_labels is not None else torch.from_numpy(np.array(ds.labels))
-            self.x, self.y = src_x.to(device), src_y.to(device)
+            # kernel-only measurements: the whole split sits on the device (staged once per process), a round's
+            # batches are views of it
+            rx, ry = ds._store.resident(ds.dataset, ds._split, device)
+            sub = ds._store.meta(ds.dataset)["subset_size"]
+            lo, hi = ds._rows[0] * sub, min(ds._rows[1] * sub, len(rx))
+            self.x, self.y = rx[lo:hi], ry[lo:hi].reshape(-1)
             self._resident = True
         elif device.type == "cuda" and ds._pinned_data is not None:
             self.x, self.y = ds._pinned_data, ds._pinned_labels
@@ -148,6 +151,7 @@ class SlicedBatches(BatchSource):
             self.x = torch.from_numpy(np.array(ds.data, copy=True))
             self.y = torch.from_numpy(np.array(ds.labels, copy=True))
         self._copy_stream = None
+        self._first = None
         if device.type == "cuda":
             self._copy_stream = _copy_stream_for(device)
 
@@ -173,11 +177,16 @@ class SlicedBatches(BatchSource):
         self.h2d_bytes += xb.numel() * xb.element_size() + yb.numel() * yb.element_size()
         return xd, yd, ev
 
+    def prestage(self) -> None:
+        """Start the copy of the first batch now (the caller is about to wait for the previous round)."""
+        if self._first is None and len(self) > 0:
+            self._first = self._stage(0)
+
     def __iter__(self):
         nb = len(self)
         if nb == 0:
             return
-        nxt = self._stage(0)
+        nxt, self._first = (self._first if self._first is not None else self._stage(0)), None
         for i in range(nb):
             xd, yd, ev = nxt
             if i + 1 < nb:

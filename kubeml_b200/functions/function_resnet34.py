@@ -24,6 +24,7 @@ from kubeml_b200.optim import SGD
 
 _MEAN = (0.485, 0.456, 0.406)
 _STD = (0.229, 0.224, 0.225)
+_STABLE = {}      # (device, batch size) -> the batch buffer the native path refills in place (one training stream per GPU)
 
 
 class Cifar10Dataset(KubeDataset):
@@ -47,14 +48,27 @@ class Cifar10Dataset(KubeDataset):
         B = x.shape[0]
         augment = self.is_training() and os.environ.get("KUBEML_RESNET_NOAUG") != "1"   # parity runs: no randomness
         if self.native and x.is_cuda:
-            out = torch.empty((B, 32, 32, 3), dtype=torch.bfloat16, device=x.device)
+            # one output buffer per (device, batch size), refilled in place for every batch on the training
+            # stream: the captured step reads it where it is (network.py `_kubeml_stable`), no per-step copy
+            out = _STABLE.get((x.device, B))
+            if out is None:
+                out = _STABLE[(x.device, B)] = torch.empty((B, 32, 32, 3), dtype=torch.bfloat16, device=x.device)
+                out._kubeml_stable = os.environ.get("KUBEML_STABLE_BATCH", "1") != "0"
             state = None
             if augment:        # flip + crop(32, padding 4) drawn inside the kernel: one launch, no host-side random tensors
                 state = self._consts.get(("aug", x.device))
                 if state is None:
                     state = self._consts[("aug", x.device)] = torch.zeros(2, dtype=torch.int64, device=x.device)
-            ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED)
-            return out, (y if y.dtype == torch.int64 else y.to(torch.int64))
+            y64 = (y if y.dtype == torch.int64 else y.to(torch.int64)).contiguous()
+            if not out._kubeml_stable:
+                ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED)
+                return out, y64
+            ybuf = _STABLE.get((x.device, B, "labels"))        # the labels travel in the same launch, same idea
+            if ybuf is None:
+                ybuf = _STABLE[(x.device, B, "labels")] = torch.empty(B, dtype=torch.int64, device=x.device)
+                ybuf._kubeml_stable = True
+            ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED, labels=y64, labels_out=ybuf)
+            return out, ybuf
         if augment:
             # RandomHorizontalFlip + RandomCrop(32, padding=4), vectorised over the batch
             flip = torch.rand(B, device=x.device) < 0.5

@@ -303,10 +303,38 @@ class KubeModel(ABC):
         import time as _time
         t_wall = _time.perf_counter()
         self._round_idx = 0
-        for round_idx, i in enumerate(intervals):
+
+        def _prepare(start):
+            self._dataset._load_train_data(start=start, end=min(assigned.stop, start + per_iter))
+            return self._dataset._batches(self.batch_size, self.device)
+
+        # The host reads the round's losses and the merge status once per round, in step with the stream.
+        # Everything the next round needs from the host (shard lookup, batch views) is prepared *before* that
+        # wait, while the GPU is still busy with this round, so that the only thing between the end of the
+        # merge and the next round's first kernel is one graph launch.
+        prefetch = on_cuda and os.environ.get("KUBEML_ROUND_PREFETCH", "1") != "0"
+        # ... and that launch is already queued: the host hands the next round's first step to the stream
+        # *before* it waits for this round's merge, and reads the losses and the merge status while that step
+        # runs.  If the status then says the merge timed out (a peer went silent - the rare path), the repeat
+        # merge of `check_round` runs behind that one extra local step.
+        lookahead = prefetch and os.environ.get("KUBEML_ROUND_LOOKAHEAD", "1") != "0"
+        starts = list(intervals)
+        ready = None
+        pending = None          # (round, event after its merge, losses pushed up to it) not read back yet
+
+        def settle() -> float:
+            nonlocal pending
+            r, ev, n = pending
+            pending = None
+            v = stage.drain(n, ev)
+            check = getattr(self._sync, "check_round", None)
+            if check is not None:
+                check(r)
+            return v
+        for round_idx, i in enumerate(starts):
             self._round_idx = round_idx
-            self._dataset._load_train_data(start=i, end=min(assigned.stop, i + per_iter))
-            batches = self._dataset._batches(self.batch_size, self.device)
+            batches = ready if ready is not None else _prepare(i)
+            ready = None
             num_iterations += len(batches)
 
             self._on_iteration_start()
@@ -315,6 +343,8 @@ class KubeModel(ABC):
             fuse_last = bool(can_fuse is not None and can_fuse(self.optimizer))
             sliced = isinstance(batches, _sliced_type())
             for idx, batch in enumerate(batches):
+                if pending is not None and idx == 1:
+                    loss_host += settle()
                 if fault and fault(a._func_id, a.epoch, round_idx, idx):
                     raise KubeMLException(f"injected fault in function {a._func_id}", 500)
                 if not sliced:
@@ -336,6 +366,8 @@ class KubeModel(ABC):
                     loss_dev = loss_dev + step_loss
                 else:
                     loss_host += float(step_loss)
+            if pending is not None:
+                loss_host += settle()
             self._on_iteration_end()
             self.h2d_bytes += getattr(batches, "h2d_bytes", 0)
             if tracing and getattr(batches, "trace", None):
@@ -344,11 +376,20 @@ class KubeModel(ABC):
             # every round but the last blocks on the merge barrier (network.py:305-306)
             if i != intervals[-1]:
                 self._sync.arrive(a._job_id, a._func_id, round_idx)
+            if prefetch and round_idx + 1 < len(starts):
+                ready = _prepare(starts[round_idx + 1])
+                if hasattr(ready, "prestage"):
+                    ready.prestage()          # first batch on its way to the device before the wait below
             if stage is not None:
-                loss_host += stage.drain()
-                check = getattr(self._sync, "check_round", None)
-                if check is not None:            # the host is in step with the stream here: did the merge go through?
-                    check(round_idx)
+                if lookahead and ready is not None:
+                    ev = torch.cuda.Event()
+                    ev.record()
+                    pending = (round_idx, ev, stage.n)
+                else:
+                    loss_host += stage.drain()
+                    check = getattr(self._sync, "check_round", None)
+                    if check is not None:        # the host is in step with the stream here: did the merge go through?
+                        check(round_idx)
 
         merge_events = list(getattr(self._sync, "_events", [])) if tracing else []
         self._sync.end_epoch(a._job_id, a._func_id, len(intervals))
@@ -435,7 +476,8 @@ class KubeModel(ABC):
             cache[key] = ent
         if ent["graph"] is not None:
             for s_t, t in zip(ent["static"], tensors):
-                s_t.copy_(t, non_blocking=True)
+                if s_t.data_ptr() != t.data_ptr():     # a dataset may hand out the same (stable) buffer every step
+                    s_t.copy_(t, non_blocking=True)
             ent["graph"].replay()
             if ent.get("deferred"):
                 opt._deferred = True          # the captured program stops short of the optimizer launch
@@ -446,7 +488,9 @@ class KubeModel(ABC):
         if ent["failed"] or ent["calls"] <= 2:
             return self._eager_step(batch, idx, defer)
         try:
-            static = [t.clone() for t in tensors]
+            # the captured program reads its inputs from fixed addresses: a private copy of each batch tensor,
+            # or the tensor itself when the dataset marks it as a buffer it refills in place for every batch
+            static = [t if getattr(t, "_kubeml_stable", False) else t.clone() for t in tensors]
             it = iter(static)
             sbatch = type(batch)(next(it) if isinstance(t, torch.Tensor) else t for t in batch) \
                 if isinstance(batch, (tuple, list)) else static[0]
@@ -557,28 +601,56 @@ class KubeModel(ABC):
 
 
 class _LossStage:
-    """Page-locked landing zone for per-step scalars (loss): async D2H now, read after a sync."""
+    """Page-locked landing zone (a ring) for per-step scalars (loss): written asynchronously now, read after a
+    sync.  The scalar travels by a one-thread kernel storing into the mapped host buffer (`kml_post_f32`), not by
+    a copy-engine transfer, which would cost two engine hand-overs between consecutive steps
+    (`KUBEML_LOSS_POST=copy` restores the memcpy)."""
 
     def __init__(self, device: torch.device, capacity: int = 4096):
         self.device = device
         self.buf = torch.zeros(capacity, dtype=torch.float32).pin_memory()
-        self.n = 0
+        self.cap = capacity
+        self.head = 0           # first slot not read yet
+        self.tail = 0           # next slot to write
+        self.carry = 0.0
         self.bytes = 0
+        self._kernel_store = os.environ.get("KUBEML_LOSS_POST", "kernel") != "copy"
+
+    @property
+    def n(self) -> int:
+        return self.tail - self.head
 
     def push(self, t: torch.Tensor) -> None:
-        if self.n == self.buf.numel():
-            self.drain_into = getattr(self, "drain_into", 0.0) + self.drain()
-        self.buf[self.n:self.n + 1].copy_(t.detach().reshape(1), non_blocking=True)
-        self.n += 1
+        if self.n == self.cap:
+            self.carry += self.drain()
+        slot = self.tail % self.cap
+        dst = self.buf[slot:slot + 1]
+        src = t.detach().reshape(1)
+        if self._kernel_store and src.dtype == torch.float32 and src.is_contiguous():
+            from .ops import nn as _K
+            _K.post_f32(src, dst)
+        else:
+            dst.copy_(src, non_blocking=True)
+        self.tail += 1
         self.bytes += 4
 
-    def drain(self) -> float:
-        if self.n == 0:
-            return getattr(self, "drain_into", 0.0)
-        torch.cuda.current_stream(self.device).synchronize()
-        v = float(self.buf[:self.n].sum()) + getattr(self, "drain_into", 0.0)
-        self.drain_into = 0.0
-        self.n = 0
+    def drain(self, count: Optional[int] = None, event=None) -> float:
+        """Sum of the oldest `count` entries (all by default) once `event` (default: everything queued on the
+        current stream) has happened."""
+        n = self.n if count is None else min(int(count), self.n)
+        v, self.carry = self.carry, 0.0
+        if n == 0:
+            return v
+        if event is not None:
+            event.synchronize()
+        else:
+            torch.cuda.current_stream(self.device).synchronize()
+        lo, hi = self.head % self.cap, (self.head + n - 1) % self.cap + 1
+        if lo < hi:
+            v += float(self.buf[lo:hi].sum())
+        else:
+            v += float(self.buf[lo:].sum()) + float(self.buf[:hi].sum())
+        self.head += n
         return v
 
 

@@ -275,6 +275,15 @@ def stamp(slots, idx: int) -> None:
         _native.check(_native.lib().kml_stamp(slots.data_ptr(), int(idx), _native.stream_ptr()), "kml_stamp")
 
 
+def post_f32(src, dst_pinned) -> None:
+    """dst_pinned (page-locked host float32, same number of elements) <- src (device float32), written by a kernel
+    on the current stream; read it after synchronising with that stream."""
+    assert src.is_cuda and src.dtype == torch.float32 and dst_pinned.dtype == torch.float32
+    assert dst_pinned.is_pinned() and src.is_contiguous() and dst_pinned.is_contiguous()
+    _native.check(_native.lib().kml_post_f32(src.data_ptr(), dst_pinned.data_ptr(), src.numel(), _native.stream_ptr()),
+                  "kml_post_f32")
+
+
 def pack_rows(src, dst) -> None:
     """dst bf16 [rows, ld] <- src fp32 [rows, cols], zero padded."""
     rows, cols = src.shape
@@ -287,17 +296,25 @@ def pack_rows(src, dst) -> None:
 
 
 def image_prep(x_u8, y, aug, pad: int, mean: Tuple[float, float, float], std: Tuple[float, float, float],
-               rand_state=None, seed: int = 0) -> None:
+               rand_state=None, seed: int = 0, labels=None, labels_out=None) -> None:
     """uint8 NHWC -> normalised bf16 NHWC with optional per-sample flip/crop codes (see header).  With
-    `rand_state` (int64[2] on the device, zeros) the codes are drawn inside the kernel instead of being passed."""
+    `rand_state` (int64[2] on the device, zeros) the codes are drawn inside the kernel instead of being passed;
+    that kernel can also carry the batch's int64 `labels` into `labels_out` (a fixed buffer) in the same launch."""
     N, H, W, C = x_u8.shape
     if x_u8.is_cuda and rand_state is not None:
         m = (ctypes.c_float * 3)(*mean)
         s = (ctypes.c_float * 3)(*std)
+        if labels_out is not None:
+            assert labels.dtype == torch.int64 and labels_out.dtype == torch.int64 and labels.numel() == N
+            assert labels.is_contiguous() and labels_out.is_contiguous() and labels_out.numel() >= N
         _native.check(_native.lib().kml_image_prep_rand(x_u8.data_ptr(), y.data_ptr(), rand_state.data_ptr(),
                                                         int(seed) & 0xFFFFFFFF, N, H, W, C, pad, m, s,
+                                                        labels.data_ptr() if labels_out is not None else None,
+                                                        labels_out.data_ptr() if labels_out is not None else None,
                                                         _native.stream_ptr()), "kml_image_prep_rand")
         return
+    if labels_out is not None:
+        labels_out[:N].copy_(labels)
     if x_u8.is_cuda:
         m = (ctypes.c_float * 3)(*mean)
         s = (ctypes.c_float * 3)(*std)

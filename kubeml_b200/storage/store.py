@@ -36,6 +36,8 @@ class ShardStore:
         self._lock = threading.RLock()
         self._mmaps: Dict[Tuple[str, str], Tuple[np.ndarray, np.ndarray]] = {}
         self._pinned: Dict[Tuple[str, str], tuple] = {}
+        self._meta: Dict[str, tuple] = {}
+        self._resident: Dict[Tuple[str, str, str], tuple] = {}
 
     # ---- catalogue -------------------------------------------------------------------
     def _dir(self, name: str) -> str:
@@ -51,10 +53,19 @@ class ShardStore:
                       if os.path.isfile(os.path.join(self.root, d, "meta.json")))
 
     def meta(self, name: str) -> dict:
-        if not self.exists(name):
+        # asked for on every round of every worker: parsed once per version of the file (one stat per call)
+        path = os.path.join(self._dir(name), "meta.json")
+        try:
+            st = os.stat(path)
+        except OSError:
             raise DatasetNotFoundError()
-        with open(os.path.join(self._dir(name), "meta.json")) as f:
-            return json.load(f)
+        stamp = (st.st_mtime_ns, st.st_size, st.st_ino)
+        hit = self._meta.get(name)
+        if hit is None or hit[0] != stamp:
+            with open(path) as f:
+                hit = (stamp, json.load(f))
+            self._meta[name] = hit
+        return hit[1]
 
     # ---- ingest ----------------------------------------------------------------------
     def create(self, name: str, x_train, y_train, x_test, y_test,
@@ -107,6 +118,8 @@ class ShardStore:
                 del self._mmaps[k]
             for k in [k for k in self._pinned if k[0] == name]:
                 del self._pinned[k]
+            for k in [k for k in self._resident if k[0] == name]:
+                del self._resident[k]
             shutil.rmtree(self._dir(name))
 
     # ---- read ------------------------------------------------------------------------
@@ -152,6 +165,17 @@ class ShardStore:
                     xt, yt = xt.pin_memory(), yt.pin_memory()
                 self._pinned[key] = (xt, yt)
             return self._pinned[key]
+
+
+    def resident(self, name: str, split: str, device):
+        """(features, labels) of a whole split as tensors on `device`, staged once per process: for kernel-only
+        measurements that want no host->device traffic inside the timed region (`device_resident_data`)."""
+        key = (name, split, str(device))
+        with self._lock:
+            if key not in self._resident:
+                px, py = self.pinned(name, split)
+                self._resident[key] = (px.to(device), py.to(device))
+            return self._resident[key]
 
 
 def load_array_file(path: str) -> np.ndarray:

@@ -90,6 +90,7 @@ class TrainJob:
         # worker and stream; written to <trace_dir>/<job>.trace.json for chrome://tracing / Perfetto.
         from ..utils.tracing import ChromeTrace
         self.trace = ChromeTrace()
+        self.worker_traces: dict = {}
         self.trace_dir: Optional[str] = None
         self.merge_log: List[Dict[str, Any]] = []   # (epoch, participants, seconds) per merge
         self.epoch_stats: List[Dict[str, Any]] = []  # per epoch: device-timed seconds, steps, bytes
@@ -252,6 +253,7 @@ class TrainJob:
             tr = p.get("trace") if isinstance(p, dict) else None
             if not tr:
                 continue
+            self.worker_traces[fid] = tr        # raw device spans of the last traced epoch (bench.py's gap table)
             for lane, key in enumerate(("step", "h2d", "merge")):
                 for r, b, t_ms, d_ms in tr.get(key, []):
                     self.trace.device_span(f"{key} r{r} b{b}" if key != "merge" else f"merge {r}",

@@ -159,3 +159,46 @@ def test_resume_on_the_device_path(kube_home, monkeypatch):
     for k in sd1:
         torch.testing.assert_close(sd2[k].float(), sd1[k].float(), rtol=1e-5, atol=1e-6)
     c.shutdown()
+
+
+def test_loss_stage_ring_posts_scalars_by_kernel_and_wraps(monkeypatch):
+    """`_LossStage`: device scalars land in page-locked memory through `kml_post_f32` (and through a memcpy with
+    KUBEML_LOSS_POST=copy); partial drains leave the younger entries in place; the ring wraps."""
+    from kubeml_b200.network import _LossStage
+    dev = torch.device("cuda", 0)
+    for mode in ("kernel", "copy"):
+        monkeypatch.setenv("KUBEML_LOSS_POST", mode)
+        st = _LossStage(dev, capacity=4)
+        vals = [torch.tensor(float(i + 1), device=dev) for i in range(11)]
+        for v in vals[:3]:
+            st.push(v)
+        ev = torch.cuda.Event(); ev.record()
+        st.push(vals[3])                                   # younger than the event: must survive the partial drain
+        assert st.drain(3, ev) == 1 + 2 + 3 and st.n == 1
+        for v in vals[4:7]:                                # slots wrap around the 4-entry ring
+            st.push(v)
+        assert st.n == 4
+        st.push(vals[7])                                   # full: the ring empties itself into the carry
+        assert st.n == 1
+        assert st.drain() == 4 + 5 + 6 + 7 + 8 and st.n == 0
+        assert st.drain() == 0.0 and st.bytes == 4 * 8
+
+
+def test_round_lookahead_trains_exactly_like_the_in_step_flow(kube_home, monkeypatch):
+    """The host queues the next round's first step before it reads the previous round back
+    (KUBEML_ROUND_LOOKAHEAD, network.py): same kernels in the same order, so the same losses to the bit."""
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    req = TrainRequest(model_type="lenet", batch_size=64, epochs=2, dataset="mnist", lr=0.01, function_name="lenet",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=2))
+    got = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("KUBEML_ROUND_LOOKAHEAD", mode)
+        monkeypatch.setenv("KUBEML_LOSS_POST", "kernel" if mode == "1" else "copy")
+        c = Cluster(home=kube_home + "/la" + mode, max_parallelism=1)
+        _mnist(c.shard_store)
+        h, job = _run(c, req)
+        got[mode] = (h.data.train_loss, h.data.validation_loss, job.epoch_stats[-1]["d2h_bytes"])
+        c.shutdown()
+    assert got["1"][0] == got["0"][0] and got["1"][1] == got["0"][1]
+    assert got["1"][2] == got["0"][2] == 4 * 8          # one scalar per step crosses to the host either way
