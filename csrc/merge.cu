@@ -213,8 +213,7 @@ kavg_merge_kernel(const kml_merge_params p) {
     const float bc1 = 1.f - powf(p.beta1, static_cast<float>(t));
     const float bc2_sqrt = sqrtf(1.f - powf(p.beta2, static_cast<float>(t)));
     const float step_size = p.lr / bc1;
-    for (size_t i = tid; i < nsgd4; i += nthreads) {
-      float4 wv = w[i], gv = __ldcs(g + i), a = m1[i], b = m2[i];
+    auto adam_one = [&](size_t i, float4 wv, float4 gv, float4 a, float4 b) {
       float* wp = &wv.x; float* gp = &gv.x; float* ap = &a.x; float* bp = &b.x;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -232,20 +231,30 @@ kavg_merge_kernel(const kml_merge_params p) {
         r.y = *reinterpret_cast<uint32_t*>(&x1);
         wb0[i] = r;
       }
+    };
+    // two elements per thread and trip: one CTA of 512 threads per SM is all that fits (90 registers), so the
+    // bytes in flight come from loads issued back to back, not from more threads
+    size_t i = tid;
+    for (; i + nthreads < nsgd4; i += 2 * nthreads) {
+      const size_t j = i + nthreads;
+      const float4 w0 = w[i], g0 = __ldcs(g + i), a0 = __ldcs(m1 + i), b0 = __ldcs(m2 + i);
+      const float4 w1 = w[j], g1 = __ldcs(g + j), a1 = __ldcs(m1 + j), b1 = __ldcs(m2 + j);
+      adam_one(i, w0, g0, a0, b0);
+      adam_one(j, w1, g1, a1, b1);
     }
+    if (i < nsgd4) adam_one(i, w[i], __ldcs(g + i), __ldcs(m1 + i), __ldcs(m2 + i));
     if (!solo) local_barrier();
   } else if (p.fuse_sgd) {
     float4* w = reinterpret_cast<float4*>(p.replica[p.my_rank]);
     const float4* g = reinterpret_cast<const float4*>(p.grad);
     const float4* m = reinterpret_cast<const float4*>(p.momentum_buf);
     const bool has_m = p.momentum != 0.f && m != nullptr;
-    for (size_t i = tid; i < nsgd4; i += nthreads) {
-      float4 wv = w[i], gv = __ldcs(g + i);
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto sgd_one = [&](size_t i, float4 wv, float4 gv, float4 mv) {
       float4 d;
       d.x = fmaf(p.weight_decay, wv.x, gv.x); d.y = fmaf(p.weight_decay, wv.y, gv.y);
       d.z = fmaf(p.weight_decay, wv.z, gv.z); d.w = fmaf(p.weight_decay, wv.w, gv.w);
       if (has_m) {
-        float4 mv = __ldcs(m + i);
         d.x = fmaf(p.momentum, mv.x, d.x); d.y = fmaf(p.momentum, mv.y, d.y);
         d.z = fmaf(p.momentum, mv.z, d.z); d.w = fmaf(p.momentum, mv.w, d.w);
       }
@@ -260,7 +269,16 @@ kavg_merge_kernel(const kml_merge_params p) {
         r.y = *reinterpret_cast<uint32_t*>(&b);
         wb0[i] = r;
       }
+    };
+    size_t i = tid;                  // two elements per thread and trip (see the Adam loop above)
+    for (; i + nthreads < nsgd4; i += 2 * nthreads) {
+      const size_t j = i + nthreads;
+      const float4 w0 = w[i], g0 = __ldcs(g + i), m0 = has_m ? __ldcs(m + i) : zero4;
+      const float4 w1 = w[j], g1 = __ldcs(g + j), m1v = has_m ? __ldcs(m + j) : zero4;
+      sgd_one(i, w0, g0, m0);
+      sgd_one(j, w1, g1, m1v);
     }
+    if (i < nsgd4) sgd_one(i, w[i], __ldcs(g + i), has_m ? __ldcs(m + i) : zero4);
     if (!solo) local_barrier();     // the whole replica is final before anyone is told so
   }
   auto reset_optimizer = [&]() {    // the reference discards optimizer state at every sync (network.py:121-128)
