@@ -179,7 +179,7 @@ class KubeModel(ABC):
             can_fuse = getattr(self._sync, "can_fuse_last_step", None)
             variants = [False] + ([True] if can_fuse is not None and can_fuse(self.optimizer) else [])
             for defer in variants:
-                for _ in range(4):            # two eager calls, the capture, one replay
+                for _ in range(4):            # eager call(s), the capture, replay(s)
                     self._graphed_step(batch, 0, defer and self._single_step is True)
                     if getattr(self.optimizer, "_deferred", False):
                         self.optimizer._deferred = False
@@ -457,7 +457,7 @@ class KubeModel(ABC):
 
     def _graphed_step(self, batch, idx, defer: bool = False):
         """First two calls per (shapes, hyper-parameters) run eagerly (allocations, lazy inits), the
-        third is captured, later ones replay.  The captured program only touches arena memory and
+        third is captured, later ones replay (one eager call once the job has a captured graph already).  The captured program only touches arena memory and
         buffers owned by the capturing KubeModel, which the cache keeps alive, so it stays valid for
         later invocations (epochs) whose fresh module objects alias the same arena."""
         ws = self._inv.worker_state if self._inv.worker_state is not None else {}
@@ -485,7 +485,11 @@ class KubeModel(ABC):
             ws["graph_launches"] = ws.get("graph_launches", 0) + ent["kernels"]
             return ent["out"]
         ent["calls"] += 1
-        if ent["failed"] or ent["calls"] <= 2:
+        # two eager calls before the first capture of a job (allocations, lazy initialisation, library
+        # heuristics); one is enough for a further signature of a job that already replays a graph - e.g. the short
+        # last batch of an epoch, which comes round once per epoch and would otherwise run eagerly for two epochs
+        warm = any(e.get("graph") is not None for k, e in cache.items() if k[0] == key[0])
+        if ent["failed"] or ent["calls"] <= (1 if warm else 2):
             return self._eager_step(batch, idx, defer)
         try:
             # the captured program reads its inputs from fixed addresses: a private copy of each batch tensor,

@@ -68,6 +68,30 @@ def test_spmd_lenet_matches_host_oracle(tmp_path, kube_home):
     assert dev_hist["parallelism"] == [2.0, 2.0]
 
 
+def test_worker_threads_on_two_gpus_of_one_process_use_the_device_merge(tmp_path):
+    """The in-process Cluster runs one worker *thread* per GPU (ThreadInvoker + ThreadedDeviceSyncGroup): kernel
+    attributes are per device, two GPUs launch the same kernels from one process, and the merge kernels of the two
+    GPUs wait for each other.  Same job with the host merge as the oracle."""
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster, make_kubeml_client
+    hist = {}
+    for mode in ("device", "host"):
+        c = Cluster(home=str(tmp_path / mode), max_parallelism=2, options={"force_host_sync": mode == "host"})
+        rng = np.random.default_rng(0)
+        c.shard_store.create("mnist", rng.integers(0, 255, (1024, 28, 28), dtype=np.uint8), rng.integers(0, 10, (1024,)),
+                             rng.integers(0, 255, (256, 28, 28), dtype=np.uint8), rng.integers(0, 10, (256,)))
+        req = TrainRequest(model_type="lenet", batch_size=64, epochs=2, dataset="mnist", lr=0.01, function_name="lenet",
+                           options=TrainOptions(default_parallelism=2, static_parallelism=True, validate_every=1, k=2))
+        jid = make_kubeml_client(c).v1().networks().train(req)
+        assert c.wait(jid, 300) is None
+        assert c.jobs[jid].device_mode == (mode == "device")
+        hist[mode] = c.histories.get(jid).data
+        c.shutdown()
+    assert hist["device"].parallelism == [2.0, 2.0]
+    np.testing.assert_allclose(hist["device"].train_loss, hist["host"].train_loss, rtol=5e-3)
+    np.testing.assert_allclose(hist["device"].validation_loss, hist["host"].validation_loss, rtol=5e-3)
+
+
 def test_elastic_parallelism_grows_between_epochs(tmp_path):
     """Scheduler policy: 1 worker, then +1 on second sight; the joining rank maps the peers' arenas,
     copies the merged model and takes part in the next epoch's merges."""
