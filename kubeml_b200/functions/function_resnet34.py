@@ -24,7 +24,19 @@ from kubeml_b200.optim import SGD
 
 _MEAN = (0.485, 0.456, 0.406)
 _STD = (0.229, 0.224, 0.225)
-_STABLE = {}      # (device, batch size) -> the batch buffer the native path refills in place (one training stream per GPU)
+_STABLE = {}      # (device, batch size) -> the batch buffer the native path refills in place, outside a worker
+
+
+def _stable_pool() -> dict:
+    """Where the in-place batch buffers live: in the worker's warm state (one worker = one training stream; the
+    buffers survive from epoch to epoch with the captured step that reads them, and two jobs whose worker threads
+    share a GPU do not share a buffer)."""
+    from kubeml_b200.runtime.context import current_invocation, has_invocation
+    if has_invocation():
+        ws = current_invocation().worker_state
+        if ws is not None:
+            return ws.setdefault("stable_batches", {})
+    return _STABLE
 
 
 class Cifar10Dataset(KubeDataset):
@@ -50,9 +62,10 @@ class Cifar10Dataset(KubeDataset):
         if self.native and x.is_cuda:
             # one output buffer per (device, batch size), refilled in place for every batch on the training
             # stream: the captured step reads it where it is (network.py `_kubeml_stable`), no per-step copy
-            out = _STABLE.get((x.device, B))
+            pool = _stable_pool()
+            out = pool.get((x.device, B))
             if out is None:
-                out = _STABLE[(x.device, B)] = torch.empty((B, 32, 32, 3), dtype=torch.bfloat16, device=x.device)
+                out = pool[(x.device, B)] = torch.empty((B, 32, 32, 3), dtype=torch.bfloat16, device=x.device)
                 out._kubeml_stable = os.environ.get("KUBEML_STABLE_BATCH", "1") != "0"
             state = None
             if augment:        # flip + crop(32, padding 4) drawn inside the kernel: one launch, no host-side random tensors
@@ -63,9 +76,9 @@ class Cifar10Dataset(KubeDataset):
             if not out._kubeml_stable:
                 ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED)
                 return out, y64
-            ybuf = _STABLE.get((x.device, B, "labels"))        # the labels travel in the same launch, same idea
+            ybuf = pool.get((x.device, B, "labels"))           # the labels travel in the same launch, same idea
             if ybuf is None:
-                ybuf = _STABLE[(x.device, B, "labels")] = torch.empty(B, dtype=torch.int64, device=x.device)
+                ybuf = pool[(x.device, B, "labels")] = torch.empty(B, dtype=torch.int64, device=x.device)
                 ybuf._kubeml_stable = True
             ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED, labels=y64, labels_out=ybuf)
             return out, ybuf
