@@ -19,10 +19,14 @@ class KubeResnet32(KubeResnet34):
 def build_network(num_classes: int = 10):
     """The hand-written-kernel model by default; KUBEML_RESNET32_IMPL=torch selects the stock modules
     (same parameter names, so checkpoints and merges are interchangeable)."""
+    depth = os.environ.get("KUBEML_CIFAR_RESNET", "resnet32")      # resnet20/32/44/56/110/1202 (resnet32.py:209-234)
+    if depth not in ("resnet20", "resnet32", "resnet44", "resnet56", "resnet110", "resnet1202"):
+        raise ValueError(f"KUBEML_CIFAR_RESNET={depth}: not one of the CIFAR ResNets")
     if os.environ.get("KUBEML_RESNET32_IMPL", "native") != "torch":
-        from kubeml_b200.models.cifar_native import resnet32 as native_resnet32
-        return native_resnet32(num_classes)
-    return resnet32(num_classes).to(memory_format=torch.channels_last)
+        from kubeml_b200.models import cifar_native
+        return getattr(cifar_native, depth)(num_classes)
+    from kubeml_b200.models import cifar_resnet
+    return getattr(cifar_resnet, depth)(num_classes).to(memory_format=torch.channels_last)
 
 
 def main():

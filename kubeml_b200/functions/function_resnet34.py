@@ -40,6 +40,9 @@ def _stable_pool() -> dict:
 
 
 class Cifar10Dataset(KubeDataset):
+    MEAN, STD = _MEAN, _STD      # per-channel normalisation of the 0..1 image
+    AUGMENT = True               # flip + crop(32, padding 4) on training batches
+
     def __init__(self, name: str = "cifar10"):
         super().__init__(name)
         self._consts = {}
@@ -48,8 +51,8 @@ class Cifar10Dataset(KubeDataset):
     def _norm(self, device):
         c = self._consts.get(device)
         if c is None:
-            mean = torch.tensor(_MEAN, device=device).view(1, 1, 1, 3) * 255.0
-            inv = 1.0 / (torch.tensor(_STD, device=device).view(1, 1, 1, 3) * 255.0)
+            mean = torch.tensor(self.MEAN, device=device).view(1, 1, 1, 3) * 255.0
+            inv = 1.0 / (torch.tensor(self.STD, device=device).view(1, 1, 1, 3) * 255.0)
             c = (mean, inv)
             self._consts[device] = c
         return c
@@ -58,7 +61,7 @@ class Cifar10Dataset(KubeDataset):
         """x: uint8 [B,32,32,3] (HWC, as CIFAR is stored).  Native models get normalised bf16 NHWC
         from one fused kernel (flip + crop + normalise); stock modules get the float NCHW view."""
         B = x.shape[0]
-        augment = self.is_training() and os.environ.get("KUBEML_RESNET_NOAUG") != "1"   # parity runs: no randomness
+        augment = self.AUGMENT and self.is_training() and os.environ.get("KUBEML_RESNET_NOAUG") != "1"   # parity runs: no randomness
         if self.native and x.is_cuda:
             # one output buffer per (device, batch size), refilled in place for every batch on the training
             # stream: the captured step reads it where it is (network.py `_kubeml_stable`), no per-step copy
@@ -74,13 +77,13 @@ class Cifar10Dataset(KubeDataset):
                     state = self._consts[("aug", x.device)] = torch.zeros(2, dtype=torch.int64, device=x.device)
             y64 = (y if y.dtype == torch.int64 else y.to(torch.int64)).contiguous()
             if not out._kubeml_stable:
-                ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED)
+                ops.nn.image_prep(x, out, None, 4, self.MEAN, self.STD, rand_state=state, seed=0x5EED)
                 return out, y64
             ybuf = pool.get((x.device, B, "labels"))           # the labels travel in the same launch, same idea
             if ybuf is None:
                 ybuf = pool[(x.device, B, "labels")] = torch.empty(B, dtype=torch.int64, device=x.device)
                 ybuf._kubeml_stable = True
-            ops.nn.image_prep(x, out, None, 4, _MEAN, _STD, rand_state=state, seed=0x5EED, labels=y64, labels_out=ybuf)
+            ops.nn.image_prep(x, out, None, 4, self.MEAN, self.STD, rand_state=state, seed=0x5EED, labels=y64, labels_out=ybuf)
             return out, ybuf
         if augment:
             # RandomHorizontalFlip + RandomCrop(32, padding=4), vectorised over the batch

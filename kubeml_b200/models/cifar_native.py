@@ -123,3 +123,4 @@ def _make(n: int):
 
 
 resnet20, resnet32, resnet44, resnet56, resnet110 = _make(3), _make(5), _make(7), _make(9), _make(18)
+resnet1202 = _make(200)       # the reference's resnet32.py:233-234 lists it too (19.4 M parameters, 1202 layers)

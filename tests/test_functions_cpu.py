@@ -46,6 +46,36 @@ def test_vgg_function_with_adam(cluster, monkeypatch):
     assert err is None and np.isfinite(job.history.train_loss[0])
 
 
+def test_vgg11_function_of_the_reference(cluster, monkeypatch):
+    """ml/experiments/kubeml/function_vgg11.py: VGG-11, CIFAR-10 statistics, no augmentation, Adam."""
+    monkeypatch.setenv("KUBEML_VGG_CLASSES", "10")
+    _cifar(cluster.shard_store, "cifar10", n=64)
+    from kubeml_b200.functions.function_vgg11 import Cifar10Plain
+    assert Cifar10Plain.AUGMENT is False and Cifar10Plain.MEAN[0] == 0.4914
+    req = TrainRequest(model_type="vgg11", batch_size=32, epochs=1, dataset="cifar10", lr=1e-4,
+                       function_name="vgg11",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=-1))
+    err, job = _run(cluster, req)
+    assert err is None and np.isfinite(job.history.train_loss[0]) and len(job.history.accuracy) == 1
+
+
+def test_cifar_resnet_depths_share_parameter_names_with_the_stock_twins(monkeypatch):
+    """resnet20 ... resnet1202 (ml/experiments/kubeml/resnet32.py:209-234): native and stock state_dicts line up."""
+    from kubeml_b200.models import cifar_native, cifar_resnet
+    for depth, blocks in (("resnet20", 3), ("resnet56", 9), ("resnet1202", 200)):
+        nat = getattr(cifar_native, depth)(10).state_dict()
+        ref = getattr(cifar_resnet, depth)(10).state_dict()
+        assert list(nat.keys()) == list(ref.keys())
+        assert all(tuple(nat[k].shape) == tuple(ref[k].shape) for k in ref)
+        assert f"layer3.{blocks - 1}.conv2.weight" in ref
+    from kubeml_b200.functions.function_resnet32 import build_network
+    monkeypatch.setenv("KUBEML_CIFAR_RESNET", "resnet44")
+    assert "layer1.6.conv1.weight" in build_network(10).state_dict()
+    monkeypatch.setenv("KUBEML_CIFAR_RESNET", "resnet33")
+    with pytest.raises(ValueError):
+        build_network(10)
+
+
 def test_resnet34_function_infer(cluster, monkeypatch):
     monkeypatch.setenv("KUBEML_RESNET_CLASSES", "10")
     monkeypatch.setenv("KUBEML_RESNET_IMPL", "compat")
