@@ -46,6 +46,7 @@ class Cluster:
 
         self.scheduler = Scheduler(max_parallelism=self.max_parallelism)
         self.ps = ParameterServer(self._make_job, scheduler=self.scheduler)
+        self.ps.job_options = self.options
         self.scheduler.ps = self.ps
         self.storage = StorageService(self.shard_store)
         self.controller = Controller(self.scheduler, self.ps, self.storage, self.histories,
@@ -106,12 +107,9 @@ class Cluster:
 
     # ---- convenience ---------------------------------------------------------------------
     def wait(self, job_id: str, timeout: Optional[float] = None) -> Optional[str]:
-        import time
-        t0 = time.time()
-        while job_id not in self.jobs:            # the scheduler thread has not created it yet
-            if timeout is not None and time.time() - t0 > timeout:
-                raise TimeoutError(job_id)
-            time.sleep(0.005)
+        """Block until the job has ended; its error text or None.  (The parameter server waits for the scheduler
+        thread to have created the job first - as a thread of this process or, with STANDALONE_JOBS, as a
+        process of its own, which never appears in `self.jobs`.)"""
         return self.ps.wait(job_id, timeout)
 
     def serve(self, host: str = const.HOST, controller_port: int = const.CONTROLLER_PORT,
@@ -120,6 +118,7 @@ class Cluster:
         self._servers.append(self.controller.serve(host, controller_port))
         if scheduler_port:
             self._servers.append(self.scheduler.serve(host, scheduler_port))
+            self.ps.scheduler_url = f"http://{'127.0.0.1' if host in ('0.0.0.0', '') else host}:{self._servers[-1].port}"
         if ps_port:
             self._servers.append(self.ps.serve(host, ps_port))
         if storage_port:
@@ -132,6 +131,7 @@ class Cluster:
 
     def shutdown(self) -> None:
         self.scheduler.stop()
+        self.ps.close()
         for s in self._servers:
             s.stop()
         self._servers.clear()

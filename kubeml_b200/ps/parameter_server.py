@@ -22,10 +22,34 @@ from .metrics import MetricsRegistry
 JobFactory = Callable[[TrainTask, "ParameterServer"], TrainJob]
 
 
+class _JobProcess:
+    """Handle of a job that runs as a child process (`task.job.handle` in stand-alone mode): what the reference
+    keeps as `JobInfo.Pod` / `JobInfo.Svc` (ml/pkg/api/types.go:59-65) plus the job client that talks to it."""
+
+    def __init__(self, proc, client, url: str):
+        self.proc, self.client, self.url = proc, client, url
+
+    def update_task(self, state: JobState) -> None:
+        self.client.update(state)
+
+    def stop(self) -> None:
+        self.client.stop()
+
+
 class ParameterServer:
-    def __init__(self, job_factory: JobFactory, scheduler: Any = None):
+    def __init__(self, job_factory: JobFactory, scheduler: Any = None, standalone_jobs: Optional[bool] = None):
         self.job_factory = job_factory
         self.scheduler = scheduler
+        # ml/cmd/ml/main.go:119-129: STANDALONE_JOBS picks pod-per-job over goroutine-per-job.  Here: a child
+        # process per job (`train/server.py`) over a thread per job; the thread is the default on one host.
+        if standalone_jobs is None:
+            import os
+            standalone_jobs = os.environ.get("STANDALONE_JOBS", "").lower() in ("1", "true", "yes")
+        self.standalone_jobs = bool(standalone_jobs)
+        self.url: Optional[str] = None              # where job processes reach this server (set by serve())
+        self.scheduler_url: Optional[str] = None    # ... and the scheduler
+        self._own_servers: list = []
+        self.job_options: dict = {}                 # JSON-able worker options handed to job processes
         self.metrics = MetricsRegistry()
         self.log = logging.getLogger("kubeml.ps")
         self._index: Dict[str, TrainTask] = {}
@@ -41,6 +65,15 @@ class ParameterServer:
             if task.job.id in self._index:
                 raise KubeMLException(f"task {task.job.id} already exists", 400)
             self._index[task.job.id] = task
+        if self.standalone_jobs:
+            try:
+                self._start_job_process(task)
+            except BaseException:
+                with self._mu:
+                    self._index.pop(task.job.id, None)      # api.go:170-176: no resources, no entry
+                raise
+            self.metrics.task_started("train")
+            return
         self._open_job_log(task.job.id)
         job = self.job_factory(task, self)
         task.job.handle = job
@@ -49,6 +82,110 @@ class ParameterServer:
         with self._mu:
             self._threads[task.job.id] = t
             t.start()
+
+    # ---- stand-alone jobs: one process per job (ps/job_pod.go:18-242, ps/api.go:162-207) -------------------
+    START_RETRIES = 10          # api.go:192
+    READY_TIMEOUT_S = 20.0      # job_pod.go:172-186 waits that long for the pod to be Running
+
+    def _start_job_process(self, task: TrainTask) -> None:
+        import os
+        import subprocess
+        import sys
+        import time
+        from ..api import const
+        from ..train.server import JobClient
+        from ..util import find_free_port
+        job_id = task.job.id
+        self._ensure_reachable()
+        port = find_free_port()
+        env = dict(os.environ)
+        env["KUBEML_PS_URL"] = self.url
+        if self.scheduler_url:
+            env["KUBEML_SCHEDULER_URL"] = self.scheduler_url
+        env["KUBEML_HOME"] = const.home()
+        if self.job_options:
+            import json
+            env["KUBEML_JOB_OPTIONS"] = json.dumps({k: v for k, v in self.job_options.items()
+                                                    if isinstance(v, (bool, int, float, str, type(None)))})
+        env.pop("STANDALONE_JOBS", None)
+        root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        env["PYTHONPATH"] = root + (os.pathsep + env["PYTHONPATH"] if env.get("PYTHONPATH") else "")
+        log_dir = os.path.join(const.home(), "logs")
+        os.makedirs(log_dir, exist_ok=True)
+        # the child's output *is* the job log (`kubeml logs --id <job>` = `kubectl logs job-<id>`, cmd/log.go:28-65)
+        logf = open(os.path.join(log_dir, f"job-{job_id}.log"), "ab", buffering=0)
+        proc = subprocess.Popen([sys.executable, "-m", "kubeml_b200", "--jobPort", str(port), "--jobId", job_id],
+                                env=env, stdout=logf, stderr=subprocess.STDOUT, stdin=subprocess.DEVNULL)
+        logf.close()
+        url = f"http://127.0.0.1:{port}"
+        client = JobClient(url)
+        handle = _JobProcess(proc, client, url)
+        deadline = time.monotonic() + float(os.environ.get("KUBEML_JOB_READY_TIMEOUT_S", self.READY_TIMEOUT_S))
+        while not client.health():                      # the readiness probe of job_pod.go:120-131
+            if proc.poll() is not None or time.monotonic() > deadline:
+                self._kill(proc)
+                raise KubeMLException(f"job process of {job_id} did not become ready "
+                                      f"(exit code {proc.poll()}, see logs/job-{job_id}.log)", 500)
+            time.sleep(0.05)
+        last = None
+        for i in range(self.START_RETRIES):             # api.go:192-207: 10 tries, 200 ms x 2i apart
+            try:
+                client.start(task)
+                last = None
+                break
+            except KubeMLException as e:
+                last = e
+                if e.status_code < 500 or proc.poll() is not None:
+                    break
+                self.log.debug("error sending the task to job %s, retrying: %s", job_id, e)
+                time.sleep(0.2 * 2 * i)
+        if last is not None:
+            self._kill(proc)
+            raise KubeMLException(f"unable to send task for job {job_id}: {last}", 500)
+        task.job.handle = handle
+        t = threading.Thread(target=self._watch_job_process, args=(job_id, proc), daemon=True, name=f"job-{job_id}")
+        with self._mu:
+            self._threads[job_id] = t
+            t.start()
+
+    def _watch_job_process(self, job_id: str, proc) -> None:
+        """The job's liveness: a process that ends without having reported `/finish` (crash, kill, wedged GPU
+        context torn down by the driver) is a failed job, not a job that runs for ever in `task list`."""
+        rc = proc.wait()
+        with self._mu:
+            reported = job_id in self._finished
+        if not reported:
+            self.job_finished(job_id, KubeMLException(f"job process exited with code {rc} without reporting", 500))
+
+    @staticmethod
+    def _kill(proc) -> None:
+        if proc.poll() is None:
+            proc.terminate()
+            try:
+                proc.wait(timeout=5)
+            except Exception:  # noqa: BLE001
+                proc.kill()
+
+    def _ensure_reachable(self) -> None:
+        """Job processes call back over HTTP: make sure this server and the scheduler listen somewhere."""
+        from ..util import find_free_port
+        if self.url is None:
+            srv = self.serve("127.0.0.1", find_free_port())
+            self._own_servers.append(srv)
+        if self.scheduler_url is None and self.scheduler is not None and hasattr(self.scheduler, "serve"):
+            srv = self.scheduler.serve("127.0.0.1", find_free_port())
+            self._own_servers.append(srv)
+            self.scheduler_url = f"http://127.0.0.1:{srv.port}"
+
+    def close(self) -> None:
+        """Stop what stand-alone mode started: listeners and job processes still running."""
+        with self._mu:
+            handles = [t.job.handle for t in self._index.values() if isinstance(t.job.handle, _JobProcess)]
+        for h in handles:
+            self._kill(h.proc)
+        for srv in self._own_servers:
+            srv.stop()
+        self._own_servers.clear()
 
     # ---- per-job log files: what `kubeml logs --id <job> [-f]` reads -------------------------------
     # The reference's `logs` verb is `kubectl logs job-<id>` (ml/pkg/kubeml-cli/cmd/log.go:28-65): the
@@ -150,6 +287,9 @@ class ParameterServer:
             task = self._index.get(model_id)
         if task is None or task.job.handle is None:
             raise KubeMLException(f"model {model_id} not found (is the job still running?)", 404)
+        if isinstance(task.job.handle, _JobProcess):
+            raise KubeMLException("the model lives in the job's own process (STANDALONE_JOBS); "
+                                  "inference runs against jobs of this process", 501)
         job: TrainJob = task.job.handle
         self.metrics.task_started("inference")
         try:
@@ -181,4 +321,6 @@ class ParameterServer:
         self.job_finished(q.params["jobId"], err)
 
     def serve(self, host: str, port: int) -> Server:
-        return Server(self.router(), host, port).start()
+        srv = Server(self.router(), host, port).start()
+        self.url = f"http://{'127.0.0.1' if host in ('0.0.0.0', '') else host}:{srv.port}"
+        return srv

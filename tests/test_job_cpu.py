@@ -194,3 +194,64 @@ def test_resume_from_checkpoint_continues_where_the_first_task_stopped(cluster):
         np.testing.assert_allclose(got, v.numpy(), rtol=1e-4, atol=1e-6)
     _, err, _ = _run(cluster, mk(1, resume="nosuchjob"))
     assert err is not None and "no checkpoint" in str(err)
+
+
+def test_standalone_job_runs_in_its_own_process_and_reports_over_http(kube_home, monkeypatch):
+    """STANDALONE_JOBS (ml/cmd/ml/main.go:119-129, ml/pkg/ps/api.go:162-207): the parameter server starts
+    `python -m kubeml_b200 --jobPort P --jobId ID`, waits for /health, posts the task to /start; the job process
+    sends its metrics and its end back to the parameter server, asks the scheduler for its parallelism, and its
+    output is the job log.  Same losses as the job run as a thread."""
+    from kubeml_b200.controller import Cluster, make_kubeml_client
+    monkeypatch.setenv("KUBEML_CUDA_GRAPH", "0")
+    monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "")
+    # two epochs: the policy's first two answers (default parallelism, then +1) do not depend on epoch times
+    req = TrainRequest(model_type="lenet", batch_size=64, epochs=2, dataset="mnist", lr=0.01, function_name="lenet",
+                       options=TrainOptions(default_parallelism=2, static_parallelism=False, validate_every=1, k=4))
+    hist = {}
+    for mode in ("thread", "process"):
+        monkeypatch.setenv("STANDALONE_JOBS", "true" if mode == "process" else "false")
+        c = Cluster(home=os.path.join(kube_home, mode), max_parallelism=4, options={"force_host_sync": True})
+        assert c.ps.standalone_jobs == (mode == "process")
+        _mnist(c.shard_store, n=64 * 16)
+        seen = []
+        orig = c.ps.update_metrics
+        c.ps.update_metrics = lambda jid, m, _o=orig: (seen.append(m), _o(jid, m))[1]
+        monkeypatch.setenv("KUBEML_HOME", os.path.join(kube_home, mode))
+        jid = make_kubeml_client(c).v1().networks().train(req)
+        err = c.wait(jid, 300)
+        assert err is None, err
+        hist[mode] = c.histories.get(jid).data
+        if mode == "process":
+            assert jid not in c.jobs                              # nothing of the job ran in this process
+            assert len(seen) >= 2                                 # MetricUpdates of every epoch, over HTTP
+            log = open(os.path.join(kube_home, mode, "logs", f"job-{jid}.log")).read()
+            assert "Starting train job" in log and "serving on" in log
+            assert c.ps.list_tasks() == []
+        c.shutdown()
+    assert hist["process"].parallelism == hist["thread"].parallelism == [2.0, 3.0]    # the policy was asked over HTTP
+    np.testing.assert_allclose(hist["process"].train_loss, hist["thread"].train_loss, rtol=1e-5)
+    np.testing.assert_allclose(hist["process"].accuracy, hist["thread"].accuracy, rtol=1e-5)
+
+
+def test_standalone_job_that_dies_is_reported_failed(kube_home, monkeypatch):
+    """Liveness of a job process: killed in mid-run, it becomes a failed task instead of a task that is listed
+    for ever (the reference relies on the pod's readiness probe and phase, ml/pkg/ps/job_pod.go:120-131,172-186)."""
+    import time
+    from kubeml_b200.controller import Cluster, make_kubeml_client
+    monkeypatch.setenv("KUBEML_CUDA_GRAPH", "0")
+    monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "")
+    monkeypatch.setenv("STANDALONE_JOBS", "true")
+    c = Cluster(home=kube_home, max_parallelism=2, options={"force_host_sync": True})
+    _mnist(c.shard_store, n=64 * 64)
+    req = TrainRequest(model_type="lenet", batch_size=16, epochs=50, dataset="mnist", lr=0.01, function_name="lenet",
+                       options=TrainOptions(default_parallelism=2, static_parallelism=True, validate_every=0, k=1))
+    jid = make_kubeml_client(c).v1().networks().train(req)
+    deadline = time.time() + 60
+    while time.time() < deadline and not any(t.job.id == jid and t.job.handle is not None for t in c.ps.list_tasks()):
+        time.sleep(0.05)
+    task = next(t for t in c.ps.list_tasks() if t.job.id == jid)
+    task.job.handle.proc.kill()
+    err = c.wait(jid, 60)
+    assert err is not None and "without reporting" in err
+    assert c.ps.list_tasks() == []
+    c.shutdown()
