@@ -127,3 +127,19 @@ def test_function_registry_user_file(kube_home, tmp_path):
         reg.create("myfn", str(src))
     reg.delete("myfn")
     assert not reg.exists("myfn") and reg.exists("lenet") and reg.exists("builtin:function_lenet")
+
+
+def test_kubeml_command_is_packaged_and_launchable():
+    """`kubeml` as a command: the launcher script of the source tree and the console-script entry of pyproject.toml
+    (the reference ships a Go binary named kubeml, ml/pkg/kubeml-cli/)."""
+    import importlib
+    import os
+    import subprocess
+    import tomllib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    meta = tomllib.load(open(os.path.join(root, "pyproject.toml"), "rb"))
+    mod, fn = meta["project"]["scripts"]["kubeml"].split(":")
+    assert callable(getattr(importlib.import_module(mod), fn))
+    out = subprocess.run([os.path.join(root, "scripts", "kubeml"), "train", "--help"], capture_output=True, text=True,
+                         timeout=120, cwd="/")
+    assert out.returncode == 0 and "--sparse-avg" in out.stdout and "--resume" in out.stdout
