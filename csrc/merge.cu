@@ -195,6 +195,7 @@ kavg_merge_kernel(const kml_merge_params p) {
   const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
   const size_t n4 = p.n_f32 / 4;
   const size_t nsgd4 = p.n_sgd / 4;
+  const size_t nfuse4 = (p.n_fuse != 0 && p.n_fuse < p.n_sgd ? p.n_fuse : p.n_sgd) / 4;   // phase 0 covers [0, nfuse4)
 
   // One participant that is also the only destination (N = 1, or a rank alone in a late round): the average
   // of one replica is that replica (x / 1.0f == x), so nothing moves.  What is left is the fused last step -
@@ -235,14 +236,14 @@ kavg_merge_kernel(const kml_merge_params p) {
     // two elements per thread and trip: one CTA of 512 threads per SM is all that fits (90 registers), so the
     // bytes in flight come from loads issued back to back, not from more threads
     size_t i = tid;
-    for (; i + nthreads < nsgd4; i += 2 * nthreads) {
+    for (; i + nthreads < nfuse4; i += 2 * nthreads) {
       const size_t j = i + nthreads;
       const float4 w0 = w[i], g0 = __ldcs(g + i), a0 = __ldcs(m1 + i), b0 = __ldcs(m2 + i);
       const float4 w1 = w[j], g1 = __ldcs(g + j), a1 = __ldcs(m1 + j), b1 = __ldcs(m2 + j);
       adam_one(i, w0, g0, a0, b0);
       adam_one(j, w1, g1, a1, b1);
     }
-    if (i < nsgd4) adam_one(i, w[i], __ldcs(g + i), __ldcs(m1 + i), __ldcs(m2 + i));
+    if (i < nfuse4) adam_one(i, w[i], __ldcs(g + i), __ldcs(m1 + i), __ldcs(m2 + i));
     if (!solo) local_barrier();
   } else if (p.fuse_sgd) {
     float4* w = reinterpret_cast<float4*>(p.replica[p.my_rank]);
@@ -271,14 +272,14 @@ kavg_merge_kernel(const kml_merge_params p) {
       }
     };
     size_t i = tid;                  // two elements per thread and trip (see the Adam loop above)
-    for (; i + nthreads < nsgd4; i += 2 * nthreads) {
+    for (; i + nthreads < nfuse4; i += 2 * nthreads) {
       const size_t j = i + nthreads;
       const float4 w0 = w[i], g0 = __ldcs(g + i), m0 = has_m ? __ldcs(m + i) : zero4;
       const float4 w1 = w[j], g1 = __ldcs(g + j), m1v = has_m ? __ldcs(m + j) : zero4;
       sgd_one(i, w0, g0, m0);
       sgd_one(j, w1, g1, m1v);
     }
-    if (i < nsgd4) sgd_one(i, w[i], __ldcs(g + i), has_m ? __ldcs(m + i) : zero4);
+    if (i < nfuse4) sgd_one(i, w[i], __ldcs(g + i), has_m ? __ldcs(m + i) : zero4);
     if (!solo) local_barrier();     // the whole replica is final before anyone is told so
   }
   auto reset_optimizer = [&]() {    // the reference discards optimizer state at every sync (network.py:121-128)
@@ -569,6 +570,7 @@ extern "C" int kml_kavg_merge(const kml_merge_params* pp, void* stream) {
   if (p.fuse_sgd) KML_CHECK(p.grad != nullptr, "fuse_sgd set without grad");
   if (p.fuse_sgd == 2) KML_CHECK(p.momentum_buf != nullptr && p.state2 != nullptr, "fused Adam step needs both moment buffers");
   KML_CHECK(p.n_sgd % 4 == 0 && p.n_sgd <= p.n_f32, "n_sgd (%zu) must be a multiple of 4 and <= n_f32", p.n_sgd);
+  KML_CHECK(p.n_fuse % 4 == 0 && p.n_fuse <= p.n_sgd, "n_fuse (%zu) must be a multiple of 4 and <= n_sgd", p.n_fuse);
   if (p.generation == 0) p.mcast = nullptr;
 
   // Cooperative launch only for the single-GPU emulation without a signal pad (tests); every real merge is

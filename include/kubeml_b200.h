@@ -99,6 +99,9 @@ typedef struct {
   float* state2;
   float beta1, beta2, eps;
   int* step_dev;
+  /* fuse_sgd applies the step to the first n_fuse floats only (0 = all n_sgd): the caller already updated the
+   * rest - the layers whose gradients were final early in the backward pass - overlapped with that pass. */
+  size_t n_fuse;
 } kml_merge_params;
 
 /* Bits of *status beyond the per-rank "did not arrive" bits 0..7. */

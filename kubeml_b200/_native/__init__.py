@@ -51,6 +51,7 @@ class MergeParams(Structure):
         ("beta2", c_float),
         ("eps", c_float),
         ("step_dev", c_void_p),
+        ("n_fuse", c_size_t),
     ]
 
 

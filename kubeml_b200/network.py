@@ -481,6 +481,7 @@ class KubeModel(ABC):
             ent["graph"].replay()
             if ent.get("deferred"):
                 opt._deferred = True          # the captured program stops short of the optimizer launch
+                opt._deferred_lo = ent.get("deferred_lo")      # ... of all of it, or of the part it left to the merge
             self._graph_replays = getattr(self, "_graph_replays", 0) + 1
             ws["graph_launches"] = ws.get("graph_launches", 0) + ent["kernels"]
             return ent["out"]
@@ -511,7 +512,7 @@ class KubeModel(ABC):
                     opt.disarm()
             deferred = armed and bool(getattr(opt, "_deferred", False))
             ent.update(graph=g, static=static, out=out, owner=self, kernels=_native_launches() - k0,
-                       deferred=deferred)
+                       deferred=deferred, deferred_lo=getattr(opt, "_deferred_lo", None) if deferred else None)
             g.replay()            # the capture itself did not execute: run this batch now
             ws["graph_launches"] = ws.get("graph_launches", 0) + ent["kernels"]
             return out

@@ -56,6 +56,7 @@ class _FlatOptimizer:
         self._step_calls = 0          # step() invocations, counted by KubeModel around each train()
         self._armed = False
         self._deferred = False
+        self._deferred_lo = None          # a deferred step covers only [0, lo): the tail was stepped early (SGD)
         self._state_clean = False     # the merge kernel zeroed the optimizer state: reset_state() has nothing to do
 
     # -- arena attachment (done by DeviceSync.attach / models) --------------------------------
@@ -135,7 +136,12 @@ class _FlatOptimizer:
         self._deferred = False
         flat = self._flat_views()
         if flat is not None:
-            self._flat_step(*flat)
+            lo, self._deferred_lo = self._deferred_lo, None
+            if lo:                       # the tail [lo, n) was already stepped when the deferral was taken
+                w, gr = flat
+                self._flat_step(w[:lo], gr[:lo])
+            else:
+                self._flat_step(*flat)
 
     def _take_deferral(self) -> bool:
         """Inside step() on the flat path: True when this call is the one the merge kernel will apply."""
@@ -144,6 +150,7 @@ class _FlatOptimizer:
         if self._armed:
             self._armed = False
             self._deferred = True
+            self._deferred_lo = None
             return True
         return False
 
@@ -187,28 +194,39 @@ class SGD(_FlatOptimizer):
         lr, mom, wd, nes = g["lr"], g["momentum"], g["weight_decay"], g["nesterov"]
         mb = self._arena.state1[: w.numel()] if mom else None
         wb = getattr(self._arena, "wbf16", None)
-        early = getattr(self._arena, "early_ready", None)
-        if early is not None and w.is_cuda and os.environ.get("KUBEML_SGD_OVERLAP", "1") != "0":
-            # The network told us that the gradients of the parameter tail [lo, n) were final early in its
-            # backward pass (ResNet: layer4 + fc, 62 % of the bytes).  Their update runs on its own stream
-            # behind exactly those two events: under graph capture it becomes a node that depends only on
-            # them, so it overlaps the rest of the backward pass instead of trailing it.
-            lo, ev_main, ev_side = early
-            self._arena.early_ready = None
-            cur = torch.cuda.current_stream(w.device)
-            st = getattr(self._arena, "_opt_stream", None)
-            if st is None:
-                st = self._arena._opt_stream = torch.cuda.Stream(device=w.device)
-            st.wait_event(ev_main)
-            st.wait_event(ev_side)
-            with torch.cuda.stream(st):
-                ops.sgd_step_(w[lo:], gr[lo:], mb[lo:] if mb is not None else None, lr, wd, mom, nes,
-                              w_bf16=wb[lo:] if wb is not None else None)
+        lo = self._early_tail_step(w, gr)
+        if lo:
             ops.sgd_step_(w[:lo], gr[:lo], mb[:lo] if mb is not None else None, lr, wd, mom, nes,
                           w_bf16=wb[:lo] if wb is not None else None)
-            cur.wait_stream(st)
+            torch.cuda.current_stream(w.device).wait_stream(self._arena._opt_stream)
             return
         ops.sgd_step_(w, gr, mb, lr, wd, mom, nes, w_bf16=wb)
+
+    def _early_tail_step(self, w, gr) -> int:
+        """The network told us that the gradients of the parameter tail [lo, n) were final early in its backward
+        pass (ResNet: layer4 + fc, 62 % of the bytes).  Their update runs on its own stream behind exactly those
+        two events: under graph capture it becomes a node that depends only on them, so it overlaps the rest of the
+        backward pass instead of trailing it.  Returns lo (0: nothing was launched); the caller joins the stream."""
+        early = getattr(self._arena, "early_ready", None)
+        if early is None or not w.is_cuda or os.environ.get("KUBEML_SGD_OVERLAP", "1") == "0":
+            return 0
+        g = self.param_groups[0]
+        lr, mom, wd, nes = g["lr"], g["momentum"], g["weight_decay"], g["nesterov"]
+        mb = self._arena.state1[: w.numel()] if mom else None
+        wb = getattr(self._arena, "wbf16", None)
+        lo, ev_main, ev_side = early
+        self._arena.early_ready = None
+        if lo <= 0 or lo >= w.numel() or lo % 4:
+            return 0
+        st = getattr(self._arena, "_opt_stream", None)
+        if st is None:
+            st = self._arena._opt_stream = torch.cuda.Stream(device=w.device)
+        st.wait_event(ev_main)
+        st.wait_event(ev_side)
+        with torch.cuda.stream(st):
+            ops.sgd_step_(w[lo:], gr[lo:], mb[lo:] if mb is not None else None, lr, wd, mom, nes,
+                          w_bf16=wb[lo:] if wb is not None else None)
+        return int(lo)
 
     @torch.no_grad()
     def step(self) -> None:
@@ -220,6 +238,14 @@ class SGD(_FlatOptimizer):
         if flat is not None:
             w, gr = flat
             if w.is_cuda and not nes and self._take_deferral():
+                # The merge kernel applies this step - but only to the layers whose gradients arrive last: the
+                # tail that was final early is stepped now, under the rest of the backward pass, which leaves
+                # the merge 38 % of the bytes to touch (KUBEML_PARTIAL_DEFER=0: the merge takes all of it).
+                if os.environ.get("KUBEML_PARTIAL_DEFER", "1") != "0":
+                    lo = self._early_tail_step(w, gr)
+                    if lo:
+                        torch.cuda.current_stream(w.device).wait_stream(self._arena._opt_stream)
+                        self._deferred_lo = lo
                 return
             self._flat_step(w, gr)
             return

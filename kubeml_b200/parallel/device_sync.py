@@ -315,6 +315,8 @@ class RankSync:
             else:
                 p.momentum = g["momentum"]
             opt._deferred = False
+            p.n_fuse = int(getattr(opt, "_deferred_lo", None) or 0)     # 0: the merge applies the whole step
+            opt._deferred_lo = None
             self._fused_steps += 1
             self.epoch_fused_steps = getattr(self, "epoch_fused_steps", 0) + 1
         uses_momentum = opt is not None and bool(getattr(opt, "defaults", {}).get("momentum", 0))

@@ -202,3 +202,28 @@ def test_round_lookahead_trains_exactly_like_the_in_step_flow(kube_home, monkeyp
         c.shutdown()
     assert got["1"][0] == got["0"][0] and got["1"][1] == got["0"][1]
     assert got["1"][2] == got["0"][2] == 4 * 8          # one scalar per step crosses to the host either way
+
+
+def test_partial_deferral_of_the_last_step_trains_like_the_full_deferral(kube_home, monkeypatch):
+    """The round's last SGD step: by default only the layers whose gradients come last are left to the merge kernel
+    (`n_fuse`), layer4 + fc are stepped under the backward pass.  Same arithmetic per element either way."""
+    from kubeml_b200.api import TrainOptions, TrainRequest
+    from kubeml_b200.controller import Cluster
+    monkeypatch.setenv("KUBEML_RESNET_CLASSES", "10")
+    monkeypatch.setenv("KUBEML_RESNET_NOAUG", "1")
+    req = TrainRequest(model_type="resnet34", batch_size=32, epochs=2, dataset="cifar10", lr=0.05,
+                       function_name="resnet34",
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=4))
+    got = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("KUBEML_PARTIAL_DEFER", mode)
+        c = Cluster(home=kube_home + "/pd" + mode, max_parallelism=1)
+        rng = np.random.default_rng(0)
+        c.shard_store.create("cifar10", rng.integers(0, 255, (512, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (512,)),
+                             rng.integers(0, 255, (64, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (64,)))
+        h, job = _run(c, req)
+        got[mode] = (h.data.train_loss, h.data.validation_loss, [e["fused_last_steps"] for e in job.epoch_stats])
+        c.shutdown()
+    assert got["1"][2] == got["0"][2] and got["1"][2][0] == 4          # 16 steps, K=4: four merges per epoch, all fused
+    np.testing.assert_allclose(got["1"][0], got["0"][0], rtol=1e-4)
+    np.testing.assert_allclose(got["1"][1], got["0"][1], rtol=1e-4)

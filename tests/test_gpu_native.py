@@ -112,6 +112,7 @@ def _merge_single_gpu(dev, replicas_f, replicas_i, parts, write, fuse=None):
         p.fuse_sgd = 1
         p.grad = fuse["grad"].data_ptr()
         p.n_sgd = fuse["n"]
+        p.n_fuse = fuse.get("n_fuse", 0)
         p.lr, p.weight_decay, p.momentum = fuse["lr"], fuse["wd"], fuse["mom"]
         p.momentum_buf = fuse["mbuf"].data_ptr() if fuse.get("mbuf") is not None else None
         if fuse.get("wbf16") is not None:
@@ -185,6 +186,37 @@ def test_merge_single_participant_is_the_fused_step_only(dev):
     before = w.clone()
     _merge_single_gpu(dev, [w], None, [0], [0])
     torch.testing.assert_close(w, before, rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("nrep", [1, 2])
+def test_merge_fuses_only_the_head_when_the_tail_was_stepped_early(dev, nrep):
+    """`n_fuse`: the caller already applied the step to [n_fuse, n_sgd) under the backward pass (layer4 + fc of the
+    ResNets); the merge kernel's phase 0 touches [0, n_fuse) only - weights, bf16 copy - and still resets the whole
+    optimizer state."""
+    torch.manual_seed(16)
+    n, npar, head = 4 * 5000, 4 * 4000, 4 * 1500
+    w = [torch.randn(n, device=dev) for _ in range(nrep)]
+    g = torch.randn(npar, device=dev)
+    mb = torch.randn(npar, device=dev)
+    wb = torch.full((npar,), 7.0, dtype=torch.bfloat16, device=dev)
+    lr, wd, mom = 0.05, 1e-3, 0.9
+    stepped = w[0].clone()
+    stepped[:head] -= lr * (mom * mb[:head] + g[:head] + wd * w[0][:head])
+    want = stepped.clone()
+    for other in w[1:]:
+        want = want + other
+    want = want / nrep
+    parts = list(range(nrep))
+    _merge_single_gpu(dev, w, None, parts, parts,
+                      fuse=dict(grad=g, n=npar, n_fuse=head, lr=lr, wd=wd, mom=mom, mbuf=mb, wbf16=wb))
+    for r in parts:
+        torch.testing.assert_close(w[r], want, rtol=1e-6, atol=1e-6)
+    assert float(mb.abs().max()) == 0.0
+    if nrep == 1:       # alone, the kernel writes the bf16 copy of what it stepped and leaves the rest to the caller
+        torch.testing.assert_close(wb[:head].float(), want[:head].bfloat16().float(), rtol=0, atol=0)
+        assert bool((wb[head:].float() == 7.0).all())
+    else:               # after a real merge the whole copy is refreshed
+        torch.testing.assert_close(wb.float(), want[:npar].bfloat16().float(), rtol=0, atol=0)
 
 
 @pytest.mark.parametrize("nrep", [1, 2])
