@@ -204,17 +204,31 @@ def test_round_lookahead_trains_exactly_like_the_in_step_flow(kube_home, monkeyp
     assert got["1"][2] == got["0"][2] == 4 * 8          # one scalar per step crosses to the host either way
 
 
-def test_partial_deferral_of_the_last_step_trains_like_the_full_deferral(kube_home, monkeypatch):
+def test_partial_deferral_of_the_last_step_trains_like_the_full_deferral(kube_home, monkeypatch, tmp_path):
     """The round's last SGD step: by default only the layers whose gradients come last are left to the merge kernel
-    (`n_fuse`), layer4 + fc are stepped under the backward pass.  Same arithmetic per element either way."""
+    (`n_fuse`), layer4 + fc are stepped under the backward pass.  Same arithmetic per element either way.
+
+    What can be compared: from the same initial weights, at a learning rate small enough for the 16 steps to be
+    taken at (nearly) the same point, every layer must have moved by the same *distance* in both modes - a step
+    applied twice or not at all in one step of four changes that distance by a quarter on the layers concerned.
+    The *direction* is compared only for fc: two runs of the same mode already differ by 7 % there and by up to
+    80 % in the first layers, because the order of the atomic gradient sums changes which bf16 roundings flip, and
+    this network amplifies a flipped rounding as much as it amplifies bf16 itself (measured with
+    bench/probe_partial_defer.py, profiles/r2/x_probe_partial_defer.txt)."""
     from kubeml_b200.api import TrainOptions, TrainRequest
     from kubeml_b200.controller import Cluster
+    from kubeml_b200.models import resnet34
+    from kubeml_b200.utils.checkpoint import load_checkpoint
     monkeypatch.setenv("KUBEML_RESNET_CLASSES", "10")
     monkeypatch.setenv("KUBEML_RESNET_NOAUG", "1")
-    req = TrainRequest(model_type="resnet34", batch_size=32, epochs=2, dataset="cifar10", lr=0.05,
+    torch.manual_seed(31)
+    init = {k: v.clone() for k, v in resnet34(num_classes=10).state_dict().items()}
+    torch.save(init, str(tmp_path / "init.pt"))
+    monkeypatch.setenv("KUBEML_RESNET_INIT", str(tmp_path / "init.pt"))
+    req = TrainRequest(model_type="resnet34", batch_size=32, epochs=1, dataset="cifar10", lr=1e-4,
                        function_name="resnet34",
-                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=1, k=4))
-    got = {}
+                       options=TrainOptions(default_parallelism=1, static_parallelism=True, validate_every=0, k=4))
+    moved, fused = {}, {}
     for mode in ("1", "0"):
         monkeypatch.setenv("KUBEML_PARTIAL_DEFER", mode)
         c = Cluster(home=kube_home + "/pd" + mode, max_parallelism=1)
@@ -222,8 +236,16 @@ def test_partial_deferral_of_the_last_step_trains_like_the_full_deferral(kube_ho
         c.shard_store.create("cifar10", rng.integers(0, 255, (512, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (512,)),
                              rng.integers(0, 255, (64, 32, 32, 3), dtype=np.uint8), rng.integers(0, 10, (64,)))
         h, job = _run(c, req)
-        got[mode] = (h.data.train_loss, h.data.validation_loss, [e["fused_last_steps"] for e in job.epoch_stats])
+        fused[mode] = [e["fused_last_steps"] for e in job.epoch_stats]
+        sd, _ = load_checkpoint(c.checkpoint_dir, job.job_id)
+        moved[mode] = {k: torch.as_tensor(sd[k]).float().cpu() - init[k].float().cpu() for k in init
+                       if k.endswith("weight") and init[k].dim() >= 2}
         c.shutdown()
-    assert got["1"][2] == got["0"][2] and got["1"][2][0] == 4          # 16 steps, K=4: four merges per epoch, all fused
-    np.testing.assert_allclose(got["1"][0], got["0"][0], rtol=1e-4)
-    np.testing.assert_allclose(got["1"][1], got["0"][1], rtol=1e-4)
+    assert fused["1"] == fused["0"] == [4]              # 16 steps, K=4: four merges, each took the round's last step
+    # measured spread between runs: < 1.5 % on layer4 / fc (the layers the partial mode steps early), < 6 % elsewhere
+    for k, tol in (("fc.weight", 0.06), ("layer4.2.conv2.weight", 0.06), ("layer4.0.conv1.weight", 0.06),
+                   ("layer3.2.conv2.weight", 0.12), ("layer1.0.conv1.weight", 0.15), ("conv1.weight", 0.12)):
+        a, b = float(moved["1"][k].norm()), float(moved["0"][k].norm())
+        assert b > 0 and abs(a - b) / b < tol, f"{k}: moved by {a:.6f} with the partial deferral, {b:.6f} with the full one"
+    rel = float((moved["1"]["fc.weight"] - moved["0"]["fc.weight"]).norm() / moved["0"]["fc.weight"].norm())
+    assert rel < 0.2, f"fc.weight moved in different directions (relative difference {rel:.3f})"
