@@ -128,3 +128,46 @@ def test_every_dashboard_query_names_a_metric_the_parameter_server_exports():
     text = reg.render()
     for name in set(exprs):
         assert re.search(rf"^{name}\{{", text, re.M), f"dashboard queries {name}, /metrics does not export it"
+
+
+def test_kubernetes_manifests_and_image_recipe_name_real_commands_ports_and_paths():
+    """deploy/k8s/kubeml.yaml + deploy/Dockerfile (the chart and the image builds of the reference):
+    every command must be one the entry points accept, every probe / scrape path one the control plane serves."""
+    import argparse
+    import yaml
+    docs = [d for d in yaml.safe_load_all(open(os.path.join(DEPLOY, "k8s", "kubeml.yaml"))) if d]
+    kinds = [d["kind"] for d in docs]
+    assert kinds == ["Namespace", "PersistentVolumeClaim", "Deployment", "Service", "ServiceMonitor"]
+    dep = docs[2]
+    c = dep["spec"]["template"]["spec"]["containers"][0]
+    assert c["resources"]["limits"]["nvidia.com/gpu"] == 8
+    cmd = c["command"]
+    assert cmd[:3] == ["python", "-m", "torch.distributed.run"] and "kubeml_b200.runtime.spmd_main" in cmd
+    assert int(cmd[cmd.index("--nproc-per-node") + 1]) == c["resources"]["limits"]["nvidia.com/gpu"]
+    # the worker entry accepts exactly these flags (same parser as runtime/spmd_main.py)
+    tail = cmd[cmd.index("kubeml_b200.runtime.spmd_main") + 1:]
+    ap = argparse.ArgumentParser(); ap.add_argument("--host"); ap.add_argument("--port", type=int)
+    args = ap.parse_args(tail)
+    port = {p["name"]: p["containerPort"] for p in c["ports"]}["http"]
+    assert args.port == port == int(_env_file()["KUBEML_CONTROLLER_PORT"])
+    # probes, Service and ServiceMonitor point at routes the controller serves
+    from kubeml_b200.controller import Cluster
+    import tempfile
+    cl = Cluster(home=tempfile.mkdtemp(), start=False)
+    routes = cl.controller.router()._routes
+    paths = {c["readinessProbe"]["httpGet"]["path"], c["livenessProbe"]["httpGet"]["path"],
+             docs[4]["spec"]["endpoints"][0]["path"]}
+    assert paths == {"/health", "/metrics"}
+    for p in paths:
+        assert any(m == "GET" and rx.fullmatch(p) for m, rx, _ in routes), f"GET {p} is not served"
+    assert docs[3]["metadata"]["name"] == "controller" and docs[3]["spec"]["ports"][0]["targetPort"] == "http"
+    assert docs[4]["spec"]["endpoints"][0]["interval"] == "10s"
+    assert docs[4]["spec"]["selector"]["matchLabels"].items() <= docs[3]["metadata"]["labels"].items()
+    cl.shutdown()
+    # the image: builds the native library for sm_100a without a GPU and starts the same entry binary
+    df = open(os.path.join(DEPLOY, "Dockerfile")).read()
+    assert "__graft_entry__" in df and 'ENTRYPOINT ["python", "-m", "kubeml_b200"]' in df
+    from kubeml_b200.cli.main import build_parser
+    m = re.search(r"^CMD (\[.*\])$", df, re.M)
+    ns = build_parser().parse_args(json.loads(m.group(1)))
+    assert ns.port == port
