@@ -18,6 +18,8 @@ import time
 from dataclasses import dataclass, field
 from typing import Callable, Dict, Iterable, List, Optional
 
+import numpy as np
+
 from ..api.types import History, TrainOptions, TrainRequest
 from ..controller.client import KubemlClient
 
@@ -172,3 +174,89 @@ def to_dataframe(records: List[ExperimentRecord]):
                      "train_loss": h.get("train_loss", []), "parallelism": h.get("parallelism", []),
                      "epoch_duration": h.get("epoch_duration", []), "error": r.error})
     return pd.DataFrame(rows)
+
+
+# ---------------------------------------------------------------------------------- the comparison system
+class StockTorchExperiment:
+    """The harness side of the comparison system: one plain-PyTorch training run, in this process, recorded the
+    way a KubeML experiment is (reference: `TensorflowExperiment` runs the Keras LeNet / ResNet-34 baselines
+    in-process under MirroredStrategy and keeps their per-epoch metrics plus the cumulative seconds of a
+    `TimeHistory` callback, ml/experiments/common/experiment.py:263-337, tflow/time_callback.py:6-12).
+
+    The model is any stock `nn.Module` factory (`function_lenet.LeNet`, `torchvision.models.resnet34`, ...), the
+    data a dataset of the shard store, the optimizer SGD with momentum 0.9 and L2 1e-4 (tflow/lenet.py,
+    tflow/resnet34.py); under `torch.distributed` (torchrun) the module is wrapped in DistributedDataParallel and
+    every rank reads its contiguous share - the gradient all-reduce system KubeML is compared with.  The record's
+    `history.data` has the same keys as a KubeML history; `epoch_duration` is per epoch and `times` cumulative."""
+
+    def __init__(self, title: str, model_factory: Callable, dataset: str, batch: int, epochs: int, lr: float,
+                 store=None, device: Optional[str] = None, transform: Optional[Callable] = None, metrics=None,
+                 momentum: float = 0.9, weight_decay: float = 1e-4):
+        self.title, self.model_factory, self.dataset = title, model_factory, dataset
+        self.batch, self.epochs, self.lr = int(batch), int(epochs), float(lr)
+        self.store, self.device, self.transform, self.metrics = store, device, transform, metrics
+        self.momentum, self.weight_decay = momentum, weight_decay
+        self.times: List[float] = []
+
+    def run(self) -> ExperimentRecord:
+        import torch
+        import torch.distributed as dist
+        import torch.nn.functional as F
+        from ..storage import default_store
+        store = self.store or default_store()
+        dev = torch.device(self.device or ("cuda" if torch.cuda.is_available() else "cpu"))
+        rank, world = (dist.get_rank(), dist.get_world_size()) if dist.is_available() and dist.is_initialized() else (0, 1)
+        rec = ExperimentRecord(self.title, {"model_type": self.title.split("-")[0], "batch_size": self.batch,
+                                            "epochs": self.epochs, "lr": self.lr, "dataset": self.dataset,
+                                            "options": {"default_parallelism": world, "static_parallelism": True, "k": 1}})
+        t_start = time.time()
+        if self.metrics is not None:
+            self.metrics.start(self.title)
+        try:
+            xtr, ytr = store.arrays(self.dataset, "train")
+            xte, yte = store.arrays(self.dataset, "test")
+            per = -(-len(xtr) // world)
+            lo, hi = rank * per, min((rank + 1) * per, len(xtr))
+            prep = self.transform or (lambda x: x.float().div(255.0).unsqueeze(1) if x.dim() == 3
+                                      else x.float().div(255.0).permute(0, 3, 1, 2))
+            net = self.model_factory().to(dev)
+            model = torch.nn.parallel.DistributedDataParallel(net) if world > 1 else net
+            opt = torch.optim.SGD(model.parameters(), lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay)
+            hist = {"train_loss": [], "validation_loss": [], "accuracy": [], "parallelism": [], "epoch_duration": []}
+            self.times = []
+            for _ in range(self.epochs):
+                t0 = time.time()
+                model.train()
+                tot, nb = 0.0, 0
+                for i in range(lo, hi, self.batch):
+                    x = prep(torch.from_numpy(np.array(xtr[i:min(i + self.batch, hi)])).to(dev))
+                    y = torch.from_numpy(np.array(ytr[i:min(i + self.batch, hi)])).to(dev).long().view(-1)
+                    opt.zero_grad()
+                    loss = F.cross_entropy(model(x), y)
+                    loss.backward()
+                    opt.step()
+                    tot, nb = tot + float(loss.detach()), nb + 1
+                model.eval()
+                vl, correct, n = 0.0, 0, 0
+                with torch.no_grad():
+                    for i in range(0, len(xte), self.batch):
+                        x = prep(torch.from_numpy(np.array(xte[i:i + self.batch])).to(dev))
+                        y = torch.from_numpy(np.array(yte[i:i + self.batch])).to(dev).long().view(-1)
+                        out = net(x)
+                        vl += float(F.cross_entropy(out, y, reduction="sum"))
+                        correct += int((out.argmax(1) == y).sum())
+                        n += len(y)
+                hist["train_loss"].append(tot / max(nb, 1))
+                hist["validation_loss"].append(vl / max(n, 1))
+                hist["accuracy"].append(100.0 * correct / max(n, 1))
+                hist["parallelism"].append(float(world))
+                hist["epoch_duration"].append(time.time() - t0)
+                self.times.append(time.time() - t_start)          # TimeHistory: cumulative seconds at each epoch end
+            rec.history = {"_id": self.title, "task": rec.request, "data": hist, "times": list(self.times)}
+        except Exception as e:  # noqa: BLE001 - recorded like a failed grid point
+            rec.error = str(e)
+        finally:
+            if self.metrics is not None:
+                rec.system_metrics = self.metrics.finish()
+            rec.wall_seconds = time.time() - t_start
+        return rec

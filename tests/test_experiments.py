@@ -63,3 +63,33 @@ def test_k_optimizer_learns_a_trend():
     t8, _ = ko.predict(128, 0.1, 4, 8)
     tinf, _ = ko.predict(128, 0.1, 4, -1)
     assert t8 > tinf
+
+
+def test_stock_torch_experiment_records_like_a_kubeml_experiment(kube_home):
+    """The comparison system in the harness (the reference's TensorflowExperiment + TimeHistory): a plain-PyTorch
+    LeNet run on a stored dataset, recorded with the same history keys, cumulative epoch times and system metrics,
+    and usable by the same analysis code."""
+    from kubeml_b200.experiments import analysis, harness
+    from kubeml_b200.experiments.sysmetrics import MetricsCollector
+    from kubeml_b200.functions.function_lenet import LeNet
+    from kubeml_b200.storage import default_store
+    rng = np.random.default_rng(0)
+    store = default_store()
+    x = rng.integers(0, 255, (256, 28, 28), dtype=np.uint8)
+    y = (x.reshape(256, -1).mean(1) > 127).astype(np.int64)          # learnable: bright vs dark images
+    store.create("mnist2", x[:192], y[:192], x[192:], y[192:])
+    exp = harness.StockTorchExperiment("lenet-batch32-epochs3", LeNet, "mnist2", batch=32, epochs=3, lr=0.05,
+                                       store=store, device="cpu", metrics=MetricsCollector(interval=0.2),
+                                       transform=lambda t: t.float().div(255.0).sub(0.5).unsqueeze(1))
+    rec = exp.run()
+    assert rec.error is None, rec.error
+    h = rec.history["data"]
+    assert set(h) == {"train_loss", "validation_loss", "accuracy", "parallelism", "epoch_duration"}
+    assert all(len(v) == 3 for v in h.values()) and h["parallelism"] == [1.0] * 3
+    assert rec.history["times"] == sorted(rec.history["times"]) and len(exp.times) == 3
+    assert abs(exp.times[-1] - sum(h["epoch_duration"])) < 0.5
+    assert np.isfinite(h["train_loss"]).all() and h["train_loss"][-1] <= h["train_loss"][0] + 0.05
+    assert "cpu" in rec.system_metrics and rec.wall_seconds > 0
+    df = harness.to_dataframe([rec])
+    assert list(df["epochs"]) == [3] and len(df["accuracy"][0]) == 3
+    assert analysis.total_time(h["epoch_duration"]) > 0
