@@ -318,6 +318,11 @@ class KubeModel(ABC):
         # runs.  If the status then says the merge timed out (a peer went silent - the rare path), the repeat
         # merge of `check_round` runs behind that one extra local step.
         lookahead = prefetch and os.environ.get("KUBEML_ROUND_LOOKAHEAD", "1") != "0"
+        # KUBEML_NVTX=1: ranges for an external timeline tool (Nsight Systems) around the epoch, every round and
+        # every merge launch; the built-in timeline is `options["trace"]` (device spans in the job's Chrome trace)
+        nvtx = torch.cuda.nvtx if (on_cuda and os.environ.get("KUBEML_NVTX") == "1") else None
+        if nvtx is not None:
+            nvtx.range_push(f"kubeml epoch {a.epoch} job {a._job_id} func {a._func_id}")
         starts = list(intervals)
         ready = None
         pending = None          # (round, event after its merge, losses pushed up to it) not read back yet
@@ -333,6 +338,8 @@ class KubeModel(ABC):
             return v
         for round_idx, i in enumerate(starts):
             self._round_idx = round_idx
+            if nvtx is not None:
+                nvtx.range_push(f"round {round_idx}")
             batches = ready if ready is not None else _prepare(i)
             ready = None
             num_iterations += len(batches)
@@ -374,8 +381,14 @@ class KubeModel(ABC):
                 trace_h2d += [(round_idx, b, e0, e1) for b, e0, e1 in batches.trace]
 
             # every round but the last blocks on the merge barrier (network.py:305-306)
+            if nvtx is not None:
+                nvtx.range_pop()
             if i != intervals[-1]:
+                if nvtx is not None:
+                    nvtx.range_push(f"merge {round_idx}")
                 self._sync.arrive(a._job_id, a._func_id, round_idx)
+                if nvtx is not None:
+                    nvtx.range_pop()
             if prefetch and round_idx + 1 < len(starts):
                 ready = _prepare(starts[round_idx + 1])
                 if hasattr(ready, "prestage"):
@@ -393,6 +406,8 @@ class KubeModel(ABC):
 
         merge_events = list(getattr(self._sync, "_events", [])) if tracing else []
         self._sync.end_epoch(a._job_id, a._func_id, len(intervals))
+        if nvtx is not None:
+            nvtx.range_pop()
         if on_cuda:
             t_ev1.record()
             torch.cuda.synchronize(self.device)
