@@ -11,10 +11,12 @@ from __future__ import annotations
 
 import logging
 import os
+import threading
 from typing import Any, Callable, Dict, List, Optional
 
 from ..api import const
 from ..api.types import TrainTask
+from ..exceptions import KubeMLException
 from ..model.store import TensorStore
 from ..ps.parameter_server import ParameterServer
 from ..runtime.functions import FunctionRegistry
@@ -47,6 +49,9 @@ class Cluster:
         self.scheduler = Scheduler(max_parallelism=self.max_parallelism)
         self.ps = ParameterServer(self._make_job, scheduler=self.scheduler)
         self.ps.job_options = self.options
+        self.ps.finished_infer = self.infer_finished
+        self._serving: Dict[str, Any] = {}          # task id -> (worker, request) of checkpoints being served
+        self._serving_lock = threading.Lock()
         self.scheduler.ps = self.ps
         self.storage = StorageService(self.shard_store)
         self.controller = Controller(self.scheduler, self.ps, self.storage, self.histories,
@@ -104,6 +109,50 @@ class Cluster:
         job.trace_dir = os.path.join(self.home, "traces")     # host timeline always; device spans with options["trace"]
         self.jobs[task.job.id] = job
         return job
+
+    # ---- serving a finished task ---------------------------------------------------------------
+    SERVING_SLOTS = 4
+
+    def infer_finished(self, model_id: str, data: Any) -> Any:
+        """`kubeml infer --id <task>` after the task has ended.  The reference can only ask a function named
+        `network` about a model whose tensors its job deleted on exit (ml/pkg/scheduler/api.go:140,
+        ml/pkg/train/util.go:208-244); here every finished task leaves a checkpoint, and inference
+        runs the task's own function (`task=infer`) on it: the checkpoint is published once as the reference
+        model `{task}:{layer}` of a private tensor store, a warm worker answers the requests."""
+        from ..runtime.worker import Worker
+        from ..utils.checkpoint import restore_into_store
+        with self._serving_lock:
+            ent = self._serving.get(model_id)
+            if ent is None:
+                try:
+                    hist = self.histories.get(model_id)
+                except Exception:  # noqa: BLE001 - unknown id
+                    raise KubeMLException(f"model {model_id} not found", 404)
+                if not os.path.isfile(os.path.join(self.checkpoint_dir, model_id, "model.pt")):
+                    raise KubeMLException(f"task {model_id} left no checkpoint (it failed or was stopped)", 404)
+                store = TensorStore()
+                restore_into_store(self.checkpoint_dir, model_id, store)
+                services = Services(shard_store=self.shard_store, tensor_store=store, barrier=None, options=self.options)
+                worker = Worker(services, self.functions, gpu_id=0 if self._cuda() else None, name=f"serve-{model_id}")
+                while len(self._serving) >= self.SERVING_SLOTS:            # oldest model makes room
+                    self._serving.pop(next(iter(self._serving)))
+                ent = self._serving[model_id] = (worker, hist.task, threading.Lock())
+        worker, req, lock = ent
+        q = {"task": "infer", "jobId": model_id, "N": 1, "K": -1, "funcId": 0, "batchSize": req.batch_size,
+             "lr": req.lr, "epoch": 1}
+        with lock:                                   # one request at a time per model: the worker owns one stream
+            payload, status = worker.invoke(req.function_name, q, body=data)
+        if status != 200:
+            raise KubeMLException(str(payload.get("error", payload)), status)
+        return payload.get("predictions")
+
+    @staticmethod
+    def _cuda() -> bool:
+        try:
+            import torch
+            return torch.cuda.is_available()
+        except Exception:  # noqa: BLE001
+            return False
 
     # ---- convenience ---------------------------------------------------------------------
     def wait(self, job_id: str, timeout: Optional[float] = None) -> Optional[str]:

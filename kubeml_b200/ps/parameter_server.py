@@ -50,6 +50,7 @@ class ParameterServer:
         self.scheduler_url: Optional[str] = None    # ... and the scheduler
         self._own_servers: list = []
         self.job_options: dict = {}                 # JSON-able worker options handed to job processes
+        self.finished_infer: Optional[Callable[[str, Any], Any]] = None   # inference on a finished task's checkpoint
         self.metrics = MetricsRegistry()
         self.log = logging.getLogger("kubeml.ps")
         self._index: Dict[str, TrainTask] = {}
@@ -285,6 +286,13 @@ class ParameterServer:
         """Run `task=infer` of the job's function on its reference model."""
         with self._mu:
             task = self._index.get(model_id)
+        if (task is None or task.job.handle is None) and self.finished_infer is not None:
+            # the task has ended: serve its checkpoint (controller/cluster.py `infer_finished`)
+            self.metrics.task_started("inference")
+            try:
+                return self.finished_infer(model_id, data)
+            finally:
+                self.metrics.task_finished("inference")
         if task is None or task.job.handle is None:
             raise KubeMLException(f"model {model_id} not found (is the job still running?)", 404)
         if isinstance(task.job.handle, _JobProcess):

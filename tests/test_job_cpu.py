@@ -255,3 +255,32 @@ def test_standalone_job_that_dies_is_reported_failed(kube_home, monkeypatch):
     assert err is not None and "without reporting" in err
     assert c.ps.list_tasks() == []
     c.shutdown()
+
+
+def test_inference_is_served_from_the_checkpoint_of_a_finished_task(cluster):
+    """`kubeml infer --id <task>` after the task ended (the reference's inference only half exists):
+    the task's own function answers from the checkpoint the task left; while it runs, from the live model."""
+    from kubeml_b200.api import InferRequest
+    from kubeml_b200.controller import make_kubeml_client
+    from kubeml_b200.exceptions import KubeMLException
+    _mnist(cluster.shard_store, n=64 * 8)
+    req = TrainRequest(model_type="lenet", batch_size=64, epochs=1, dataset="mnist", lr=0.01, function_name="lenet",
+                       options=TrainOptions(default_parallelism=2, static_parallelism=True, validate_every=0, k=2))
+    jid, err, job = _run(cluster, req)
+    assert err is None and cluster.ps.list_tasks() == []
+    cl = make_kubeml_client(cluster)
+    x = np.random.default_rng(1).integers(0, 255, (5, 28, 28)).astype(np.float32).tolist()
+    preds = cl.v1().networks().infer(InferRequest(model_id=jid, data=x))
+    assert len(preds) == 5 and all(0 <= int(p) < 10 for p in preds)
+    # same answer as the trained network evaluated directly
+    from kubeml_b200.functions.function_lenet import LeNet
+    from kubeml_b200.utils.checkpoint import load_checkpoint
+    sd, _ = load_checkpoint(cluster.checkpoint_dir, jid)
+    net = LeNet(); net.load_state_dict(sd); net.eval()
+    with torch.no_grad():
+        want = net(torch.tensor(x).view(-1, 1, 28, 28)).argmax(1).tolist()
+    assert [int(p) for p in preds] == want
+    assert cl.v1().networks().infer(InferRequest(model_id=jid, data=x[:2])) == preds[:2]      # the warm worker again
+    with pytest.raises(KubeMLException) as e:
+        cl.v1().networks().infer(InferRequest(model_id="deadbeef", data=x))
+    assert e.value.status_code == 404
