@@ -93,3 +93,30 @@ def test_stock_torch_experiment_records_like_a_kubeml_experiment(kube_home):
     df = harness.to_dataframe([rec])
     assert list(df["epochs"]) == [3] and len(df["accuracy"][0]) == 3
     assert analysis.total_time(h["epoch_duration"]) > 0
+
+
+def test_experiment_driver_runs_a_grid_resumes_and_summarises(kube_home, tmp_path, capsys):
+    """`python -m kubeml_b200.experiments` (the reference's train.py / time_to_accuracy.py drivers): grid from the
+    command line, one result file per point, a second invocation recomputes nothing, summary with both TTA values."""
+    import json
+    from kubeml_b200.experiments.__main__ import main
+    from kubeml_b200.storage import default_store
+    rng = np.random.default_rng(0)
+    x = rng.integers(0, 255, (64 * 6, 28, 28), dtype=np.uint8)
+    y = (x.reshape(len(x), -1).mean(1) > 127).astype(np.int64)
+    default_store().create("mnist", x[:64 * 4], y[:64 * 4], x[64 * 4:], y[64 * 4:])
+    out = str(tmp_path / "grid")
+    argv = ["--function", "lenet", "--dataset", "mnist", "--lr", "0.01", "--epochs", "2", "--batch", "64",
+            "--k", "-1", "2", "--parallelism", "1", "2", "--goal", "30", "--out", out, "--local", "--timeout", "300"]
+    assert main(argv) == 0
+    files = sorted(f for f in os.listdir(out) if f.startswith("lenet-"))
+    assert files == ["lenet-b64-k-1-p1.json", "lenet-b64-k-1-p2.json", "lenet-b64-k2-p1.json", "lenet-b64-k2-p2.json"]
+    summ = json.load(open(os.path.join(out, "summary.json")))
+    assert len(summ["rows"]) == 4 and all(r["error"] is None and r["total_time_s"] > 0 for r in summ["rows"])
+    assert {(r["k"], r["parallelism"]) for r in summ["rows"]} == {(-1, 1), (-1, 2), (2, 1), (2, 2)}
+    assert all("tta_s" in r and "tta_crossbow_s" in r for r in summ["rows"])
+    stamp = {f: os.path.getmtime(os.path.join(out, f)) for f in files}
+    capsys.readouterr()
+    assert main(argv) == 0                               # resume: every point already has its file
+    assert {f: os.path.getmtime(os.path.join(out, f)) for f in files} == stamp
+    assert "4 of 4 grid points" in capsys.readouterr().out
