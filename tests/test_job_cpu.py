@@ -204,6 +204,7 @@ def test_standalone_job_runs_in_its_own_process_and_reports_over_http(kube_home,
     from kubeml_b200.controller import Cluster, make_kubeml_client
     monkeypatch.setenv("KUBEML_CUDA_GRAPH", "0")
     monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "")
+    monkeypatch.setenv("KUBEML_JOB_READY_TIMEOUT_S", "180")     # a cold `import torch` in the child can take a minute
     # two epochs: the policy's first two answers (default parallelism, then +1) do not depend on epoch times
     req = TrainRequest(model_type="lenet", batch_size=64, epochs=2, dataset="mnist", lr=0.01, function_name="lenet",
                        options=TrainOptions(default_parallelism=2, static_parallelism=False, validate_every=1, k=4))
@@ -240,6 +241,7 @@ def test_standalone_job_that_dies_is_reported_failed(kube_home, monkeypatch):
     from kubeml_b200.controller import Cluster, make_kubeml_client
     monkeypatch.setenv("KUBEML_CUDA_GRAPH", "0")
     monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "")
+    monkeypatch.setenv("KUBEML_JOB_READY_TIMEOUT_S", "180")     # a cold `import torch` in the child can take a minute
     monkeypatch.setenv("STANDALONE_JOBS", "true")
     c = Cluster(home=kube_home, max_parallelism=2, options={"force_host_sync": True})
     _mnist(c.shard_store, n=64 * 64)
