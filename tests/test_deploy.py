@@ -38,7 +38,7 @@ def _free_port():
     return p
 
 
-def _wait_http(url, timeout=90):
+def _wait_http(url, timeout=240):
     from kubeml_b200.httpd import http_call
     deadline = time.time() + timeout
     while time.time() < deadline:
